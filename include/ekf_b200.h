@@ -1,0 +1,124 @@
+/* ekf_b200.h — C-ABI of the B200-native EKF-SLAM filter core (libekf_b200.so, sm_100a).
+ *
+ * Drop-in boundary for the predict/update hot path of AHHHZ975/SLAM-Duckietown. The reference has no FFI of
+ * its own (src/ekf_bindings.py is an empty file); the entry points below are what a ctypes binding in that
+ * file binds so that the reference's module-level functions keep their signatures:
+ *
+ *   delta_phi            src/replay_no_ros.py:250-266   -> ekf_delta_phi
+ *   displacement         src/replay_no_ros.py:484-497   -> ekf_displacement
+ *   EKF_pose_estimation  src/replay_no_ros.py:269-482   -> ekf_lm_* (single filter, any n) /
+ *                                                          ekf_batch_* (many filters, fused step)
+ *   predict              src/EKF-SLAM.py:29-56          -> ekf3_predict
+ *   update               src/EKF-SLAM.py:59-84          -> ekf3_update
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative EKF_E* code on failure; ekf_last_error() gives the
+ *     thread-local message. No C++ exception and no abort() crosses this boundary.
+ *   - pointers named *_dev are DEVICE pointers owned by the caller (e.g. torch tensor storage); *_host are
+ *     host pointers. `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - all arithmetic is IEEE float64; slots / ids / ticks are integers.
+ *   - there is no CPU fallback: without a CUDA device every compute entry point fails with EKF_ECUDA.
+ */
+#ifndef EKF_B200_H
+#define EKF_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EKF_OK 0
+#define EKF_EINVAL (-1)  /* bad argument */
+#define EKF_ECUDA (-2)   /* CUDA runtime error (message has cudaGetErrorString) */
+#define EKF_ESTATE (-3)  /* handle not bound / wrong mode */
+#define EKF_ENCCL (-4)   /* NCCL error */
+
+/* covariance update forms */
+#define EKF_COV_PLAIN 0  /* P <- P - K (H P): the reference, replay_no_ros.py:480 */
+#define EKF_COV_JOSEPH 1 /* P <- (I-KH) P (I-KH)^T + K Q K^T as a one-pass rank-4 update */
+
+int ekf_version(void);
+const char* ekf_last_error(void);
+int ekf_device_count(int* count);
+
+/* ---- a1/a2: odometry from wheel-encoder ticks (host scalars) ------------------------------------------ */
+double ekf_delta_phi(int64_t ticks, int64_t prev_ticks, int64_t resolution); /* replay_no_ros.py:262-266 */
+int ekf_displacement(double wheel_radius, double baseline, double dphi_left, double dphi_right,
+                     double* angular, double* linear);                        /* replay_no_ros.py:491-497 */
+
+/* ---- batched mode: B independent filters of fixed capacity, one CTA per filter ------------------------- */
+typedef struct ekf_batch ekf_batch_t;
+
+/* Device layout of one filter (n = 3 + 2*n_landmarks, ld = n rounded up to 4):
+ *   mu  : mu_stride doubles (= ld), entries [n, ld) zero
+ *   P   : p_stride doubles (= n*ld), row-major with leading dimension ld, pad columns zero            */
+int ekf_batch_layout(int n_landmarks, int* n, int* ld, int64_t* p_stride, int64_t* mu_stride);
+int ekf_batch_create(int n_landmarks, int64_t batch, int device, ekf_batch_t** out);
+int ekf_batch_destroy(ekf_batch_t* h);
+/* mu_dev [batch][mu_stride], p_dev [batch][p_stride], n_known_dev [batch] (landmarks initialised so far) */
+int ekf_batch_bind_state(ekf_batch_t* h, double* mu_dev, double* p_dev, int32_t* n_known_dev);
+/* per-filter MOTION_MODEL_VARIANCE / MEASUREMENT_MODEL_VARIANCE (replay_no_ros.py:15-16), [batch] each */
+int ekf_batch_set_noise(ekf_batch_t* h, const double* motion_var_dev, const double* meas_var_dev);
+/* ENABLE_CIRCULAR_INTERPOLATION, ENABLE_MEASUREMENT_MODEL, DISABLE_MOTION_MODEL (:18-19,:28), cov form */
+int ekf_batch_set_flags(ekf_batch_t* h, int circular, int measurement, int disable_motion, int cov_form);
+/* mu = 0, P = p0_diag * I3 (replay_no_ros.py:69-70), n_known = 0 */
+int ekf_batch_init(ekf_batch_t* h, double p0_diag, void* stream);
+/* One fused filter-step for every filter (replay_no_ros.py:341-480): augment slots >= n_known from the
+ * pre-predict pose, odometry predict, then up to m sequential range-bearing updates in the given order.
+ * ang/lin [batch]; slot/rng/brg [batch][m], slot < 0 = no observation.                                   */
+int ekf_batch_step(ekf_batch_t* h, const double* ang_dev, const double* lin_dev, const int32_t* slot_dev,
+                   const double* rng_dev, const double* brg_dev, int m, void* stream);
+/* Same, odometry given as encoder ticks: delta_phi + displacement (a1/a2) are evaluated on the device.  */
+int ekf_batch_step_ticks(ekf_batch_t* h, const int32_t* ticks_left_dev, const int32_t* ticks_right_dev,
+                         const int32_t* prev_left_dev, const int32_t* prev_right_dev, double wheel_radius,
+                         double baseline, int resolution, const int32_t* slot_dev, const double* rng_dev,
+                         const double* brg_dev, int m, void* stream);
+/* Reference layout (mean (n,), covariance (n,n) C-order per filter, device memory) <-> device layout.   */
+int ekf_batch_pack(ekf_batch_t* h, const double* mean_ref_dev, const double* cov_ref_dev, int64_t first,
+                   int64_t count, void* stream);
+int ekf_batch_unpack(ekf_batch_t* h, double* mean_ref_dev, double* cov_ref_dev, int64_t first, int64_t count,
+                     void* stream);
+/* End-to-end call with HOST buffers: pinned staging + H2D of this step's inputs, the fused step, D2H of the
+ * robot pose (x, y, theta) of every filter into pose_host [batch][3]; synchronous.                       */
+int ekf_batch_step_host(ekf_batch_t* h, const double* ang_host, const double* lin_host,
+                        const int32_t* slot_host, const double* rng_host, const double* brg_host, int m,
+                        double* pose_host);
+/* number of filters that saw an out-of-order new slot or a non-finite innovation since init            */
+int ekf_batch_fault_count(ekf_batch_t* h, int64_t* count);
+
+/* ---- large-map mode: ONE filter, P streamed from HBM, optional row-block shard ------------------------- */
+typedef struct ekf_lm ekf_lm_t;
+
+int ekf_lm_layout(int capacity_landmarks, int* n, int64_t* ld);
+int ekf_lm_create(int capacity_landmarks, int device, ekf_lm_t** out);
+int ekf_lm_destroy(ekf_lm_t* h);
+/* mu_dev [ld]; p_dev holds rows [row_begin, row_end) of P, row-major with leading dimension ld.
+ * Single GPU: row_begin = 0, row_end = n. Pad entries must be zero.                                     */
+int ekf_lm_bind_state(ekf_lm_t* h, double* mu_dev, double* p_dev, int64_t ld, int row_begin, int row_end);
+int ekf_lm_set_noise(ekf_lm_t* h, double motion_var, double meas_var);
+int ekf_lm_set_flags(ekf_lm_t* h, int circular, int measurement, int disable_motion, int cov_form);
+/* a5: new landmark `slot` at (gx, gy): mu entries + 10000 on the two new diagonals (:355-360)            */
+int ekf_lm_augment(ekf_lm_t* h, int slot, double gx, double gy, void* stream);
+/* a6-a7: odometry predict on the robot block rows/columns of P (:368-430)                               */
+int ekf_lm_predict(ekf_lm_t* h, double ang, double lin, void* stream);
+/* a8-a11: one range-bearing update of landmark `slot` (:436-480)                                        */
+int ekf_lm_update(ekf_lm_t* h, int slot, double rng, double brg, void* stream);
+/* Row-block shards: export this shard's share of rows {0,1,2,j,j+1} (+ mu entries) into rows5_dev
+ * [5][ld+4] (rows it does not own are left untouched), then — after the owners' rows were exchanged
+ * (NCCL broadcast by the host) — run the update on the local block from the replicated buffer.          */
+int ekf_lm_export_rows(ekf_lm_t* h, int slot, double* rows5_dev, void* stream);
+int ekf_lm_update_from_rows(ekf_lm_t* h, int slot, double rng, double brg, const double* rows5_dev,
+                            void* stream);
+int ekf_lm_sync(ekf_lm_t* h);
+
+/* ---- 3-state localisation EKF of src/EKF-SLAM.py, batched, SoA: state [3][B], cov [9][B] --------------- */
+int ekf3_predict(int64_t batch, double* state_dev, double* cov_dev, const double* v_dev,
+                 const double* omega_dev, const double* dt_dev, void* stream);
+int ekf3_update(int64_t batch, double* state_dev, double* cov_dev, const double* rng_dev,
+                const double* brg_dev, const double* lx_dev, const double* ly_dev, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EKF_B200_H */

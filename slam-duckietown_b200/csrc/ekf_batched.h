@@ -1,0 +1,41 @@
+// ekf_batched.h — argument block and launchers of the batched fused-step kernels (internal).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ekf {
+
+constexpr int BATCH_MAX_M = 8;  // observations per filter-step (the surrogate bag peaks at 6)
+
+struct BatchStepArgs {
+  double* mu;                    // [B][LD]
+  double* P;                     // [B][N*LD]
+  int* n_known;                  // [B]
+  const double* motion_var;      // [B]
+  const double* meas_var;        // [B]
+  const double* ang;             // [B] (or null when ticks are given)
+  const double* lin;             // [B]
+  const int32_t *ticks_l, *ticks_r, *prev_l, *prev_r;  // [B] each, or null
+  double wheel_radius, baseline;
+  long long resolution;
+  const int32_t* slot;           // [B][m]
+  const double* rng;             // [B][m]
+  const double* brg;             // [B][m]
+  unsigned long long* faults;    // device counter
+  int m;
+  int flags;
+};
+
+bool batch_capacity_supported(int n_landmarks);
+size_t batch_step_smem_bytes(int n_landmarks, int m, bool joseph);
+cudaError_t batch_launch_step(int n_landmarks, const BatchStepArgs& a, int64_t batch, bool joseph,
+                              cudaStream_t st);
+cudaError_t batch_launch_init(double* mu, double* P, int* n_known, int64_t batch, int n, int ld, double p0,
+                              cudaStream_t st);
+cudaError_t batch_launch_pack(double* mu, double* P, const double* mean_ref, const double* cov_ref,
+                              int64_t first, int64_t count, int n, int ld, cudaStream_t st);
+cudaError_t batch_launch_unpack(const double* mu, const double* P, double* mean_ref, double* cov_ref,
+                                int64_t first, int64_t count, int n, int ld, cudaStream_t st);
+cudaError_t batch_launch_pose(const double* mu, double* pose, int64_t batch, int ld, cudaStream_t st);
+
+}  // namespace ekf

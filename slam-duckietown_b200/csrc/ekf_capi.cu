@@ -1,0 +1,489 @@
+// ekf_capi.cu — the C-ABI of libekf_b200.so (see include/ekf_b200.h for the contract and the reference
+// interfaces each entry point replaces). Plain pointers and sizes only; no torch types; errors are returned
+// as negative codes with a thread-local message.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "../../include/ekf_b200.h"
+#include "ekf3.h"
+#include "ekf_batched.h"
+#include "ekf_common.cuh"
+#include "ekf_largemap.h"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CU(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess) return fail(EKF_ECUDA, "%s: %s", #call, cudaGetErrorString(e_));   \
+  } while (0)
+
+int make_flags(int circular, int measurement, int disable_motion, int cov_form) {
+  return (circular ? ekf::kFlagCircular : 0) | (measurement ? ekf::kFlagMeasurement : 0) |
+         (disable_motion ? ekf::kFlagDisableMotion : 0) | (cov_form == EKF_COV_JOSEPH ? ekf::kFlagJoseph : 0);
+}
+
+}  // namespace
+
+struct ekf_batch {
+  int nlm, n, ld, device;
+  int64_t batch;
+  double *mu = nullptr, *P = nullptr;
+  int32_t* n_known = nullptr;
+  const double *mv = nullptr, *mm = nullptr;
+  int flags = ekf::kFlagCircular | ekf::kFlagMeasurement;
+  unsigned long long* faults = nullptr;
+  // staging for the host-buffer entry point
+  cudaStream_t stream = nullptr;
+  double *d_ang = nullptr, *d_lin = nullptr, *d_rng = nullptr, *d_brg = nullptr, *d_pose = nullptr;
+  int32_t* d_slot = nullptr;
+};
+
+struct ekf_lm {
+  int cap, n, device;
+  int64_t ld = 0, ldw = 0;
+  double *mu = nullptr, *P = nullptr;
+  int row_begin = 0, row_end = 0;
+  double mv = 0.1, mm = 0.7;
+  int flags = ekf::kFlagCircular | ekf::kFlagMeasurement;
+  double *K0 = nullptr, *K1 = nullptr, *A0 = nullptr, *A1 = nullptr, *W0 = nullptr, *W1 = nullptr,
+         *scal = nullptr;
+  int variant = 0;
+};
+
+extern "C" {
+
+int ekf_version(void) { return 100; }
+const char* ekf_last_error(void) { return g_err.c_str(); }
+
+int ekf_device_count(int* count) {
+  if (!count) return fail(EKF_EINVAL, "count is null");
+  CU(cudaGetDeviceCount(count));
+  return EKF_OK;
+}
+
+double ekf_delta_phi(int64_t ticks, int64_t prev_ticks, int64_t resolution) {
+  return ekf::delta_phi(ticks, prev_ticks, resolution);
+}
+
+int ekf_displacement(double wheel_radius, double baseline, double dphi_left, double dphi_right, double* angular,
+                     double* linear) {
+  if (!angular || !linear) return fail(EKF_EINVAL, "output pointer is null");
+  ekf::displacement(wheel_radius, baseline, dphi_left, dphi_right, angular, linear);
+  return EKF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// batched
+// ---------------------------------------------------------------------------------------------------------
+int ekf_batch_layout(int n_landmarks, int* n, int* ld, int64_t* p_stride, int64_t* mu_stride) {
+  if (n_landmarks < 0) return fail(EKF_EINVAL, "n_landmarks < 0");
+  const int nn = 3 + 2 * n_landmarks, l = (nn + 3) & ~3;
+  if (n) *n = nn;
+  if (ld) *ld = l;
+  if (p_stride) *p_stride = (int64_t)nn * l;
+  if (mu_stride) *mu_stride = l;
+  return EKF_OK;
+}
+
+int ekf_batch_create(int n_landmarks, int64_t batch, int device, ekf_batch_t** out) {
+  if (!out) return fail(EKF_EINVAL, "out is null");
+  if (!ekf::batch_capacity_supported(n_landmarks))
+    return fail(EKF_EINVAL, "landmark capacity %d not built (use 4, 8, 12, 16, 20, 24 or 28)", n_landmarks);
+  if (batch <= 0 || batch > 0x7fffffffLL) return fail(EKF_EINVAL, "batch out of range");
+  CU(cudaSetDevice(device));
+  ekf_batch* h = new (std::nothrow) ekf_batch();
+  if (!h) return fail(EKF_EINVAL, "out of host memory");
+  h->nlm = n_landmarks;
+  h->n = 3 + 2 * n_landmarks;
+  h->ld = (h->n + 3) & ~3;
+  h->device = device;
+  h->batch = batch;
+  cudaError_t e = cudaMalloc(&h->faults, sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMemset(h->faults, 0, sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) {
+    ekf_batch_destroy(h);
+    return fail(EKF_ECUDA, "ekf_batch_create: %s", cudaGetErrorString(e));
+  }
+  *out = h;
+  return EKF_OK;
+}
+
+int ekf_batch_destroy(ekf_batch_t* h) {
+  if (!h) return EKF_OK;
+  cudaSetDevice(h->device);
+  cudaFree(h->faults);
+  cudaFree(h->d_ang);
+  cudaFree(h->d_lin);
+  cudaFree(h->d_rng);
+  cudaFree(h->d_brg);
+  cudaFree(h->d_slot);
+  cudaFree(h->d_pose);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+  return EKF_OK;
+}
+
+int ekf_batch_bind_state(ekf_batch_t* h, double* mu_dev, double* p_dev, int32_t* n_known_dev) {
+  if (!h || !mu_dev || !p_dev || !n_known_dev) return fail(EKF_EINVAL, "null argument");
+  if (((uintptr_t)mu_dev & 31) || ((uintptr_t)p_dev & 31))
+    return fail(EKF_EINVAL, "mu/P must be 32-byte aligned (256-bit accesses, TMA bulk copies)");
+  h->mu = mu_dev;
+  h->P = p_dev;
+  h->n_known = n_known_dev;
+  return EKF_OK;
+}
+
+int ekf_batch_set_noise(ekf_batch_t* h, const double* motion_var_dev, const double* meas_var_dev) {
+  if (!h || !motion_var_dev || !meas_var_dev) return fail(EKF_EINVAL, "null argument");
+  h->mv = motion_var_dev;
+  h->mm = meas_var_dev;
+  return EKF_OK;
+}
+
+int ekf_batch_set_flags(ekf_batch_t* h, int circular, int measurement, int disable_motion, int cov_form) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  if (cov_form != EKF_COV_PLAIN && cov_form != EKF_COV_JOSEPH) return fail(EKF_EINVAL, "unknown cov_form");
+  h->flags = make_flags(circular, measurement, disable_motion, cov_form);
+  return EKF_OK;
+}
+
+int ekf_batch_init(ekf_batch_t* h, double p0_diag, void* stream) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  if (!h->mu) return fail(EKF_ESTATE, "state not bound");
+  CU(cudaSetDevice(h->device));
+  CU(ekf::batch_launch_init(h->mu, h->P, h->n_known, h->batch, h->n, h->ld, p0_diag, (cudaStream_t)stream));
+  CU(cudaMemsetAsync(h->faults, 0, sizeof(unsigned long long), (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+static int batch_step_common(ekf_batch_t* h, ekf::BatchStepArgs& a, int m, void* stream) {
+  if (!h->mu) return fail(EKF_ESTATE, "state not bound");
+  if (!h->mv) return fail(EKF_ESTATE, "noise not set");
+  if (m < 0 || m > ekf::BATCH_MAX_M) return fail(EKF_EINVAL, "m must be in [0, %d]", ekf::BATCH_MAX_M);
+  if (m > 0 && (!a.slot || !a.rng || !a.brg)) return fail(EKF_EINVAL, "observation arrays are null");
+  a.mu = h->mu;
+  a.P = h->P;
+  a.n_known = h->n_known;
+  a.motion_var = h->mv;
+  a.meas_var = h->mm;
+  a.faults = h->faults;
+  a.m = m;
+  a.flags = h->flags;
+  CU(cudaSetDevice(h->device));
+  CU(ekf::batch_launch_step(h->nlm, a, h->batch, (h->flags & ekf::kFlagJoseph) != 0, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf_batch_step(ekf_batch_t* h, const double* ang_dev, const double* lin_dev, const int32_t* slot_dev,
+                   const double* rng_dev, const double* brg_dev, int m, void* stream) {
+  if (!h || !ang_dev || !lin_dev) return fail(EKF_EINVAL, "null argument");
+  ekf::BatchStepArgs a{};
+  a.ang = ang_dev;
+  a.lin = lin_dev;
+  a.slot = slot_dev;
+  a.rng = rng_dev;
+  a.brg = brg_dev;
+  return batch_step_common(h, a, m, stream);
+}
+
+int ekf_batch_step_ticks(ekf_batch_t* h, const int32_t* ticks_left_dev, const int32_t* ticks_right_dev,
+                         const int32_t* prev_left_dev, const int32_t* prev_right_dev, double wheel_radius,
+                         double baseline, int resolution, const int32_t* slot_dev, const double* rng_dev,
+                         const double* brg_dev, int m, void* stream) {
+  if (!h || !ticks_left_dev || !ticks_right_dev || !prev_left_dev || !prev_right_dev)
+    return fail(EKF_EINVAL, "null argument");
+  if (resolution == 0 || baseline == 0.0) return fail(EKF_EINVAL, "resolution / baseline must be non-zero");
+  ekf::BatchStepArgs a{};
+  a.ticks_l = ticks_left_dev;
+  a.ticks_r = ticks_right_dev;
+  a.prev_l = prev_left_dev;
+  a.prev_r = prev_right_dev;
+  a.wheel_radius = wheel_radius;
+  a.baseline = baseline;
+  a.resolution = resolution;
+  a.slot = slot_dev;
+  a.rng = rng_dev;
+  a.brg = brg_dev;
+  return batch_step_common(h, a, m, stream);
+}
+
+int ekf_batch_pack(ekf_batch_t* h, const double* mean_ref_dev, const double* cov_ref_dev, int64_t first,
+                   int64_t count, void* stream) {
+  if (!h || !mean_ref_dev || !cov_ref_dev) return fail(EKF_EINVAL, "null argument");
+  if (!h->mu) return fail(EKF_ESTATE, "state not bound");
+  if (first < 0 || count < 0 || first + count > h->batch) return fail(EKF_EINVAL, "filter range out of bounds");
+  CU(cudaSetDevice(h->device));
+  if (count)
+    CU(ekf::batch_launch_pack(h->mu, h->P, mean_ref_dev, cov_ref_dev, first, count, h->n, h->ld,
+                              (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf_batch_unpack(ekf_batch_t* h, double* mean_ref_dev, double* cov_ref_dev, int64_t first, int64_t count,
+                     void* stream) {
+  if (!h || !mean_ref_dev || !cov_ref_dev) return fail(EKF_EINVAL, "null argument");
+  if (!h->mu) return fail(EKF_ESTATE, "state not bound");
+  if (first < 0 || count < 0 || first + count > h->batch) return fail(EKF_EINVAL, "filter range out of bounds");
+  CU(cudaSetDevice(h->device));
+  if (count)
+    CU(ekf::batch_launch_unpack(h->mu, h->P, mean_ref_dev, cov_ref_dev, first, count, h->n, h->ld,
+                                (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf_batch_step_host(ekf_batch_t* h, const double* ang_host, const double* lin_host,
+                        const int32_t* slot_host, const double* rng_host, const double* brg_host, int m,
+                        double* pose_host) {
+  if (!h || !ang_host || !lin_host || !pose_host) return fail(EKF_EINVAL, "null argument");
+  if (m < 0 || m > ekf::BATCH_MAX_M) return fail(EKF_EINVAL, "m must be in [0, %d]", ekf::BATCH_MAX_M);
+  if (m > 0 && (!slot_host || !rng_host || !brg_host)) return fail(EKF_EINVAL, "observation arrays are null");
+  CU(cudaSetDevice(h->device));
+  const int64_t B = h->batch;
+  if (!h->d_ang) {
+    CU(cudaMalloc(&h->d_ang, B * sizeof(double)));
+    CU(cudaMalloc(&h->d_lin, B * sizeof(double)));
+    CU(cudaMalloc(&h->d_rng, B * ekf::BATCH_MAX_M * sizeof(double)));
+    CU(cudaMalloc(&h->d_brg, B * ekf::BATCH_MAX_M * sizeof(double)));
+    CU(cudaMalloc(&h->d_slot, B * ekf::BATCH_MAX_M * sizeof(int32_t)));
+    CU(cudaMalloc(&h->d_pose, B * 3 * sizeof(double)));
+  }
+  cudaStream_t st = h->stream;
+  CU(cudaMemcpyAsync(h->d_ang, ang_host, B * sizeof(double), cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(h->d_lin, lin_host, B * sizeof(double), cudaMemcpyHostToDevice, st));
+  if (m > 0) {
+    CU(cudaMemcpyAsync(h->d_slot, slot_host, B * m * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(h->d_rng, rng_host, B * m * sizeof(double), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(h->d_brg, brg_host, B * m * sizeof(double), cudaMemcpyHostToDevice, st));
+  }
+  int rc = ekf_batch_step(h, h->d_ang, h->d_lin, h->d_slot, h->d_rng, h->d_brg, m, st);
+  if (rc != EKF_OK) return rc;
+  CU(ekf::batch_launch_pose(h->mu, h->d_pose, B, h->ld, st));
+  CU(cudaMemcpyAsync(pose_host, h->d_pose, B * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return EKF_OK;
+}
+
+int ekf_batch_fault_count(ekf_batch_t* h, int64_t* count) {
+  if (!h || !count) return fail(EKF_EINVAL, "null argument");
+  CU(cudaSetDevice(h->device));
+  unsigned long long v = 0;
+  CU(cudaMemcpy(&v, h->faults, sizeof(v), cudaMemcpyDeviceToHost));
+  *count = (int64_t)v;
+  return EKF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// large map
+// ---------------------------------------------------------------------------------------------------------
+int ekf_lm_layout(int capacity_landmarks, int* n, int64_t* ld) {
+  if (capacity_landmarks < 0) return fail(EKF_EINVAL, "capacity < 0");
+  const int nn = 3 + 2 * capacity_landmarks;
+  if (n) *n = nn;
+  if (ld) *ld = ((int64_t)nn + 15) & ~15LL;
+  return EKF_OK;
+}
+
+int ekf_lm_create(int capacity_landmarks, int device, ekf_lm_t** out) {
+  if (!out) return fail(EKF_EINVAL, "out is null");
+  if (capacity_landmarks < 0 || capacity_landmarks > 500000000) return fail(EKF_EINVAL, "capacity out of range");
+  CU(cudaSetDevice(device));
+  ekf_lm* h = new (std::nothrow) ekf_lm();
+  if (!h) return fail(EKF_EINVAL, "out of host memory");
+  h->cap = capacity_landmarks;
+  h->n = 3 + 2 * capacity_landmarks;
+  h->device = device;
+  h->ldw = (((int64_t)h->n + 15) & ~15LL) + 16;
+  const char* v = getenv("EKF_LM_VARIANT");
+  h->variant = v ? atoi(v) : 0;
+  double* ws = nullptr;
+  cudaError_t e = cudaMalloc(&ws, (6 * h->ldw + ekf::kScalCount) * sizeof(double));
+  if (e == cudaSuccess) e = cudaMemset(ws, 0, (6 * h->ldw + ekf::kScalCount) * sizeof(double));
+  if (e != cudaSuccess) {
+    cudaFree(ws);
+    delete h;
+    return fail(EKF_ECUDA, "ekf_lm_create: %s", cudaGetErrorString(e));
+  }
+  h->K0 = ws;
+  h->K1 = ws + h->ldw;
+  h->A0 = ws + 2 * h->ldw;
+  h->A1 = ws + 3 * h->ldw;
+  h->W0 = ws + 4 * h->ldw;
+  h->W1 = ws + 5 * h->ldw;
+  h->scal = ws + 6 * h->ldw;
+  *out = h;
+  return EKF_OK;
+}
+
+int ekf_lm_destroy(ekf_lm_t* h) {
+  if (!h) return EKF_OK;
+  cudaSetDevice(h->device);
+  cudaFree(h->K0);
+  delete h;
+  return EKF_OK;
+}
+
+int ekf_lm_bind_state(ekf_lm_t* h, double* mu_dev, double* p_dev, int64_t ld, int row_begin, int row_end) {
+  if (!h || !mu_dev || !p_dev) return fail(EKF_EINVAL, "null argument");
+  if (ld < h->n || (ld & 3)) return fail(EKF_EINVAL, "ld must be >= n and a multiple of 4");
+  if (((uintptr_t)p_dev & 31)) return fail(EKF_EINVAL, "P must be 32-byte aligned");
+  if (row_begin < 0 || row_end > h->n || row_begin > row_end) return fail(EKF_EINVAL, "bad row range");
+  if (row_begin != 0 && (row_begin < 3 || ((row_begin - 3) & 1)))
+    return fail(EKF_EINVAL, "row blocks must start on a landmark pair (row 3 + 2k)");
+  h->mu = mu_dev;
+  h->P = p_dev;
+  h->ld = ld;
+  h->row_begin = row_begin;
+  h->row_end = row_end;
+  return EKF_OK;
+}
+
+int ekf_lm_set_noise(ekf_lm_t* h, double motion_var, double meas_var) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  h->mv = motion_var;
+  h->mm = meas_var;
+  return EKF_OK;
+}
+
+int ekf_lm_set_flags(ekf_lm_t* h, int circular, int measurement, int disable_motion, int cov_form) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  if (cov_form != EKF_COV_PLAIN && cov_form != EKF_COV_JOSEPH) return fail(EKF_EINVAL, "unknown cov_form");
+  h->flags = make_flags(circular, measurement, disable_motion, cov_form);
+  return EKF_OK;
+}
+
+int ekf_lm_augment(ekf_lm_t* h, int slot, double gx, double gy, void* stream) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  if (!h->P) return fail(EKF_ESTATE, "state not bound");
+  if (slot < 0 || slot >= h->cap) return fail(EKF_EINVAL, "slot %d outside capacity %d", slot, h->cap);
+  CU(cudaSetDevice(h->device));
+  CU(ekf::lm_launch_augment(h->mu, h->P, h->ld, h->row_begin, h->row_end, 3 + 2 * slot, gx, gy,
+                            (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf_lm_predict(ekf_lm_t* h, double ang, double lin, void* stream) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  if (!h->P) return fail(EKF_ESTATE, "state not bound");
+  CU(cudaSetDevice(h->device));
+  CU(ekf::lm_launch_predict(h->mu, h->P, h->ld, h->n, h->row_begin, h->row_end, h->scal, ang, lin, h->mv,
+                            h->flags, true, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+static int lm_update_impl(ekf_lm_t* h, int slot, double rng, double brg, const double* rows5, void* stream) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  if (!h->P) return fail(EKF_ESTATE, "state not bound");
+  if (slot < 0 || slot >= h->cap) return fail(EKF_EINVAL, "slot %d outside capacity %d", slot, h->cap);
+  if (!(h->flags & ekf::kFlagMeasurement)) return EKF_OK;  // ENABLE_MEASUREMENT_MODEL = False (:435)
+  const bool whole = (h->row_begin == 0 && h->row_end == h->n);
+  if (!rows5 && !whole) return fail(EKF_ESTATE, "row-block shard: use ekf_lm_update_from_rows");
+  const bool joseph = (h->flags & ekf::kFlagJoseph) != 0;
+  if (joseph && !whole) return fail(EKF_EINVAL, "Joseph form is not available on a row-block shard");
+  CU(cudaSetDevice(h->device));
+  const int j = 3 + 2 * slot;
+  const int idx5[5] = {0, 1, 2, j, j + 1};
+  ekf::LmGatherArgs g{};
+  g.P = h->P;
+  const int64_t ldx = h->ld + 4;
+  for (int k = 0; k < 5; ++k) {
+    if (rows5) {
+      g.row[k] = rows5 + k * ldx;
+      g.mu5[k] = rows5 + k * ldx + h->ld;
+    } else {
+      g.row[k] = h->P + (int64_t)idx5[k] * h->ld;
+      g.mu5[k] = h->mu + idx5[k];
+    }
+  }
+  g.K0 = h->K0; g.K1 = h->K1; g.A0 = h->A0; g.A1 = h->A1; g.W0 = h->W0; g.W1 = h->W1; g.scal = h->scal;
+  g.ld = h->ld;
+  g.n = h->n;
+  g.row_begin = h->row_begin;
+  g.row_end = h->row_end;
+  g.j = j;
+  g.flags = h->flags;
+  g.rng = rng;
+  g.brg = brg;
+  g.mm = h->mm;
+  g.shard = rows5 ? 1 : 0;
+  g.mu_out = h->mu;
+  CU(ekf::lm_launch_gather(g, (cudaStream_t)stream));
+  ekf::LmUpdateArgs u{};
+  u.P = h->P;
+  u.mu = h->mu;
+  u.K0 = h->K0; u.K1 = h->K1; u.A0 = h->A0; u.A1 = h->A1; u.W0 = h->W0; u.W1 = h->W1; u.scal = h->scal;
+  u.ld = h->ld;
+  u.n = h->n;
+  u.row_begin = h->row_begin;
+  u.row_end = h->row_end;
+  CU(ekf::lm_launch_update(u, joseph, h->variant, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf_lm_update(ekf_lm_t* h, int slot, double rng, double brg, void* stream) {
+  return lm_update_impl(h, slot, rng, brg, nullptr, stream);
+}
+
+int ekf_lm_export_rows(ekf_lm_t* h, int slot, double* rows5_dev, void* stream) {
+  if (!h || !rows5_dev) return fail(EKF_EINVAL, "null argument");
+  if (!h->P) return fail(EKF_ESTATE, "state not bound");
+  if (slot < 0 || slot >= h->cap) return fail(EKF_EINVAL, "slot %d outside capacity %d", slot, h->cap);
+  CU(cudaSetDevice(h->device));
+  CU(ekf::lm_launch_export_rows(h->P, h->mu, h->ld, h->row_begin, h->row_end, 3 + 2 * slot, rows5_dev,
+                                h->ld + 4, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf_lm_update_from_rows(ekf_lm_t* h, int slot, double rng, double brg, const double* rows5_dev,
+                            void* stream) {
+  if (!rows5_dev) return fail(EKF_EINVAL, "rows5_dev is null");
+  return lm_update_impl(h, slot, rng, brg, rows5_dev, stream);
+}
+
+int ekf_lm_sync(ekf_lm_t* h) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  CU(cudaSetDevice(h->device));
+  CU(cudaDeviceSynchronize());
+  return EKF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// 3-state EKF
+// ---------------------------------------------------------------------------------------------------------
+int ekf3_predict(int64_t batch, double* state_dev, double* cov_dev, const double* v_dev, const double* omega_dev,
+                 const double* dt_dev, void* stream) {
+  if (batch < 0) return fail(EKF_EINVAL, "batch < 0");
+  if (!state_dev || !cov_dev || !v_dev || !omega_dev || !dt_dev) return fail(EKF_EINVAL, "null argument");
+  CU(ekf::ekf3_launch_predict(batch, state_dev, cov_dev, v_dev, omega_dev, dt_dev, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf3_update(int64_t batch, double* state_dev, double* cov_dev, const double* rng_dev, const double* brg_dev,
+                const double* lx_dev, const double* ly_dev, void* stream) {
+  if (batch < 0) return fail(EKF_EINVAL, "batch < 0");
+  if (!state_dev || !cov_dev || !rng_dev || !brg_dev || !lx_dev || !ly_dev)
+    return fail(EKF_EINVAL, "null argument");
+  CU(ekf::ekf3_launch_update(batch, state_dev, cov_dev, rng_dev, brg_dev, lx_dev, ly_dev, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,117 @@
+// ekf_common.cuh — device helpers shared by the batched, large-map and 3-state kernels (sm_100a, fp64).
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+namespace ekf {
+
+constexpr double kPi = 3.14159265358979323846;
+constexpr double kTwoPi = 6.28318530717958647692;
+constexpr double kNewLandmarkVar = 10000.0;  // replay_no_ros.py:356-357
+
+// flag bits shared by host and device
+enum : int { kFlagCircular = 1, kFlagMeasurement = 2, kFlagDisableMotion = 4, kFlagJoseph = 8 };
+
+// (a + pi) % (2 pi) - pi with Python float-modulo semantics (replay_no_ros.py:397,:458): fmod keeps the sign
+// of the dividend, Python's % that of the divisor.
+__host__ __device__ __forceinline__ double wrap_pi(double a) {
+  double r = fmod(a + kPi, kTwoPi);
+  if (r < 0.0) r += kTwoPi;
+  return r - kPi;
+}
+
+// a1/a2 (replay_no_ros.py:262-266, :491-497)
+__host__ __device__ __forceinline__ double delta_phi(long long ticks, long long prev, long long resolution) {
+  return (double)(ticks - prev) * (kTwoPi / (double)resolution);
+}
+__host__ __device__ __forceinline__ void displacement(double R, double baseline, double dl, double dr,
+                                                      double* ang, double* lin) {
+  const double wr = R * dr, wl = R * dl;
+  *lin = (wl + wr) / 2.0;
+  *ang = (wr - wl) / baseline;
+}
+
+// a6 (replay_no_ros.py:368-417): pose increment, new heading and Jacobian column g0 = G[0,2], g1 = G[1,2]
+struct Motion {
+  double dx, dy, theta, g0, g1;
+};
+__device__ __forceinline__ Motion motion_step(double th, double ang, double lin, int flags) {
+  Motion m;
+  if (flags & kFlagDisableMotion) {
+    m.dx = 0.0; m.dy = 0.0; m.theta = th; m.g0 = 0.0; m.g1 = 0.0;
+    return m;
+  }
+  double s, c;
+  sincos(th, &s, &c);
+  if ((flags & kFlagCircular) && fabs(ang) > 1e-2) {
+    const double r = lin / ang;
+    double s2, c2;
+    sincos(th + ang, &s2, &c2);
+    m.dx = -r * s + r * s2;
+    m.dy = r * c - r * c2;
+    m.theta = wrap_pi(th + ang);
+    m.g0 = -r * c + r * c2;
+    m.g1 = -r * s + r * s2;
+  } else {
+    m.dx = lin * c;
+    m.dy = lin * s;
+    // straight branch of the circular model leaves theta alone; the linear model adds ang unwrapped (:405-410)
+    m.theta = (flags & kFlagCircular) ? th : th + ang;
+    m.g0 = -lin * s;
+    m.g1 = lin * c;
+  }
+  return m;
+}
+
+// a8 (replay_no_ros.py:443-469): innovation y and the 2x5 block of H over columns {0,1,2,j,j+1}
+struct Innov {
+  double y0, y1;
+  double h[2][5];
+  double q;
+};
+__device__ __forceinline__ Innov innovation(double mx, double my, double mth, double lx, double ly, double rng,
+                                            double brg) {
+  Innov o;
+  const double dx = lx - mx, dy = ly - my;
+  const double q = dx * dx + dy * dy;
+  const double sq = sqrt(q);
+  o.q = q;
+  o.y0 = rng - sq;
+  o.y1 = wrap_pi(brg - (atan2(dy, dx) - mth));
+  o.h[0][0] = (-sq * dx) / q; o.h[0][1] = (-sq * dy) / q; o.h[0][2] = 0.0;
+  o.h[0][3] = (sq * dx) / q;  o.h[0][4] = (sq * dy) / q;
+  o.h[1][0] = dy / q;  o.h[1][1] = -dx / q; o.h[1][2] = -q / q;
+  o.h[1][3] = -dy / q; o.h[1][4] = dx / q;
+  return o;
+}
+
+// closed-form inverse of the 2x2 innovation covariance (replaces np.linalg.inv, :473)
+__device__ __forceinline__ void inv2(const double s[2][2], double si[2][2]) {
+  const double det = s[0][0] * s[1][1] - s[0][1] * s[1][0];
+  si[0][0] = s[1][1] / det;  si[0][1] = -s[0][1] / det;
+  si[1][0] = -s[1][0] / det; si[1][1] = s[0][0] / det;
+}
+
+// 256-bit global accesses (sm_100a: LDG.E.256 / STG.E.256)
+struct __align__(32) double4x {
+  double a, b, c, d;
+};
+__device__ __forceinline__ double4x ldg256_stream(const double* p) {
+  double4x v;
+  asm volatile("ld.global.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];"
+               : "=d"(v.a), "=d"(v.b), "=d"(v.c), "=d"(v.d) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ double4x ldg256(const double* p) {
+  double4x v;
+  asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];"
+               : "=d"(v.a), "=d"(v.b), "=d"(v.c), "=d"(v.d) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void stg256(double* p, const double4x& v) {
+  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(v.a), "d"(v.b), "d"(v.c), "d"(v.d)
+               : "memory");
+}
+
+}  // namespace ekf

@@ -1,0 +1,391 @@
+// ekf_largemap.cu — large-map single-filter EKF-SLAM kernels (sm_100a, fp64, HBM-streaming).
+//
+// One filter whose dense covariance P (n x n, n = 3 + 2N, row-major, leading dimension ld = n rounded up
+// to 16 doubles so every row starts on a 128-byte line) lives in HBM. A GPU holds rows [row_begin, row_end)
+// of P (the whole matrix on one GPU, a row block when sharded).
+//
+// Reference semantics (src/replay_no_ros.py): augment :341-360, predict :368-430, update :436-480.
+// The reference multiplies dense n x n matrices (O(n^3)); the same algebra is a gather of 5 rows and
+// 5 columns plus a rank-2 (plain) or rank-4 (Joseph, one pass) in-place update of P:
+//
+//   K  = P[:, idx5] H5^T S^-1      from COLUMNS of P        idx5 = {0, 1, 2, j, j+1}, j = 3 + 2*slot
+//   HP = H5 P[idx5, :]             from ROWS of P
+//   plain : P -= K HP                                   Joseph: P -= K W + AHt K^T,
+//                                                        W = HP - Q K^T, AHt = P H^T - K (S - Q)
+// Rows and columns are both read for real: substituting (P H^T)^T for H P on full, slightly asymmetric
+// storage is numerically unstable.
+//
+// Roofline: HBM. Algorithmic bytes per update = 16 n^2 (read + write P) + 96 n (gathers + mu); the
+// streaming kernel `lm_rank_update_kernel` moves the 16 n^2 with 256-bit loads/stores.
+#include "ekf_common.cuh"
+#include "ekf_largemap.h"
+
+namespace ekf {
+
+// -------------------------------------------------------------------------------------------------------
+// a5 augment (replay_no_ros.py:355-360): rows/columns of a not-yet-seen landmark are zero by invariant.
+// -------------------------------------------------------------------------------------------------------
+__global__ void lm_augment_kernel(double* __restrict__ mu, double* __restrict__ P, int64_t ld, int row_begin,
+                                  int row_end, int j, double gx, double gy) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  mu[j] = gx;
+  mu[j + 1] = gy;
+  if (j >= row_begin && j < row_end) P[(int64_t)(j - row_begin) * ld + j] = kNewLandmarkVar;
+  if (j + 1 >= row_begin && j + 1 < row_end) P[(int64_t)(j + 1 - row_begin) * ld + j + 1] = kNewLandmarkVar;
+}
+
+// -------------------------------------------------------------------------------------------------------
+// a6 predict mean (:368-417): one thread; leaves g0, g1 in the workspace for the covariance kernel.
+// -------------------------------------------------------------------------------------------------------
+__global__ void lm_predict_mean_kernel(double* __restrict__ mu, double* __restrict__ scal, double ang,
+                                       double lin, int flags) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const Motion m = motion_step(mu[2], ang, lin, flags);
+  mu[0] += m.dx;
+  mu[1] += m.dy;
+  mu[2] = m.theta;
+  scal[kScalG0] = m.g0;
+  scal[kScalG1] = m.g1;
+}
+
+// -------------------------------------------------------------------------------------------------------
+// a7 predict covariance (:420-430): P <- G_F P G_F^T + F^T R F touches rows 0-1, columns 0-1 and three
+// diagonal entries. Thread t >= 3 does column t of rows 0-1 and row t of columns 0-1; thread 0 does the
+// 3x3 robot block in the same order (rows first, then columns with the updated rows, then the noise).
+// -------------------------------------------------------------------------------------------------------
+__global__ void lm_predict_cov_kernel(double* __restrict__ P, int64_t ld, int n, int row_begin, int row_end,
+                                      const double* __restrict__ scal, double mv) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const double g0 = scal[kScalG0], g1 = scal[kScalG1];
+  const bool own_robot = (row_begin == 0);
+  if (t >= 3 && t < n) {
+    if (own_robot) {  // rows 0-1, column t
+      const double p2 = P[2 * ld + t];
+      P[0 * ld + t] += g0 * p2;
+      P[1 * ld + t] += g1 * p2;
+    }
+    if (t >= row_begin && t < row_end) {  // row t, columns 0-1
+      double* row = P + (int64_t)(t - row_begin) * ld;
+      const double p2 = row[2];
+      row[0] += g0 * p2;
+      row[1] += g1 * p2;
+    }
+  } else if (t == 0 && own_robot) {
+    double b[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) b[i][c] = P[i * ld + c];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      b[0][c] += g0 * b[2][c];
+      b[1][c] += g1 * b[2][c];
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      b[i][0] += g0 * b[i][2];
+      b[i][1] += g1 * b[i][2];
+    }
+    b[0][0] += mv * mv;
+    b[1][1] += mv * mv;
+    b[2][2] += (mv / 2.0) * (mv / 2.0);
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) P[i * ld + c] = b[i][c];
+  }
+}
+
+// -------------------------------------------------------------------------------------------------------
+// a8-a9 gather (:443-473): every CTA recomputes the innovation, H5, S and S^-1 (25 + 5 loads), then
+// thread t produces HP[:, t] from the 5 rows (coalesced) and, for a local row t, PHt[t, :] from the
+// 5 columns (one or two 32-byte sectors per row) and K[t, :]. Nothing in P or mu is written here, so the
+// streaming kernel that follows can update P in place.
+// -------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
+  __shared__ double sh[2][5];
+  __shared__ double ssi[2][2];
+  __shared__ double ssq[2][2];  // S - Q
+  __shared__ double sy[2];
+  const int j = a.j;
+  const int idx5[5] = {0, 1, 2, j, j + 1};
+  if (threadIdx.x == 0) {
+    const Innov in = innovation(*a.mu5[0], *a.mu5[1], *a.mu5[2], *a.mu5[3], *a.mu5[4], a.rng, a.brg);
+    double hp5[2][5];
+#pragma unroll
+    for (int c = 0; c < 5; ++c) {
+      double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const double p = a.row[k][idx5[c]];
+        s0 = fma(in.h[0][k], p, s0);
+        s1 = fma(in.h[1][k], p, s1);
+      }
+      hp5[0][c] = s0;
+      hp5[1][c] = s1;
+    }
+    double s[2][2], si[2][2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        double acc = 0.0;
+#pragma unroll
+        for (int c = 0; c < 5; ++c) acc = fma(hp5[r][c], in.h[b][c], acc);
+        s[r][b] = acc;
+      }
+    const double qn = a.mm * a.mm;
+    ssq[0][0] = s[0][0]; ssq[0][1] = s[0][1]; ssq[1][0] = s[1][0]; ssq[1][1] = s[1][1];
+    s[0][0] += qn;
+    s[1][1] += qn;
+    inv2(s, si);
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+#pragma unroll
+      for (int k = 0; k < 5; ++k) sh[r][k] = in.h[r][k];
+      ssi[r][0] = si[r][0];
+      ssi[r][1] = si[r][1];
+    }
+    sy[0] = in.y0;
+    sy[1] = in.y1;
+    if (blockIdx.x == 0) {
+      a.scal[kScalY0] = in.y0;
+      a.scal[kScalY1] = in.y1;
+    }
+  }
+  __syncthreads();
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= a.n) return;
+  if (a.shard && t < 3 && !(t >= a.row_begin && t < a.row_end)) {
+    // row-block shard that does not own the robot rows: keep the replicated pose entries of mu current.
+    // K[t, :] of rows 0-2 is rebuilt from the exchanged rows (mu5 points into the exchange buffer, so
+    // writing mu here does not race with the innovation above).
+    double ph0 = 0.0, ph1 = 0.0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      const double p = a.row[t][idx5[k]];
+      ph0 = fma(p, sh[0][k], ph0);
+      ph1 = fma(p, sh[1][k], ph1);
+    }
+    const double kk0 = ph0 * ssi[0][0] + ph1 * ssi[1][0];
+    const double kk1 = ph0 * ssi[0][1] + ph1 * ssi[1][1];
+    a.mu_out[t] += kk0 * sy[0] + kk1 * sy[1];
+  }
+  double hp0 = 0.0, hp1 = 0.0;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    const double p = a.row[k][t];
+    hp0 = fma(sh[0][k], p, hp0);
+    hp1 = fma(sh[1][k], p, hp1);
+  }
+  double k0 = 0.0, k1 = 0.0, pht0 = 0.0, pht1 = 0.0;
+  const bool local = (t >= a.row_begin && t < a.row_end);
+  if (local) {
+    const double* prow = a.P + (int64_t)(t - a.row_begin) * a.ld;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      const double p = prow[idx5[k]];
+      pht0 = fma(p, sh[0][k], pht0);
+      pht1 = fma(p, sh[1][k], pht1);
+    }
+    k0 = pht0 * ssi[0][0] + pht1 * ssi[1][0];
+    k1 = pht0 * ssi[0][1] + pht1 * ssi[1][1];
+    a.K0[t] = k0;
+    a.K1[t] = k1;
+  }
+  if (a.flags & kFlagJoseph) {
+    // single-GPU only (the host refuses Joseph on a shard): K[t] of every column t is local.
+    const double qn = a.mm * a.mm;
+    a.W0[t] = hp0 - qn * k0;
+    a.W1[t] = hp1 - qn * k1;
+    a.A0[t] = pht0 - (k0 * ssq[0][0] + k1 * ssq[1][0]);
+    a.A1[t] = pht1 - (k0 * ssq[0][1] + k1 * ssq[1][1]);
+  } else {
+    a.W0[t] = hp0;
+    a.W1[t] = hp1;
+  }
+}
+
+// -------------------------------------------------------------------------------------------------------
+// a10-a11 streaming update (:476-480): P[i, c] -= K[i,0] W[0,c] + K[i,1] W[1,c]  (+ Joseph terms), in place.
+//
+// Tiling: a CTA of LM_THREADS threads owns LM_THREADS column groups of 4 doubles (one 256-bit access per
+// thread per row) and RB rows; the two W values of a thread's 4 columns stay in registers for all RB rows,
+// K of the RB rows is staged in shared memory, and UNROLL rows of P are in flight per thread
+// (UNROLL x 32 B x threads x resident CTAs per SM of loads outstanding). Columns beyond the last full tile
+// are done by an extra column of CTAs with a (row, group) mapping. CTAs of column tile 0 also apply
+// mu += K y for their rows.
+// -------------------------------------------------------------------------------------------------------
+template <int RB, int UNROLL, bool JOSEPH>
+__global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs a) {
+  __shared__ double sk[RB][4];
+  const int tid = threadIdx.x;
+  const int r0 = a.row_begin + blockIdx.y * RB;          // first global row of this CTA
+  const int nrows = min(RB, a.row_end - r0);
+  for (int r = tid; r < nrows; r += LM_THREADS) {
+    sk[r][0] = a.K0[r0 + r];
+    sk[r][1] = a.K1[r0 + r];
+    if (JOSEPH) {
+      sk[r][2] = a.A0[r0 + r];
+      sk[r][3] = a.A1[r0 + r];
+    }
+  }
+  __syncthreads();
+  if (blockIdx.x == 0) {  // a10: mu += K y for this CTA's rows
+    const double y0 = a.scal[kScalY0], y1 = a.scal[kScalY1];
+    for (int r = tid; r < nrows; r += LM_THREADS) a.mu[r0 + r] += sk[r][0] * y0 + sk[r][1] * y1;
+  }
+  double* __restrict__ Pblk = a.P + (int64_t)(r0 - a.row_begin) * a.ld;
+  if ((int)blockIdx.x < a.full_tiles) {
+    const int c = (blockIdx.x * LM_THREADS + tid) * 4;
+    const double4x w0 = ldg256(a.W0 + c), w1 = ldg256(a.W1 + c);
+    double4x kc0, kc1;
+    if (JOSEPH) {
+      kc0 = ldg256(a.K0 + c);
+      kc1 = ldg256(a.K1 + c);
+    }
+    double* p = Pblk + c;
+    int r = 0;
+    for (; r + UNROLL <= nrows; r += UNROLL) {
+      double4x v[UNROLL];
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) v[u] = ldg256_stream(p + (int64_t)(r + u) * a.ld);
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) {
+        const double k0 = -sk[r + u][0], k1 = -sk[r + u][1];
+        v[u].a = fma(k1, w1.a, fma(k0, w0.a, v[u].a));
+        v[u].b = fma(k1, w1.b, fma(k0, w0.b, v[u].b));
+        v[u].c = fma(k1, w1.c, fma(k0, w0.c, v[u].c));
+        v[u].d = fma(k1, w1.d, fma(k0, w0.d, v[u].d));
+        if (JOSEPH) {
+          const double a0 = -sk[r + u][2], a1 = -sk[r + u][3];
+          v[u].a = fma(a1, kc1.a, fma(a0, kc0.a, v[u].a));
+          v[u].b = fma(a1, kc1.b, fma(a0, kc0.b, v[u].b));
+          v[u].c = fma(a1, kc1.c, fma(a0, kc0.c, v[u].c));
+          v[u].d = fma(a1, kc1.d, fma(a0, kc0.d, v[u].d));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) stg256(p + (int64_t)(r + u) * a.ld, v[u]);
+    }
+    for (; r < nrows; ++r) {
+      double4x v = ldg256_stream(p + (int64_t)r * a.ld);
+      const double k0 = -sk[r][0], k1 = -sk[r][1];
+      v.a = fma(k1, w1.a, fma(k0, w0.a, v.a));
+      v.b = fma(k1, w1.b, fma(k0, w0.b, v.b));
+      v.c = fma(k1, w1.c, fma(k0, w0.c, v.c));
+      v.d = fma(k1, w1.d, fma(k0, w0.d, v.d));
+      if (JOSEPH) {
+        const double a0 = -sk[r][2], a1 = -sk[r][3];
+        v.a = fma(a1, kc1.a, fma(a0, kc0.a, v.a));
+        v.b = fma(a1, kc1.b, fma(a0, kc0.b, v.b));
+        v.c = fma(a1, kc1.c, fma(a0, kc0.c, v.c));
+        v.d = fma(a1, kc1.d, fma(a0, kc0.d, v.d));
+      }
+      stg256(p + (int64_t)r * a.ld, v);
+    }
+  } else {
+    // column tail: a.tail_groups (< LM_THREADS) groups per row, (row, group) mapping
+    const int tg = a.tail_groups;
+    const int cbase = a.full_tiles * LM_THREADS * 4;
+    for (int e = tid; e < nrows * tg; e += LM_THREADS) {
+      const int r = e / tg, c = cbase + (e - r * tg) * 4;
+      const double4x w0 = ldg256(a.W0 + c), w1 = ldg256(a.W1 + c);
+      double4x v = ldg256_stream(Pblk + (int64_t)r * a.ld + c);
+      const double k0 = -sk[r][0], k1 = -sk[r][1];
+      v.a = fma(k1, w1.a, fma(k0, w0.a, v.a));
+      v.b = fma(k1, w1.b, fma(k0, w0.b, v.b));
+      v.c = fma(k1, w1.c, fma(k0, w0.c, v.c));
+      v.d = fma(k1, w1.d, fma(k0, w0.d, v.d));
+      if (JOSEPH) {
+        const double4x kc0 = ldg256(a.K0 + c), kc1 = ldg256(a.K1 + c);
+        const double a0 = -sk[r][2], a1 = -sk[r][3];
+        v.a = fma(a1, kc1.a, fma(a0, kc0.a, v.a));
+        v.b = fma(a1, kc1.b, fma(a0, kc0.b, v.b));
+        v.c = fma(a1, kc1.c, fma(a0, kc0.c, v.c));
+        v.d = fma(a1, kc1.d, fma(a0, kc0.d, v.d));
+      }
+      stg256(Pblk + (int64_t)r * a.ld + c, v);
+    }
+  }
+}
+
+// shard export: copy the locally owned ones of rows {0,1,2,j,j+1} (and their mu entries, stashed at column
+// ld of each exported row) into the replicated exchange buffer.
+__global__ void lm_export_rows_kernel(const double* __restrict__ P, const double* __restrict__ mu, int64_t ld,
+                                      int row_begin, int row_end, int j, double* __restrict__ rows5,
+                                      int64_t ldx) {
+  const int k = blockIdx.y;
+  const int row = (k < 3) ? k : j + (k - 3);
+  if (row < row_begin || row >= row_end) return;
+  const double* src = P + (int64_t)(row - row_begin) * ld;
+  double* dst = rows5 + (int64_t)k * ldx;
+  for (int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; c < ld; c += (int64_t)gridDim.x * blockDim.x)
+    dst[c] = src[c];
+  if (blockIdx.x == 0 && threadIdx.x == 0) dst[ld] = mu[row];
+}
+
+// after a sharded update every rank refreshes its replicated copy of the 5 mu entries from K rows it can
+// rebuild out of the exchanged rows: K[r, :] = (rows5[k][idx5] . H5^T) S^-1 — done inside the gather kernel
+// of the NEXT update through the stash, so nothing is needed here.
+
+// -------------------------------------------------------------------------------------------------------
+// host launchers
+// -------------------------------------------------------------------------------------------------------
+cudaError_t lm_launch_augment(double* mu, double* P, int64_t ld, int row_begin, int row_end, int j, double gx,
+                              double gy, cudaStream_t st) {
+  lm_augment_kernel<<<1, 32, 0, st>>>(mu, P, ld, row_begin, row_end, j, gx, gy);
+  return cudaGetLastError();
+}
+
+cudaError_t lm_launch_predict(double* mu, double* P, int64_t ld, int n, int row_begin, int row_end,
+                              double* scal, double ang, double lin, double mv, int flags, bool update_mean,
+                              cudaStream_t st) {
+  if (update_mean) lm_predict_mean_kernel<<<1, 32, 0, st>>>(mu, scal, ang, lin, flags);
+  const int threads = 256;
+  lm_predict_cov_kernel<<<(n + threads - 1) / threads, threads, 0, st>>>(P, ld, n, row_begin, row_end, scal,
+                                                                         mv);
+  return cudaGetLastError();
+}
+
+cudaError_t lm_launch_gather(const LmGatherArgs& a, cudaStream_t st) {
+  const int threads = 256;
+  lm_gather_kernel<<<(a.n + threads - 1) / threads, threads, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+template <int RB, int UNROLL>
+static cudaError_t launch_update_t(const LmUpdateArgs& a0, bool joseph, cudaStream_t st) {
+  LmUpdateArgs a = a0;
+  const int groups = (a.n + 3) / 4;  // groups holding at least one real column
+  a.full_tiles = groups / LM_THREADS;
+  a.tail_groups = groups - a.full_tiles * LM_THREADS;
+  const int rows = a.row_end - a.row_begin;
+  if (rows <= 0) return cudaSuccess;
+  dim3 grid(a.full_tiles + (a.tail_groups ? 1 : 0), (rows + RB - 1) / RB);
+  if (joseph)
+    lm_rank_update_kernel<RB, UNROLL, true><<<grid, LM_THREADS, 0, st>>>(a);
+  else
+    lm_rank_update_kernel<RB, UNROLL, false><<<grid, LM_THREADS, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t lm_launch_update(const LmUpdateArgs& a, bool joseph, int variant, cudaStream_t st) {
+  switch (variant) {
+    case 1: return launch_update_t<16, 8>(a, joseph, st);
+    case 2: return launch_update_t<64, 8>(a, joseph, st);
+    case 3: return launch_update_t<32, 4>(a, joseph, st);
+    case 4: return launch_update_t<128, 8>(a, joseph, st);
+    case 5: return launch_update_t<32, 16>(a, joseph, st);
+    default: return launch_update_t<32, 8>(a, joseph, st);
+  }
+}
+
+cudaError_t lm_launch_export_rows(const double* P, const double* mu, int64_t ld, int row_begin, int row_end,
+                                  int j, double* rows5, int64_t ldx, cudaStream_t st) {
+  dim3 grid(8, 5);
+  lm_export_rows_kernel<<<grid, 256, 0, st>>>(P, mu, ld, row_begin, row_end, j, rows5, ldx);
+  return cudaGetLastError();
+}
+
+}  // namespace ekf

@@ -1,0 +1,377 @@
+"""Drop-in Python call surface of the reference's EKF hot path, backed by libekf_b200.so (sm_100a CUDA).
+
+This is the module ``src/ekf_bindings.py`` of the reference was meant to be (it is an empty file there): the
+five module-level functions keep the reference's names, positional order and return order, so ``replay()``
+(``src/replay_no_ros.py:66-248``) drives them unchanged once its globals are rebound (see ``replay.py``):
+
+    delta_phi(ticks, prev_ticks, resolution) -> float                      replay_no_ros.py:250-266
+    displacement(R, baseline, dphi_left, dphi_right) -> (angular, linear)  replay_no_ros.py:484-497
+    EKF_pose_estimation(ang, lin, mean, cov, delta_t, pairs, TAG_INDEX)
+        -> (mean, covariance, tags_positions)                              replay_no_ros.py:269-482
+    predict(state, covariance, control, dt) -> (state, covariance)         EKF-SLAM.py:29-56
+    update(state, covariance, observation, landmark_pos) -> (state, cov)   EKF-SLAM.py:59-84
+
+plus the handle classes that keep state resident in HBM: ``BatchedEKF`` (B filters, fused step kernel) and
+``LargeMapEKF`` (one filter, streamed covariance, optional row-block shard).
+
+PyTorch is used only to own device memory and streams. There is NO CPU fallback: every compute call raises
+if the CUDA library or a device is missing.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import capi
+
+# --- module constants the reference reads at call time (replay_no_ros.py:15-36) ---------------------------
+MOTION_MODEL_VARIANCE = 0.1
+MEASUREMENT_MODEL_VARIANCE = 0.7
+ENABLE_MEASUREMENT_MODEL = True
+ENABLE_CIRCULAR_INTERPOLATION = True
+DISABLE_MOTION_MODEL = False
+IGNORE_TAGS = []
+JOSEPH_FORM = False          # False = plain (I-KH)P like the reference (:480); True = one-pass Joseph
+
+_flag_source = None          # module whose globals override the constants above (set by replay.py)
+
+
+def use_flags_from(module) -> None:
+    """Read the flag constants from ``module``'s globals at call time, as the reference does."""
+    global _flag_source
+    _flag_source = module
+
+
+def _flag(name):
+    if _flag_source is not None and hasattr(_flag_source, name):
+        return getattr(_flag_source, name)
+    return globals()[name]
+
+
+def _torch():
+    import torch
+    if not torch.cuda.is_available():
+        raise capi.EkfLibraryError("no CUDA device: the EKF core has no CPU fallback")
+    return torch
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr())
+
+
+def _stream_ptr(torch):
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# a1 / a2
+# ---------------------------------------------------------------------------------------------------------
+def delta_phi(ticks: int, prev_ticks: int, resolution: int) -> float:
+    return float(capi.lib().ekf_delta_phi(int(ticks), int(prev_ticks), int(resolution)))
+
+
+def displacement(R: float, baseline: float, delta_phi_left: float, delta_phi_right: float):
+    ang, lin = C.c_double(), C.c_double()
+    capi.call("ekf_displacement", float(R), float(baseline), float(delta_phi_left), float(delta_phi_right),
+              C.byref(ang), C.byref(lin))
+    return ang.value, lin.value
+
+
+# ---------------------------------------------------------------------------------------------------------
+# a3 / a4 — host bookkeeping for the single-filter call surface (integers, dict order: bit-exact by
+# construction). The batched path has its own device kernel for perturbed detections.
+# ---------------------------------------------------------------------------------------------------------
+def associate_window(mean, timestamp_detectedTags_pair_list, TAG_INDEX, ignore_tags=()):
+    """Gate, slot assignment (mutates TAG_INDEX), window average, range/bearing and global guess
+    (replay_no_ros.py:280-337). Returns dict slot -> [gx, gy, err, tag_id, range, bearing] in
+    first-seen-in-window order."""
+    buckets = {}
+    for _ts, dets in timestamp_detectedTags_pair_list:
+        for tag in dets:
+            if tag.tag_id in ignore_tags:
+                continue
+            tx, tz = float(tag.pose_t[0][0]), float(tag.pose_t[2][0])
+            if tz * tz + tx * tx > 2.25:
+                continue
+            if tag.tag_id not in TAG_INDEX:
+                TAG_INDEX[tag.tag_id] = len(TAG_INDEX)
+            acc = buckets.setdefault(TAG_INDEX[tag.tag_id], [0.0, 0.0, 0.0, 0])
+            acc[0] += tx                 # sequential sums == np.mean along the window axis
+            acc[1] += tz
+            acc[2] += float(tag.pose_err)
+            acc[3] += 1
+    inv = {slot: tid for tid, slot in TAG_INDEX.items()}
+    px, py, pth = float(mean[0]), float(mean[1]), float(mean[2])
+    out = {}
+    for slot, (sx, sz, se, k) in buckets.items():
+        x_rel, y_rel = sz / k, -(sx / k)
+        rng = math.sqrt(x_rel * x_rel + y_rel * y_rel)
+        brg = math.atan2(y_rel, x_rel)
+        out[slot] = [px + rng * math.cos(brg + pth), py + rng * math.sin(brg + pth), se / k, inv[slot], rng, brg]
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# large-map / single-filter handle
+# ---------------------------------------------------------------------------------------------------------
+class LargeMapEKF:
+    """One EKF-SLAM filter with its state resident on one GPU (or one row block of it).
+
+    ``capacity`` landmarks are pre-allocated (n = 3 + 2*capacity, leading dimension padded to 16 doubles);
+    landmarks not yet augmented have zero rows/columns, which leaves every result identical to the
+    reference's growing arrays.
+    """
+
+    def __init__(self, capacity: int, device: int = 0, row_range=None):
+        torch = _torch()
+        self.torch = torch
+        self.capacity = int(capacity)
+        self.device = int(device)
+        n, ld = C.c_int(), C.c_int64()
+        capi.call("ekf_lm_layout", self.capacity, C.byref(n), C.byref(ld))
+        self.n, self.ld = n.value, ld.value
+        self.row_begin, self.row_end = (0, self.n) if row_range is None else map(int, row_range)
+        dev = torch.device("cuda", self.device)
+        self.mu = torch.zeros(self.ld, dtype=torch.float64, device=dev)
+        self.P = torch.zeros((self.row_end - self.row_begin, self.ld), dtype=torch.float64, device=dev)
+        h = C.c_void_p()
+        capi.call("ekf_lm_create", self.capacity, self.device, C.byref(h))
+        self._h = h
+        capi.call("ekf_lm_bind_state", h, _ptr(self.mu), _ptr(self.P), self.ld, self.row_begin, self.row_end)
+        self.rows5 = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            capi.lib().ekf_lm_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    # -- configuration ----------------------------------------------------------------------------------
+    def set_noise(self, motion_var: float, meas_var: float):
+        capi.call("ekf_lm_set_noise", self._h, float(motion_var), float(meas_var))
+
+    def set_flags(self, circular=True, measurement=True, disable_motion=False, joseph=False):
+        capi.call("ekf_lm_set_flags", self._h, int(circular), int(measurement), int(disable_motion),
+                  capi.EKF_COV_JOSEPH if joseph else capi.EKF_COV_PLAIN)
+
+    # -- state transfer (reference layout <-> device layout) ---------------------------------------------
+    def load(self, mean: np.ndarray, cov: np.ndarray):
+        """Upload a reference-layout state of size m <= n (rows of this block only)."""
+        torch = self.torch
+        m = len(mean)
+        if m > self.n or cov.shape != (m, m):
+            raise ValueError("state larger than capacity or inconsistent shapes")
+        mu = np.zeros(self.ld)
+        mu[:m] = mean
+        self.mu.copy_(torch.from_numpy(mu))
+        blk = np.zeros((self.row_end - self.row_begin, self.ld))
+        lo, hi = self.row_begin, min(self.row_end, m)
+        if hi > lo:
+            blk[: hi - lo, :m] = cov[lo:hi, :]
+        self.P.copy_(torch.from_numpy(blk))
+
+    def state(self, m: int | None = None):
+        """Download (mean[:m], cov block[:, :m]) as numpy float64."""
+        m = self.n if m is None else m
+        mu = self.mu[:m].cpu().numpy().copy()
+        hi = min(self.row_end, m)
+        blk = self.P[: max(hi - self.row_begin, 0), :m].cpu().numpy().copy()
+        return mu, blk
+
+    # -- steps ------------------------------------------------------------------------------------------
+    def augment(self, slot: int, gx: float, gy: float):
+        capi.call("ekf_lm_augment", self._h, int(slot), float(gx), float(gy), _stream_ptr(self.torch))
+
+    def predict(self, ang: float, lin: float):
+        capi.call("ekf_lm_predict", self._h, float(ang), float(lin), _stream_ptr(self.torch))
+
+    def update(self, slot: int, rng: float, brg: float):
+        capi.call("ekf_lm_update", self._h, int(slot), float(rng), float(brg), _stream_ptr(self.torch))
+
+    def export_rows(self, slot: int):
+        if self.rows5 is None:
+            self.rows5 = self.torch.zeros((5, self.ld + 4), dtype=self.torch.float64, device=self.mu.device)
+        capi.call("ekf_lm_export_rows", self._h, int(slot), _ptr(self.rows5), _stream_ptr(self.torch))
+        return self.rows5
+
+    def update_from_rows(self, slot: int, rng: float, brg: float, rows5=None):
+        rows5 = self.rows5 if rows5 is None else rows5
+        capi.call("ekf_lm_update_from_rows", self._h, int(slot), float(rng), float(brg), _ptr(rows5),
+                  _stream_ptr(self.torch))
+
+    def sync(self):
+        capi.call("ekf_lm_sync", self._h)
+
+
+_scalar_cache = {}
+
+
+def _scalar_filter(n_landmarks: int) -> LargeMapEKF:
+    cap = max(4, 1 << max(0, (n_landmarks - 1)).bit_length())   # round capacity up to a power of two
+    f = _scalar_cache.get(cap)
+    if f is None:
+        f = _scalar_cache[cap] = LargeMapEKF(cap)
+    return f
+
+
+def EKF_pose_estimation(angular_displacement, linear_displacement, motion_model_mean, motion_model_covariance,
+                        delta_t, timestamp_detectedTags_pair_list, TAG_INDEX):
+    """Drop-in for replay_no_ros.py:269-482: NEW (mean, covariance) arrays come back, TAG_INDEX is mutated in
+    place, ``tags_positions`` is the reference's dict of 6-element lists. ``delta_t`` is unused (as there)."""
+    mean_in = np.asarray(motion_model_mean, dtype=np.float64)
+    cov_in = np.asarray(motion_model_covariance, dtype=np.float64)
+    tags = associate_window(mean_in, timestamp_detectedTags_pair_list, TAG_INDEX, tuple(_flag("IGNORE_TAGS")))
+    n_old = len(mean_in)
+    n_new = max(n_old, 3 + 2 * len(TAG_INDEX))
+    f = _scalar_filter((n_new - 3) // 2)
+    f.set_noise(_flag("MOTION_MODEL_VARIANCE"), _flag("MEASUREMENT_MODEL_VARIANCE"))
+    f.set_flags(_flag("ENABLE_CIRCULAR_INTERPOLATION"), _flag("ENABLE_MEASUREMENT_MODEL"),
+                _flag("DISABLE_MOTION_MODEL"), JOSEPH_FORM)
+    f.load(mean_in, cov_in)
+    for i in range(n_old, n_new, 2):                      # :355-360 (KeyError like the reference at :359)
+        slot = (i - 3) // 2
+        f.augment(slot, tags[slot][0], tags[slot][1])
+    f.predict(float(angular_displacement), float(linear_displacement))
+    for slot, rec in tags.items():                        # first-seen-in-window order (:436)
+        f.update(slot, rec[4], rec[5])
+    mean, cov = f.state(n_new)
+    return mean, cov, tags
+
+
+# ---------------------------------------------------------------------------------------------------------
+# batched handle
+# ---------------------------------------------------------------------------------------------------------
+class BatchedEKF:
+    """B independent EKF-SLAM filters of fixed landmark capacity, state resident in HBM (SoA records)."""
+
+    def __init__(self, batch: int, n_landmarks: int, device: int = 0):
+        torch = _torch()
+        self.torch = torch
+        self.batch, self.n_landmarks, self.device = int(batch), int(n_landmarks), int(device)
+        n, ld, ps, ms = C.c_int(), C.c_int(), C.c_int64(), C.c_int64()
+        capi.call("ekf_batch_layout", self.n_landmarks, C.byref(n), C.byref(ld), C.byref(ps), C.byref(ms))
+        self.n, self.ld, self.p_stride, self.mu_stride = n.value, ld.value, ps.value, ms.value
+        dev = torch.device("cuda", self.device)
+        self.dev = dev
+        self.mu = torch.zeros((self.batch, self.mu_stride), dtype=torch.float64, device=dev)
+        self.P = torch.zeros((self.batch, self.p_stride), dtype=torch.float64, device=dev)
+        self.n_known = torch.zeros(self.batch, dtype=torch.int32, device=dev)
+        self.motion_var = torch.full((self.batch,), MOTION_MODEL_VARIANCE, dtype=torch.float64, device=dev)
+        self.meas_var = torch.full((self.batch,), MEASUREMENT_MODEL_VARIANCE, dtype=torch.float64, device=dev)
+        h = C.c_void_p()
+        capi.call("ekf_batch_create", self.n_landmarks, self.batch, self.device, C.byref(h))
+        self._h = h
+        capi.call("ekf_batch_bind_state", h, _ptr(self.mu), _ptr(self.P), _ptr(self.n_known))
+        capi.call("ekf_batch_set_noise", h, _ptr(self.motion_var), _ptr(self.meas_var))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            capi.lib().ekf_batch_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def set_noise(self, motion_var, meas_var):
+        t = self.torch
+        self.motion_var.copy_(t.as_tensor(np.broadcast_to(motion_var, (self.batch,)).copy(), dtype=t.float64))
+        self.meas_var.copy_(t.as_tensor(np.broadcast_to(meas_var, (self.batch,)).copy(), dtype=t.float64))
+
+    def set_flags(self, circular=True, measurement=True, disable_motion=False, joseph=False):
+        capi.call("ekf_batch_set_flags", self._h, int(circular), int(measurement), int(disable_motion),
+                  capi.EKF_COV_JOSEPH if joseph else capi.EKF_COV_PLAIN)
+
+    def init(self, p0_diag: float = MOTION_MODEL_VARIANCE):
+        """mean = 0, covariance = p0 * I3 (replay_no_ros.py:69-70), no landmark known."""
+        capi.call("ekf_batch_init", self._h, float(p0_diag), _stream_ptr(self.torch))
+
+    def step(self, ang, lin, slot=None, rng=None, brg=None):
+        """One fused filter-step; arguments are DEVICE tensors: ang/lin (B,), slot int32 / rng / brg (B, m)."""
+        m = 0 if slot is None else int(slot.shape[1])
+        z = C.c_void_p(0)
+        capi.call("ekf_batch_step", self._h, _ptr(ang), _ptr(lin), _ptr(slot) if m else z,
+                  _ptr(rng) if m else z, _ptr(brg) if m else z, m, _stream_ptr(self.torch))
+
+    def step_ticks(self, ticks_l, ticks_r, prev_l, prev_r, wheel_radius, baseline, resolution, slot=None,
+                   rng=None, brg=None):
+        m = 0 if slot is None else int(slot.shape[1])
+        z = C.c_void_p(0)
+        capi.call("ekf_batch_step_ticks", self._h, _ptr(ticks_l), _ptr(ticks_r), _ptr(prev_l), _ptr(prev_r),
+                  float(wheel_radius), float(baseline), int(resolution), _ptr(slot) if m else z,
+                  _ptr(rng) if m else z, _ptr(brg) if m else z, m, _stream_ptr(self.torch))
+
+    def step_host(self, ang, lin, slot, rng, brg, pose_out):
+        """End-to-end step with HOST (ideally pinned) torch tensors / numpy arrays: H2D, step, D2H of the
+        pose (B, 3) into ``pose_out``; synchronous."""
+        def hp(a):
+            return C.c_void_p(a.data_ptr() if hasattr(a, "data_ptr") else a.ctypes.data)
+        m = 0 if slot is None else int(slot.shape[1])
+        z = C.c_void_p(0)
+        capi.call("ekf_batch_step_host", self._h, hp(ang), hp(lin), hp(slot) if m else z, hp(rng) if m else z,
+                  hp(brg) if m else z, m, hp(pose_out))
+
+    def load(self, mean: np.ndarray, cov: np.ndarray, first: int = 0):
+        """Upload reference-layout states: mean (k, n), cov (k, n, n) -> filters [first, first+k)."""
+        t = self.torch
+        mean = np.ascontiguousarray(mean, dtype=np.float64)
+        cov = np.ascontiguousarray(cov, dtype=np.float64)
+        k = mean.shape[0]
+        assert mean.shape == (k, self.n) and cov.shape == (k, self.n, self.n)
+        dm, dc = t.from_numpy(mean).to(self.dev), t.from_numpy(cov).to(self.dev)
+        capi.call("ekf_batch_pack", self._h, _ptr(dm), _ptr(dc), int(first), int(k), _stream_ptr(t))
+        t.cuda.current_stream().synchronize()
+
+    def state(self, first: int = 0, count: int | None = None):
+        """Download reference-layout (mean (k, n), cov (k, n, n)) of filters [first, first+count)."""
+        t = self.torch
+        count = self.batch - first if count is None else count
+        dm = t.empty((count, self.n), dtype=t.float64, device=self.dev)
+        dc = t.empty((count, self.n, self.n), dtype=t.float64, device=self.dev)
+        capi.call("ekf_batch_unpack", self._h, _ptr(dm), _ptr(dc), int(first), int(count), _stream_ptr(t))
+        return dm.cpu().numpy(), dc.cpu().numpy()
+
+    def fault_count(self) -> int:
+        v = C.c_int64()
+        capi.call("ekf_batch_fault_count", self._h, C.byref(v))
+        return v.value
+
+
+# ---------------------------------------------------------------------------------------------------------
+# 3-state surface (src/EKF-SLAM.py)
+# ---------------------------------------------------------------------------------------------------------
+def predict3_batched(state, cov, v, omega, dt):
+    """In place on device tensors: state (3, B), cov (9, B), v / omega / dt (B,)."""
+    torch = _torch()
+    capi.call("ekf3_predict", int(state.shape[1]), _ptr(state), _ptr(cov), _ptr(v), _ptr(omega), _ptr(dt),
+              _stream_ptr(torch))
+
+
+def update3_batched(state, cov, rng, brg, lx, ly):
+    torch = _torch()
+    capi.call("ekf3_update", int(state.shape[1]), _ptr(state), _ptr(cov), _ptr(rng), _ptr(brg), _ptr(lx),
+              _ptr(ly), _stream_ptr(torch))
+
+
+def _dev1(torch, x):
+    return torch.tensor([float(x)], dtype=torch.float64, device="cuda")
+
+
+def predict(state, covariance, control, dt):
+    """Drop-in for EKF-SLAM.py:29-56 (returns new arrays)."""
+    torch = _torch()
+    st = torch.tensor(np.asarray(state, dtype=np.float64).reshape(3, 1), device="cuda")
+    cv = torch.tensor(np.asarray(covariance, dtype=np.float64).reshape(9, 1), device="cuda")
+    predict3_batched(st, cv, _dev1(torch, control[0]), _dev1(torch, control[1]), _dev1(torch, dt))
+    return st.cpu().numpy().reshape(3), cv.cpu().numpy().reshape(3, 3)
+
+
+def update(state, covariance, observation, landmark_pos):
+    """Drop-in for EKF-SLAM.py:59-84 (returns new arrays)."""
+    torch = _torch()
+    st = torch.tensor(np.asarray(state, dtype=np.float64).reshape(3, 1), device="cuda")
+    cv = torch.tensor(np.asarray(covariance, dtype=np.float64).reshape(9, 1), device="cuda")
+    update3_batched(st, cv, _dev1(torch, observation[0]), _dev1(torch, observation[1]),
+                    _dev1(torch, landmark_pos[0]), _dev1(torch, landmark_pos[1]))
+    return st.cpu().numpy().reshape(3), cv.cpu().numpy().reshape(3, 3)
