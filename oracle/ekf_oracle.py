@@ -259,7 +259,8 @@ def ekf_pose_estimation(ang, lin, mean, cov, delta_t, pairs, tag_index, flags: F
     return mean, cov, tags
 
 
-def step_from_observations(mean, cov, ang, lin, obs, flags: Flags | None = None, n_lm_known=None):
+def step_from_observations(mean, cov, ang, lin, obs, flags: Flags | None = None, n_lm_known=None,
+                           form: str = "rank"):
     """Steady-state / batched form of one filter-step on a FIXED-capacity state: ``obs`` is a list of
     (slot, range, bearing) already associated and averaged. Slots >= n_lm_known are augmented first from
     the pre-predict pose (Appendix A.3). In place on copies; returns (mean, cov, n_lm_known)."""
@@ -280,6 +281,12 @@ def step_from_observations(mean, cov, ang, lin, obs, flags: Flags | None = None,
     mean[0] += dx
     mean[1] += dy
     mean[2] = th
+    if form == "dense":      # the reference's own O(n^3) cost profile (:430, :473, :480)
+        cov = _predict_cov_dense(cov, g0, g1, flags.motion_var)
+        if flags.enable_measurement:
+            for slot, rng, brg in obs:
+                mean, cov = _update_dense(mean, cov, slot, rng, brg, flags.meas_var, flags.joseph)
+        return mean, cov, n_lm_known
     predict_cov_rank(cov, g0, g1, flags.motion_var)
     if flags.enable_measurement:
         for slot, rng, brg in obs:

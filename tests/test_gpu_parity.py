@@ -1,0 +1,399 @@
+"""GPU parity tests: the CUDA path (through the C-ABI, via ekf_bindings) against the golden vectors dumped
+from the unmodified reference and against the numpy oracle on the same seeded inputs.
+
+Tolerance: 1e-9 (BASELINE.json north star) on max-norm mu, max-norm P and covariance-scaled P; landmark
+association / slot bookkeeping must be identical."""
+import numpy as np
+import pytest
+
+from conftest import TOL, assert_parity, golden
+from oracle import ekf_oracle as eo
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eb():
+    import torch
+    assert torch.cuda.is_available()
+    from slam_duckietown_b200 import capi, ekf_bindings
+    capi.lib()          # fail loudly if the extension is missing
+    return ekf_bindings
+
+
+def _dev(t, a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).to(t)
+
+
+def _run_batched(eb, z, joseph=False, ticks=False):
+    L = int(z["n_landmarks"])
+    T, B, m = z["slot"].shape
+    f = eb.BatchedEKF(B, L)
+    f.set_noise(z["motion_var"], z["meas_var"])
+    f.set_flags(joseph=joseph)
+    f.init(0.1)
+    out = {}
+    keep = {int(t): i for i, t in enumerate(z["keep_t"])}
+    for t in range(T):
+        f.step(_dev(f.dev, z["ang"][t]), _dev(f.dev, z["lin"][t]), _dev(f.dev, z["slot"][t]),
+               _dev(f.dev, z["rng"][t]), _dev(f.dev, z["brg"][t]))
+        if t in keep:
+            out[t] = f.state()
+    assert f.fault_count() == 0
+    assert np.all(f.n_known.cpu().numpy() == L)
+    return out, keep
+
+
+@pytest.mark.parametrize("name", ["batched_b48_l20.npz", "batched_b32_l8.npz"])
+@pytest.mark.parametrize("joseph", [False, True])
+def test_batched_vs_reference_golden(eb, name, joseph):
+    z = golden(name)
+    out, keep = _run_batched(eb, z, joseph)
+    worst = 0.0
+    for t, (mu, p) in out.items():
+        for b in range(mu.shape[0]):
+            worst = max(worst, *assert_parity(mu[b], p[b], z["mean"][keep[t], b], z["cov"][keep[t], b],
+                                              what=f"{name} joseph={joseph} t={t} b={b}"))
+    print(f"{name} joseph={joseph}: worst parity {worst:.3e}")
+
+
+def test_batched_pack_unpack_roundtrip_and_pad(eb):
+    rng = np.random.default_rng(0)
+    f = eb.BatchedEKF(7, 20)
+    mean = rng.normal(size=(7, 43))
+    cov = rng.normal(size=(7, 43, 43))
+    f.load(mean, cov)
+    m2, c2 = f.state()
+    np.testing.assert_array_equal(m2, mean)
+    np.testing.assert_array_equal(c2, cov)
+    P = f.P.cpu().numpy().reshape(7, 43, 44)
+    assert np.all(P[:, :, 43] == 0) and np.all(f.mu.cpu().numpy()[:, 43] == 0)
+
+
+def test_batched_ticks_odometry_equals_displacement(eb):
+    """a1/a2 on the device (ticks) must give the same step as host delta_phi/displacement + step."""
+    import torch
+    z = golden("batched_b32_l8.npz")
+    B, L = 32, 8
+    rng = np.random.default_rng(3)
+    prev_l, prev_r = rng.integers(900, 1100, B).astype(np.int32), rng.integers(900, 1100, B).astype(np.int32)
+    cur_l, cur_r = prev_l + rng.integers(-3, 12, B).astype(np.int32), prev_r + rng.integers(-3, 12, B).astype(np.int32)
+    ang = np.zeros(B)
+    lin = np.zeros(B)
+    for b in range(B):
+        ang[b], lin[b] = eb.displacement(0.0318, 0.1, eb.delta_phi(int(cur_l[b]), int(prev_l[b]), 135),
+                                         eb.delta_phi(int(cur_r[b]), int(prev_r[b]), 135))
+        a_o, l_o = eo.displacement(0.0318, 0.1, eo.delta_phi(int(cur_l[b]), int(prev_l[b]), 135),
+                                   eo.delta_phi(int(cur_r[b]), int(prev_r[b]), 135))
+        assert (ang[b], lin[b]) == (a_o, l_o)            # integer ticks -> identical doubles
+    res = []
+    for mode in ("disp", "ticks"):
+        f = eb.BatchedEKF(B, L)
+        f.set_noise(z["motion_var"], z["meas_var"])
+        f.init(0.1)
+        sl, r, q = _dev(f.dev, z["slot"][0]), _dev(f.dev, z["rng"][0]), _dev(f.dev, z["brg"][0])
+        if mode == "disp":
+            f.step(_dev(f.dev, ang), _dev(f.dev, lin), sl, r, q)
+        else:
+            f.step_ticks(_dev(f.dev, cur_l), _dev(f.dev, cur_r), _dev(f.dev, prev_l), _dev(f.dev, prev_r),
+                         0.0318, 0.1, 135, sl, r, q)
+        torch.cuda.synchronize()
+        res.append(f.state())
+    np.testing.assert_array_equal(res[0][0], res[1][0])
+    np.testing.assert_array_equal(res[0][1], res[1][1])
+
+
+def test_batched_faults_and_skips(eb):
+    """slot -1 = no observation; a slot that skips first-seen order is refused and counted."""
+    f = eb.BatchedEKF(4, 8)
+    f.init(0.1)
+    z = np.zeros(4)
+    slot = np.array([[0, -1], [-1, -1], [2, 0], [0, 1]], dtype=np.int32)
+    r = np.full((4, 2), 1.0)
+    b = np.array([[0.1, 0.0], [0.0, 0.0], [0.2, -0.2], [0.3, -0.3]])
+    f.step(_dev(f.dev, z + 0.05), _dev(f.dev, z + 0.03), _dev(f.dev, slot), _dev(f.dev, r), _dev(f.dev, b))
+    assert f.fault_count() == 1
+    assert list(f.n_known.cpu().numpy()) == [1, 0, 1, 2]
+    mu, p = f.state()
+    for k, obs in enumerate([[(0, 1.0, 0.1)], [], [(0, 1.0, -0.2)], [(0, 1.0, 0.3), (1, 1.0, -0.3)]]):
+        m0 = np.zeros(19)
+        c0 = np.zeros((19, 19))
+        c0[:3, :3] = 0.1 * np.eye(3)
+        m_o, c_o, _ = eo.step_from_observations(m0, c0, 0.05, 0.03, obs, eo.Flags(), 0)
+        assert_parity(mu[k], p[k], m_o, c_o, what=f"filter {k}")
+
+
+@pytest.mark.parametrize("flags", [dict(circular=False), dict(disable_motion=True), dict(measurement=False)])
+def test_batched_flag_variants_vs_oracle(eb, flags):
+    z = golden("batched_b32_l8.npz")
+    T, B, m = z["slot"].shape
+    f = eb.BatchedEKF(B, 8)
+    f.set_noise(z["motion_var"], z["meas_var"])
+    f.set_flags(**flags)
+    f.init(0.1)
+    for t in range(6):
+        f.step(_dev(f.dev, z["ang"][t]), _dev(f.dev, z["lin"][t]), _dev(f.dev, z["slot"][t]),
+               _dev(f.dev, z["rng"][t]), _dev(f.dev, z["brg"][t]))
+    mu, p = f.state()
+    for b in range(0, B, 7):
+        fl = eo.Flags(motion_var=float(z["motion_var"][b]), meas_var=float(z["meas_var"][b]),
+                      circular=flags.get("circular", True), disable_motion=flags.get("disable_motion", False),
+                      enable_measurement=flags.get("measurement", True))
+        m_o = np.zeros(19)
+        c_o = np.zeros((19, 19))
+        c_o[:3, :3] = 0.1 * np.eye(3)
+        nk = 0
+        for t in range(6):
+            obs = [(int(s), float(r), float(q)) for s, r, q in zip(z["slot"][t, b], z["rng"][t, b], z["brg"][t, b]) if s >= 0]
+            m_o, c_o, nk = eo.step_from_observations(m_o, c_o, float(z["ang"][t, b]), float(z["lin"][t, b]), obs, fl, nk)
+        assert_parity(mu[b], p[b], m_o, c_o, what=f"{flags} b={b}")
+
+
+# ---------------------------------------------------------------------------------------------------------
+# large map
+# ---------------------------------------------------------------------------------------------------------
+def _run_large(eb, name, joseph=False):
+    from slam_duckietown_b200 import workloads as wl
+    z = golden(name)
+    L = int(z["n_landmarks"])
+    w = wl.make_large_map(L, updates=2 * len(z["sched"]))
+    g = eb.LargeMapEKF(L)
+    g.set_noise(0.1, 0.7)
+    g.set_flags(joseph=joseph)
+    g.load(w.mu0, w.p0())
+    for row in z["sched"]:
+        g.predict(float(row[0]), float(row[1]))
+        for i in range(int(row[2])):
+            g.update(int(row[3 + 3 * i]), float(row[4 + 3 * i]), float(row[5 + 3 * i]))
+    mu, p = g.state()
+    return z, mu, p
+
+
+@pytest.mark.parametrize("name", ["large_l256.npz", "large_l1024.npz", "large_l4096.npz"])
+@pytest.mark.parametrize("joseph", [False, True])
+def test_large_map_vs_reference_golden(eb, name, joseph):
+    z, mu, p = _run_large(eb, name, joseph)
+    rows = z["rows"]
+    d = np.sqrt(z["p_diag"])
+    e_mu = np.max(np.abs(mu - z["mean"])) / np.max(np.abs(z["mean"]))
+    e_rows = np.max(np.abs(p[rows] - z["p_rows"]) / (d[rows][:, None] * d[None, :]))
+    e_cols = np.max(np.abs(p[:, rows[:8]] - z["p_cols"]) / (d[:, None] * d[rows[:8]][None, :]))
+    e_diag = np.max(np.abs(np.diag(p) - z["p_diag"]) / z["p_diag"])
+    e_sum = abs(p.sum() - z["p_sum"][0]) / z["p_sum"][1]
+    print(f"{name} joseph={joseph}: mu {e_mu:.2e} rows {e_rows:.2e} cols {e_cols:.2e} diag {e_diag:.2e} sum {e_sum:.2e}")
+    assert max(e_mu, e_rows, e_cols, e_diag, e_sum) <= TOL
+
+
+def test_large_map_50_steps_vs_oracle_and_pad(eb):
+    from slam_duckietown_b200 import workloads as wl
+    w = wl.make_large_map(700, updates=50)          # n = 1403: column tail + row tail both non-trivial
+    g = eb.LargeMapEKF(700)
+    g.set_noise(0.2, 0.5)
+    g.load(w.mu0, w.p0())
+    m_o, c_o = w.mu0.copy(), w.p0()
+    fl = eo.Flags(motion_var=0.2, meas_var=0.5)
+    for op in w.ops:
+        if op[0] == "update":
+            g.update(op[1], op[2], op[3])
+            eo.update_rank(m_o, c_o, op[1], op[2], op[3], 0.5)
+        else:
+            g.predict(op[1], op[2])
+            dx, dy, th, g0, g1 = eo.motion_step(m_o[2], op[1], op[2], fl)
+            m_o[0] += dx; m_o[1] += dy; m_o[2] = th
+            eo.predict_cov_rank(c_o, g0, g1, 0.2)
+    mu, p = g.state()
+    assert_parity(mu, p, m_o, c_o, what="50 ops n=1403")
+    full = g.P.cpu().numpy()
+    assert np.all(full[:, g.n:] == 0.0), "pad columns must stay exactly zero"
+
+
+def test_large_map_augment_matches_growing_arrays(eb):
+    """capacity pre-allocation == the reference's zero-padded growth (:341-360)."""
+    g = eb.LargeMapEKF(16)
+    g.set_noise(0.1, 0.7)
+    g.load(np.array([0.1, 0.2, 0.3]), np.eye(3) * 0.1)
+    m_o = np.zeros(35)
+    m_o[:3] = [0.1, 0.2, 0.3]
+    c_o = np.zeros((35, 35))
+    c_o[:3, :3] = np.eye(3) * 0.1
+    nk = 0
+    rng = np.random.default_rng(2)
+    for t in range(8):
+        obs = [(s, float(rng.uniform(0.3, 1.4)), float(rng.uniform(-1, 1))) for s in ([2 * t, 2 * t + 1] if t < 8 else [])]
+        pose = m_o[:3].copy()
+        for s, r, b in obs:
+            g.augment(s, pose[0] + r * np.cos(b + pose[2]), pose[1] + r * np.sin(b + pose[2]))
+        g.predict(0.1, 0.04)
+        for s, r, b in obs:
+            g.update(s, r, b)
+        m_o, c_o, nk = eo.step_from_observations(m_o, c_o, 0.1, 0.04, obs, eo.Flags(), nk)
+    mu, p = g.state()
+    assert_parity(mu, p, m_o, c_o, what="augment")
+
+
+# ---------------------------------------------------------------------------------------------------------
+# reference call surface
+# ---------------------------------------------------------------------------------------------------------
+def test_scalar_surface_unit_cases(eb):
+    z = golden("unit_cases.npz")
+    names = ("ENABLE_CIRCULAR_INTERPOLATION", "DISABLE_MOTION_MODEL", "ENABLE_MEASUREMENT_MODEL", "IGNORE_TAGS",
+             "MOTION_MODEL_VARIANCE", "MEASUREMENT_MODEL_VARIANCE")
+    defaults = {k: getattr(eb, k) for k in names}
+    for i, name in enumerate(z["names"]):
+        p = f"c{i}_"
+        flags = {str(k): eval(str(v)) for k, v in zip(z[p + "flags_keys"], z[p + "flags_vals"])}
+        dets = [[], []]
+        for img, tag, pt, err in zip(z[p + "det_img"], z[p + "det_tag"], z[p + "det_pose_t"], z[p + "det_err"]):
+            dets[int(img)].append(eo.Detection(int(tag), pt.reshape(3, 1), float(err)))
+        ti = {int(a): int(b) for a, b in zip(z[p + "ti_in_ids"], z[p + "ti_in_slots"])}
+        mean_in, cov_in = z[p + "mean_in"].copy(), z[p + "cov_in"].copy()
+        try:
+            for k, v in flags.items():
+                setattr(eb, k, v)
+            m, c, tags = eb.EKF_pose_estimation(float(z[p + "ang"]), float(z[p + "lin"]), mean_in, cov_in, 0.7,
+                                                [("0", dets[0]), ("1", dets[1])], ti)
+        finally:
+            for k, v in defaults.items():
+                setattr(eb, k, v)
+        np.testing.assert_array_equal(mean_in, z[p + "mean_in"])       # inputs untouched, new arrays returned
+        assert list(ti.keys()) == list(z[p + "ti_out_ids"]) and list(ti.values()) == list(z[p + "ti_out_slots"])
+        assert list(tags.keys()) == list(z[p + "order"]), name
+        got = np.array([[float(x) for x in v] for v in tags.values()]).reshape(-1, 6)
+        np.testing.assert_array_equal(got[:, 3], z[p + "tags"][:, 3])           # tag ids
+        np.testing.assert_allclose(got, z[p + "tags"], rtol=1e-13, atol=1e-13)
+        assert m.shape == z[p + "mean_out"].shape
+        assert_parity(m, c, z[p + "mean_out"], z[p + "cov_out"], what=str(name))
+
+
+def test_scalar_surface_closed_loop(eb):
+    z = golden("closed_loop_n20.npz")
+    mean, cov, ti = np.zeros(3), np.eye(3) * 0.1, {}
+    keep = {int(t): i for i, t in enumerate(z["keep_t"])}
+    ds = z["det_step"]
+    worst = 0.0
+    for t in range(len(z["ang"])):
+        sel = np.flatnonzero(ds == t)
+        pairs = [(str(t), [eo.Detection(int(z["det_tag"][k]), z["det_pose_t"][k].reshape(3, 1), float(z["det_err"][k]))
+                           for k in sel if z["det_img"][k] == im]) for im in range(3)]
+        mean, cov, _ = eb.EKF_pose_estimation(float(z["ang"][t]), float(z["lin"][t]), mean, cov, 0.7, pairs, ti)
+        if t in keep:
+            i, n = keep[t], int(z["keep_n"][keep[t]])
+            assert len(mean) == n
+            worst = max(worst, *assert_parity(mean, cov, z["keep_mean"][i][:n], z["keep_cov"][i][:n, :n], what=f"step {t}"))
+    assert list(ti.keys()) == list(z["tag_ids"]) and list(ti.values()) == list(z["tag_slots"])
+    print(f"closed loop 300 steps: worst parity {worst:.3e}")
+
+
+def test_surrogate_bag_replay(eb, surrogate):
+    """Configuration 1: the decoded-bag event loop drives the CUDA core; every one of the 70 EKF steps must match
+    what the reference's own replay() produced on the same events."""
+    from slam_duckietown_b200 import replay
+    lines, dets, ref = surrogate
+    recs = replay.replay_events(lines, dets)
+    assert len(recs) == len(ref["n"]) == 70
+    worst = 0.0
+    for i, r in enumerate(recs):
+        n = int(ref["n"][i])
+        assert len(r["mean"]) == n
+        assert r["order"] == [int(x) for x in ref["order"][i] if x >= 0]
+        assert r["ang"] == ref["ang"][i] and r["lin"] == ref["lin"][i]
+        worst = max(worst, *assert_parity(r["mean"], r["cov"], ref["mean"][i][:n], ref["cov"][i][:n, :n], what=f"step {i}"))
+    assert list(recs[-1]["tag_index"].keys()) == list(ref["tag_ids"])
+    assert list(recs[-1]["tag_index"].values()) == list(ref["tag_slots"])
+    print(f"surrogate replay: worst parity {worst:.3e}")
+
+
+def test_ekf3_surface(eb):
+    import torch
+    z = golden("ekf3.npz")
+    K = len(z["v"])
+    dev = torch.device("cuda")
+    st = _dev(dev, z["state"].T.copy())
+    cv = _dev(dev, z["cov"].reshape(K, 9).T.copy())
+    eb.predict3_batched(st, cv, _dev(dev, z["v"]), _dev(dev, z["omega"]), _dev(dev, z["dt"]))
+    np.testing.assert_allclose(st.cpu().numpy().T, z["pred_state"], rtol=0, atol=1e-12)
+    np.testing.assert_allclose(cv.cpu().numpy().T.reshape(K, 3, 3), z["pred_cov"], rtol=1e-11, atol=1e-13)
+    eb.update3_batched(st, cv, _dev(dev, z["obs"][:, 0].copy()), _dev(dev, z["obs"][:, 1].copy()),
+                       _dev(dev, z["lm"][:, 0].copy()), _dev(dev, z["lm"][:, 1].copy()))
+    np.testing.assert_allclose(st.cpu().numpy().T, z["upd_state"], rtol=0, atol=1e-9)
+    np.testing.assert_allclose(cv.cpu().numpy().T.reshape(K, 3, 3), z["upd_cov"], rtol=1e-9, atol=1e-11)
+    s, c = eb.predict(z["state"][3], z["cov"][3], (z["v"][3], z["omega"][3]), z["dt"][3])
+    np.testing.assert_allclose(s, z["pred_state"][3], atol=1e-12)
+    s, c = eb.update(s, c, z["obs"][3], z["lm"][3])
+    np.testing.assert_allclose(c, z["upd_cov"][3], rtol=1e-9, atol=1e-11)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# full-size properties (BASELINE.json sizes; no oracle at this scale)
+# ---------------------------------------------------------------------------------------------------------
+def test_batched_full_size_properties(eb):
+    """65,536 x 20 landmarks: filters fed identical inputs must end bitwise identical wherever they sit in the
+    batch; the first 48 filters must still match the reference golden; P stays symmetric to rounding and
+    its diagonal positive; an update never increases a variance."""
+    import torch
+    z = golden("batched_b48_l20.npz")
+    T, B0, m = z["slot"].shape
+    B = 65536
+    reps = B // B0 + 1
+
+    def tile(a):
+        return np.concatenate([a] * reps, axis=0)[:B].copy()
+    f = eb.BatchedEKF(B, 20)
+    f.set_noise(tile(z["motion_var"]), tile(z["meas_var"]))
+    f.init(0.1)
+    for t in range(T):
+        f.step(_dev(f.dev, tile(z["ang"][t])), _dev(f.dev, tile(z["lin"][t])), _dev(f.dev, tile(z["slot"][t])),
+               _dev(f.dev, tile(z["rng"][t])), _dev(f.dev, tile(z["brg"][t])))
+    assert f.fault_count() == 0
+    P = f.P.view(B, 43, 44)
+    mu = f.mu
+    last = (B // B0 - 1) * B0
+    assert torch.equal(P[:B0], P[last:last + B0]) and torch.equal(mu[:B0], mu[last:last + B0])
+    assert torch.equal(P[:B0], P[B0 * 700:B0 * 701])
+    mu0, p0 = f.state(0, B0)
+    i = len(z["keep_t"]) - 1
+    for b in range(B0):
+        assert_parity(mu0[b], p0[b], z["mean"][i, b], z["cov"][i, b], what=f"full-size b={b}")
+    Pm = P[:, :, :43]
+    d = torch.diagonal(Pm, dim1=1, dim2=2)
+    assert bool((d > 0).all())
+    asym = (Pm - Pm.transpose(1, 2)).abs().amax(dim=(1, 2)) / d.amax(dim=1)
+    assert float(asym.max()) < 1e-9
+    assert bool((P[:, :, 43] == 0).all())
+
+
+def test_large_map_full_size_properties(eb):
+    """4096 landmarks (n = 8195): update properties that hold at any size — the updated landmark's variance
+    drops, trace(P) does not increase, P stays symmetric to rounding, a second filter fed the same ops is
+    bitwise identical, and plain vs Joseph agree to 1e-9 covariance-scaled."""
+    import torch
+    from slam_duckietown_b200 import workloads as wl
+    w = wl.make_large_map(4096, updates=6)
+    outs = []
+    for joseph in (False, True, False):
+        g = eb.LargeMapEKF(4096)
+        g.set_noise(0.1, 0.7)
+        g.set_flags(joseph=joseph)
+        g.load(w.mu0, w.p0())
+        tr0 = float(torch.diagonal(g.P[:, :g.n]).sum())
+        for op in w.ops:
+            if op[0] == "update":
+                j = 3 + 2 * op[1]
+                before = float(g.P[j, j])
+                g.update(op[1], op[2], op[3])
+                assert float(g.P[j, j]) < before
+            else:
+                g.predict(op[1], op[2])
+        Pm = g.P[:, :g.n]
+        assert float(torch.diagonal(Pm).sum()) < tr0 + 3 * 0.1 ** 2 * 2
+        d = torch.sqrt(torch.diagonal(Pm))
+        asym = ((Pm - Pm.T).abs() / (d[:, None] * d[None, :])).max()
+        assert float(asym) < 1e-9
+        assert bool((g.P[:, g.n:] == 0).all())
+        outs.append((g.mu.clone(), Pm.clone()))
+        g.close()
+    assert torch.equal(outs[0][1], outs[2][1]) and torch.equal(outs[0][0], outs[2][0])
+    d = torch.sqrt(torch.diagonal(outs[0][1]))
+    rel = ((outs[0][1] - outs[1][1]).abs() / (d[:, None] * d[None, :])).max()
+    assert float(rel) < 1e-9
