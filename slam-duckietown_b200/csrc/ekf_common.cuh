@@ -27,9 +27,17 @@ __host__ __device__ __forceinline__ double delta_phi(long long ticks, long long 
 }
 __host__ __device__ __forceinline__ void displacement(double R, double baseline, double dl, double dr,
                                                       double* ang, double* lin) {
+#ifdef __CUDA_ARCH__
+  // no FMA contraction: numpy rounds R*dphi before the add, and tick-derived odometry must be bit-identical
+  // to the host path (tests: ticks entry point == delta_phi/displacement on the host + plain step)
+  const double wr = __dmul_rn(R, dr), wl = __dmul_rn(R, dl);
+  *lin = __dadd_rn(wl, wr) / 2.0;
+  *ang = __dsub_rn(wr, wl) / baseline;
+#else
   const double wr = R * dr, wl = R * dl;
   *lin = (wl + wr) / 2.0;
   *ang = (wr - wl) / baseline;
+#endif
 }
 
 // a6 (replay_no_ros.py:368-417): pose increment, new heading and Jacobian column g0 = G[0,2], g1 = G[1,2]
