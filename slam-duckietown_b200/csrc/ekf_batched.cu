@@ -1,4 +1,4 @@
-// ekf_batched.cu — fused EKF-SLAM filter-step for B independent filters, one CTA per filter (sm_100a, fp64).
+// ekf_batched.cu — fused EKF-SLAM filter-step for B independent filters, ONE WARP per filter (sm_100a, fp64).
 //
 // Reference semantics: one EKF_pose_estimation call (src/replay_no_ros.py:341-480) on an already associated
 // window: augment new slots from the PRE-predict pose (:355-360), odometry predict (:368-430), then the
@@ -11,15 +11,19 @@
 // bulk copy (cp.async.bulk + mbarrier) and leaves through coalesced 256-bit stores. Algorithmic traffic per
 // filter-step: one read + one write of mu and P regardless of the number of updates.
 //
+// Why a warp per filter (round-1 ncu, profiles/): the step is a chain of short dependent phases (motion
+// model -> [innovation -> S^-1 -> K -> mu] x m). With a CTA per filter 46 % of all stall samples were CTA
+// barriers around single-thread sections; a warp needs only __syncwarp, and the ~11 resident warps of an SM
+// (20 KB of shared memory each) are independent filters whose chains overlap.
+//
 // Algorithm (bitwise equal to applying the updates one after the other):
-//   phase 0  TMA bulk load of P, mu; per-filter inputs into registers/shared memory
-//   phase 1  augment + motion model (thread 0), predict of the robot rows/columns of P in shared memory
+//   phase 0  TMA bulk load of P, mu; per-filter inputs into registers
+//   phase 1  augment + motion model (computed warp-uniformly), predict of the robot rows/columns of P in smem
 //   phase 2  for each update u: the 5 rows / 5 columns it touches are rebuilt from the staged P0 and the
 //            earlier (K_v, W_v), giving H5, S^-1, K_u (from columns), W_u = H5 P[idx5,:] (from rows),
 //            mu += K_u y_u. O(n) work per update, P0 is not modified.
-//   phase 3  one pass over P: P[i,c] = P0[i,c] - sum_u K_u[i,:] W_u[:,c] (plain; rank-4 per update for
-//            Joseph), each thread owning a fixed group of 4 columns (W in registers) and PASSES rows,
-//            streamed to HBM with 256-bit stores.
+//   phase 3  one pass over P in 4x4 register blocks: P[i,c] = P0[i,c] - sum_u K_u[i,:] W_u[:,c] (plain; rank-4
+//            per update for Joseph), streamed to HBM with 256-bit stores.
 // Rows and columns are both gathered for real — (P H^T)^T is never used for H P.
 #include "ekf_batched.h"
 #include "ekf_common.cuh"
@@ -61,341 +65,264 @@ __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_
 __device__ __forceinline__ double rank2(double v, double k0, double k1, double w0, double w1) {
   return fma(-k1, w1, fma(-k0, w0, v));
 }
+__device__ __forceinline__ void rank2x4(double4x& p, double k0, double k1, const double4x& w0,
+                                        const double4x& w1) {
+  p.a = rank2(p.a, k0, k1, w0.a, w1.a);
+  p.b = rank2(p.b, k0, k1, w0.b, w1.b);
+  p.c = rank2(p.c, k0, k1, w0.c, w1.c);
+  p.d = rank2(p.d, k0, k1, w0.d, w1.d);
+}
 
-constexpr int kScalDoubles = 96;
+constexpr int kTailDoubles = 32;  // sV[25] + mbarrier
+constexpr unsigned kFull = 0xffffffffu;
 
-struct __align__(16) d2 {
-  double x, y;
-};
+__device__ __forceinline__ double4x lds256(const double* p) { return *reinterpret_cast<const double4x*>(p); }
 
-template <int NLM, int THREADS, bool JOSEPH>
-__global__ void __launch_bounds__(THREADS) batch_step_kernel(BatchStepArgs a) {
+template <int NLM, bool JOSEPH>
+__global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
-  constexpr int G = LD / 4;
-  constexpr int R = THREADS / G;
-  constexpr int PASSES = (N + R - 1) / R;
-  constexpr int HALF = THREADS / 2;
-  static_assert(N <= HALF, "row and column workers are the two halves of the CTA");
-  static_assert(R >= 1, "CTA narrower than one row of column groups");
+  constexpr int G = LD / 4;          // column groups of 4 doubles
+  constexpr int NRB = (N + 3) / 4;   // row blocks of 4 rows
+  constexpr int HIST = 2 * LD;       // doubles of one update's K (or W, or A) record: [2][LD]
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   double* sP = reinterpret_cast<double*>(smem_raw);  // [N][LD]
   double* sMu = sP + N * LD;                         // [LD]
-  double* sScal = sMu + LD;                          // kScalDoubles doubles of scalars
-  double* sK = sScal + kScalDoubles;                          // [m][LD][2]
+  double* sK = sMu + LD;                             // [m][2][LD]  K_u[:,0] then K_u[:,1]
   const int m = a.m;
-  double* sW = sK + m * LD * 2;                      // [m][2][LD]
-  double* sA = sW + m * 2 * LD;                      // [m][LD][2] (Joseph only)
-  double* sH = sScal;                                // [2][5]
-  double* sSi = sScal + 10;                          // [2][2]
-  double* sSq = sScal + 14;                          // [2][2] S - Q
-  double* sY = sScal + 18;                           // [2]
-  double* sG = sScal + 20;                           // g0, g1
-  double* sV = sScal + 24;                           // [5][5] rebuilt P[idx5, idx5]
-  double* sRng = sScal + 56;                         // [BATCH_MAX_M]
-  double* sBrg = sScal + 64;                         // [BATCH_MAX_M]
-  int* sSlot = reinterpret_cast<int*>(sScal + 72);   // [BATCH_MAX_M]
-  uint64_t* bar = reinterpret_cast<uint64_t*>(sScal + 76);
+  double* sW = sK + m * HIST;                        // [m][2][LD]  W_u[0,:] then W_u[1,:]
+  double* sA = sW + m * HIST;                        // [m][2][LD]  (Joseph only)
+  double* sV = (JOSEPH ? sA + m * HIST : sA);        // [25] rebuilt P[idx5, idx5]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sV + 26);
 
-  const int tid = threadIdx.x;
+  const int lane = threadIdx.x;
   const int64_t b = blockIdx.x;
   double* __restrict__ gP = a.P + b * (int64_t)(N * LD);
   double* __restrict__ gMu = a.mu + b * (int64_t)LD;
 
   // ---- phase 0: TMA bulk load + per-filter inputs --------------------------------------------------
-  if (tid == 0) {
+  if (lane == 0) {
     mbar_init(bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     mbar_expect_tx(bar, (uint32_t)((N * LD + LD) * sizeof(double)));
     tma_bulk_g2s(sP, gP, (uint32_t)(N * LD * sizeof(double)), bar);
     tma_bulk_g2s(sMu, gMu, (uint32_t)(LD * sizeof(double)), bar);
   }
-  double ang = 0.0, lin = 0.0, mv = 0.0;
-  int nk = 0;
-  if (tid == 0) {
-    if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
-      const double dl = delta_phi(a.ticks_l[b], a.prev_l[b], a.resolution);
-      const double dr = delta_phi(a.ticks_r[b], a.prev_r[b], a.resolution);
-      displacement(a.wheel_radius, a.baseline, dl, dr, &ang, &lin);
-    } else {
-      ang = a.ang[b];
-      lin = a.lin[b];
-    }
-    mv = a.motion_var[b];
-    nk = a.n_known[b];
+  double ang, lin;
+  if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
+    const double dl = delta_phi(a.ticks_l[b], a.prev_l[b], a.resolution);
+    const double dr = delta_phi(a.ticks_r[b], a.prev_r[b], a.resolution);
+    displacement(a.wheel_radius, a.baseline, dl, dr, &ang, &lin);
+  } else {
+    ang = a.ang[b];
+    lin = a.lin[b];
   }
+  const double mv = a.motion_var[b];
   const double mm = a.meas_var[b];
+  const double qn = mm * mm;
+  int nk = a.n_known[b];
+  // observation u lives in lane u and is broadcast with a shuffle when its turn comes
   double o_rng = 0.0, o_brg = 0.0;
   int o_slot = -1;
-  if (tid < m) {
-    o_slot = a.slot[b * m + tid];
-    o_rng = a.rng[b * m + tid];
-    o_brg = a.brg[b * m + tid];
-    sSlot[tid] = o_slot;
-    sRng[tid] = o_rng;
-    sBrg[tid] = o_brg;
+  if (lane < m) {
+    o_slot = a.slot[b * m + lane];
+    o_rng = a.rng[b * m + lane];
+    o_brg = a.brg[b * m + lane];
   }
-  // zero the pads of K / W / A so pad columns of P stay exactly zero
-  for (int e = tid; e < m * LD * 2; e += THREADS) {
-    sK[e] = 0.0;
-    sW[e] = 0.0;
-    if (JOSEPH) sA[e] = 0.0;
-  }
-  __syncthreads();  // barrier init + staged observations visible
+  __syncwarp();
   mbar_wait(bar, 0);
 
-  // ---- phase 1: augment (:355-360) + motion model (:368-417), thread 0 ------------------------------
-  if (tid == 0) {
+  // ---- phase 1: augment (:355-360) + motion model (:368-417), warp-uniform ---------------------------
+  unsigned valid = 0;  // bit u: update u is applied
+  {
     const double px = sMu[0], py = sMu[1], pth = sMu[2];
+    __syncwarp();
     int fault = 0;
     for (int u = 0; u < m; ++u) {
-      const int s = sSlot[u];
+      const int s = __shfl_sync(kFull, o_slot, u);
       if (s < 0) continue;
       if (s >= NLM || s > nk) {  // beyond capacity, or a slot that skips first-seen order (:359 KeyError)
-        sSlot[u] = -1;
         fault = 1;
         continue;
       }
+      valid |= 1u << u;
       if (s == nk) {
         const int j = 3 + 2 * s;
-        const double r = sRng[u], be = sBrg[u];
+        const double r = __shfl_sync(kFull, o_rng, u), be = __shfl_sync(kFull, o_brg, u);
         double sn, cs;
         sincos(be + pth, &sn, &cs);
-        sMu[j] = px + r * cs;
-        sMu[j + 1] = py + r * sn;
-        sP[j * LD + j] = kNewLandmarkVar;
-        sP[(j + 1) * LD + j + 1] = kNewLandmarkVar;
+        if (lane == 0) {
+          sMu[j] = px + r * cs;
+          sMu[j + 1] = py + r * sn;
+          sP[j * LD + j] = kNewLandmarkVar;
+          sP[(j + 1) * LD + j + 1] = kNewLandmarkVar;
+        }
         ++nk;
       }
     }
-    if (!(a.flags & kFlagMeasurement))
-      for (int u = 0; u < m; ++u) sSlot[u] = -1;
+    if (!(a.flags & kFlagMeasurement)) valid = 0;
     const Motion mo = motion_step(pth, ang, lin, a.flags);
-    sMu[0] = px + mo.dx;
-    sMu[1] = py + mo.dy;
-    sMu[2] = mo.theta;
-    sG[0] = mo.g0;
-    sG[1] = mo.g1;
-    sG[2] = mv;
-    a.n_known[b] = nk;
-    if (fault) atomicAdd(a.faults, 1ULL);
-  }
-  __syncthreads();
-
-  // ---- predict covariance in shared memory (:420-430) -----------------------------------------------
-  {
-    const double g0 = sG[0], g1 = sG[1];
-    if (tid >= 3 && tid < N) {  // column tid of rows 0-1
-      const double p2 = sP[2 * LD + tid];
-      sP[0 * LD + tid] += g0 * p2;
-      sP[1 * LD + tid] += g1 * p2;
-    } else if (tid >= HALF + 3 && tid < HALF + N) {  // row i of columns 0-1
-      double* row = sP + (tid - HALF) * LD;
+    if (lane == 0) {
+      sMu[0] = px + mo.dx;
+      sMu[1] = py + mo.dy;
+      sMu[2] = mo.theta;
+      a.n_known[b] = nk;
+      if (fault) atomicAdd(a.faults, 1ULL);
+    }
+    __syncwarp();
+    // predict covariance in shared memory (:420-430): rows 0-1 += g * row 2 over ALL columns, then columns
+    // 0-1 += g * column 2 over ALL rows (using the updated rows 0-1), then the three noise terms.
+    const double g0 = mo.g0, g1 = mo.g1;
+    for (int t = lane; t < N; t += 32) {
+      const double p2 = sP[2 * LD + t];
+      sP[0 * LD + t] += g0 * p2;
+      sP[1 * LD + t] += g1 * p2;
+    }
+    __syncwarp();
+    for (int i = lane; i < N; i += 32) {
+      double* row = sP + i * LD;
       const double p2 = row[2];
       row[0] += g0 * p2;
       row[1] += g1 * p2;
-    } else if (tid == 0) {
-      const double mvv = sG[2];
-      double blk[3][3];
-#pragma unroll
-      for (int i = 0; i < 3; ++i)
-#pragma unroll
-        for (int c = 0; c < 3; ++c) blk[i][c] = sP[i * LD + c];
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        blk[0][c] += g0 * blk[2][c];
-        blk[1][c] += g1 * blk[2][c];
-      }
-#pragma unroll
-      for (int i = 0; i < 3; ++i) {
-        blk[i][0] += g0 * blk[i][2];
-        blk[i][1] += g1 * blk[i][2];
-      }
-      blk[0][0] += mvv * mvv;
-      blk[1][1] += mvv * mvv;
-      blk[2][2] += (mvv / 2.0) * (mvv / 2.0);
-#pragma unroll
-      for (int i = 0; i < 3; ++i)
-#pragma unroll
-        for (int c = 0; c < 3; ++c) sP[i * LD + c] = blk[i][c];
     }
+    __syncwarp();
+    if (lane == 0) {
+      sP[0] += mv * mv;
+      sP[LD + 1] += mv * mv;
+      sP[2 * LD + 2] += (mv / 2.0) * (mv / 2.0);
+    }
+    __syncwarp();
   }
-  __syncthreads();
 
   // ---- phase 2: sequential updates on the touched rows / columns only --------------------------------
   for (int u = 0; u < m; ++u) {
-    const int s = sSlot[u];
-    if (s < 0) continue;  // uniform across the CTA; K_u = W_u = 0 so phase 3 is a no-op for this u
+    if (!((valid >> u) & 1u)) continue;  // warp-uniform
+    const int s = __shfl_sync(kFull, o_slot, u);
+    const double z_rng = __shfl_sync(kFull, o_rng, u), z_brg = __shfl_sync(kFull, o_brg, u);
     const int j = 3 + 2 * s;
-    // (a) rebuilt 5x5 block, innovation, S, S^-1 — warp 0
-    if (tid < 25) {
-      const int k = tid / 5, c = tid - 5 * k;
+    // (a) rebuilt 5x5 block P_u[idx5, idx5], one entry per lane
+    if (lane < 25) {
+      const int k = lane / 5, c = lane - 5 * k;
       const int rk = (k < 3) ? k : j + (k - 3);
       const int cc = (c < 3) ? c : j + (c - 3);
       double v = sP[rk * LD + cc];
       for (int w = 0; w < u; ++w) {
-        const double* kw = sK + (w * LD + rk) * 2;
-        const double* ww = sW + w * 2 * LD;
-        v = rank2(v, kw[0], kw[1], ww[cc], ww[LD + cc]);
+        if (!((valid >> w) & 1u)) continue;
+        const double* kw = sK + w * HIST;
+        const double* ww = sW + w * HIST;
+        v = rank2(v, kw[rk], kw[LD + rk], ww[cc], ww[LD + cc]);
         if (JOSEPH) {
-          const double* aw = sA + (w * LD + rk) * 2;
-          const double* kc = sK + (w * LD + cc) * 2;
-          v = rank2(v, aw[0], aw[1], kc[0], kc[1]);
+          const double* aw = sA + w * HIST;
+          v = rank2(v, aw[rk], aw[LD + rk], kw[cc], kw[LD + cc]);
         }
       }
-      sV[tid] = v;
+      sV[lane] = v;
     }
-    if (tid < 32) {
-      __syncwarp();
-      if (tid == 0) {
-        const Innov in = innovation(sMu[0], sMu[1], sMu[2], sMu[j], sMu[j + 1], sRng[u], sBrg[u]);
-        double hp5[2][5];
+    // (b) innovation and H5 (:443-469), warp-uniform
+    const Innov in = innovation(sMu[0], sMu[1], sMu[2], sMu[j], sMu[j + 1], z_rng, z_brg);
+    __syncwarp();
+    // (c) S = H5 V H5^T + Q and its inverse (:473), warp-uniform from the staged block
+    double hp5[2][5];
 #pragma unroll
-        for (int c = 0; c < 5; ++c) {
-          double s0 = 0.0, s1 = 0.0;
+    for (int c = 0; c < 5; ++c) {
+      double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-          for (int k = 0; k < 5; ++k) {
-            s0 = fma(in.h[0][k], sV[k * 5 + c], s0);
-            s1 = fma(in.h[1][k], sV[k * 5 + c], s1);
-          }
-          hp5[0][c] = s0;
-          hp5[1][c] = s1;
-        }
-        double S[2][2], Si[2][2];
-#pragma unroll
-        for (int r = 0; r < 2; ++r)
-#pragma unroll
-          for (int q = 0; q < 2; ++q) {
-            double acc = 0.0;
-#pragma unroll
-            for (int c = 0; c < 5; ++c) acc = fma(hp5[r][c], in.h[q][c], acc);
-            S[r][q] = acc;
-          }
-        sSq[0] = S[0][0]; sSq[1] = S[0][1]; sSq[2] = S[1][0]; sSq[3] = S[1][1];
-        S[0][0] += mm * mm;
-        S[1][1] += mm * mm;
-        inv2(S, Si);
-        sSi[0] = Si[0][0]; sSi[1] = Si[0][1]; sSi[2] = Si[1][0]; sSi[3] = Si[1][1];
-#pragma unroll
-        for (int k = 0; k < 5; ++k) {
-          sH[k] = in.h[0][k];
-          sH[5 + k] = in.h[1][k];
-        }
-        sY[0] = in.y0;
-        sY[1] = in.y1;
+      for (int k = 0; k < 5; ++k) {
+        const double v = sV[k * 5 + c];
+        s0 = fma(in.h[0][k], v, s0);
+        s1 = fma(in.h[1][k], v, s1);
       }
+      hp5[0][c] = s0;
+      hp5[1][c] = s1;
     }
-    __syncthreads();
-    // (b) first half of the CTA: W_u[:, t] from the 5 ROWS; second half: K_u[i, :] from the 5 COLUMNS
-    if (tid < N) {
-      const int t = tid;
-      double hp0 = 0.0, hp1 = 0.0;
+    double S[2][2], Si[2][2], Sq[2][2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        double acc = 0.0;
+#pragma unroll
+        for (int c = 0; c < 5; ++c) acc = fma(hp5[r][c], in.h[q][c], acc);
+        S[r][q] = acc;
+        Sq[r][q] = acc;
+      }
+    S[0][0] += qn;
+    S[1][1] += qn;
+    inv2(S, Si);
+    // (d) lane t: W_u[:, t] from the 5 ROWS and K_u[t, :] from the 5 COLUMNS (t = lane, lane + 32)
+    for (int t = lane; t < LD; t += 32) {
+      double hp0 = 0.0, hp1 = 0.0, pht0 = 0.0, pht1 = 0.0;
+      const bool real = (t < N);
 #pragma unroll
       for (int k = 0; k < 5; ++k) {
         const int rk = (k < 3) ? k : j + (k - 3);
-        double v = sP[rk * LD + t];
+        double vr = sP[rk * LD + t];                  // row rk, column t
+        double vc = real ? sP[t * LD + rk] : 0.0;     // row t, column rk
         for (int w = 0; w < u; ++w) {
-          const double* kw = sK + (w * LD + rk) * 2;
-          const double* ww = sW + w * 2 * LD;
-          v = rank2(v, kw[0], kw[1], ww[t], ww[LD + t]);
+          if (!((valid >> w) & 1u)) continue;
+          const double* kw = sK + w * HIST;
+          const double* ww = sW + w * HIST;
+          vr = rank2(vr, kw[rk], kw[LD + rk], ww[t], ww[LD + t]);
+          vc = rank2(vc, kw[t], kw[LD + t], ww[rk], ww[LD + rk]);
           if (JOSEPH) {
-            const double* aw = sA + (w * LD + rk) * 2;
-            const double* kc = sK + (w * LD + t) * 2;
-            v = rank2(v, aw[0], aw[1], kc[0], kc[1]);
+            const double* aw = sA + w * HIST;
+            vr = rank2(vr, aw[rk], aw[LD + rk], kw[t], kw[LD + t]);
+            vc = rank2(vc, aw[t], aw[LD + t], kw[rk], kw[LD + rk]);
           }
         }
-        hp0 = fma(sH[k], v, hp0);
-        hp1 = fma(sH[5 + k], v, hp1);
+        hp0 = fma(in.h[0][k], vr, hp0);
+        hp1 = fma(in.h[1][k], vr, hp1);
+        pht0 = fma(vc, in.h[0][k], pht0);
+        pht1 = fma(vc, in.h[1][k], pht1);
       }
-      sW[u * 2 * LD + t] = hp0;
-      sW[u * 2 * LD + LD + t] = hp1;
-    } else if (tid >= HALF && tid < HALF + N) {
-      const int i = tid - HALF;
-      double pht0 = 0.0, pht1 = 0.0;
-#pragma unroll
-      for (int k = 0; k < 5; ++k) {
-        const int ck = (k < 3) ? k : j + (k - 3);
-        double v = sP[i * LD + ck];
-        for (int w = 0; w < u; ++w) {
-          const double* kw = sK + (w * LD + i) * 2;
-          const double* ww = sW + w * 2 * LD;
-          v = rank2(v, kw[0], kw[1], ww[ck], ww[LD + ck]);
-          if (JOSEPH) {
-            const double* aw = sA + (w * LD + i) * 2;
-            const double* kc = sK + (w * LD + ck) * 2;
-            v = rank2(v, aw[0], aw[1], kc[0], kc[1]);
-          }
-        }
-        pht0 = fma(v, sH[k], pht0);
-        pht1 = fma(v, sH[5 + k], pht1);
+      const double k0 = pht0 * Si[0][0] + pht1 * Si[1][0];
+      const double k1 = pht0 * Si[0][1] + pht1 * Si[1][1];
+      sK[u * HIST + t] = k0;          // zero for the pad row (vc = 0)
+      sK[u * HIST + LD + t] = k1;
+      if (JOSEPH) {  // W = H P - Q K^T, AHt = P H^T - K (S - Q)   (App. A.4)
+        sW[u * HIST + t] = hp0 - qn * k0;
+        sW[u * HIST + LD + t] = hp1 - qn * k1;
+        sA[u * HIST + t] = pht0 - (k0 * Sq[0][0] + k1 * Sq[1][0]);
+        sA[u * HIST + LD + t] = pht1 - (k0 * Sq[0][1] + k1 * Sq[1][1]);
+      } else {
+        sW[u * HIST + t] = hp0;       // zero for the pad column (P pad columns are zero)
+        sW[u * HIST + LD + t] = hp1;
       }
-      const double k0 = pht0 * sSi[0] + pht1 * sSi[2];
-      const double k1 = pht0 * sSi[1] + pht1 * sSi[3];
-      sK[(u * LD + i) * 2 + 0] = k0;
-      sK[(u * LD + i) * 2 + 1] = k1;
-      if (JOSEPH) {
-        sA[(u * LD + i) * 2 + 0] = pht0 - (k0 * sSq[0] + k1 * sSq[2]);
-        sA[(u * LD + i) * 2 + 1] = pht1 - (k0 * sSq[1] + k1 * sSq[3]);
-      }
-      sMu[i] += k0 * sY[0] + k1 * sY[1];  // a10 (:476)
+      if (real) sMu[t] += k0 * in.y0 + k1 * in.y1;  // a10 (:476)
     }
-    __syncthreads();
-    if (JOSEPH) {  // W = H P - Q K^T (App. A.4)
-      if (tid < N) {
-        const double qn = mm * mm;
-        sW[u * 2 * LD + tid] -= qn * sK[(u * LD + tid) * 2 + 0];
-        sW[u * 2 * LD + LD + tid] -= qn * sK[(u * LD + tid) * 2 + 1];
-      }
-      __syncthreads();
-    }
+    __syncwarp();
   }
 
-  // ---- phase 3: one pass over P, all updates applied in order, streamed to HBM -----------------------
-  if (tid < G * R) {
-    const int g = tid % G, rs = tid / G;
-    const int c = 4 * g;
-    double4x p[PASSES];
+  // ---- phase 3: one pass over P in 4x4 blocks, all updates applied in order, streamed to HBM ---------
+  for (int blk = lane; blk < NRB * G; blk += 32) {
+    const int rb = blk / G, g = blk - rb * G;
+    const int i0 = 4 * rb, c = 4 * g;
+    double4x p[4];
 #pragma unroll
-    for (int q = 0; q < PASSES; ++q) {
-      const int i = rs + q * R;
-      if (i < N) p[q] = *reinterpret_cast<const double4x*>(sP + i * LD + c);
-    }
+    for (int r = 0; r < 4; ++r) p[r] = lds256(sP + (i0 + r) * LD + c);  // a row >= N reads mu: never stored
     for (int u = 0; u < m; ++u) {
-      if (sSlot[u] < 0) continue;
-      const double4x w0 = *reinterpret_cast<const double4x*>(sW + u * 2 * LD + c);
-      const double4x w1 = *reinterpret_cast<const double4x*>(sW + u * 2 * LD + LD + c);
-      d2 kc[4];
+      if (!((valid >> u) & 1u)) continue;
+      const double4x w0 = lds256(sW + u * HIST + c), w1 = lds256(sW + u * HIST + LD + c);
+      const double4x k0 = lds256(sK + u * HIST + i0), k1 = lds256(sK + u * HIST + LD + i0);
+      rank2x4(p[0], k0.a, k1.a, w0, w1);
+      rank2x4(p[1], k0.b, k1.b, w0, w1);
+      rank2x4(p[2], k0.c, k1.c, w0, w1);
+      rank2x4(p[3], k0.d, k1.d, w0, w1);
       if (JOSEPH) {
-#pragma unroll
-        for (int e = 0; e < 4; ++e) kc[e] = *reinterpret_cast<const d2*>(sK + (u * LD + c + e) * 2);
-      }
-#pragma unroll
-      for (int q = 0; q < PASSES; ++q) {
-        const int i = rs + q * R;
-        if (i < N) {
-          const d2 k = *reinterpret_cast<const d2*>(sK + (u * LD + i) * 2);
-          p[q].a = rank2(p[q].a, k.x, k.y, w0.a, w1.a);
-          p[q].b = rank2(p[q].b, k.x, k.y, w0.b, w1.b);
-          p[q].c = rank2(p[q].c, k.x, k.y, w0.c, w1.c);
-          p[q].d = rank2(p[q].d, k.x, k.y, w0.d, w1.d);
-          if (JOSEPH) {
-            const d2 av = *reinterpret_cast<const d2*>(sA + (u * LD + i) * 2);
-            p[q].a = rank2(p[q].a, av.x, av.y, kc[0].x, kc[0].y);
-            p[q].b = rank2(p[q].b, av.x, av.y, kc[1].x, kc[1].y);
-            p[q].c = rank2(p[q].c, av.x, av.y, kc[2].x, kc[2].y);
-            p[q].d = rank2(p[q].d, av.x, av.y, kc[3].x, kc[3].y);
-          }
-        }
+        const double4x a0 = lds256(sA + u * HIST + i0), a1 = lds256(sA + u * HIST + LD + i0);
+        const double4x kc0 = lds256(sK + u * HIST + c), kc1 = lds256(sK + u * HIST + LD + c);
+        rank2x4(p[0], a0.a, a1.a, kc0, kc1);
+        rank2x4(p[1], a0.b, a1.b, kc0, kc1);
+        rank2x4(p[2], a0.c, a1.c, kc0, kc1);
+        rank2x4(p[3], a0.d, a1.d, kc0, kc1);
       }
     }
 #pragma unroll
-    for (int q = 0; q < PASSES; ++q) {
-      const int i = rs + q * R;
-      if (i < N) stg256(gP + i * LD + c, p[q]);
-    }
+    for (int r = 0; r < 4; ++r)
+      if (i0 + r < N) stg256(gP + (i0 + r) * LD + c, p[r]);
   }
-  if (tid < LD) gMu[tid] = sMu[tid];
+  for (int t = lane; t < LD; t += 32) gMu[t] = sMu[t];
 }
 
 // -------------------------------------------------------------------------------------------------------
@@ -452,25 +379,21 @@ __global__ void batch_pose_kernel(const double* __restrict__ mu, double* __restr
 // -------------------------------------------------------------------------------------------------------
 size_t batch_step_smem_bytes(int n_landmarks, int m, bool joseph) {
   const int n = 3 + 2 * n_landmarks, ld = (n + 3) & ~3;
-  size_t d = (size_t)n * ld + ld + kScalDoubles + (size_t)m * ld * 2 * (joseph ? 3 : 2);
+  size_t d = (size_t)n * ld + ld + (size_t)m * 2 * ld * (joseph ? 3 : 2) + kTailDoubles;
   return d * sizeof(double);
 }
 
-template <int NLM, int THREADS>
-static cudaError_t launch_step_t(const BatchStepArgs& a, int64_t batch, bool joseph, cudaStream_t st) {
-  const size_t smem = batch_step_smem_bytes(NLM, a.m, joseph);
-  cudaError_t e;
-  if (joseph) {
-    e = cudaFuncSetAttribute(batch_step_kernel<NLM, THREADS, true>,
-                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    batch_step_kernel<NLM, THREADS, true><<<(unsigned)batch, THREADS, smem, st>>>(a);
-  } else {
-    e = cudaFuncSetAttribute(batch_step_kernel<NLM, THREADS, false>,
-                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    batch_step_kernel<NLM, THREADS, false><<<(unsigned)batch, THREADS, smem, st>>>(a);
-  }
+template <int NLM, bool JOSEPH>
+static cudaError_t launch_step_t(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+  const size_t smem = batch_step_smem_bytes(NLM, a.m, JOSEPH);
+  cudaError_t e = cudaFuncSetAttribute(batch_step_kernel<NLM, JOSEPH>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  // as many one-warp CTAs per SM as shared memory allows (11 at n = 43, m = 3)
+  e = cudaFuncSetAttribute(batch_step_kernel<NLM, JOSEPH>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                           cudaSharedmemCarveoutMaxShared);
+  if (e != cudaSuccess) return e;
+  batch_step_kernel<NLM, JOSEPH><<<(unsigned)batch, 32, smem, st>>>(a);
   return cudaGetLastError();
 }
 
@@ -481,19 +404,22 @@ bool batch_capacity_supported(int n_landmarks) {
   }
 }
 
+#define EKF_STEP_CASE(L) \
+  case L: return joseph ? launch_step_t<L, true>(a, batch, st) : launch_step_t<L, false>(a, batch, st)
 cudaError_t batch_launch_step(int n_landmarks, const BatchStepArgs& a, int64_t batch, bool joseph,
                               cudaStream_t st) {
   switch (n_landmarks) {
-    case 4: return launch_step_t<4, 64>(a, batch, joseph, st);
-    case 8: return launch_step_t<8, 64>(a, batch, joseph, st);
-    case 12: return launch_step_t<12, 64>(a, batch, joseph, st);
-    case 16: return launch_step_t<16, 128>(a, batch, joseph, st);
-    case 20: return launch_step_t<20, 128>(a, batch, joseph, st);
-    case 24: return launch_step_t<24, 128>(a, batch, joseph, st);
-    case 28: return launch_step_t<28, 128>(a, batch, joseph, st);
+    EKF_STEP_CASE(4);
+    EKF_STEP_CASE(8);
+    EKF_STEP_CASE(12);
+    EKF_STEP_CASE(16);
+    EKF_STEP_CASE(20);
+    EKF_STEP_CASE(24);
+    EKF_STEP_CASE(28);
     default: return cudaErrorInvalidValue;
   }
 }
+#undef EKF_STEP_CASE
 
 cudaError_t batch_launch_init(double* mu, double* P, int* n_known, int64_t batch, int n, int ld, double p0,
                               cudaStream_t st) {
