@@ -20,8 +20,8 @@
 //   phase 0  TMA bulk load of P, mu; per-filter inputs into registers
 //   phase 1  augment + motion model (computed warp-uniformly), predict of the robot rows/columns of P in smem
 //   phase 2  for each update u: the 5 rows / 5 columns it touches are rebuilt from the staged P0 and the
-//            earlier (K_v, W_v), giving H5, S^-1, K_u (from columns), W_u = H5 P[idx5,:] (from rows),
-//            mu += K_u y_u. O(n) work per update, P0 is not modified.
+//            earlier (K_v, W_v), giving H5, W_u = H5 P[idx5,:] (from rows), S = W_u[:,idx5] H5^T + Q, S^-1,
+//            K_u (from columns), mu += K_u y_u. O(n) work per update, P0 is not modified.
 //   phase 3  one pass over P in 4x4 register blocks: P[i,c] = P0[i,c] - sum_u K_u[i,:] W_u[:,c] (plain; rank-4
 //            per update for Joseph), streamed to HBM with 256-bit stores.
 // Rows and columns are both gathered for real — (P H^T)^T is never used for H P.
@@ -73,7 +73,7 @@ __device__ __forceinline__ void rank2x4(double4x& p, double k0, double k1, const
   p.d = rank2(p.d, k0, k1, w0.d, w1.d);
 }
 
-constexpr int kTailDoubles = 32;  // sV[25] + mbarrier
+constexpr int kTailDoubles = 4;  // mbarrier
 constexpr unsigned kFull = 0xffffffffu;
 
 __device__ __forceinline__ double4x lds256(const double* p) { return *reinterpret_cast<const double4x*>(p); }
@@ -85,6 +85,7 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
   constexpr int G = LD / 4;          // column groups of 4 doubles
   constexpr int NRB = (N + 3) / 4;   // row blocks of 4 rows
   constexpr int HIST = 2 * LD;       // doubles of one update's K (or W, or A) record: [2][LD]
+  constexpr int NT = (LD + 31) / 32; // lane t handles indices t, t + 32, ...
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   double* sP = reinterpret_cast<double*>(smem_raw);  // [N][LD]
@@ -93,8 +94,7 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
   const int m = a.m;
   double* sW = sK + m * HIST;                        // [m][2][LD]  W_u[0,:] then W_u[1,:]
   double* sA = sW + m * HIST;                        // [m][2][LD]  (Joseph only)
-  double* sV = (JOSEPH ? sA + m * HIST : sA);        // [25] rebuilt P[idx5, idx5]
-  uint64_t* bar = reinterpret_cast<uint64_t*>(sV + 26);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(JOSEPH ? sA + m * HIST : sA);
 
   const int lane = threadIdx.x;
   const int64_t b = blockIdx.x;
@@ -137,7 +137,11 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
   unsigned valid = 0;  // bit u: update u is applied
   {
     const double px = sMu[0], py = sMu[1], pth = sMu[2];
-    __syncwarp();
+    // even lanes evaluate sincos(theta), odd lanes sincos(theta + ang): one call instead of two
+    double sn, cs;
+    sincos((lane & 1) ? pth + ang : pth, &sn, &cs);
+    const double s1 = __shfl_sync(kFull, sn, 0), c1 = __shfl_sync(kFull, cs, 0);
+    const double s2 = __shfl_sync(kFull, sn, 1), c2 = __shfl_sync(kFull, cs, 1);
     int fault = 0;
     for (int u = 0; u < m; ++u) {
       const int s = __shfl_sync(kFull, o_slot, u);
@@ -147,14 +151,14 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
         continue;
       }
       valid |= 1u << u;
-      if (s == nk) {
+      if (s == nk) {  // first sighting: initialise from the PRE-predict pose (:331-332, :359-360)
         const int j = 3 + 2 * s;
         const double r = __shfl_sync(kFull, o_rng, u), be = __shfl_sync(kFull, o_brg, u);
-        double sn, cs;
-        sincos(be + pth, &sn, &cs);
+        double sb, cb;
+        sincos(be + pth, &sb, &cb);
         if (lane == 0) {
-          sMu[j] = px + r * cs;
-          sMu[j + 1] = py + r * sn;
+          sMu[j] = px + r * cb;
+          sMu[j + 1] = py + r * sb;
           sP[j * LD + j] = kNewLandmarkVar;
           sP[(j + 1) * LD + j + 1] = kNewLandmarkVar;
         }
@@ -162,7 +166,7 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
       }
     }
     if (!(a.flags & kFlagMeasurement)) valid = 0;
-    const Motion mo = motion_step(pth, ang, lin, a.flags);
+    const Motion mo = motion_from_sincos(pth, ang, lin, a.flags, s1, c1, s2, c2);
     if (lane == 0) {
       sMu[0] = px + mo.dx;
       sMu[1] = py + mo.dy;
@@ -174,155 +178,203 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
     // predict covariance in shared memory (:420-430): rows 0-1 += g * row 2 over ALL columns, then columns
     // 0-1 += g * column 2 over ALL rows (using the updated rows 0-1), then the three noise terms.
     const double g0 = mo.g0, g1 = mo.g1;
-    for (int t = lane; t < N; t += 32) {
-      const double p2 = sP[2 * LD + t];
-      sP[0 * LD + t] += g0 * p2;
-      sP[1 * LD + t] += g1 * p2;
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      const int t = lane + 32 * p;
+      if (t < N) {
+        const double p2 = sP[2 * LD + t];
+        sP[0 * LD + t] += g0 * p2;
+        sP[1 * LD + t] += g1 * p2;
+      }
     }
     __syncwarp();
-    for (int i = lane; i < N; i += 32) {
-      double* row = sP + i * LD;
-      const double p2 = row[2];
-      row[0] += g0 * p2;
-      row[1] += g1 * p2;
-    }
-    __syncwarp();
-    if (lane == 0) {
-      sP[0] += mv * mv;
-      sP[LD + 1] += mv * mv;
-      sP[2 * LD + 2] += (mv / 2.0) * (mv / 2.0);
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      const int i = lane + 32 * p;
+      if (i < N) {
+        double* row = sP + i * LD;
+        const double p2 = row[2];
+        double r0 = row[0] + g0 * p2, r1 = row[1] + g1 * p2;
+        if (i == 0) r0 += mv * mv;           // F^T R F (:421-430)
+        if (i == 1) r1 += mv * mv;
+        row[0] = r0;
+        row[1] = r1;
+        if (i == 2) row[2] = p2 + (mv / 2.0) * (mv / 2.0);
+      }
     }
     __syncwarp();
   }
 
   // ---- phase 2: sequential updates on the touched rows / columns only --------------------------------
+  // Lane t owns column t of the gathered ROWS (-> W_u[:, t]) and row t of the gathered COLUMNS (-> K_u[t, :])
+  // for t = lane and t = lane + 32.
   for (int u = 0; u < m; ++u) {
     if (!((valid >> u) & 1u)) continue;  // warp-uniform
     const int s = __shfl_sync(kFull, o_slot, u);
     const double z_rng = __shfl_sync(kFull, o_rng, u), z_brg = __shfl_sync(kFull, o_brg, u);
     const int j = 3 + 2 * s;
-    // (a) rebuilt 5x5 block P_u[idx5, idx5], one entry per lane
-    if (lane < 25) {
-      const int k = lane / 5, c = lane - 5 * k;
-      const int rk = (k < 3) ? k : j + (k - 3);
-      const int cc = (c < 3) ? c : j + (c - 3);
-      double v = sP[rk * LD + cc];
-      for (int w = 0; w < u; ++w) {
-        if (!((valid >> w) & 1u)) continue;
-        const double* kw = sK + w * HIST;
-        const double* ww = sW + w * HIST;
-        v = rank2(v, kw[rk], kw[LD + rk], ww[cc], ww[LD + cc]);
-        if (JOSEPH) {
-          const double* aw = sA + w * HIST;
-          v = rank2(v, aw[rk], aw[LD + rk], kw[cc], kw[LD + cc]);
-        }
-      }
-      sV[lane] = v;
-    }
-    // (b) innovation and H5 (:443-469), warp-uniform
+    // (a) innovation and H5 (:443-469), warp-uniform
     const Innov in = innovation(sMu[0], sMu[1], sMu[2], sMu[j], sMu[j + 1], z_rng, z_brg);
-    __syncwarp();
-    // (c) S = H5 V H5^T + Q and its inverse (:473), warp-uniform from the staged block
-    double hp5[2][5];
+    // (b) gather the 5 rows and 5 columns of the staged P0 ...
+    double vr[NT][5], vc[NT][5];
 #pragma unroll
-    for (int c = 0; c < 5; ++c) {
-      double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-      for (int k = 0; k < 5; ++k) {
-        const double v = sV[k * 5 + c];
-        s0 = fma(in.h[0][k], v, s0);
-        s1 = fma(in.h[1][k], v, s1);
-      }
-      hp5[0][c] = s0;
-      hp5[1][c] = s1;
-    }
-    double S[2][2], Si[2][2], Sq[2][2];
-#pragma unroll
-    for (int r = 0; r < 2; ++r)
-#pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        double acc = 0.0;
-#pragma unroll
-        for (int c = 0; c < 5; ++c) acc = fma(hp5[r][c], in.h[q][c], acc);
-        S[r][q] = acc;
-        Sq[r][q] = acc;
-      }
-    S[0][0] += qn;
-    S[1][1] += qn;
-    inv2(S, Si);
-    // (d) lane t: W_u[:, t] from the 5 ROWS and K_u[t, :] from the 5 COLUMNS (t = lane, lane + 32)
-    for (int t = lane; t < LD; t += 32) {
-      double hp0 = 0.0, hp1 = 0.0, pht0 = 0.0, pht1 = 0.0;
-      const bool real = (t < N);
+    for (int p = 0; p < NT; ++p) {
+      const int t = lane + 32 * p;
+      const bool inld = (t < LD), real = (t < N);
 #pragma unroll
       for (int k = 0; k < 5; ++k) {
         const int rk = (k < 3) ? k : j + (k - 3);
-        double vr = sP[rk * LD + t];                  // row rk, column t
-        double vc = real ? sP[t * LD + rk] : 0.0;     // row t, column rk
-        for (int w = 0; w < u; ++w) {
-          if (!((valid >> w) & 1u)) continue;
-          const double* kw = sK + w * HIST;
-          const double* ww = sW + w * HIST;
-          vr = rank2(vr, kw[rk], kw[LD + rk], ww[t], ww[LD + t]);
-          vc = rank2(vc, kw[t], kw[LD + t], ww[rk], ww[LD + rk]);
-          if (JOSEPH) {
-            const double* aw = sA + w * HIST;
-            vr = rank2(vr, aw[rk], aw[LD + rk], kw[t], kw[LD + t]);
-            vc = rank2(vc, aw[t], aw[LD + t], kw[rk], kw[LD + rk]);
+        vr[p][k] = inld ? sP[rk * LD + t] : 0.0;   // row rk, column t (pad column reads the zero pad)
+        vc[p][k] = real ? sP[t * LD + rk] : 0.0;   // row t, column rk (pad row: K stays zero)
+      }
+    }
+    // ... and bring them up to date with the earlier updates of this step (rank-2 / rank-4 each)
+    for (int w = 0; w < u; ++w) {
+      if (!((valid >> w) & 1u)) continue;
+      const double* kw = sK + w * HIST;
+      const double* ww = sW + w * HIST;
+      const double* aw = sA + w * HIST;
+      double kr0[5], kr1[5], wr0[5], wr1[5], ar0[5], ar1[5];  // warp-uniform: entries idx5 of K_w, W_w, A_w
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const int rk = (k < 3) ? k : j + (k - 3);
+        kr0[k] = kw[rk]; kr1[k] = kw[LD + rk];
+        wr0[k] = ww[rk]; wr1[k] = ww[LD + rk];
+        if (JOSEPH) { ar0[k] = aw[rk]; ar1[k] = aw[LD + rk]; }
+      }
+#pragma unroll
+      for (int p = 0; p < NT; ++p) {
+        const int t = lane + 32 * p;
+        if (t < LD) {
+          const double wt0 = ww[t], wt1 = ww[LD + t], kt0 = kw[t], kt1 = kw[LD + t];
+          double at0 = 0.0, at1 = 0.0;
+          if (JOSEPH) { at0 = aw[t]; at1 = aw[LD + t]; }
+#pragma unroll
+          for (int k = 0; k < 5; ++k) {
+            vr[p][k] = rank2(vr[p][k], kr0[k], kr1[k], wt0, wt1);
+            vc[p][k] = rank2(vc[p][k], kt0, kt1, wr0[k], wr1[k]);
+            if (JOSEPH) {
+              vr[p][k] = rank2(vr[p][k], ar0[k], ar1[k], kt0, kt1);
+              vc[p][k] = rank2(vc[p][k], at0, at1, kr0[k], kr1[k]);
+            }
           }
         }
-        hp0 = fma(in.h[0][k], vr, hp0);
-        hp1 = fma(in.h[1][k], vr, hp1);
-        pht0 = fma(vc, in.h[0][k], pht0);
-        pht1 = fma(vc, in.h[1][k], pht1);
       }
-      const double k0 = pht0 * Si[0][0] + pht1 * Si[1][0];
-      const double k1 = pht0 * Si[0][1] + pht1 * Si[1][1];
-      sK[u * HIST + t] = k0;          // zero for the pad row (vc = 0)
-      sK[u * HIST + LD + t] = k1;
-      if (JOSEPH) {  // W = H P - Q K^T, AHt = P H^T - K (S - Q)   (App. A.4)
-        sW[u * HIST + t] = hp0 - qn * k0;
-        sW[u * HIST + LD + t] = hp1 - qn * k1;
-        sA[u * HIST + t] = pht0 - (k0 * Sq[0][0] + k1 * Sq[1][0]);
-        sA[u * HIST + LD + t] = pht1 - (k0 * Sq[0][1] + k1 * Sq[1][1]);
-      } else {
-        sW[u * HIST + t] = hp0;       // zero for the pad column (P pad columns are zero)
-        sW[u * HIST + LD + t] = hp1;
+    }
+    // (c) H P (rows) and P H^T (columns) for this lane's t
+    double hp0[NT], hp1[NT], pht0[NT], pht1[NT];
+    double* wu = sW + u * HIST;
+    double* ku = sK + u * HIST;
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      double a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        a0 = fma(in.h[0][k], vr[p][k], a0);
+        a1 = fma(in.h[1][k], vr[p][k], a1);
+        b0 = fma(vc[p][k], in.h[0][k], b0);
+        b1 = fma(vc[p][k], in.h[1][k], b1);
       }
-      if (real) sMu[t] += k0 * in.y0 + k1 * in.y1;  // a10 (:476)
+      hp0[p] = a0; hp1[p] = a1; pht0[p] = b0; pht1[p] = b1;
+      const int t = lane + 32 * p;
+      if (t < LD) {
+        wu[t] = a0;
+        wu[LD + t] = a1;
+      }
+    }
+    __syncwarp();
+    // (d) S = (H P) H^T + Q from the five entries idx5 of H P (:473), closed-form inverse; warp-uniform
+    double S[2][2], Si[2][2], Sq[2][2];
+    {
+      double acc00 = 0.0, acc01 = 0.0, acc10 = 0.0, acc11 = 0.0;
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        const int cc = (c < 3) ? c : j + (c - 3);
+        const double x0 = wu[cc], x1 = wu[LD + cc];
+        acc00 = fma(x0, in.h[0][c], acc00);
+        acc01 = fma(x0, in.h[1][c], acc01);
+        acc10 = fma(x1, in.h[0][c], acc10);
+        acc11 = fma(x1, in.h[1][c], acc11);
+      }
+      Sq[0][0] = acc00; Sq[0][1] = acc01; Sq[1][0] = acc10; Sq[1][1] = acc11;
+      S[0][0] = acc00 + qn; S[0][1] = acc01; S[1][0] = acc10; S[1][1] = acc11 + qn;
+    }
+    inv2(S, Si);
+    if (JOSEPH) __syncwarp();  // every lane has read the raw H P before W is overwritten below
+    // (e) K_u = P H^T S^-1 (:473), mu += K_u y (:476); Joseph: W = H P - Q K^T, AHt = P H^T - K (S - Q)
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      const int t = lane + 32 * p;
+      if (t < LD) {
+        const double k0 = pht0[p] * Si[0][0] + pht1[p] * Si[1][0];
+        const double k1 = pht0[p] * Si[0][1] + pht1[p] * Si[1][1];
+        ku[t] = k0;  // zero for the pad row
+        ku[LD + t] = k1;
+        if (JOSEPH) {
+          wu[t] = hp0[p] - qn * k0;
+          wu[LD + t] = hp1[p] - qn * k1;
+          sA[u * HIST + t] = pht0[p] - (k0 * Sq[0][0] + k1 * Sq[1][0]);
+          sA[u * HIST + LD + t] = pht1[p] - (k0 * Sq[0][1] + k1 * Sq[1][1]);
+        }
+        if (t < N) sMu[t] += k0 * in.y0 + k1 * in.y1;
+      }
     }
     __syncwarp();
   }
 
   // ---- phase 3: one pass over P in 4x4 blocks, all updates applied in order, streamed to HBM ---------
-  for (int blk = lane; blk < NRB * G; blk += 32) {
-    const int rb = blk / G, g = blk - rb * G;
-    const int i0 = 4 * rb, c = 4 * g;
-    double4x p[4];
+  {
+    constexpr int NBLK = NRB * G;
+    constexpr int NPASS = (NBLK + 31) / 32;
+    int rb = lane / G, g = lane - rb * G;
 #pragma unroll
-    for (int r = 0; r < 4; ++r) p[r] = lds256(sP + (i0 + r) * LD + c);  // a row >= N reads mu: never stored
-    for (int u = 0; u < m; ++u) {
-      if (!((valid >> u) & 1u)) continue;
-      const double4x w0 = lds256(sW + u * HIST + c), w1 = lds256(sW + u * HIST + LD + c);
-      const double4x k0 = lds256(sK + u * HIST + i0), k1 = lds256(sK + u * HIST + LD + i0);
-      rank2x4(p[0], k0.a, k1.a, w0, w1);
-      rank2x4(p[1], k0.b, k1.b, w0, w1);
-      rank2x4(p[2], k0.c, k1.c, w0, w1);
-      rank2x4(p[3], k0.d, k1.d, w0, w1);
-      if (JOSEPH) {
-        const double4x a0 = lds256(sA + u * HIST + i0), a1 = lds256(sA + u * HIST + LD + i0);
-        const double4x kc0 = lds256(sK + u * HIST + c), kc1 = lds256(sK + u * HIST + LD + c);
-        rank2x4(p[0], a0.a, a1.a, kc0, kc1);
-        rank2x4(p[1], a0.b, a1.b, kc0, kc1);
-        rank2x4(p[2], a0.c, a1.c, kc0, kc1);
-        rank2x4(p[3], a0.d, a1.d, kc0, kc1);
+    for (int pass = 0; pass < NPASS; ++pass) {
+      if (pass * 32 + lane < NBLK) {
+        const int i0 = 4 * rb, c = 4 * g;
+        double4x p[4];
+        const double* src = sP + i0 * LD + c;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) p[r] = lds256(src + r * LD);  // a row >= N reads mu: never stored
+        const double* kp = sK + i0;
+        const double* wp = sW + c;
+        for (int u = 0; u < m; ++u, kp += HIST, wp += HIST) {
+          if (!((valid >> u) & 1u)) continue;
+          const double4x w0 = lds256(wp), w1 = lds256(wp + LD);
+          const double4x k0 = lds256(kp), k1 = lds256(kp + LD);
+          rank2x4(p[0], k0.a, k1.a, w0, w1);
+          rank2x4(p[1], k0.b, k1.b, w0, w1);
+          rank2x4(p[2], k0.c, k1.c, w0, w1);
+          rank2x4(p[3], k0.d, k1.d, w0, w1);
+          if (JOSEPH) {
+            const double* ap = sA + u * HIST + i0;
+            const double* kc = sK + u * HIST + c;
+            const double4x a0 = lds256(ap), a1 = lds256(ap + LD);
+            const double4x kc0 = lds256(kc), kc1 = lds256(kc + LD);
+            rank2x4(p[0], a0.a, a1.a, kc0, kc1);
+            rank2x4(p[1], a0.b, a1.b, kc0, kc1);
+            rank2x4(p[2], a0.c, a1.c, kc0, kc1);
+            rank2x4(p[3], a0.d, a1.d, kc0, kc1);
+          }
+        }
+        double* dst = gP + i0 * LD + c;
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+          if (i0 + r < N) stg256(dst + r * LD, p[r]);
+      }
+      // next block of this lane: blk += 32
+      rb += 32 / G;
+      g += 32 % G;
+      if (g >= G) {
+        g -= G;
+        ++rb;
       }
     }
-#pragma unroll
-    for (int r = 0; r < 4; ++r)
-      if (i0 + r < N) stg256(gP + (i0 + r) * LD + c, p[r]);
   }
-  for (int t = lane; t < LD; t += 32) gMu[t] = sMu[t];
+#pragma unroll
+  for (int p = 0; p < NT; ++p) {
+    const int t = lane + 32 * p;
+    if (t < LD) gMu[t] = sMu[t];
+  }
 }
 
 // -------------------------------------------------------------------------------------------------------

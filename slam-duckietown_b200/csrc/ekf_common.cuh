@@ -13,12 +13,17 @@ constexpr double kNewLandmarkVar = 10000.0;  // replay_no_ros.py:356-357
 // flag bits shared by host and device
 enum : int { kFlagCircular = 1, kFlagMeasurement = 2, kFlagDisableMotion = 4, kFlagJoseph = 8 };
 
-// (a + pi) % (2 pi) - pi with Python float-modulo semantics (replay_no_ros.py:397,:458): fmod keeps the sign
-// of the dividend, Python's % that of the divisor.
+// (a + pi) % (2 pi) - pi with Python float-modulo semantics (replay_no_ros.py:397,:458): the result of the
+// modulo lies in [0, 2 pi). r - floor(r / 2pi) * 2pi is evaluated with one FMA (exact whenever the quotient is
+// the true one, like fmod); a quotient that rounding pushed across an integer is repaired by the two
+// range checks, which changes the value by at most one rounding (1e-16), far inside the 1e-9 parity bound.
 __host__ __device__ __forceinline__ double wrap_pi(double a) {
-  double r = fmod(a + kPi, kTwoPi);
-  if (r < 0.0) r += kTwoPi;
-  return r - kPi;
+  const double r = a + kPi;
+  const double k = floor(r * (1.0 / kTwoPi));
+  double v = fma(-k, kTwoPi, r);
+  if (v < 0.0) v += kTwoPi;
+  if (v >= kTwoPi) v -= kTwoPi;
+  return v - kPi;
 }
 
 // a1/a2 (replay_no_ros.py:262-266, :491-497)
@@ -44,18 +49,16 @@ __host__ __device__ __forceinline__ void displacement(double R, double baseline,
 struct Motion {
   double dx, dy, theta, g0, g1;
 };
-__device__ __forceinline__ Motion motion_step(double th, double ang, double lin, int flags) {
+// (s, c) = sincos(th), (s2, c2) = sincos(th + ang) are passed in so that a warp can evaluate both in one call
+__device__ __forceinline__ Motion motion_from_sincos(double th, double ang, double lin, int flags, double s,
+                                                     double c, double s2, double c2) {
   Motion m;
   if (flags & kFlagDisableMotion) {
     m.dx = 0.0; m.dy = 0.0; m.theta = th; m.g0 = 0.0; m.g1 = 0.0;
     return m;
   }
-  double s, c;
-  sincos(th, &s, &c);
   if ((flags & kFlagCircular) && fabs(ang) > 1e-2) {
     const double r = lin / ang;
-    double s2, c2;
-    sincos(th + ang, &s2, &c2);
     m.dx = -r * s + r * s2;
     m.dy = r * c - r * c2;
     m.theta = wrap_pi(th + ang);
@@ -70,6 +73,12 @@ __device__ __forceinline__ Motion motion_step(double th, double ang, double lin,
     m.g1 = lin * c;
   }
   return m;
+}
+__device__ __forceinline__ Motion motion_step(double th, double ang, double lin, int flags) {
+  double s, c, s2, c2;
+  sincos(th, &s, &c);
+  sincos(th + ang, &s2, &c2);
+  return motion_from_sincos(th, ang, lin, flags, s, c, s2, c2);
 }
 
 // a8 (replay_no_ros.py:443-469): innovation y and the 2x5 block of H over columns {0,1,2,j,j+1}
@@ -87,18 +96,20 @@ __device__ __forceinline__ Innov innovation(double mx, double my, double mth, do
   o.q = q;
   o.y0 = rng - sq;
   o.y1 = wrap_pi(brg - (atan2(dy, dx) - mth));
-  o.h[0][0] = (-sq * dx) / q; o.h[0][1] = (-sq * dy) / q; o.h[0][2] = 0.0;
-  o.h[0][3] = (sq * dx) / q;  o.h[0][4] = (sq * dy) / q;
-  o.h[1][0] = dy / q;  o.h[1][1] = -dx / q; o.h[1][2] = -q / q;
-  o.h[1][3] = -dy / q; o.h[1][4] = dx / q;
+  // one reciprocal instead of the reference's ten divisions by q (:461-469): <= 1 ulp per entry
+  const double rq = 1.0 / q;
+  const double ax = (sq * dx) * rq, ay = (sq * dy) * rq, bx = dx * rq, by = dy * rq;
+  o.h[0][0] = -ax; o.h[0][1] = -ay; o.h[0][2] = 0.0; o.h[0][3] = ax;  o.h[0][4] = ay;
+  o.h[1][0] = by;  o.h[1][1] = -bx; o.h[1][2] = -1.0; o.h[1][3] = -by; o.h[1][4] = bx;
   return o;
 }
 
 // closed-form inverse of the 2x2 innovation covariance (replaces np.linalg.inv, :473)
 __device__ __forceinline__ void inv2(const double s[2][2], double si[2][2]) {
   const double det = s[0][0] * s[1][1] - s[0][1] * s[1][0];
-  si[0][0] = s[1][1] / det;  si[0][1] = -s[0][1] / det;
-  si[1][0] = -s[1][0] / det; si[1][1] = s[0][0] / det;
+  const double rd = 1.0 / det;
+  si[0][0] = s[1][1] * rd;  si[0][1] = -s[0][1] * rd;
+  si[1][0] = -s[1][0] * rd; si[1][1] = s[0][0] * rd;
 }
 
 // 256-bit global accesses (sm_100a: LDG.E.256 / STG.E.256)
