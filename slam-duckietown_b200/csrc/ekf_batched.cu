@@ -22,8 +22,8 @@
 //   phase 2  for each update u: the 5 rows / 5 columns it touches are rebuilt from the staged P0 and the
 //            earlier (K_v, W_v), giving H5, W_u = H5 P[idx5,:] (from rows), S = W_u[:,idx5] H5^T + Q, S^-1,
 //            K_u (from columns), mu += K_u y_u. O(n) work per update, P0 is not modified.
-//   phase 3  one pass over P in 4x4 register blocks: P[i,c] = P0[i,c] - sum_u K_u[i,:] W_u[:,c] (plain; rank-4
-//            per update for Joseph), streamed to HBM with 256-bit stores.
+//   phase 3  one pass over P: P[i,c] = P0[i,c] - sum_u K_u[i,:] W_u[:,c] (plain; rank-4 per update for Joseph),
+//            a lane keeping W_u of its 4 columns in registers, streamed to HBM with coalesced 256-bit stores.
 // Rows and columns are both gathered for real — (P H^T)^T is never used for H P.
 #include "ekf_batched.h"
 #include "ekf_common.cuh"
@@ -76,24 +76,27 @@ __device__ __forceinline__ void rank2x4(double4x& p, double k0, double k1, const
 constexpr int kTailDoubles = 4;  // mbarrier
 constexpr unsigned kFull = 0xffffffffu;
 
+struct __align__(16) d2 {
+  double x, y;
+};
 __device__ __forceinline__ double4x lds256(const double* p) { return *reinterpret_cast<const double4x*>(p); }
+__device__ __forceinline__ d2 lds128(const double* p) { return *reinterpret_cast<const d2*>(p); }
 
 template <int NLM, bool JOSEPH>
 __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
   constexpr int G = LD / 4;          // column groups of 4 doubles
-  constexpr int NRB = (N + 3) / 4;   // row blocks of 4 rows
   constexpr int HIST = 2 * LD;       // doubles of one update's K (or W, or A) record: [2][LD]
   constexpr int NT = (LD + 31) / 32; // lane t handles indices t, t + 32, ...
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   double* sP = reinterpret_cast<double*>(smem_raw);  // [N][LD]
   double* sMu = sP + N * LD;                         // [LD]
-  double* sK = sMu + LD;                             // [m][2][LD]  K_u[:,0] then K_u[:,1]
+  double* sK = sMu + LD;                             // [m][LD][2]  (K_u[i,0], K_u[i,1]) pairs
   const int m = a.m;
   double* sW = sK + m * HIST;                        // [m][2][LD]  W_u[0,:] then W_u[1,:]
-  double* sA = sW + m * HIST;                        // [m][2][LD]  (Joseph only)
+  double* sA = sW + m * HIST;                        // [m][LD][2]  AHt_u pairs (Joseph only)
   uint64_t* bar = reinterpret_cast<uint64_t*>(JOSEPH ? sA + m * HIST : sA);
 
   const int lane = threadIdx.x;
@@ -231,31 +234,34 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
     // ... and bring them up to date with the earlier updates of this step (rank-2 / rank-4 each)
     for (int w = 0; w < u; ++w) {
       if (!((valid >> w) & 1u)) continue;
-      const double* kw = sK + w * HIST;
-      const double* ww = sW + w * HIST;
-      const double* aw = sA + w * HIST;
-      double kr0[5], kr1[5], wr0[5], wr1[5], ar0[5], ar1[5];  // warp-uniform: entries idx5 of K_w, W_w, A_w
+      const double* kw = sK + w * HIST;   // [LD][2]
+      const double* ww = sW + w * HIST;   // [2][LD]
+      const double* aw = sA + w * HIST;   // [LD][2]
+      d2 kr[5], ar[5];                    // warp-uniform: entries idx5 of K_w, A_w, W_w
+      double wr0[5], wr1[5];
 #pragma unroll
       for (int k = 0; k < 5; ++k) {
         const int rk = (k < 3) ? k : j + (k - 3);
-        kr0[k] = kw[rk]; kr1[k] = kw[LD + rk];
-        wr0[k] = ww[rk]; wr1[k] = ww[LD + rk];
-        if (JOSEPH) { ar0[k] = aw[rk]; ar1[k] = aw[LD + rk]; }
+        kr[k] = lds128(kw + 2 * rk);
+        wr0[k] = ww[rk];
+        wr1[k] = ww[LD + rk];
+        if (JOSEPH) ar[k] = lds128(aw + 2 * rk);
       }
 #pragma unroll
       for (int p = 0; p < NT; ++p) {
         const int t = lane + 32 * p;
         if (t < LD) {
-          const double wt0 = ww[t], wt1 = ww[LD + t], kt0 = kw[t], kt1 = kw[LD + t];
-          double at0 = 0.0, at1 = 0.0;
-          if (JOSEPH) { at0 = aw[t]; at1 = aw[LD + t]; }
+          const double wt0 = ww[t], wt1 = ww[LD + t];
+          const d2 kt = lds128(kw + 2 * t);
+          d2 at = {0.0, 0.0};
+          if (JOSEPH) at = lds128(aw + 2 * t);
 #pragma unroll
           for (int k = 0; k < 5; ++k) {
-            vr[p][k] = rank2(vr[p][k], kr0[k], kr1[k], wt0, wt1);
-            vc[p][k] = rank2(vc[p][k], kt0, kt1, wr0[k], wr1[k]);
+            vr[p][k] = rank2(vr[p][k], kr[k].x, kr[k].y, wt0, wt1);
+            vc[p][k] = rank2(vc[p][k], kt.x, kt.y, wr0[k], wr1[k]);
             if (JOSEPH) {
-              vr[p][k] = rank2(vr[p][k], ar0[k], ar1[k], kt0, kt1);
-              vc[p][k] = rank2(vc[p][k], at0, at1, kr0[k], kr1[k]);
+              vr[p][k] = rank2(vr[p][k], ar[k].x, ar[k].y, kt.x, kt.y);
+              vc[p][k] = rank2(vc[p][k], at.x, at.y, kr[k].x, kr[k].y);
             }
           }
         }
@@ -306,67 +312,74 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
     for (int p = 0; p < NT; ++p) {
       const int t = lane + 32 * p;
       if (t < LD) {
-        const double k0 = pht0[p] * Si[0][0] + pht1[p] * Si[1][0];
-        const double k1 = pht0[p] * Si[0][1] + pht1[p] * Si[1][1];
-        ku[t] = k0;  // zero for the pad row
-        ku[LD + t] = k1;
+        d2 kk;
+        kk.x = pht0[p] * Si[0][0] + pht1[p] * Si[1][0];
+        kk.y = pht0[p] * Si[0][1] + pht1[p] * Si[1][1];
+        *reinterpret_cast<d2*>(ku + 2 * t) = kk;  // zero for the pad row
         if (JOSEPH) {
-          wu[t] = hp0[p] - qn * k0;
-          wu[LD + t] = hp1[p] - qn * k1;
-          sA[u * HIST + t] = pht0[p] - (k0 * Sq[0][0] + k1 * Sq[1][0]);
-          sA[u * HIST + LD + t] = pht1[p] - (k0 * Sq[0][1] + k1 * Sq[1][1]);
+          wu[t] = hp0[p] - qn * kk.x;
+          wu[LD + t] = hp1[p] - qn * kk.y;
+          d2 av;
+          av.x = pht0[p] - (kk.x * Sq[0][0] + kk.y * Sq[1][0]);
+          av.y = pht1[p] - (kk.x * Sq[0][1] + kk.y * Sq[1][1]);
+          *reinterpret_cast<d2*>(sA + u * HIST + 2 * t) = av;
         }
-        if (t < N) sMu[t] += k0 * in.y0 + k1 * in.y1;
+        if (t < N) sMu[t] += kk.x * in.y0 + kk.y * in.y1;
       }
     }
     __syncwarp();
   }
 
-  // ---- phase 3: one pass over P in 4x4 blocks, all updates applied in order, streamed to HBM ---------
+  // ---- phase 3: one pass over P, all updates applied in order, streamed to HBM -------------------------
+  // Lane (ph, g): column group g (4 doubles, W_u of those columns in registers) and rows ph, ph + RP, ...;
+  // the RP rows of one iteration are adjacent, so a warp store covers RP * LD contiguous doubles. K_u of a row
+  // is one 128-bit load shared by the G lanes of that row (round-1 ncu: a (row block, column group) mapping
+  // spent 1100 shared-memory wavefronts per filter on redundant 256-bit K/W loads; this one ~440).
   {
-    constexpr int NBLK = NRB * G;
-    constexpr int NPASS = (NBLK + 31) / 32;
-    int rb = lane / G, g = lane - rb * G;
+    constexpr int RP = 32 / G;              // rows per iteration
+    constexpr int NIT = (N + RP - 1) / RP;  // iterations
+    constexpr int CH = 8;                   // rows of P in registers per lane between W reloads
+    const int ph = lane / G, g = lane - ph * G;
+    if (ph < RP) {
+      const int c = 4 * g;
 #pragma unroll
-    for (int pass = 0; pass < NPASS; ++pass) {
-      if (pass * 32 + lane < NBLK) {
-        const int i0 = 4 * rb, c = 4 * g;
-        double4x p[4];
-        const double* src = sP + i0 * LD + c;
+      for (int it0 = 0; it0 < NIT; it0 += CH) {
+        double4x p[CH];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) p[r] = lds256(src + r * LD);  // a row >= N reads mu: never stored
-        const double* kp = sK + i0;
-        const double* wp = sW + c;
-        for (int u = 0; u < m; ++u, kp += HIST, wp += HIST) {
+        for (int q = 0; q < CH; ++q) {
+          const int r = (it0 + q) * RP + ph;
+          if (it0 + q < NIT && r < N) p[q] = lds256(sP + r * LD + c);
+        }
+        for (int u = 0; u < m; ++u) {
           if (!((valid >> u) & 1u)) continue;
-          const double4x w0 = lds256(wp), w1 = lds256(wp + LD);
-          const double4x k0 = lds256(kp), k1 = lds256(kp + LD);
-          rank2x4(p[0], k0.a, k1.a, w0, w1);
-          rank2x4(p[1], k0.b, k1.b, w0, w1);
-          rank2x4(p[2], k0.c, k1.c, w0, w1);
-          rank2x4(p[3], k0.d, k1.d, w0, w1);
+          const double* ku = sK + u * HIST;
+          const double4x w0 = lds256(sW + u * HIST + c), w1 = lds256(sW + u * HIST + LD + c);
+          double4x kca, kcb;  // Joseph: K_u pairs of this lane's 4 columns
           if (JOSEPH) {
-            const double* ap = sA + u * HIST + i0;
-            const double* kc = sK + u * HIST + c;
-            const double4x a0 = lds256(ap), a1 = lds256(ap + LD);
-            const double4x kc0 = lds256(kc), kc1 = lds256(kc + LD);
-            rank2x4(p[0], a0.a, a1.a, kc0, kc1);
-            rank2x4(p[1], a0.b, a1.b, kc0, kc1);
-            rank2x4(p[2], a0.c, a1.c, kc0, kc1);
-            rank2x4(p[3], a0.d, a1.d, kc0, kc1);
+            kca = lds256(ku + 2 * c);
+            kcb = lds256(ku + 2 * c + 4);
+          }
+#pragma unroll
+          for (int q = 0; q < CH; ++q) {
+            const int r = (it0 + q) * RP + ph;
+            if (it0 + q < NIT && r < N) {
+              const d2 k = lds128(ku + 2 * r);
+              rank2x4(p[q], k.x, k.y, w0, w1);
+              if (JOSEPH) {
+                const d2 av = lds128(sA + u * HIST + 2 * r);
+                p[q].a = rank2(p[q].a, av.x, av.y, kca.a, kca.b);
+                p[q].b = rank2(p[q].b, av.x, av.y, kca.c, kca.d);
+                p[q].c = rank2(p[q].c, av.x, av.y, kcb.a, kcb.b);
+                p[q].d = rank2(p[q].d, av.x, av.y, kcb.c, kcb.d);
+              }
+            }
           }
         }
-        double* dst = gP + i0 * LD + c;
 #pragma unroll
-        for (int r = 0; r < 4; ++r)
-          if (i0 + r < N) stg256(dst + r * LD, p[r]);
-      }
-      // next block of this lane: blk += 32
-      rb += 32 / G;
-      g += 32 % G;
-      if (g >= G) {
-        g -= G;
-        ++rb;
+        for (int q = 0; q < CH; ++q) {
+          const int r = (it0 + q) * RP + ph;
+          if (it0 + q < NIT && r < N) stg256(gP + r * LD + c, p[q]);
+        }
       }
     }
   }
