@@ -8,7 +8,7 @@
 //   mu [B][LD]        LD = n rounded up to 4 doubles, pad zero
 //   P  [B][N*LD]      row-major, leading dimension LD, pad column(s) zero
 // so a filter's covariance is ONE contiguous block: it is brought into shared memory with a single TMA
-// bulk copy (cp.async.bulk + mbarrier) and leaves through coalesced 256-bit stores. Algorithmic traffic per
+// bulk copy (cp.async.bulk + mbarrier) and leaves through coalesced 128-bit stores. Algorithmic traffic per
 // filter-step: one read + one write of mu and P regardless of the number of updates.
 //
 // Why a warp per filter (round-1 ncu, profiles/): the step is a chain of short dependent phases (motion
@@ -23,7 +23,7 @@
 //            earlier (K_v, W_v), giving H5, W_u = H5 P[idx5,:] (from rows), S = W_u[:,idx5] H5^T + Q, S^-1,
 //            K_u (from columns), mu += K_u y_u. O(n) work per update, P0 is not modified.
 //   phase 3  one pass over P: P[i,c] = P0[i,c] - sum_u K_u[i,:] W_u[:,c] (plain; rank-4 per update for Joseph),
-//            a lane keeping W_u of its 4 columns in registers, streamed to HBM with coalesced 256-bit stores.
+//            a lane keeping W_u of its 4 columns in registers, streamed to HBM with coalesced 128-bit stores.
 // Rows and columns are both gathered for real — (P H^T)^T is never used for H P.
 #include "ekf_batched.h"
 #include "ekf_common.cuh"
@@ -81,6 +81,9 @@ struct __align__(16) d2 {
 };
 __device__ __forceinline__ double4x lds256(const double* p) { return *reinterpret_cast<const double4x*>(p); }
 __device__ __forceinline__ d2 lds128(const double* p) { return *reinterpret_cast<const d2*>(p); }
+__device__ __forceinline__ void stg128(double* p, const d2& v) {
+  asm volatile("st.global.v2.f64 [%0], {%1,%2};" ::"l"(p), "d"(v.x), "d"(v.y) : "memory");
+}
 
 template <int NLM, bool JOSEPH>
 __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
@@ -331,46 +334,58 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
   }
 
   // ---- phase 3: one pass over P, all updates applied in order, streamed to HBM -------------------------
-  // Lane (ph, g): column group g (4 doubles, W_u of those columns in registers) and rows ph, ph + RP, ...;
-  // the RP rows of one iteration are adjacent, so a warp store covers RP * LD contiguous doubles. K_u of a row
-  // is one 128-bit load shared by the G lanes of that row (round-1 ncu: a (row block, column group) mapping
-  // spent 1100 shared-memory wavefronts per filter on redundant 256-bit K/W loads; this one ~440).
+  // Lane (ph, g): columns {2g, 2g+1} and {LD/2 + 2g, LD/2 + 2g+1} (W_u of those columns in registers) and rows
+  // ph, ph + RP, ...; consecutive lanes are 16 bytes apart, which is what makes the 128-bit shared-memory loads
+  // conflict-free (round-1 ncu: 256-bit accesses are issued as two LDS.128 with lanes 32 bytes apart = 2-way
+  // conflicts, and a (row block, column group) mapping spent 1100 wavefronts per filter on redundant K/W loads).
+  // The RP rows of one iteration are adjacent in memory. K_u of a row is one 128-bit load shared by its G lanes.
   {
     constexpr int RP = 32 / G;              // rows per iteration
     constexpr int NIT = (N + RP - 1) / RP;  // iterations
     constexpr int CH = 8;                   // rows of P in registers per lane between W reloads
+    constexpr int HALF = LD / 2;
     const int ph = lane / G, g = lane - ph * G;
     if (ph < RP) {
-      const int c = 4 * g;
+      const int ca = 2 * g, cb = HALF + 2 * g;
 #pragma unroll
       for (int it0 = 0; it0 < NIT; it0 += CH) {
-        double4x p[CH];
+        d2 pa[CH], pb[CH];
 #pragma unroll
         for (int q = 0; q < CH; ++q) {
           const int r = (it0 + q) * RP + ph;
-          if (it0 + q < NIT && r < N) p[q] = lds256(sP + r * LD + c);
+          if (it0 + q < NIT && r < N) {
+            pa[q] = lds128(sP + r * LD + ca);
+            pb[q] = lds128(sP + r * LD + cb);
+          }
         }
         for (int u = 0; u < m; ++u) {
           if (!((valid >> u) & 1u)) continue;
           const double* ku = sK + u * HIST;
-          const double4x w0 = lds256(sW + u * HIST + c), w1 = lds256(sW + u * HIST + LD + c);
-          double4x kca, kcb;  // Joseph: K_u pairs of this lane's 4 columns
+          const double* wu = sW + u * HIST;
+          const d2 w0a = lds128(wu + ca), w0b = lds128(wu + cb);
+          const d2 w1a = lds128(wu + LD + ca), w1b = lds128(wu + LD + cb);
+          d2 kc[4];  // Joseph: K_u pairs of this lane's 4 columns
           if (JOSEPH) {
-            kca = lds256(ku + 2 * c);
-            kcb = lds256(ku + 2 * c + 4);
+            kc[0] = lds128(ku + 2 * ca);
+            kc[1] = lds128(ku + 2 * ca + 2);
+            kc[2] = lds128(ku + 2 * cb);
+            kc[3] = lds128(ku + 2 * cb + 2);
           }
 #pragma unroll
           for (int q = 0; q < CH; ++q) {
             const int r = (it0 + q) * RP + ph;
             if (it0 + q < NIT && r < N) {
               const d2 k = lds128(ku + 2 * r);
-              rank2x4(p[q], k.x, k.y, w0, w1);
+              pa[q].x = rank2(pa[q].x, k.x, k.y, w0a.x, w1a.x);
+              pa[q].y = rank2(pa[q].y, k.x, k.y, w0a.y, w1a.y);
+              pb[q].x = rank2(pb[q].x, k.x, k.y, w0b.x, w1b.x);
+              pb[q].y = rank2(pb[q].y, k.x, k.y, w0b.y, w1b.y);
               if (JOSEPH) {
                 const d2 av = lds128(sA + u * HIST + 2 * r);
-                p[q].a = rank2(p[q].a, av.x, av.y, kca.a, kca.b);
-                p[q].b = rank2(p[q].b, av.x, av.y, kca.c, kca.d);
-                p[q].c = rank2(p[q].c, av.x, av.y, kcb.a, kcb.b);
-                p[q].d = rank2(p[q].d, av.x, av.y, kcb.c, kcb.d);
+                pa[q].x = rank2(pa[q].x, av.x, av.y, kc[0].x, kc[0].y);
+                pa[q].y = rank2(pa[q].y, av.x, av.y, kc[1].x, kc[1].y);
+                pb[q].x = rank2(pb[q].x, av.x, av.y, kc[2].x, kc[2].y);
+                pb[q].y = rank2(pb[q].y, av.x, av.y, kc[3].x, kc[3].y);
               }
             }
           }
@@ -378,7 +393,10 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
 #pragma unroll
         for (int q = 0; q < CH; ++q) {
           const int r = (it0 + q) * RP + ph;
-          if (it0 + q < NIT && r < N) stg256(gP + r * LD + c, p[q]);
+          if (it0 + q < NIT && r < N) {
+            stg128(gP + r * LD + ca, pa[q]);
+            stg128(gP + r * LD + cb, pb[q]);
+          }
         }
       }
     }
