@@ -1,0 +1,164 @@
+"""Row-block sharding of ONE large-map EKF-SLAM filter across GPUs.
+
+GPU g owns a contiguous block of rows of P whose boundaries fall on landmark pairs (rows j, j+1 share an
+owner); rank 0 also owns the robot rows 0-2. Per range-bearing update there is exactly one exchange: the five
+rows {0, 1, 2, j, j+1} of P (with their mu entries riding at column ``ld`` of each exported row) travel from
+their owners to every rank — a broadcast of three rows from rank 0 and of two rows from owner(j), 40*n bytes —
+after which every rank runs the gather + streaming rank-2 update on its own block
+(``ekf_lm_export_rows`` / ``ekf_lm_update_from_rows``). ``K`` needs only columns of local rows; predict is
+communication-free (reference semantics: replay_no_ros.py:420-430 touches rows/columns 0-1 only).
+
+It is ROWS that travel: the reference keeps full, slightly asymmetric storage (replay_no_ros.py:480), where
+using (P H^T)^T for H P is numerically unstable.
+
+The partition helpers and ``exchange_rows`` are device-agnostic (they are covered by world_size-2 ``gloo`` tests
+on CPU); everything that computes goes through the CUDA library and fails loudly without it.
+"""
+from __future__ import annotations
+
+from . import ekf_bindings as eb
+
+
+def row_partition(n_landmarks: int, world: int):
+    """[(row_begin, row_end)] per rank: landmarks split into ``world`` contiguous, near-equal ranges; rank 0
+    additionally owns rows 0-2. Every boundary is at a row 3 + 2k."""
+    if world < 1:
+        raise ValueError("world must be >= 1")
+    base, extra = divmod(n_landmarks, world)
+    out, lm = [], 0
+    for r in range(world):
+        cnt = base + (1 if r < extra else 0)
+        begin = 0 if r == 0 else 3 + 2 * lm
+        lm += cnt
+        out.append((begin, 3 + 2 * lm))
+    return out
+
+
+def owner_of_slot(slot: int, n_landmarks: int, world: int) -> int:
+    """Rank that owns rows 3+2*slot and 4+2*slot under ``row_partition``."""
+    if not 0 <= slot < n_landmarks:
+        raise ValueError(f"slot {slot} outside [0, {n_landmarks})")
+    base, extra = divmod(n_landmarks, world)
+    split = extra * (base + 1)
+    if slot < split:
+        return slot // (base + 1)
+    return extra + (slot - split) // base
+
+
+def exchange_rows(rows5, owner: int, group=None):
+    """The per-update collective: rows 0-2 from rank 0, rows 3-4 (= P rows j, j+1) from ``owner``.
+    ``rows5`` is a (5, ld+4) tensor (CUDA -> NCCL over NVLink; CPU -> gloo in the tests)."""
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return
+    dist.broadcast(rows5[0:3], src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    dist.broadcast(rows5[3:5], src=dist.get_global_rank(group, owner) if group is not None else owner,
+                   group=group)
+
+
+class ShardedLargeMapEKF:
+    """One process per GPU; every rank calls the same methods with the same arguments (SPMD)."""
+
+    def __init__(self, capacity: int, rank: int, world: int, device: int | None = None, group=None):
+        self.capacity, self.rank, self.world, self.group = int(capacity), int(rank), int(world), group
+        self.ranges = row_partition(self.capacity, self.world)
+        self.local = eb.LargeMapEKF(self.capacity, device=self.rank if device is None else device,
+                                    row_range=self.ranges[self.rank])
+        self.n, self.ld = self.local.n, self.local.ld
+        torch = self.local.torch
+        self.rows5 = torch.zeros((5, self.ld + 4), dtype=torch.float64, device=self.local.mu.device)
+        self.local.rows5 = self.rows5
+
+    def close(self):
+        self.local.close()
+
+    def set_noise(self, motion_var: float, meas_var: float):
+        self.local.set_noise(motion_var, meas_var)
+
+    def set_flags(self, circular=True, measurement=True, disable_motion=False):
+        self.local.set_flags(circular, measurement, disable_motion, joseph=False)
+
+    def load(self, mean, cov_rows):
+        """``mean`` (m,) replicated; ``cov_rows``: the FULL (m, m) covariance or a callable
+        (row_begin, row_end) -> (rows, m) block, so that a 34 GB matrix never has to exist on one host."""
+        import numpy as np
+        lo, hi = self.ranges[self.rank]
+        m = len(mean)
+        hi = min(hi, m)
+        blk = cov_rows(lo, hi) if callable(cov_rows) else np.asarray(cov_rows)[lo:hi, :]
+        torch = self.local.torch
+        mu = np.zeros(self.ld)
+        mu[:m] = mean
+        self.local.mu.copy_(torch.from_numpy(mu))
+        self.local.P.zero_()
+        if hi > lo:
+            self.local.P[: hi - lo, :m] = torch.from_numpy(np.ascontiguousarray(blk)).to(self.local.P.device)
+
+    def augment(self, slot: int, gx: float, gy: float):
+        self.local.augment(slot, gx, gy)       # mu entries everywhere, diagonal on the owner only
+
+    def predict(self, ang: float, lin: float):
+        self.local.predict(ang, lin)           # no communication
+
+    def update(self, slot: int, rng: float, brg: float):
+        self.local.export_rows(slot)
+        exchange_rows(self.rows5, owner_of_slot(slot, self.capacity, self.world), self.group)
+        self.local.update_from_rows(slot, rng, brg, self.rows5)
+
+    def local_state(self):
+        """(mu slice owned by this rank incl. the replicated pose on rank 0, P row block) as numpy."""
+        lo, hi = self.ranges[self.rank]
+        mu, blk = self.local.state()
+        return mu[lo:hi], blk
+
+
+class EmulatedShards:
+    """All shards of a ``ShardedLargeMapEKF`` job inside ONE process on ONE GPU (the exchange is a device copy
+    instead of a broadcast). Same kernels, same entry points, same per-element operation order — used by the
+    single-GPU tests to check sharded == unsharded bitwise without needing a multi-GPU box."""
+
+    def __init__(self, capacity: int, world: int, device: int = 0):
+        self.capacity, self.world = int(capacity), int(world)
+        self.ranges = row_partition(self.capacity, self.world)
+        self.shards = [eb.LargeMapEKF(self.capacity, device=device, row_range=r) for r in self.ranges]
+        self.n, self.ld = self.shards[0].n, self.shards[0].ld
+
+    def close(self):
+        for s in self.shards:
+            s.close()
+
+    def set_noise(self, mv, mm):
+        for s in self.shards:
+            s.set_noise(mv, mm)
+
+    def load(self, mean, cov):
+        for s in self.shards:
+            s.load(mean, cov)
+
+    def augment(self, slot, gx, gy):
+        for s in self.shards:
+            s.augment(slot, gx, gy)
+
+    def predict(self, ang, lin):
+        for s in self.shards:
+            s.predict(ang, lin)
+
+    def update(self, slot, rng, brg):
+        owner = owner_of_slot(slot, self.capacity, self.world)
+        bufs = [s.export_rows(slot) for s in self.shards]
+        for r, s in enumerate(self.shards):           # "broadcast": copy the owners' rows to everyone
+            if r != 0:
+                bufs[r][0:3].copy_(bufs[0][0:3])
+            if r != owner:
+                bufs[r][3:5].copy_(bufs[owner][3:5])
+        for s in self.shards:
+            s.update_from_rows(slot, rng, brg)
+
+    def state(self):
+        import numpy as np
+        mus, blks = [], []
+        for (lo, hi), s in zip(self.ranges, self.shards):
+            mu, blk = s.state()
+            mus.append(mu[lo:hi])
+            blks.append(blk)
+        return np.concatenate(mus), np.concatenate(blks, axis=0)

@@ -1,0 +1,119 @@
+"""Row-block sharding of the large-map filter: host logic on CPU (partition, owners, the
+per-update row exchange over a world_size-2 gloo group), and — on the GPU — sharded == unsharded BITWISE."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import assert_parity
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("n_lm,world", [(4096, 1), (4096, 2), (4096, 8), (32768, 8), (13, 4), (3, 8), (700, 3)])
+def test_row_partition_covers_rows_on_landmark_pairs(n_lm, world):
+    from slam_duckietown_b200.sharded import owner_of_slot, row_partition
+    parts = row_partition(n_lm, world)
+    n = 3 + 2 * n_lm
+    assert len(parts) == world and parts[0][0] == 0 and parts[-1][1] == n
+    for r, (lo, hi) in enumerate(parts):
+        assert lo <= hi
+        if r:
+            assert lo == parts[r - 1][1] and (lo - 3) % 2 == 0 and lo >= 3      # boundary on a landmark pair
+    sizes = [(hi - max(lo, 3)) // 2 for lo, hi in parts]
+    assert sum(sizes) == n_lm and max(sizes) - min(sizes) <= 1                  # near-equal blocks
+    for slot in sorted({0, n_lm - 1, n_lm // 2, n_lm // 3, min(5, n_lm - 1)}):
+        o = owner_of_slot(slot, n_lm, world)
+        lo, hi = parts[o]
+        assert lo <= 3 + 2 * slot and 4 + 2 * slot < hi                          # rows j, j+1 share the owner
+    with pytest.raises(ValueError):
+        owner_of_slot(n_lm, n_lm, world)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _gloo_worker(rank, world, port, n_lm, slots, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from slam_duckietown_b200.sharded import exchange_rows, owner_of_slot, row_partition
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    n = 3 + 2 * n_lm
+    ld = (n + 15) // 16 * 16
+    lo, hi = row_partition(n_lm, world)[rank]
+    # the "covariance" every rank could see if it owned everything; a rank only exports rows it owns
+    full = torch.arange(n * ld, dtype=torch.float64).reshape(n, ld)
+    ok = True
+    for slot in slots:
+        j = 3 + 2 * slot
+        rows5 = torch.full((5, ld + 4), -1.0 - rank, dtype=torch.float64)
+        for k, row in enumerate((0, 1, 2, j, j + 1)):
+            if lo <= row < hi:                        # what ekf_lm_export_rows does on the device
+                rows5[k, :ld] = full[row]
+                rows5[k, ld] = 1000.0 + row           # the mu entry riding along
+        exchange_rows(rows5, owner_of_slot(slot, n_lm, world))
+        for k, row in enumerate((0, 1, 2, j, j + 1)):
+            ok &= bool(torch.equal(rows5[k, :ld], full[row])) and float(rows5[k, ld]) == 1000.0 + row
+    # the bench's max-over-ranks reduction
+    t = torch.tensor([float(rank + 1)], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ok &= float(t) == float(world)
+    dist.barrier()
+    dist.destroy_process_group()
+    with open(os.path.join(out_dir, f"ok{rank}"), "w") as fh:
+        fh.write("1" if ok else "0")
+
+
+def test_row_exchange_over_gloo_world2(tmp_path):
+    """world_size 2, gloo, CPU: after the exchange every rank holds the owners' five rows and mu entries."""
+    import torch.multiprocessing as mp
+    n_lm, world = 37, 2
+    slots = [0, 5, 18, 19, 36]                        # owners 0,0,0,1,1 (19 landmarks on rank 0)
+    mp.spawn(_gloo_worker, args=(world, _free_port(), n_lm, slots, str(tmp_path)), nprocs=world, join=True)
+    assert [open(tmp_path / f"ok{r}").read() for r in range(world)] == ["1", "1"]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_sharded_equals_unsharded_bitwise(world):
+    """Every shard's block after 30 ops (updates + predicts) is bit-identical to the same rows of the single-GPU
+    filter, which is itself oracle-checked (test_gpu_parity). All shards run on this one GPU."""
+    from oracle import ekf_oracle as eo
+    from slam_duckietown_b200 import ekf_bindings as eb, workloads as wl
+    from slam_duckietown_b200.sharded import EmulatedShards
+    n_lm = 300
+    w = wl.make_large_map(n_lm, updates=30)
+    single = eb.LargeMapEKF(n_lm)
+    single.set_noise(0.1, 0.7)
+    single.load(w.mu0, w.p0())
+    sh = EmulatedShards(n_lm, world)
+    sh.set_noise(0.1, 0.7)
+    sh.load(w.mu0, w.p0())
+    m_o, c_o = w.mu0.copy(), w.p0()
+    for op in w.ops:
+        if op[0] == "update":
+            single.update(op[1], op[2], op[3])
+            sh.update(op[1], op[2], op[3])
+            eo.update_rank(m_o, c_o, op[1], op[2], op[3], 0.7)
+        else:
+            single.predict(op[1], op[2])
+            sh.predict(op[1], op[2])
+            dx, dy, th, g0, g1 = eo.motion_step(m_o[2], op[1], op[2], eo.Flags())
+            m_o[0] += dx; m_o[1] += dy; m_o[2] = th
+            eo.predict_cov_rank(c_o, g0, g1, 0.1)
+    mu1, p1 = single.state()
+    mu2, p2 = sh.state()
+    np.testing.assert_array_equal(p2, p1)
+    np.testing.assert_array_equal(mu2, mu1)
+    assert_parity(mu2, p2, m_o, c_o, what=f"sharded x{world}")
+    # every shard keeps the replicated robot pose current
+    for s in sh.shards:
+        np.testing.assert_array_equal(s.state()[0][:3], mu1[:3])
+    sh.close()
+    single.close()
