@@ -39,6 +39,14 @@ METRIC, UNIT = "EKF filter-steps/s (B=65536, 20 lm)", "filter-steps/s"
 WORKLOAD = "batched Monte Carlo replay: 65536 filters x 20 landmarks (n=43), predict + 3 updates per step"
 
 
+def make_config(joseph=False):
+    """The `config` object both arms print (same workload, same keys)."""
+    return {"workload": WORKLOAD, "filters_per_gpu": BATCH, "landmarks": NLM, "updates_per_step": M,
+            "cov_form": "joseph" if joseph else "plain (reference, replay_no_ros.py:480)",
+            "l2": "inputs larger than L2 (0.99 GB of covariance per GPU streamed every step)",
+            "sharding": "filters split across ranks, no data-path collective"}
+
+
 def measured_peak_gbs():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
@@ -149,18 +157,18 @@ def run_reference_arm(args, rank, world):
     per_step = []
     total = args.warmup + args.steps
     for i in range(total):
-        rate, cores, work, _ = cpu_filter_steps_per_s(filters_per_core=16, steps=6, form="dense", cores=cores)
+        rate, cores, work, _ = cpu_filter_steps_per_s(filters_per_core=32, steps=60, form="dense", cores=cores)
         if i >= args.warmup:
             per_step.append((rate, work))
     value = float(np.mean([r for r, _ in per_step]))
-    sample = (f"{per_step[0][1]} filter-steps per bench step (16 filters x 6 steady-state steps per core) of the "
+    sample = (f"{per_step[0][1]} filter-steps per bench step (32 filters x 60 steady-state steps per core) of the "
               f"{WORKLOAD}; dense numpy restatement of replay_no_ros.py:269-482 (oracle port; the Python reference "
               "itself cannot travel to the GPU box), one process per core, OPENBLAS_NUM_THREADS=1")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * per_step[0][1] / value, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "filters": BATCH, "landmarks": NLM, "updates_per_step": M},
+            "config": make_config(args.joseph),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -284,14 +292,112 @@ def run_own_arm(args, world):
     ok = bool(torch.isfinite(f.mu).all()) and f.fault_count() == 0
 
     # ---- end to end: host buffers in, pose out, through the C-ABI host entry point -----------------------
+    # every step: H2D of that step's pinned inputs, the fused step, D2H of every filter's pose; the pipelined
+    # entry point overlaps step i's copies with step i-1's kernel (three streams, two staging sets)
+    poses = [pose, torch.empty_like(pose).pin_memory()]
     for i in range(W):
-        f.step_host(*pinned[i % distinct], pose)
+        f.step_host_async(*pinned[i % distinct], poses[i & 1])
+    f.host_sync()
     _barrier(world)
+    t0 = time.perf_counter()
+    for i in range(K):
+        f.step_host_async(*pinned[(W + i) % distinct], poses[i & 1])
+    f.host_sync()
+    _barrier(world)
+    e2e_s = _max_over_ranks(time.perf_counter() - t0, world)
+    # the synchronous call (one step at a time, nothing overlapped), for reference
     t0 = time.perf_counter()
     for i in range(K):
         f.step_host(*pinned[(W + i) % distinct], pose)
     _barrier(world)
+    e2e_sync_s = _max_over_ranks(time.perf_counter() - t0, world)
+    ok = ok and bool(np.isfinite(poses[0].numpy()).all()) and bool(np.isfinite(poses[1].numpy()).all())
+    clk = clocks.stop() if rank == 0 else None
+    h2d = BATCH * (8 + 8 + M * (4 + 8 + 8))
+    d2h = BATCH * 3 * 8
+
+    if rank != 0:
+        return
+    peak, which = measured_peak_gbs()
+    ach = BYTES_PER_FILTER_STEP * BATCH / (kern_ms * 1e-3) / 1e9
+    value = BATCH * world * K / (total_ms * 1e-3)
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": make_config(args.joseph),
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "peak_source": which, "unit": "GB/s",
+                         "frac": ach / peak, "frac_of_8TBs": ach / 8000.0, "bytes_per_update": LM_BYTES_PER_UPDATE,
+                         "traffic": ncu_traffic("lm_rank_update_kernel"),
+                         "note": "gather + streaming kernels of one update timed together"}}
+
+
+def run_own_arm(args, world):
+    import torch
+    from slam_duckietown_b200 import capi, ekf_bindings as eb, workloads as wl
+    capi.lib()
+    rank, local = _dist_setup(world)
+    K, W = args.steps, max(args.warmup, 3)
+    distinct = min(K + W, 24)                   # distinct steady-state input sets, cycled
+    w = wl.make_batched(BATCH, NLM, M, steps=-(-NLM // M) + distinct, perturb_seed=2 + rank)
+    f = eb.BatchedEKF(BATCH, NLM, device=local)
+    f.set_noise(w.motion_var, w.meas_var)
+    f.set_flags(joseph=args.joseph)
+    f.init(0.1)
+    dev = f.dev
+
+    def up(a):
+        return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    for t in range(w.warm_steps):               # untimed: every landmark gets initialised
+        f.step(up(w.ang[t]), up(w.lin[t]), up(w.slot[t]), up(w.rng[t]), up(w.brg[t]))
+    steady = [(up(w.ang[t]), up(w.lin[t]), up(w.slot[t]), up(w.rng[t]), up(w.brg[t]))
+              for t in range(w.warm_steps, w.warm_steps + distinct)]
+    pinned = [tuple(torch.from_numpy(np.ascontiguousarray(a[t])).pin_memory()
+                    for a in (w.ang, w.lin, w.slot, w.rng, w.brg))
+              for t in range(w.warm_steps, w.warm_steps + distinct)]
+    pose = torch.empty((BATCH, 3), dtype=torch.float64).pin_memory()
+    assert f.fault_count() == 0 and int(f.n_known.min()) == NLM
+
+    # ---- device-resident timing: K launches, CUDA events on the launching stream ----------------------
+    for i in range(W):
+        f.step(*steady[i % distinct])
+    _barrier(world)
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    t_all0, t_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_all0.record()
+    for i in range(K):
+        ev[i][0].record()
+        f.step(*steady[(W + i) % distinct])
+        ev[i][1].record()
+    t_all1.record()
+    _barrier(world)
+    total_ms = _max_over_ranks(t_all0.elapsed_time(t_all1), world)
+    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    ok = bool(torch.isfinite(f.mu).all()) and f.fault_count() == 0
+
+    # ---- end to end: host buffers in, pose out, through the C-ABI host entry point -----------------------
+    # every step: H2D of that step's pinned inputs, the fused step, D2H of every filter's pose; the pipelined
+    # entry point overlaps step i's copies with step i-1's kernel (three streams, two staging sets)
+    poses = [pose, torch.empty_like(pose).pin_memory()]
+    for i in range(W):
+        f.step_host_async(*pinned[i % distinct], poses[i & 1])
+    f.host_sync()
+    _barrier(world)
+    t0 = time.perf_counter()
+    for i in range(K):
+        f.step_host_async(*pinned[(W + i) % distinct], poses[i & 1])
+    f.host_sync()
+    _barrier(world)
     e2e_s = _max_over_ranks(time.perf_counter() - t0, world)
+    # the synchronous call (one step at a time, nothing overlapped), for reference
+    t0 = time.perf_counter()
+    for i in range(K):
+        f.step_host(*pinned[(W + i) % distinct], pose)
+    _barrier(world)
+    e2e_sync_s = _max_over_ranks(time.perf_counter() - t0, world)
+    ok = ok and bool(np.isfinite(poses[0].numpy()).all()) and bool(np.isfinite(poses[1].numpy()).all())
     clk = clocks.stop() if rank == 0 else None
     h2d = BATCH * (8 + 8 + M * (4 + 8 + 8))
     d2h = BATCH * 3 * 8
@@ -310,19 +416,22 @@ def run_own_arm(args, world):
                        "sharding": "filters split across ranks, no data-path collective"},
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "peak_source": which, "unit": "GB/s",
                          "frac": ach / peak, "frac_of_8TBs": ach / 8000.0,
-                         "bytes_per_filter_step": BYTES_PER_FILTER_STEP, "kernel": "batch_step_kernel<20,128>",
+                         "bytes_per_filter_step": BYTES_PER_FILTER_STEP, "kernel": "batch_step_kernel<20,false> (one warp per filter)",
                          "kernel_ms": kern_ms, "traffic": ncu_traffic("batch_step_kernel")},
             "e2e": {"value": BATCH * world * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h,
-                    "note": "ekf_batch_step_host: pinned host odometry+observations in, fused step, robot pose "
-                            "(x,y,theta) of every filter out; filter state stays resident in HBM"},
+                    "unpipelined_value": BATCH * world * K / e2e_sync_s,
+                    "note": "ekf_batch_step_host_async + ekf_batch_host_sync: every step copies its pinned host "
+                            "odometry+observations in, runs the fused step and copies the robot pose (x,y,theta) of "
+                            "every filter out; copies of step i overlap the kernel of step i-1; filter state stays "
+                            "resident in HBM. unpipelined_value = the synchronous ekf_batch_step_host"},
             "gpu_launches": K, "clocks": clk, "finite_and_faultless": ok}
     if world == 1:
         if not args.no_cpu_baseline:
-            rate, cores, work, wall = cpu_filter_steps_per_s(filters_per_core=48, steps=12, form="dense")
+            rate, cores, work, wall = cpu_filter_steps_per_s(filters_per_core=192, steps=200, form="dense")
             line["cpu_baseline"] = {
                 "value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                "sample": f"{work} filter-steps ({cores} processes x 48 filters x 12 steady-state steps) of the same "
+                "sample": f"{work} filter-steps ({cores} processes x 192 filters x 200 steady-state steps) of the same "
                           "workload through the dense numpy restatement of replay_no_ros.py:269-482 "
                           f"(oracle port), OPENBLAS_NUM_THREADS=1, {wall:.1f} s wall"}
         if not args.no_large_map:

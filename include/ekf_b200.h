@@ -84,6 +84,13 @@ int ekf_batch_unpack(ekf_batch_t* h, double* mean_ref_dev, double* cov_ref_dev, 
 int ekf_batch_step_host(ekf_batch_t* h, const double* ang_host, const double* lin_host,
                         const int32_t* slot_host, const double* rng_host, const double* brg_host, int m,
                         double* pose_host);
+/* Pipelined form of the same call: returns once the work is enqueued; step i's H2D copies overlap step i-1's
+ * kernel and step i-2's D2H (three streams, two staging sets). Host buffers must stay valid and pose_host
+ * unread until ekf_batch_host_sync returns.                                                             */
+int ekf_batch_step_host_async(ekf_batch_t* h, const double* ang_host, const double* lin_host,
+                              const int32_t* slot_host, const double* rng_host, const double* brg_host, int m,
+                              double* pose_host);
+int ekf_batch_host_sync(ekf_batch_t* h);
 /* number of filters that saw an out-of-order new slot or a non-finite innovation since init            */
 int ekf_batch_fault_count(ekf_batch_t* h, int64_t* count);
 

@@ -51,6 +51,8 @@ SIGNATURES = {
     "ekf_batch_pack": (_i, [_p, _p, _p, _l, _l, _p]),
     "ekf_batch_unpack": (_i, [_p, _p, _p, _l, _l, _p]),
     "ekf_batch_step_host": (_i, [_p, _p, _p, _p, _p, _p, _i, _p]),
+    "ekf_batch_step_host_async": (_i, [_p, _p, _p, _p, _p, _p, _i, _p]),
+    "ekf_batch_host_sync": (_i, [_p]),
     "ekf_batch_fault_count": (_i, [_p, C.POINTER(_l)]),
     "ekf_lm_layout": (_i, [_i, C.POINTER(_i), C.POINTER(_l)]),
     "ekf_lm_create": (_i, [_i, _i, C.POINTER(_p)]),

@@ -55,6 +55,11 @@ struct ekf_batch {
   cudaStream_t stream = nullptr;
   double *d_ang = nullptr, *d_lin = nullptr, *d_rng = nullptr, *d_brg = nullptr, *d_pose = nullptr;
   int32_t* d_slot = nullptr;
+  // pipelined host entry point: copy-in / compute / copy-out streams over two staging sets
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+  double* p_stage[2] = {nullptr, nullptr};  // per set: ang | lin | rng[M] | brg[M] | pose[3] doubles, slot[M] ints
+  int64_t pipe_step = 0;
 };
 
 struct ekf_lm {
@@ -138,6 +143,14 @@ int ekf_batch_destroy(ekf_batch_t* h) {
   cudaFree(h->d_brg);
   cudaFree(h->d_slot);
   cudaFree(h->d_pose);
+  for (int i = 0; i < 2; ++i) {
+    cudaFree(h->p_stage[i]);
+    if (h->ev_in[i]) cudaEventDestroy(h->ev_in[i]);
+    if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
+    if (h->ev_out[i]) cudaEventDestroy(h->ev_out[i]);
+  }
+  if (h->s_in) cudaStreamDestroy(h->s_in);
+  if (h->s_out) cudaStreamDestroy(h->s_out);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
   return EKF_OK;
@@ -280,6 +293,75 @@ int ekf_batch_step_host(ekf_batch_t* h, const double* ang_host, const double* li
   CU(ekf::batch_launch_pose(h->mu, h->d_pose, B, h->ld, st));
   CU(cudaMemcpyAsync(pose_host, h->d_pose, B * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
+  return EKF_OK;
+}
+
+// Pipelined variant of ekf_batch_step_host: returns as soon as the work is enqueued. Step i's H2D copies run on
+// a copy-in stream while step i-1's kernel runs on the compute stream and step i-2's poses drain on a copy-out
+// stream (two staging sets, ordered by events). Host buffers must stay valid, and pose_host must not be read,
+// until ekf_batch_host_sync returns.
+int ekf_batch_step_host_async(ekf_batch_t* h, const double* ang_host, const double* lin_host,
+                              const int32_t* slot_host, const double* rng_host, const double* brg_host, int m,
+                              double* pose_host) {
+  if (!h || !ang_host || !lin_host || !pose_host) return fail(EKF_EINVAL, "null argument");
+  if (m < 0 || m > ekf::BATCH_MAX_M) return fail(EKF_EINVAL, "m must be in [0, %d]", ekf::BATCH_MAX_M);
+  if (m > 0 && (!slot_host || !rng_host || !brg_host)) return fail(EKF_EINVAL, "observation arrays are null");
+  CU(cudaSetDevice(h->device));
+  const int64_t B = h->batch;
+  const int M = ekf::BATCH_MAX_M;
+  const size_t set_doubles = (size_t)B * (2 + 2 * M + 3) + (size_t)(B * M + 1) / 2 + 4;
+  if (!h->s_in) {
+    CU(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      CU(cudaMalloc(&h->p_stage[i], set_doubles * sizeof(double)));
+      CU(cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&h->ev_out[i], cudaEventDisableTiming));
+    }
+  }
+  const int set = (int)(h->pipe_step & 1);
+  double* d_ang = h->p_stage[set];
+  double* d_lin = d_ang + B;
+  double* d_rng = d_lin + B;
+  double* d_brg = d_rng + B * M;
+  double* d_pose = d_brg + B * M;
+  int32_t* d_slot = reinterpret_cast<int32_t*>(d_pose + B * 3);
+  // copy-in: the set is free once the kernel of step i-2 (its last reader) is done
+  if (h->pipe_step >= 2) CU(cudaStreamWaitEvent(h->s_in, h->ev_done[set], 0));
+  CU(cudaMemcpyAsync(d_ang, ang_host, B * sizeof(double), cudaMemcpyHostToDevice, h->s_in));
+  CU(cudaMemcpyAsync(d_lin, lin_host, B * sizeof(double), cudaMemcpyHostToDevice, h->s_in));
+  if (m > 0) {
+    CU(cudaMemcpyAsync(d_slot, slot_host, B * m * sizeof(int32_t), cudaMemcpyHostToDevice, h->s_in));
+    CU(cudaMemcpyAsync(d_rng, rng_host, B * m * sizeof(double), cudaMemcpyHostToDevice, h->s_in));
+    CU(cudaMemcpyAsync(d_brg, brg_host, B * m * sizeof(double), cudaMemcpyHostToDevice, h->s_in));
+  }
+  CU(cudaEventRecord(h->ev_in[set], h->s_in));
+  // compute: after this step's inputs have landed and the pose buffer of step i-2 has drained
+  CU(cudaStreamWaitEvent(h->stream, h->ev_in[set], 0));
+  if (h->pipe_step >= 2) CU(cudaStreamWaitEvent(h->stream, h->ev_out[set], 0));
+  int rc = ekf_batch_step(h, d_ang, d_lin, d_slot, d_rng, d_brg, m, h->stream);
+  if (rc != EKF_OK) return rc;
+  CU(ekf::batch_launch_pose(h->mu, d_pose, B, h->ld, h->stream));
+  CU(cudaEventRecord(h->ev_done[set], h->stream));
+  // copy-out
+  CU(cudaStreamWaitEvent(h->s_out, h->ev_done[set], 0));
+  CU(cudaMemcpyAsync(pose_host, d_pose, B * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->s_out));
+  CU(cudaEventRecord(h->ev_out[set], h->s_out));
+  ++h->pipe_step;
+  return EKF_OK;
+}
+
+int ekf_batch_host_sync(ekf_batch_t* h) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  CU(cudaSetDevice(h->device));
+  if (h->s_in) {
+    CU(cudaStreamSynchronize(h->s_in));
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaStreamSynchronize(h->s_out));
+  } else if (h->stream) {
+    CU(cudaStreamSynchronize(h->stream));
+  }
   return EKF_OK;
 }
 

@@ -312,6 +312,19 @@ class BatchedEKF:
         capi.call("ekf_batch_step_host", self._h, hp(ang), hp(lin), hp(slot) if m else z, hp(rng) if m else z,
                   hp(brg) if m else z, m, hp(pose_out))
 
+    def step_host_async(self, ang, lin, slot, rng, brg, pose_out):
+        """Pipelined ``step_host``: enqueue only. Keep the (pinned) host buffers alive and do not read
+        ``pose_out`` until ``host_sync()``; consecutive calls overlap H2D, the fused step and D2H."""
+        def hp(a):
+            return C.c_void_p(a.data_ptr() if hasattr(a, "data_ptr") else a.ctypes.data)
+        m = 0 if slot is None else int(slot.shape[1])
+        z = C.c_void_p(0)
+        capi.call("ekf_batch_step_host_async", self._h, hp(ang), hp(lin), hp(slot) if m else z,
+                  hp(rng) if m else z, hp(brg) if m else z, m, hp(pose_out))
+
+    def host_sync(self):
+        capi.call("ekf_batch_host_sync", self._h)
+
     def load(self, mean: np.ndarray, cov: np.ndarray, first: int = 0):
         """Upload reference-layout states: mean (k, n), cov (k, n, n) -> filters [first, first+k)."""
         t = self.torch
