@@ -26,66 +26,13 @@
 //            a lane keeping W_u of its 4 columns in registers, streamed to HBM with coalesced 128-bit stores.
 // Rows and columns are both gathered for real — (P H^T)^T is never used for H P.
 #include "ekf_batched.h"
-#include "ekf_common.cuh"
+#include "ekf_batched_dev.cuh"
 
 namespace ekf {
 
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\n"
-      "bra WAIT_%=;\n"
-      "DONE_%=:\n"
-      "}\n" ::"r"(smem_u32(bar)), "r"(parity)
-      : "memory");
-}
-// 1-D TMA bulk copy global -> shared, completion signalled on the mbarrier (SASS: UBLKCP)
-__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                   smem_u32(dst)),
-               "l"(src), "r"(bytes), "r"(smem_u32(bar))
-               : "memory");
-}
-
-// one rank-2 (plain) step on a single element; the SAME sequence is used wherever an entry of an
-// intermediate P_u is needed, so phase 2's rebuilt rows/columns equal what phase 3 finally writes.
-__device__ __forceinline__ double rank2(double v, double k0, double k1, double w0, double w1) {
-  return fma(-k1, w1, fma(-k0, w0, v));
-}
-__device__ __forceinline__ void rank2x4(double4x& p, double k0, double k1, const double4x& w0,
-                                        const double4x& w1) {
-  p.a = rank2(p.a, k0, k1, w0.a, w1.a);
-  p.b = rank2(p.b, k0, k1, w0.b, w1.b);
-  p.c = rank2(p.c, k0, k1, w0.c, w1.c);
-  p.d = rank2(p.d, k0, k1, w0.d, w1.d);
-}
-
-constexpr int kTailDoubles = 4;  // mbarrier
-constexpr unsigned kFull = 0xffffffffu;
-
-struct __align__(16) d2 {
-  double x, y;
-};
-__device__ __forceinline__ double4x lds256(const double* p) { return *reinterpret_cast<const double4x*>(p); }
-__device__ __forceinline__ d2 lds128(const double* p) { return *reinterpret_cast<const d2*>(p); }
-__device__ __forceinline__ void stg128(double* p, const d2& v) {
-  asm volatile("st.global.v2.f64 [%0], {%1,%2};" ::"l"(p), "d"(v.x), "d"(v.y) : "memory");
-}
-
-template <int NLM, bool JOSEPH>
+// MT = number of observation slots per filter-step when known at compile time (the update loops unroll and the
+// per-update validity tests become predicates), 0 = read it from the arguments.
+template <int NLM, bool JOSEPH, int MT>
 __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
@@ -97,7 +44,7 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
   double* sP = reinterpret_cast<double*>(smem_raw);  // [N][LD]
   double* sMu = sP + N * LD;                         // [LD]
   double* sK = sMu + LD;                             // [m][LD][2]  (K_u[i,0], K_u[i,1]) pairs
-  const int m = a.m;
+  const int m = MT ? MT : a.m;
   double* sW = sK + m * HIST;                        // [m][2][LD]  W_u[0,:] then W_u[1,:]
   double* sA = sW + m * HIST;                        // [m][LD][2]  AHt_u pairs (Joseph only)
   uint64_t* bar = reinterpret_cast<uint64_t*>(JOSEPH ? sA + m * HIST : sA);
@@ -466,18 +413,26 @@ size_t batch_step_smem_bytes(int n_landmarks, int m, bool joseph) {
   return d * sizeof(double);
 }
 
-template <int NLM, bool JOSEPH>
-static cudaError_t launch_step_t(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+template <int NLM, bool JOSEPH, int MT>
+static cudaError_t launch_step_mt(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
   const size_t smem = batch_step_smem_bytes(NLM, a.m, JOSEPH);
-  cudaError_t e = cudaFuncSetAttribute(batch_step_kernel<NLM, JOSEPH>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  auto kernel = batch_step_kernel<NLM, JOSEPH, MT>;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   // as many one-warp CTAs per SM as shared memory allows (11 at n = 43, m = 3)
-  e = cudaFuncSetAttribute(batch_step_kernel<NLM, JOSEPH>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                           cudaSharedmemCarveoutMaxShared);
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   if (e != cudaSuccess) return e;
-  batch_step_kernel<NLM, JOSEPH><<<(unsigned)batch, 32, smem, st>>>(a);
+  kernel<<<(unsigned)batch, 32, smem, st>>>(a);
   return cudaGetLastError();
+}
+
+template <int NLM, bool JOSEPH>
+static cudaError_t launch_step_t(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+  switch (a.m) {  // the common observation counts get unrolled update loops
+    case 2: return launch_step_mt<NLM, JOSEPH, 2>(a, batch, st);
+    case 3: return launch_step_mt<NLM, JOSEPH, 3>(a, batch, st);
+    default: return launch_step_mt<NLM, JOSEPH, 0>(a, batch, st);
+  }
 }
 
 bool batch_capacity_supported(int n_landmarks) {

@@ -30,6 +30,9 @@ bool batch_capacity_supported(int n_landmarks);
 size_t batch_step_smem_bytes(int n_landmarks, int m, bool joseph);
 cudaError_t batch_launch_step(int n_landmarks, const BatchStepArgs& a, int64_t batch, bool joseph,
                               cudaStream_t st);
+// streaming variant (ekf_batched_stream.cu): stages only the touched rows/columns; plain covariance form
+size_t batch_stream_smem_bytes(int n_landmarks, int m);
+cudaError_t batch_launch_step_stream(int n_landmarks, const BatchStepArgs& a, int64_t batch, cudaStream_t st);
 cudaError_t batch_launch_init(double* mu, double* P, int* n_known, int64_t batch, int n, int ld, double p0,
                               cudaStream_t st);
 cudaError_t batch_launch_pack(double* mu, double* P, const double* mean_ref, const double* cov_ref,

@@ -50,6 +50,7 @@ struct ekf_batch {
   int32_t* n_known = nullptr;
   const double *mv = nullptr, *mm = nullptr;
   int flags = ekf::kFlagCircular | ekf::kFlagMeasurement;
+  int kernel = 0;  // 0 = fully staged (default, faster), 1 = streaming (touched rows/columns staged); EKF_BATCH_KERNEL=staged|stream
   unsigned long long* faults = nullptr;
   // staging for the host-buffer entry point
   cudaStream_t stream = nullptr;
@@ -122,6 +123,7 @@ int ekf_batch_create(int n_landmarks, int64_t batch, int device, ekf_batch_t** o
   h->ld = (h->n + 3) & ~3;
   h->device = device;
   h->batch = batch;
+  if (const char* k = getenv("EKF_BATCH_KERNEL")) h->kernel = (strcmp(k, "stream") == 0) ? 1 : 0;
   cudaError_t e = cudaMalloc(&h->faults, sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaMemset(h->faults, 0, sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
@@ -203,7 +205,11 @@ static int batch_step_common(ekf_batch_t* h, ekf::BatchStepArgs& a, int m, void*
   a.m = m;
   a.flags = h->flags;
   CU(cudaSetDevice(h->device));
-  CU(ekf::batch_launch_step(h->nlm, a, h->batch, (h->flags & ekf::kFlagJoseph) != 0, (cudaStream_t)stream));
+  const bool joseph = (h->flags & ekf::kFlagJoseph) != 0;
+  if (!joseph && h->kernel == 1)
+    CU(ekf::batch_launch_step_stream(h->nlm, a, h->batch, (cudaStream_t)stream));
+  else
+    CU(ekf::batch_launch_step(h->nlm, a, h->batch, joseph, (cudaStream_t)stream));
   return EKF_OK;
 }
 
