@@ -324,92 +324,6 @@ def run_own_arm(args, world):
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": make_config(args.joseph),
-            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "peak_source": which, "unit": "GB/s",
-                         "frac": ach / peak, "frac_of_8TBs": ach / 8000.0, "bytes_per_update": LM_BYTES_PER_UPDATE,
-                         "traffic": ncu_traffic("lm_rank_update_kernel"),
-                         "note": "gather + streaming kernels of one update timed together"}}
-
-
-def run_own_arm(args, world):
-    import torch
-    from slam_duckietown_b200 import capi, ekf_bindings as eb, workloads as wl
-    capi.lib()
-    rank, local = _dist_setup(world)
-    K, W = args.steps, max(args.warmup, 3)
-    distinct = min(K + W, 24)                   # distinct steady-state input sets, cycled
-    w = wl.make_batched(BATCH, NLM, M, steps=-(-NLM // M) + distinct, perturb_seed=2 + rank)
-    f = eb.BatchedEKF(BATCH, NLM, device=local)
-    f.set_noise(w.motion_var, w.meas_var)
-    f.set_flags(joseph=args.joseph)
-    f.init(0.1)
-    dev = f.dev
-
-    def up(a):
-        return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
-    for t in range(w.warm_steps):               # untimed: every landmark gets initialised
-        f.step(up(w.ang[t]), up(w.lin[t]), up(w.slot[t]), up(w.rng[t]), up(w.brg[t]))
-    steady = [(up(w.ang[t]), up(w.lin[t]), up(w.slot[t]), up(w.rng[t]), up(w.brg[t]))
-              for t in range(w.warm_steps, w.warm_steps + distinct)]
-    pinned = [tuple(torch.from_numpy(np.ascontiguousarray(a[t])).pin_memory()
-                    for a in (w.ang, w.lin, w.slot, w.rng, w.brg))
-              for t in range(w.warm_steps, w.warm_steps + distinct)]
-    pose = torch.empty((BATCH, 3), dtype=torch.float64).pin_memory()
-    assert f.fault_count() == 0 and int(f.n_known.min()) == NLM
-
-    # ---- device-resident timing: K launches, CUDA events on the launching stream ----------------------
-    for i in range(W):
-        f.step(*steady[i % distinct])
-    _barrier(world)
-    clocks = ClockSampler(local)
-    if rank == 0:
-        clocks.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    t_all0, t_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t_all0.record()
-    for i in range(K):
-        ev[i][0].record()
-        f.step(*steady[(W + i) % distinct])
-        ev[i][1].record()
-    t_all1.record()
-    _barrier(world)
-    total_ms = _max_over_ranks(t_all0.elapsed_time(t_all1), world)
-    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
-    ok = bool(torch.isfinite(f.mu).all()) and f.fault_count() == 0
-
-    # ---- end to end: host buffers in, pose out, through the C-ABI host entry point -----------------------
-    # every step: H2D of that step's pinned inputs, the fused step, D2H of every filter's pose; the pipelined
-    # entry point overlaps step i's copies with step i-1's kernel (three streams, two staging sets)
-    poses = [pose, torch.empty_like(pose).pin_memory()]
-    for i in range(W):
-        f.step_host_async(*pinned[i % distinct], poses[i & 1])
-    f.host_sync()
-    _barrier(world)
-    t0 = time.perf_counter()
-    for i in range(K):
-        f.step_host_async(*pinned[(W + i) % distinct], poses[i & 1])
-    f.host_sync()
-    _barrier(world)
-    e2e_s = _max_over_ranks(time.perf_counter() - t0, world)
-    # the synchronous call (one step at a time, nothing overlapped), for reference
-    t0 = time.perf_counter()
-    for i in range(K):
-        f.step_host(*pinned[(W + i) % distinct], pose)
-    _barrier(world)
-    e2e_sync_s = _max_over_ranks(time.perf_counter() - t0, world)
-    ok = ok and bool(np.isfinite(poses[0].numpy()).all()) and bool(np.isfinite(poses[1].numpy()).all())
-    clk = clocks.stop() if rank == 0 else None
-    h2d = BATCH * (8 + 8 + M * (4 + 8 + 8))
-    d2h = BATCH * 3 * 8
-
-    if rank != 0:
-        return
-    peak, which = measured_peak_gbs()
-    ach = BYTES_PER_FILTER_STEP * BATCH / (kern_ms * 1e-3) / 1e9
-    value = BATCH * world * K / (total_ms * 1e-3)
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOAD, "filters_per_gpu": BATCH, "landmarks": NLM, "updates_per_step": M,
                        "cov_form": "joseph" if args.joseph else "plain (reference, replay_no_ros.py:480)",
                        "l2": "inputs larger than L2 (0.99 GB of covariance per GPU streamed every step)",

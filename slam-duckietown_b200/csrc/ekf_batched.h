@@ -33,6 +33,10 @@ cudaError_t batch_launch_step(int n_landmarks, const BatchStepArgs& a, int64_t b
 // streaming variant (ekf_batched_stream.cu): stages only the touched rows/columns; plain covariance form
 size_t batch_stream_smem_bytes(int n_landmarks, int m);
 cudaError_t batch_launch_step_stream(int n_landmarks, const BatchStepArgs& a, int64_t batch, cudaStream_t st);
+// W-in-registers variant (ekf_batched_regw.cu): plain covariance form, 1 <= m <= 4 observation slots
+bool batch_regw_supported(int m);
+size_t batch_regw_smem_bytes(int n_landmarks, int m);
+cudaError_t batch_launch_step_regw(int n_landmarks, const BatchStepArgs& a, int64_t batch, cudaStream_t st);
 cudaError_t batch_launch_init(double* mu, double* P, int* n_known, int64_t batch, int n, int ld, double p0,
                               cudaStream_t st);
 cudaError_t batch_launch_pack(double* mu, double* P, const double* mean_ref, const double* cov_ref,

@@ -1,0 +1,457 @@
+// ekf_batched_regw.cu — fused EKF-SLAM filter-step, one warp per filter, W-IN-REGISTERS variant (sm_100a, fp64).
+//
+// Same reference semantics (src/replay_no_ros.py:341-480) and the same per-element operation sequence as
+// batch_step_kernel (ekf_batched.cu), so results are bitwise equal; what changes is where the step's small
+// operands live. Round-1 ncu of the staged kernel (profiles/r1f_batch.*): shared-memory pipe 76 % busy, issue
+// slots 41 %, 11 resident warps per SM limited by 19.7 KB of shared memory per filter. Here
+//   * lane t owns COLUMN t (and t + 32) of P in every phase, so W_u[:, t] = (H P)[:, t] and K_u[t, :] are
+//     produced in the registers of the lane that consumes them: the W history never touches shared memory
+//     (2.1 KB less per filter -> 12 resident warps), only K_u is stored (phase 3 broadcasts it per row);
+//   * the robot rows/columns {0,1,2}, which every update touches, stay in registers across the predict and
+//     all updates and are brought up to date ONCE per update instead of being re-gathered (8-way bank
+//     conflicted column reads) and rebuilt from P0 every time;
+//   * the uniform operands an update needs from other lanes (W_w[:, j], the five S entries) travel by
+//     warp shuffle;
+//   * phase 3 packs the 12-column tail of TWO rows into one instruction (lanes 0-11 / 12-23).
+// Plain covariance form with a compile-time observation count only; everything else runs on batch_step_kernel.
+#include "ekf_batched.h"
+#include "ekf_batched_dev.cuh"
+
+namespace ekf {
+
+namespace {
+
+// value of column c (warp-uniform) from the lane that owns it: x[0] covers columns 0-31, x[1] columns 32-63
+template <int NT>
+__device__ __forceinline__ double col_bcast(const double (&x)[NT], int c) {
+  // c is warp-uniform: every lane offers its value of the half that holds column c, lane c % 32 is read
+  const double mine = (NT > 1 && c >= 32) ? x[NT > 1 ? 1 : 0] : x[0];
+  return __shfl_sync(kFull, mine, c & 31);
+}
+
+// Phase-3 worker: NPQ row pairs starting at row r0 (sp = sP + r0 LD, sk = sK + 2 r0, gp = gP + r0 LD). Every
+// bound is a compile-time constant, so loads/stores carry immediate offsets and no predicates besides the tail's.
+// Main part: lane = column (W of it in mw0/mw1); tail: columns 32.. of row (2q + half), W of them in tw0/tw1.
+// ODD: the last pair has only its first row. PACK: both rows' tails in one instruction (lanes [0,T) / [T,2T)).
+template <int LD, int HIST, int M, int NPQ, bool ODD, bool PACK>
+__device__ __forceinline__ void regw_stream_pairs(const double* __restrict__ sp, const double* __restrict__ sk,
+                                                  double* __restrict__ gp, const double (&mw0)[M],
+                                                  const double (&mw1)[M], const double (&tw0)[M],
+                                                  const double (&tw1)[M], unsigned valid, int lane, int half,
+                                                  int tcol, bool tact) {
+  double va[NPQ], vb[NPQ], vt[NPQ], vs[PACK ? 1 : NPQ];
+  const int toff = half * LD + tcol;  // tail element of this lane within a row pair
+#pragma unroll
+  for (int q = 0; q < NPQ; ++q) {
+    const bool two = !(ODD && q == NPQ - 1);
+    va[q] = sp[2 * q * LD + lane];
+    if (two) vb[q] = sp[(2 * q + 1) * LD + lane];
+    if (tact && (two || !half)) vt[q] = sp[2 * q * LD + toff];
+    if (!PACK && two && tact) vs[q] = sp[(2 * q + 1) * LD + tcol];
+  }
+#pragma unroll
+  for (int u = 0; u < M; ++u) {
+    if (!((valid >> u) & 1u)) continue;
+    const double* ku = sk + u * HIST;
+#pragma unroll
+    for (int q = 0; q < NPQ; ++q) {
+      const bool two = !(ODD && q == NPQ - 1);
+      const d2 ka = lds128(ku + 4 * q);
+      const d2 kt = PACK ? lds128(ku + 4 * q + 2 * half) : ka;  // K of the row this lane's tail element is in
+      va[q] = rank2(va[q], ka.x, ka.y, mw0[u], mw1[u]);
+      vt[q] = rank2(vt[q], kt.x, kt.y, tw0[u], tw1[u]);
+      if (two) {
+        const d2 kb = lds128(ku + 4 * q + 2);
+        vb[q] = rank2(vb[q], kb.x, kb.y, mw0[u], mw1[u]);
+        if (!PACK) vs[q] = rank2(vs[q], kb.x, kb.y, tw0[u], tw1[u]);
+      }
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < NPQ; ++q) {
+    const bool two = !(ODD && q == NPQ - 1);
+    gp[2 * q * LD + lane] = va[q];
+    if (two) gp[(2 * q + 1) * LD + lane] = vb[q];
+    if (tact && (two || !half)) gp[2 * q * LD + toff] = vt[q];
+    if (!PACK && two && tact) gp[(2 * q + 1) * LD + tcol] = vs[q];
+  }
+}
+
+}  // namespace
+
+template <int NLM, int MT>
+__global__ void __launch_bounds__(32) batch_step_regw_kernel(BatchStepArgs a) {
+  constexpr int N = 3 + 2 * NLM;
+  constexpr int LD = (N + 3) & ~3;
+  constexpr int HIST = 2 * LD;        // doubles of one update's K record: [LD][2]
+  constexpr int NT = (LD + 31) / 32;  // lane t handles indices t, t + 32
+  constexpr int m = MT;
+  static_assert(NT <= 2, "lane owns at most two columns");
+  static_assert(MT >= 1 && MT <= BATCH_MAX_M, "observation count");
+
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double* sP = reinterpret_cast<double*>(smem_raw);  // [N][LD]
+  double* sMu = sP + N * LD;                         // [LD]
+  double* sK = sMu + LD;                             // [m][LD][2]  (K_u[i,0], K_u[i,1]) pairs
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sK + m * HIST);  // [2]: mu, P
+
+  const int lane = threadIdx.x;
+  const int64_t b = blockIdx.x;
+  double* __restrict__ gP = a.P + b * (int64_t)(N * LD);
+  double* __restrict__ gMu = a.mu + b * (int64_t)LD;
+
+  // ---- phase 0: TMA bulk load + per-filter inputs --------------------------------------------------
+  // mu arrives on its own mbarrier: the scalar part of phase 1 (sincos, augment, motion model) runs while the
+  // 15 KB of P are still in flight
+  if (lane == 0) {
+    mbar_init(bar, 1);
+    mbar_init(bar + 1, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_expect_tx(bar, (uint32_t)(LD * sizeof(double)));
+    tma_bulk_g2s(sMu, gMu, (uint32_t)(LD * sizeof(double)), bar);
+    mbar_expect_tx(bar + 1, (uint32_t)(N * LD * sizeof(double)));
+    tma_bulk_g2s(sP, gP, (uint32_t)(N * LD * sizeof(double)), bar + 1);
+  }
+  double ang, lin;
+  if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
+    const double dl = delta_phi(a.ticks_l[b], a.prev_l[b], a.resolution);
+    const double dr = delta_phi(a.ticks_r[b], a.prev_r[b], a.resolution);
+    displacement(a.wheel_radius, a.baseline, dl, dr, &ang, &lin);
+  } else {
+    ang = a.ang[b];
+    lin = a.lin[b];
+  }
+  const double mv = a.motion_var[b];
+  const double mm = a.meas_var[b];
+  const double qn = mm * mm;
+  int nk = a.n_known[b];
+  double o_rng = 0.0, o_brg = 0.0;  // observation u lives in lane u
+  int o_slot = -1;
+  if (lane < m) {
+    o_slot = a.slot[b * m + lane];
+    o_rng = a.rng[b * m + lane];
+    o_brg = a.brg[b * m + lane];
+  }
+  __syncwarp();
+  mbar_wait(bar, 0);
+
+  // robot rows / columns of the CURRENT covariance, lane t: rr[k][p] = P[k][t], rc[k][p] = P[t][k], t = lane + 32 p
+  double rr[3][NT], rc[3][NT];
+
+  // ---- phase 1: augment (:355-360) + motion model (:368-417), warp-uniform ---------------------------
+  unsigned valid = 0;   // bit u: update u is applied
+  unsigned fresh = 0;   // bit u: update u is the first sighting of its landmark
+  int sl[m];            // slot of observation u (warp-uniform)
+  {
+    const double px = sMu[0], py = sMu[1], pth = sMu[2];
+    double sn, cs;  // even lanes sincos(theta), odd lanes sincos(theta + ang): one call instead of two
+    sincos((lane & 1) ? pth + ang : pth, &sn, &cs);
+    const double s1 = __shfl_sync(kFull, sn, 0), c1 = __shfl_sync(kFull, cs, 0);
+    const double s2 = __shfl_sync(kFull, sn, 1), c2 = __shfl_sync(kFull, cs, 1);
+    int fault = 0;
+#pragma unroll
+    for (int u = 0; u < m; ++u) {
+      const int s = __shfl_sync(kFull, o_slot, u);
+      sl[u] = s;
+      if (s < 0) continue;
+      if (s >= NLM || s > nk) {  // beyond capacity, or a slot that skips first-seen order (:359 KeyError)
+        fault = 1;
+        continue;
+      }
+      valid |= 1u << u;
+      if (s == nk) {  // first sighting: initialise from the PRE-predict pose (:331-332, :359-360)
+        const int j = 3 + 2 * s;
+        const double r = __shfl_sync(kFull, o_rng, u), be = __shfl_sync(kFull, o_brg, u);
+        double sb, cb;
+        sincos(be + pth, &sb, &cb);
+        if (lane == 0) {
+          sMu[j] = px + r * cb;
+          sMu[j + 1] = py + r * sb;
+        }
+        fresh |= 1u << u;
+        ++nk;
+      }
+    }
+    if (!(a.flags & kFlagMeasurement)) valid = 0;
+    const Motion mo = motion_from_sincos(pth, ang, lin, a.flags, s1, c1, s2, c2);
+    if (lane == 0) {
+      sMu[0] = px + mo.dx;
+      sMu[1] = py + mo.dy;
+      sMu[2] = mo.theta;
+      a.n_known[b] = nk;
+      if (fault) atomicAdd(a.faults, 1ULL);
+    }
+    mbar_wait(bar + 1, 0);
+    if (fresh && lane == 0) {  // new landmarks' diagonals (:356-357)
+#pragma unroll
+      for (int u = 0; u < m; ++u)
+        if ((fresh >> u) & 1u) {
+          const int j = 3 + 2 * sl[u];
+          sP[j * LD + j] = kNewLandmarkVar;
+          sP[(j + 1) * LD + j + 1] = kNewLandmarkVar;
+        }
+    }
+    __syncwarp();
+    // predict covariance (:420-430): rows 0-1 += g * row 2 over ALL columns, then columns 0-1 += g * column 2
+    // over ALL rows (using the updated rows 0-1), then the three noise terms. Shared memory keeps the result
+    // (phase 3 reads it); the robot rows/columns also stay in registers.
+    const double g0 = mo.g0, g1 = mo.g1;
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      const int t = lane + 32 * p;
+      rr[0][p] = rr[1][p] = rr[2][p] = 0.0;
+      if (t < N) {
+        const double p2 = sP[2 * LD + t];
+        rr[0][p] = sP[0 * LD + t] + g0 * p2;
+        rr[1][p] = sP[1 * LD + t] + g1 * p2;
+        rr[2][p] = p2;
+        sP[0 * LD + t] = rr[0][p];
+        sP[1 * LD + t] = rr[1][p];
+      }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      const int i = lane + 32 * p;
+      rc[0][p] = rc[1][p] = rc[2][p] = 0.0;
+      if (i < N) {
+        double* row = sP + i * LD;
+        const d2 r01 = lds128(row);
+        const double p2 = row[2];
+        double r0 = r01.x + g0 * p2, r1 = r01.y + g1 * p2, r2 = p2;
+        if (i == 0) r0 += mv * mv;  // F^T R F (:421-430)
+        if (i == 1) r1 += mv * mv;
+        if (i == 2) r2 = p2 + (mv / 2.0) * (mv / 2.0);
+        d2 o;
+        o.x = r0; o.y = r1;
+        *reinterpret_cast<d2*>(row) = o;
+        if (i == 2) row[2] = r2;
+        rc[0][p] = r0; rc[1][p] = r1; rc[2][p] = r2;
+      }
+    }
+    __syncwarp();
+    if (lane < 3) {  // the 3x3 robot block was changed by the column pass: refresh the row registers
+      rr[0][0] = sP[0 * LD + lane];
+      rr[1][0] = sP[1 * LD + lane];
+      rr[2][0] = sP[2 * LD + lane];
+    }
+  }
+
+  // ---- phase 2: sequential updates on the touched rows / columns only --------------------------------
+  // history in registers: hW[u][.][p] = W_u[:, t], hK[u][p] = K_u[t, :] of this lane's t = lane + 32 p
+  double hW0[m][NT], hW1[m][NT];
+  d2 hK[m][NT];
+#pragma unroll
+  for (int u = 0; u < m; ++u) {
+    if (!((valid >> u) & 1u)) continue;  // warp-uniform
+    const double z_rng = __shfl_sync(kFull, o_rng, u), z_brg = __shfl_sync(kFull, o_brg, u);
+    const int j = 3 + 2 * sl[u];
+    // (a) innovation and H5 (:443-469), warp-uniform
+    const Innov in = innovation(sMu[0], sMu[1], sMu[2], sMu[j], sMu[j + 1], z_rng, z_brg);
+    // (b) landmark rows / columns j, j+1 from the staged P0, brought up to date with the earlier updates
+    double lr[2][NT], lc[2][NT];
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      const int t = lane + 32 * p;
+      const bool inld = (t < LD), real = (t < N);
+      lr[0][p] = inld ? sP[j * LD + t] : 0.0;
+      lr[1][p] = inld ? sP[(j + 1) * LD + t] : 0.0;
+      lc[0][p] = real ? sP[t * LD + j] : 0.0;
+      lc[1][p] = real ? sP[t * LD + j + 1] : 0.0;
+    }
+#pragma unroll
+    for (int w = 0; w < m - 1; ++w) {  // static trip count keeps the register history statically indexed
+      if (w >= u || !((valid >> w) & 1u)) continue;
+      const d2 kj0 = lds128(sK + w * HIST + 2 * j), kj1 = lds128(sK + w * HIST + 2 * j + 2);
+      const double w0j0 = col_bcast<NT>(hW0[w], j), w1j0 = col_bcast<NT>(hW1[w], j);
+      const double w0j1 = col_bcast<NT>(hW0[w], j + 1), w1j1 = col_bcast<NT>(hW1[w], j + 1);
+#pragma unroll
+      for (int p = 0; p < NT; ++p) {
+        lr[0][p] = rank2(lr[0][p], kj0.x, kj0.y, hW0[w][p], hW1[w][p]);
+        lr[1][p] = rank2(lr[1][p], kj1.x, kj1.y, hW0[w][p], hW1[w][p]);
+        lc[0][p] = rank2(lc[0][p], hK[w][p].x, hK[w][p].y, w0j0, w1j0);
+        lc[1][p] = rank2(lc[1][p], hK[w][p].x, hK[w][p].y, w0j1, w1j1);
+      }
+    }
+    // (c) H P (rows) and P H^T (columns) for this lane's t, accumulated in idx5 order
+    double pht0[NT], pht1[NT];
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      double a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const double vr = (k < 3) ? rr[k < 3 ? k : 0][p] : lr[k < 3 ? 0 : k - 3][p];
+        const double vc = (k < 3) ? rc[k < 3 ? k : 0][p] : lc[k < 3 ? 0 : k - 3][p];
+        a0 = fma(in.h[0][k], vr, a0);
+        a1 = fma(in.h[1][k], vr, a1);
+        b0 = fma(vc, in.h[0][k], b0);
+        b1 = fma(vc, in.h[1][k], b1);
+      }
+      hW0[u][p] = a0; hW1[u][p] = a1; pht0[p] = b0; pht1[p] = b1;
+    }
+    // (d) S = (H P) H^T + Q from the five entries idx5 of H P (:473), closed-form inverse; warp-uniform
+    double x0[5], x1[5];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      x0[c] = __shfl_sync(kFull, hW0[u][0], c);
+      x1[c] = __shfl_sync(kFull, hW1[u][0], c);
+    }
+    x0[3] = col_bcast<NT>(hW0[u], j);     x1[3] = col_bcast<NT>(hW1[u], j);
+    x0[4] = col_bcast<NT>(hW0[u], j + 1); x1[4] = col_bcast<NT>(hW1[u], j + 1);
+    double S[2][2], Si[2][2];
+    {
+      double acc00 = 0.0, acc01 = 0.0, acc10 = 0.0, acc11 = 0.0;
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        acc00 = fma(x0[c], in.h[0][c], acc00);
+        acc01 = fma(x0[c], in.h[1][c], acc01);
+        acc10 = fma(x1[c], in.h[0][c], acc10);
+        acc11 = fma(x1[c], in.h[1][c], acc11);
+      }
+      S[0][0] = acc00 + qn; S[0][1] = acc01; S[1][0] = acc10; S[1][1] = acc11 + qn;
+    }
+    inv2(S, Si);
+    // (e) K_u = P H^T S^-1 (:473), mu += K_u y (:476)
+    double* ku = sK + u * HIST;
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      const int t = lane + 32 * p;
+      d2 kk;
+      kk.x = pht0[p] * Si[0][0] + pht1[p] * Si[1][0];
+      kk.y = pht0[p] * Si[0][1] + pht1[p] * Si[1][1];
+      hK[u][p] = kk;  // zero for the pad row and beyond
+      if (t < LD) {
+        *reinterpret_cast<d2*>(ku + 2 * t) = kk;
+        if (t < N) sMu[t] += kk.x * in.y0 + kk.y * in.y1;
+      }
+    }
+    __syncwarp();
+    // (f) bring the robot rows / columns up to date for the next update
+    if (u + 1 < m) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const d2 kr = lds128(ku + 2 * k);
+#pragma unroll
+        for (int p = 0; p < NT; ++p) {
+          rr[k][p] = rank2(rr[k][p], kr.x, kr.y, hW0[u][p], hW1[u][p]);
+          rc[k][p] = rank2(rc[k][p], hK[u][p].x, hK[u][p].y, x0[k], x1[k]);
+        }
+      }
+    }
+  }
+
+  // ---- phase 3: one pass over P, all updates applied in order, streamed to HBM -------------------------
+  // Lane t: column t of every row (W_u[:, t] in registers); the tail columns 32..LD-1 of rows r and r+1 are
+  // handled together by lanes [0, TAIL) and [TAIL, 2 TAIL). K_u of a row is one broadcast 128-bit load.
+  if constexpr (NT == 2) {
+    constexpr int TAIL = LD - 32;
+    constexpr bool PACK = (2 * TAIL <= 32);             // both tails of a row pair in one instruction
+    const int half = (PACK && lane >= TAIL) ? 1 : 0;   // which row of the pair this lane's tail element is in
+    const int tcol = 32 + lane - half * TAIL;          // its column
+    const bool tact = lane < (PACK ? 2 * TAIL : TAIL);
+    double tW0[m], tW1[m];
+#pragma unroll
+    for (int u = 0; u < m; ++u) {
+      tW0[u] = __shfl_sync(kFull, hW0[u][1], lane - half * TAIL);
+      tW1[u] = __shfl_sync(kFull, hW1[u][1], lane - half * TAIL);
+    }
+    double mW0[m], mW1[m];
+#pragma unroll
+    for (int u = 0; u < m; ++u) {
+      mW0[u] = hW0[u][0];
+      mW1[u] = hW1[u][0];
+    }
+    constexpr int CH = 4;  // row PAIRS in registers per lane
+    constexpr int NPAIR = (N + 1) / 2;  // N is odd: the last pair holds one row
+    constexpr int REM = (NPAIR % CH == 0) ? CH : NPAIR % CH;
+    constexpr int MAINCH = (NPAIR - REM) / CH;
+    const double* sp = sP;
+    const double* sk = sK;
+    double* gp = gP;
+#pragma unroll 1
+    for (int c = 0; c < MAINCH; ++c) {
+      regw_stream_pairs<LD, HIST, m, CH, false, PACK>(sp, sk, gp, mW0, mW1, tW0, tW1, valid, lane, half, tcol, tact);
+      sp += 2 * CH * LD;
+      sk += 4 * CH;
+      gp += 2 * CH * LD;
+    }
+    regw_stream_pairs<LD, HIST, m, REM, true, PACK>(sp, sk, gp, mW0, mW1, tW0, tW1, valid, lane, half, tcol, tact);
+  } else {
+    constexpr int CH = 8;
+#pragma unroll 1
+    for (int r0 = 0; r0 < N; r0 += CH) {
+      double v[CH];
+#pragma unroll
+      for (int q = 0; q < CH; ++q)
+        if (r0 + q < N && lane < LD) v[q] = sP[(r0 + q) * LD + lane];
+#pragma unroll
+      for (int u = 0; u < m; ++u) {
+        if (!((valid >> u) & 1u)) continue;
+        const double* ku = sK + u * HIST;
+#pragma unroll
+        for (int q = 0; q < CH; ++q) {
+          if (r0 + q < N) {
+            const d2 k = lds128(ku + 2 * (r0 + q));
+            v[q] = rank2(v[q], k.x, k.y, hW0[u][0], hW1[u][0]);
+          }
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < CH; ++q)
+        if (r0 + q < N && lane < LD) gP[(r0 + q) * LD + lane] = v[q];
+    }
+  }
+#pragma unroll
+  for (int p = 0; p < NT; ++p) {
+    const int t = lane + 32 * p;
+    if (t < LD) gMu[t] = sMu[t];
+  }
+}
+
+// -------------------------------------------------------------------------------------------------------
+// launchers
+// -------------------------------------------------------------------------------------------------------
+size_t batch_regw_smem_bytes(int n_landmarks, int m) {
+  const int n = 3 + 2 * n_landmarks, ld = (n + 3) & ~3;
+  return ((size_t)n * ld + ld + (size_t)m * 2 * ld + 2) * sizeof(double);
+}
+
+bool batch_regw_supported(int m) { return m >= 1 && m <= 4; }
+
+template <int NLM, int MT>
+static cudaError_t launch_regw_mt(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+  const size_t smem = batch_regw_smem_bytes(NLM, MT);
+  auto kernel = batch_step_regw_kernel<NLM, MT>;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  if (e != cudaSuccess) return e;
+  kernel<<<(unsigned)batch, 32, smem, st>>>(a);
+  return cudaGetLastError();
+}
+
+template <int NLM>
+static cudaError_t launch_regw_t(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+  switch (a.m) {
+    case 1: return launch_regw_mt<NLM, 1>(a, batch, st);
+    case 2: return launch_regw_mt<NLM, 2>(a, batch, st);
+    case 3: return launch_regw_mt<NLM, 3>(a, batch, st);
+    case 4: return launch_regw_mt<NLM, 4>(a, batch, st);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+cudaError_t batch_launch_step_regw(int n_landmarks, const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+  switch (n_landmarks) {
+    case 4: return launch_regw_t<4>(a, batch, st);
+    case 8: return launch_regw_t<8>(a, batch, st);
+    case 12: return launch_regw_t<12>(a, batch, st);
+    case 16: return launch_regw_t<16>(a, batch, st);
+    case 20: return launch_regw_t<20>(a, batch, st);
+    case 24: return launch_regw_t<24>(a, batch, st);
+    case 28: return launch_regw_t<28>(a, batch, st);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+}  // namespace ekf

@@ -50,7 +50,9 @@ struct ekf_batch {
   int32_t* n_known = nullptr;
   const double *mv = nullptr, *mm = nullptr;
   int flags = ekf::kFlagCircular | ekf::kFlagMeasurement;
-  int kernel = 0;  // 0 = fully staged (default, faster), 1 = streaming (touched rows/columns staged); EKF_BATCH_KERNEL=staged|stream
+  // 0 = auto (W-in-registers kernel where it applies: plain form, 1-4 observation slots; else fully staged),
+  // 1 = streaming (touched rows/columns staged), 2 = fully staged; EKF_BATCH_KERNEL=auto|stream|staged
+  int kernel = 0;
   unsigned long long* faults = nullptr;
   // staging for the host-buffer entry point
   cudaStream_t stream = nullptr;
@@ -123,7 +125,8 @@ int ekf_batch_create(int n_landmarks, int64_t batch, int device, ekf_batch_t** o
   h->ld = (h->n + 3) & ~3;
   h->device = device;
   h->batch = batch;
-  if (const char* k = getenv("EKF_BATCH_KERNEL")) h->kernel = (strcmp(k, "stream") == 0) ? 1 : 0;
+  if (const char* k = getenv("EKF_BATCH_KERNEL"))
+    h->kernel = (strcmp(k, "stream") == 0) ? 1 : (strcmp(k, "staged") == 0) ? 2 : 0;
   cudaError_t e = cudaMalloc(&h->faults, sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaMemset(h->faults, 0, sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
@@ -208,6 +211,8 @@ static int batch_step_common(ekf_batch_t* h, ekf::BatchStepArgs& a, int m, void*
   const bool joseph = (h->flags & ekf::kFlagJoseph) != 0;
   if (!joseph && h->kernel == 1)
     CU(ekf::batch_launch_step_stream(h->nlm, a, h->batch, (cudaStream_t)stream));
+  else if (!joseph && h->kernel == 0 && ekf::batch_regw_supported(m))
+    CU(ekf::batch_launch_step_regw(h->nlm, a, h->batch, (cudaStream_t)stream));
   else
     CU(ekf::batch_launch_step(h->nlm, a, h->batch, joseph, (cudaStream_t)stream));
   return EKF_OK;

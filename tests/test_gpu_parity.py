@@ -324,6 +324,24 @@ def test_ekf3_surface(eb):
     np.testing.assert_allclose(c, z["upd_cov"][3], rtol=1e-9, atol=1e-11)
 
 
+@pytest.mark.parametrize("name", ["batched_b48_l20.npz", "batched_b32_l8.npz"])
+def test_batched_kernel_variants_bitwise_equal(eb, name, monkeypatch):
+    """The W-in-registers kernel (default), the fully staged kernel and the streaming kernel apply the same
+    per-element operation sequence: their states must be BITWISE equal at every kept step."""
+    import torch
+    z = golden(name)
+    outs = {}
+    for variant in ("auto", "staged", "stream"):
+        monkeypatch.setenv("EKF_BATCH_KERNEL", variant)      # read by ekf_batch_create
+        outs[variant], _ = _run_batched(eb, z)
+    for variant in ("staged", "stream"):
+        for t, (mu, p) in outs["auto"].items():
+            mu2, p2 = outs[variant][t]
+            assert np.array_equal(mu, mu2), f"{name} {variant} mu differs at t={t}"
+            assert np.array_equal(p, p2), f"{name} {variant} P differs at t={t}"
+
+
+
 # ---------------------------------------------------------------------------------------------------------
 # full-size properties (BASELINE.json sizes; no oracle at this scale)
 # ---------------------------------------------------------------------------------------------------------
