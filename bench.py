@@ -330,7 +330,7 @@ def run_own_arm(args, world):
                        "sharding": "filters split across ranks, no data-path collective"},
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "peak_source": which, "unit": "GB/s",
                          "frac": ach / peak, "frac_of_8TBs": ach / 8000.0,
-                         "bytes_per_filter_step": BYTES_PER_FILTER_STEP, "kernel": "batch_step_kernel<20,false> (one warp per filter)",
+                         "bytes_per_filter_step": BYTES_PER_FILTER_STEP, "kernel": "batch_step_regw_kernel<20,3,1> (one warp per filter, W in registers)",
                          "kernel_ms": kern_ms, "traffic": ncu_traffic("batch_step_kernel")},
             "e2e": {"value": BATCH * world * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h,

@@ -17,6 +17,8 @@
 #include "ekf_batched.h"
 #include "ekf_batched_dev.cuh"
 
+#include <cstdlib>
+
 namespace ekf {
 
 namespace {
@@ -79,38 +81,54 @@ __device__ __forceinline__ void regw_stream_pairs(const double* __restrict__ sp,
 
 }  // namespace
 
-template <int NLM, int MT>
-__global__ void __launch_bounds__(32) batch_step_regw_kernel(BatchStepArgs a) {
+// WPC = warps per CTA. WPC == 1: one filter per one-warp CTA (the hardware CTA scheduler balances the load).
+// WPC > 1: ONE persistent CTA per SM whose warps each pull filters from a device-side work counter — the
+// 1 KB of shared memory the system reserves per CTA is then paid once per SM instead of once per filter,
+// which is what lets a 13th filter fit at n = 43 (13 x 17.2 KB + 1 KB <= 228 KB). Opt-in (see launch_regw_mt).
+template <int NLM, int MT, int WPC>
+__global__ void __launch_bounds__(32 * WPC, 1) batch_step_regw_kernel(BatchStepArgs a, int64_t batch) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
   constexpr int HIST = 2 * LD;        // doubles of one update's K record: [LD][2]
   constexpr int NT = (LD + 31) / 32;  // lane t handles indices t, t + 32
   constexpr int m = MT;
+  constexpr int SLICE = N * LD + LD + m * HIST + 2;  // doubles of shared memory per warp
   static_assert(NT <= 2, "lane owns at most two columns");
   static_assert(MT >= 1 && MT <= BATCH_MAX_M, "observation count");
+  static_assert(SLICE % 2 == 0, "16-byte aligned slices");
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  double* sP = reinterpret_cast<double*>(smem_raw);  // [N][LD]
-  double* sMu = sP + N * LD;                         // [LD]
-  double* sK = sMu + LD;                             // [m][LD][2]  (K_u[i,0], K_u[i,1]) pairs
-  uint64_t* bar = reinterpret_cast<uint64_t*>(sK + m * HIST);  // [2]: mu, P
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  double* sP = reinterpret_cast<double*>(smem_raw) + warp * SLICE;  // [N][LD]
+  double* sMu = sP + N * LD;                                        // [LD]
+  double* sK = sMu + LD;                                            // [m][LD][2]  (K_u[i,0], K_u[i,1]) pairs
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sK + m * HIST);       // [2]: mu, P
 
-  const int lane = threadIdx.x;
-  const int64_t b = blockIdx.x;
+  if (lane == 0) {
+    mbar_init(bar, 1);
+    mbar_init(bar + 1, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  const int64_t total_warps = (int64_t)gridDim.x * WPC;
+  unsigned long long* work = a.faults + 1;  // [1] filters handed out beyond the static first round, [2] warps done
+  uint32_t parity = 0;
+  for (int64_t b = (int64_t)blockIdx.x * WPC + warp; b < batch; parity ^= 1u) {
   double* __restrict__ gP = a.P + b * (int64_t)(N * LD);
   double* __restrict__ gMu = a.mu + b * (int64_t)LD;
 
   // ---- phase 0: TMA bulk load + per-filter inputs --------------------------------------------------
   // mu arrives on its own mbarrier: the scalar part of phase 1 (sincos, augment, motion model) runs while the
   // 15 KB of P are still in flight
+  int64_t b_next = batch;
   if (lane == 0) {
-    mbar_init(bar, 1);
-    mbar_init(bar + 1, 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    if (WPC > 1) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // earlier generic writes vs TMA
     mbar_expect_tx(bar, (uint32_t)(LD * sizeof(double)));
     tma_bulk_g2s(sMu, gMu, (uint32_t)(LD * sizeof(double)), bar);
     mbar_expect_tx(bar + 1, (uint32_t)(N * LD * sizeof(double)));
     tma_bulk_g2s(sP, gP, (uint32_t)(N * LD * sizeof(double)), bar + 1);
+    if (WPC > 1) b_next = total_warps + (int64_t)atomicAdd(work, 1ULL);  // latency hidden behind this filter
   }
   double ang, lin;
   if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
@@ -133,7 +151,7 @@ __global__ void __launch_bounds__(32) batch_step_regw_kernel(BatchStepArgs a) {
     o_brg = a.brg[b * m + lane];
   }
   __syncwarp();
-  mbar_wait(bar, 0);
+  mbar_wait(bar, parity);
 
   // robot rows / columns of the CURRENT covariance, lane t: rr[k][p] = P[k][t], rc[k][p] = P[t][k], t = lane + 32 p
   double rr[3][NT], rc[3][NT];
@@ -181,7 +199,7 @@ __global__ void __launch_bounds__(32) batch_step_regw_kernel(BatchStepArgs a) {
       a.n_known[b] = nk;
       if (fault) atomicAdd(a.faults, 1ULL);
     }
-    mbar_wait(bar + 1, 0);
+    mbar_wait(bar + 1, parity);
     if (fresh && lane == 0) {  // new landmarks' diagonals (:356-357)
 #pragma unroll
       for (int u = 0; u < m; ++u)
@@ -406,6 +424,16 @@ __global__ void __launch_bounds__(32) batch_step_regw_kernel(BatchStepArgs a) {
     const int t = lane + 32 * p;
     if (t < LD) gMu[t] = sMu[t];
   }
+  __syncwarp();  // every lane is done with this filter's shared memory before the next TMA lands
+  b = __shfl_sync(kFull, b_next, 0);
+  }  // filter loop
+  if (WPC > 1 && lane == 0) {  // the last warp out re-arms the work counter for the next launch
+    __threadfence();
+    if (atomicAdd(work + 1, 1ULL) == (unsigned long long)(total_warps - 1)) {
+      work[0] = 0ULL;
+      work[1] = 0ULL;
+    }
+  }
 }
 
 // -------------------------------------------------------------------------------------------------------
@@ -418,16 +446,46 @@ size_t batch_regw_smem_bytes(int n_landmarks, int m) {
 
 bool batch_regw_supported(int m) { return m >= 1 && m <= 4; }
 
-template <int NLM, int MT>
-static cudaError_t launch_regw_mt(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
-  const size_t smem = batch_regw_smem_bytes(NLM, MT);
-  auto kernel = batch_step_regw_kernel<NLM, MT>;
+// warps of one persistent CTA that fit an SM (shared memory: 227 KB per CTA; registers: <= 16 warps), and
+// resident one-warp CTAs (each also pays the 1 KB system reservation; <= 32 CTAs per SM)
+constexpr int regw_slice_bytes(int nlm, int m) {
+  return (((3 + 2 * nlm) * (((3 + 2 * nlm) + 3) & ~3)) + (((3 + 2 * nlm) + 3) & ~3) * (1 + 2 * m) + 2) * 8;
+}
+constexpr int regw_persist_warps(int nlm, int m) {
+  return (232448 / regw_slice_bytes(nlm, m)) < 16 ? (232448 / regw_slice_bytes(nlm, m)) : 16;
+}
+constexpr int regw_single_warps(int nlm, int m) {
+  return (233472 / (regw_slice_bytes(nlm, m) + 1024)) < 16 ? (233472 / (regw_slice_bytes(nlm, m) + 1024)) : 16;
+}
+
+template <int NLM, int MT, int WPC>
+static cudaError_t launch_regw_wpc(const BatchStepArgs& a, int64_t batch, unsigned grid, cudaStream_t st) {
+  const size_t smem = batch_regw_smem_bytes(NLM, MT) * WPC;
+  auto kernel = batch_step_regw_kernel<NLM, MT, WPC>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   if (e != cudaSuccess) return e;
-  kernel<<<(unsigned)batch, 32, smem, st>>>(a);
+  kernel<<<grid, 32 * WPC, smem, st>>>(a, batch);
   return cudaGetLastError();
+}
+
+template <int NLM, int MT>
+static cudaError_t launch_regw_mt(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+  constexpr int PW = regw_persist_warps(NLM, MT);
+  // EKF_BATCH_PERSIST=1 selects the persistent CTA. Measured on B200 at n = 43, m = 3: 13 warps per SM but
+  // 0.433 ms per 65 536-filter step against 0.327 ms for one-warp CTAs (persistent warps stay phase-locked, so
+  // the TMA loads of all 1 924 warps arrive in bursts) — kept for experiments, off by default.
+  static const bool persist = [] { const char* v = getenv("EKF_BATCH_PERSIST"); return v && atoi(v) == 1; }();
+  if (persist && PW > 1) {
+    int dev = 0, sms = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return e;
+    const int64_t need = (batch + PW - 1) / PW;
+    return launch_regw_wpc<NLM, MT, (PW > 1 ? PW : 2)>(a, batch, (unsigned)(need < sms ? need : sms), st);
+  }
+  return launch_regw_wpc<NLM, MT, 1>(a, batch, (unsigned)batch, st);
 }
 
 template <int NLM>

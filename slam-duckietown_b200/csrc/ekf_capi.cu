@@ -53,7 +53,7 @@ struct ekf_batch {
   // 0 = auto (W-in-registers kernel where it applies: plain form, 1-4 observation slots; else fully staged),
   // 1 = streaming (touched rows/columns staged), 2 = fully staged; EKF_BATCH_KERNEL=auto|stream|staged
   int kernel = 0;
-  unsigned long long* faults = nullptr;
+  unsigned long long* faults = nullptr;  // [0] fault count, [1..2] work / done counters of the persistent kernel
   // staging for the host-buffer entry point
   cudaStream_t stream = nullptr;
   double *d_ang = nullptr, *d_lin = nullptr, *d_rng = nullptr, *d_brg = nullptr, *d_pose = nullptr;
@@ -127,8 +127,8 @@ int ekf_batch_create(int n_landmarks, int64_t batch, int device, ekf_batch_t** o
   h->batch = batch;
   if (const char* k = getenv("EKF_BATCH_KERNEL"))
     h->kernel = (strcmp(k, "stream") == 0) ? 1 : (strcmp(k, "staged") == 0) ? 2 : 0;
-  cudaError_t e = cudaMalloc(&h->faults, sizeof(unsigned long long));
-  if (e == cudaSuccess) e = cudaMemset(h->faults, 0, sizeof(unsigned long long));
+  cudaError_t e = cudaMalloc(&h->faults, 4 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMemset(h->faults, 0, 4 * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) {
     ekf_batch_destroy(h);
