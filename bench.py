@@ -233,6 +233,18 @@ def bench_large_map(updates=60, warm=6):
         e1.record()
     torch.cuda.synchronize()
     ms = np.array([e0.elapsed_time(e1) for e0, e1 in ev])
+    # fused form: the 3 updates of a step in ONE pass over P (ekf_lm_update_multi)
+    trip = [ups[i:i + 3] for i in range(0, len(ups) - 2, 3)]
+    for t3 in trip[:2]:
+        g.update_multi([o[1] for o in t3], [o[2] for o in t3], [o[3] for o in t3])
+    torch.cuda.synchronize()
+    ev3 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in trip[2:]]
+    for (e0, e1), t3 in zip(ev3, trip[2:]):
+        e0.record()
+        g.update_multi([o[1] for o in t3], [o[2] for o in t3], [o[3] for o in t3])
+        e1.record()
+    torch.cuda.synchronize()
+    ms3 = np.array([e0.elapsed_time(e1) for e0, e1 in ev3])
     finite = bool(torch.isfinite(g.mu).all())
     g.close()
     peak, which = measured_peak_gbs()
@@ -242,7 +254,13 @@ def bench_large_map(updates=60, warm=6):
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "peak_source": which, "unit": "GB/s",
                          "frac": ach / peak, "frac_of_8TBs": ach / 8000.0, "bytes_per_update": LM_BYTES_PER_UPDATE,
                          "traffic": ncu_traffic("lm_rank_update_kernel"),
-                         "note": "gather + streaming kernels of one update timed together"}}
+                         "note": "gather + streaming kernels of one update timed together"},
+            "fused_step": {"updates_per_step": 3, "ms_per_step": float(np.mean(ms3)),
+                           "ms_per_update_equiv": float(np.mean(ms3)) / 3.0, "steps": len(ms3),
+                           "hbm_gbs": (LM_BYTES_PER_UPDATE - 96 * (3 + 2 * LM_LANDMARKS)
+                                       + 3 * 96 * (3 + 2 * LM_LANDMARKS)) / (float(np.mean(ms3)) * 1e-3) / 1e9,
+                           "note": "ekf_lm_update_multi: 3 sequential updates with one read + write of P "
+                                   "(16 n^2 + 3 x 96 n bytes per step), bitwise equal to 3 ekf_lm_update calls"}}
 
 
 def run_own_arm(args, world):

@@ -111,6 +111,13 @@ int ekf_lm_augment(ekf_lm_t* h, int slot, double gx, double gy, void* stream);
 int ekf_lm_predict(ekf_lm_t* h, double ang, double lin, void* stream);
 /* a8-a11: one range-bearing update of landmark `slot` (:436-480)                                        */
 int ekf_lm_update(ekf_lm_t* h, int slot, double rng, double brg, void* stream);
+/* The m sequential updates of one step (the reference's update loop :436-480, in the given order) with ONE read +
+ * write of P: the 5 rows / 5 columns of update u are rebuilt from the step's initial P and the earlier (K, H P)
+ * records, then all m rank-2 terms are applied per element in order. Bitwise equal to m ekf_lm_update calls.
+ * slots / rng / brg are HOST arrays of length m; groups of 4 are fused; on a row-block shard or with the Joseph
+ * form the call falls back to the sequential kernels.                                                   */
+int ekf_lm_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
+                        const double* brg_host, void* stream);
 /* Row-block shards: export this shard's share of rows {0,1,2,j,j+1} (+ mu entries) into rows5_dev
  * [5][ld+4] (rows it does not own are left untouched), then — after the owners' rows were exchanged
  * (NCCL broadcast by the host) — run the update on the local block from the replicated buffer.          */

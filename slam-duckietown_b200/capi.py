@@ -63,6 +63,7 @@ SIGNATURES = {
     "ekf_lm_augment": (_i, [_p, _i, _d, _d, _p]),
     "ekf_lm_predict": (_i, [_p, _d, _d, _p]),
     "ekf_lm_update": (_i, [_p, _i, _d, _d, _p]),
+    "ekf_lm_update_multi": (_i, [_p, _i, _p, _p, _p, _p]),
     "ekf_lm_export_rows": (_i, [_p, _i, _p, _p]),
     "ekf_lm_update_from_rows": (_i, [_p, _i, _d, _d, _p, _p]),
     "ekf_lm_sync": (_i, [_p]),

@@ -74,6 +74,7 @@ struct ekf_lm {
   int flags = ekf::kFlagCircular | ekf::kFlagMeasurement;
   double *K0 = nullptr, *K1 = nullptr, *A0 = nullptr, *A1 = nullptr, *W0 = nullptr, *W1 = nullptr,
          *scal = nullptr;
+  double *mK = nullptr, *mW = nullptr, *my = nullptr;  // fused multi-update records [LM_MAX_FUSED][2][ldw], y [..][2]
   int variant = 0;
 };
 
@@ -409,8 +410,9 @@ int ekf_lm_create(int capacity_landmarks, int device, ekf_lm_t** out) {
   const char* v = getenv("EKF_LM_VARIANT");
   h->variant = v ? atoi(v) : 0;
   double* ws = nullptr;
-  cudaError_t e = cudaMalloc(&ws, (6 * h->ldw + ekf::kScalCount) * sizeof(double));
-  if (e == cudaSuccess) e = cudaMemset(ws, 0, (6 * h->ldw + ekf::kScalCount) * sizeof(double));
+  const size_t ws_doubles = (size_t)(6 + 4 * ekf::LM_MAX_FUSED) * h->ldw + ekf::kScalCount + 2 * ekf::LM_MAX_FUSED;
+  cudaError_t e = cudaMalloc(&ws, ws_doubles * sizeof(double));
+  if (e == cudaSuccess) e = cudaMemset(ws, 0, ws_doubles * sizeof(double));
   if (e != cudaSuccess) {
     cudaFree(ws);
     delete h;
@@ -423,6 +425,9 @@ int ekf_lm_create(int capacity_landmarks, int device, ekf_lm_t** out) {
   h->W0 = ws + 4 * h->ldw;
   h->W1 = ws + 5 * h->ldw;
   h->scal = ws + 6 * h->ldw;
+  h->my = h->scal + ekf::kScalCount;
+  h->mK = h->my + 2 * ekf::LM_MAX_FUSED;
+  h->mW = h->mK + 2 * ekf::LM_MAX_FUSED * h->ldw;
   *out = h;
   return EKF_OK;
 }
@@ -534,6 +539,46 @@ static int lm_update_impl(ekf_lm_t* h, int slot, double rng, double brg, const d
 
 int ekf_lm_update(ekf_lm_t* h, int slot, double rng, double brg, void* stream) {
   return lm_update_impl(h, slot, rng, brg, nullptr, stream);
+}
+
+int ekf_lm_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
+                        const double* brg_host, void* stream) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  if (m < 0) return fail(EKF_EINVAL, "m < 0");
+  if (m > 0 && (!slots_host || !rng_host || !brg_host)) return fail(EKF_EINVAL, "observation arrays are null");
+  if (!h->P) return fail(EKF_ESTATE, "state not bound");
+  const bool whole = (h->row_begin == 0 && h->row_end == h->n);
+  const bool joseph = (h->flags & ekf::kFlagJoseph) != 0;
+  for (int u = 0; u < m; ++u)
+    if (slots_host[u] < 0 || slots_host[u] >= h->cap)
+      return fail(EKF_EINVAL, "slot %d outside capacity %d", slots_host[u], h->cap);
+  if (!(h->flags & ekf::kFlagMeasurement)) return EKF_OK;
+  if (!whole || joseph) {  // no fused form there: the sequential path (fails on a shard like ekf_lm_update)
+    for (int u = 0; u < m; ++u) {
+      const int rc = lm_update_impl(h, slots_host[u], rng_host[u], brg_host[u], nullptr, stream);
+      if (rc != EKF_OK) return rc;
+    }
+    return EKF_OK;
+  }
+  CU(cudaSetDevice(h->device));
+  for (int first = 0; first < m; first += ekf::LM_MAX_FUSED) {  // groups of <= LM_MAX_FUSED, each ONE pass over P
+    const int g = (m - first < ekf::LM_MAX_FUSED) ? m - first : ekf::LM_MAX_FUSED;
+    if (g == 1) {
+      const int rc = lm_update_impl(h, slots_host[first], rng_host[first], brg_host[first], nullptr, stream);
+      if (rc != EKF_OK) return rc;
+      continue;
+    }
+    ekf::LmMultiArgs a{};
+    a.P = h->P; a.mu = h->mu; a.K = h->mK; a.W = h->mW; a.y = h->my;
+    a.ld = h->ld; a.ldw = h->ldw; a.n = h->n; a.m = g; a.mm = h->mm;
+    for (int u = 0; u < g; ++u) {
+      a.j[u] = 3 + 2 * slots_host[first + u];
+      a.rng[u] = rng_host[first + u];
+      a.brg[u] = brg_host[first + u];
+    }
+    CU(ekf::lm_launch_update_multi(a, (cudaStream_t)stream));
+  }
+  return EKF_OK;
 }
 
 int ekf_lm_export_rows(ekf_lm_t* h, int slot, double* rows5_dev, void* stream) {

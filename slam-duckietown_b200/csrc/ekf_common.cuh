@@ -112,6 +112,12 @@ __device__ __forceinline__ void inv2(const double s[2][2], double si[2][2]) {
   si[1][0] = -s[1][0] * rd; si[1][1] = s[0][0] * rd;
 }
 
+// a10 (replay_no_ros.py:476) for one entry: mu + (K[i,0] y0 + K[i,1] y1), with the rounding sequence spelled out so
+// that every large-map kernel that applies it (sequential, fused multi-update, shard pose refresh) agrees bitwise
+__device__ __forceinline__ double mu_inc(double mu, double k0, double k1, double y0, double y1) {
+  return __dadd_rn(mu, fma(k1, y1, __dmul_rn(k0, y0)));
+}
+
 // 256-bit global accesses (sm_100a: LDG.E.256 / STG.E.256)
 struct __align__(32) double4x {
   double a, b, c, d;

@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
     }
     const double kk0 = ph0 * ssi[0][0] + ph1 * ssi[1][0];
     const double kk1 = ph0 * ssi[0][1] + ph1 * ssi[1][1];
-    a.mu_out[t] += kk0 * sy[0] + kk1 * sy[1];
+    a.mu_out[t] = mu_inc(a.mu_out[t], kk0, kk1, sy[0], sy[1]);
   }
   double hp0 = 0.0, hp1 = 0.0;
 #pragma unroll
@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs
   __syncthreads();
   if (blockIdx.x == 0) {  // a10: mu += K y for this CTA's rows
     const double y0 = a.scal[kScalY0], y1 = a.scal[kScalY1];
-    for (int r = tid; r < nrows; r += LM_THREADS) a.mu[r0 + r] += sk[r][0] * y0 + sk[r][1] * y1;
+    for (int r = tid; r < nrows; r += LM_THREADS) a.mu[r0 + r] = mu_inc(a.mu[r0 + r], sk[r][0], sk[r][1], y0, y1);
   }
   double* __restrict__ Pblk = a.P + (int64_t)(r0 - a.row_begin) * a.ld;
   if ((int)blockIdx.x < a.full_tiles) {

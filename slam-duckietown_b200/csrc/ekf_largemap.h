@@ -31,6 +31,24 @@ struct LmUpdateArgs {
   int full_tiles, tail_groups;  // filled by the launcher
 };
 
+constexpr int LM_MAX_FUSED = 4;  // updates fused into one pass over P (ekf_largemap_multi.cu)
+
+// fused multi-update: m sequential updates of one step, ONE read + write of P (plain form, whole matrix on one GPU)
+struct LmMultiArgs {
+  double* P;
+  double* mu;
+  double* K;    // [m][2][ldw]: K_u[:,0] at K + 2u ldw, K_u[:,1] at K + (2u+1) ldw
+  double* W;    // [m][2][ldw]: (H P)_u rows, same indexing
+  double* y;    // [m][2] innovations
+  int64_t ld, ldw;
+  int n, m;
+  int j[LM_MAX_FUSED];
+  double rng[LM_MAX_FUSED], brg[LM_MAX_FUSED];
+  double mm;
+  int full_tiles, tail_groups;  // filled by the launcher
+};
+cudaError_t lm_launch_update_multi(const LmMultiArgs& a, cudaStream_t st);
+
 cudaError_t lm_launch_augment(double* mu, double* P, int64_t ld, int row_begin, int row_end, int j, double gx,
                               double gy, cudaStream_t st);
 cudaError_t lm_launch_predict(double* mu, double* P, int64_t ld, int n, int row_begin, int row_end,

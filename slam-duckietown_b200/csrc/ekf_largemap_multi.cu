@@ -1,0 +1,240 @@
+// ekf_largemap_multi.cu — large-map filter: the m sequential range-bearing updates of ONE step fused into a
+// single pass over P (reference update loop src/replay_no_ros.py:436-480).
+//
+// The reference applies the updates one after the other, each a dense (I - K H) P product. In rank form update u
+// touches P only through its five rows / five columns idx5(u) = {0, 1, 2, j_u, j_u + 1}; those 10 n entries of the
+// INTERMEDIATE covariance P_u can be rebuilt from the step's initial P0 and the earlier (K_w, W_w = H_w P_w):
+//     P_u[i, c] = P0[i, c] - sum_{w < u} K_w[i, :] W_w[:, c]        (applied in order, same rounding sequence)
+// so the O(n) part of every update (innovation, S^-1, K_u, W_u, the five mu entries) runs first — m small gather
+// kernels, update u costing O(n (10 + 4u)) — and ONE streaming kernel then applies all m rank-2 terms to every
+// element in order. HBM traffic per step drops from m x 16 n^2 to 16 n^2 bytes; the per-element operation
+// sequence is that of the sequential kernels (lm_gather_kernel + lm_rank_update_kernel), so the result is bitwise
+// the same (tests/test_gpu_parity.py::test_large_map_fused_multi_update_bitwise).
+// Plain covariance form, whole matrix on one GPU.
+#include "ekf_common.cuh"
+#include "ekf_largemap.h"
+
+namespace ekf {
+
+namespace {
+
+__device__ __forceinline__ double rank2e(double v, double k0, double k1, double w0, double w1) {
+  return fma(-k1, w1, fma(-k0, w0, v));  // == lm_rank_update_kernel's fma(-k1, w1, fma(-k0, w0, v))
+}
+
+}  // namespace
+
+// a8-a9 for update u of the step, on the covariance as it stands after updates 0..u-1 (never materialised).
+__global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int u) {
+  __shared__ double sh[2][5];
+  __shared__ double ssi[2][2];
+  __shared__ double skw[LM_MAX_FUSED][5][2];  // K_w[idx5(u), :] of the earlier updates
+  __shared__ double sww[LM_MAX_FUSED][2][5];  // W_w[:, idx5(u)]
+  const int j = a.j[u];
+  const int idx5[5] = {0, 1, 2, j, j + 1};
+  const double* __restrict__ P = a.P;
+  if (threadIdx.x < 5 * u) {  // uniform operands of the rebuild
+    const int w = threadIdx.x / 5, k = threadIdx.x - 5 * w;
+    skw[w][k][0] = a.K[(2 * w) * a.ldw + idx5[k]];
+    skw[w][k][1] = a.K[(2 * w + 1) * a.ldw + idx5[k]];
+    sww[w][0][k] = a.W[(2 * w) * a.ldw + idx5[k]];
+    sww[w][1][k] = a.W[(2 * w + 1) * a.ldw + idx5[k]];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double mu5[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      double v = a.mu[idx5[k]];  // mu is written by the streaming kernel only: still the step's initial mean
+      for (int w = 0; w < u; ++w) v = mu_inc(v, skw[w][k][0], skw[w][k][1], a.y[2 * w], a.y[2 * w + 1]);
+      mu5[k] = v;
+    }
+    const Innov in = innovation(mu5[0], mu5[1], mu5[2], mu5[3], mu5[4], a.rng[u], a.brg[u]);
+    double hp5[2][5];
+#pragma unroll
+    for (int c = 0; c < 5; ++c) {
+      double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        double p = P[(int64_t)idx5[k] * a.ld + idx5[c]];
+        for (int w = 0; w < u; ++w) p = rank2e(p, skw[w][k][0], skw[w][k][1], sww[w][0][c], sww[w][1][c]);
+        s0 = fma(in.h[0][k], p, s0);
+        s1 = fma(in.h[1][k], p, s1);
+      }
+      hp5[0][c] = s0;
+      hp5[1][c] = s1;
+    }
+    double s[2][2], si[2][2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        double acc = 0.0;
+#pragma unroll
+        for (int c = 0; c < 5; ++c) acc = fma(hp5[r][c], in.h[b][c], acc);
+        s[r][b] = acc;
+      }
+    const double qn = a.mm * a.mm;
+    s[0][0] += qn;
+    s[1][1] += qn;
+    inv2(s, si);
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+#pragma unroll
+      for (int k = 0; k < 5; ++k) sh[r][k] = in.h[r][k];
+      ssi[r][0] = si[r][0];
+      ssi[r][1] = si[r][1];
+    }
+    if (blockIdx.x == 0) {
+      a.y[2 * u] = in.y0;
+      a.y[2 * u + 1] = in.y1;
+    }
+  }
+  __syncthreads();
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= a.n) return;
+  // this thread's entries of the earlier records
+  double kt0[LM_MAX_FUSED], kt1[LM_MAX_FUSED], wt0[LM_MAX_FUSED], wt1[LM_MAX_FUSED];
+#pragma unroll
+  for (int w = 0; w < LM_MAX_FUSED; ++w)
+    if (w < u) {
+      kt0[w] = a.K[(2 * w) * a.ldw + t];
+      kt1[w] = a.K[(2 * w + 1) * a.ldw + t];
+      wt0[w] = a.W[(2 * w) * a.ldw + t];
+      wt1[w] = a.W[(2 * w + 1) * a.ldw + t];
+    }
+  double hp0 = 0.0, hp1 = 0.0, pht0 = 0.0, pht1 = 0.0;
+  const double* prow = P + (int64_t)t * a.ld;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    double pr = P[(int64_t)idx5[k] * a.ld + t];  // row idx5[k], column t
+    double pc = prow[idx5[k]];                   // row t, column idx5[k]
+#pragma unroll
+    for (int w = 0; w < LM_MAX_FUSED; ++w)
+      if (w < u) {
+        pr = rank2e(pr, skw[w][k][0], skw[w][k][1], wt0[w], wt1[w]);
+        pc = rank2e(pc, kt0[w], kt1[w], sww[w][0][k], sww[w][1][k]);
+      }
+    hp0 = fma(sh[0][k], pr, hp0);
+    hp1 = fma(sh[1][k], pr, hp1);
+    pht0 = fma(pc, sh[0][k], pht0);
+    pht1 = fma(pc, sh[1][k], pht1);
+  }
+  a.K[(2 * u) * a.ldw + t] = pht0 * ssi[0][0] + pht1 * ssi[1][0];
+  a.K[(2 * u + 1) * a.ldw + t] = pht0 * ssi[0][1] + pht1 * ssi[1][1];
+  a.W[(2 * u) * a.ldw + t] = hp0;
+  a.W[(2 * u + 1) * a.ldw + t] = hp1;
+}
+
+// a10-a11 for all M updates of the step in one pass: P[i, c] <- P0[i, c] - sum_u K_u[i, :] W_u[:, c] in update
+// order, mu[i] += K_u[i, :] y_u in update order. Tiling as lm_rank_update_kernel: a CTA owns LM_THREADS column
+// groups of 4 doubles x RB rows; W_u of a thread's 4 columns stays in registers (8 M doubles), K_u of the RB rows
+// in shared memory, UNROLL rows of P in flight per thread (256-bit streaming loads, in-place 256-bit stores).
+template <int RB, int UNROLL, int M>
+__global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMultiArgs a) {
+  __shared__ double sk[RB][2 * M];
+  const int tid = threadIdx.x;
+  const int r0 = blockIdx.y * RB;
+  const int nrows = min(RB, a.n - r0);
+  for (int e = tid; e < nrows * 2 * M; e += LM_THREADS) {
+    const int r = e / (2 * M), q = e - r * (2 * M);
+    sk[r][q] = a.K[(int64_t)q * a.ldw + r0 + r];
+  }
+  __syncthreads();
+  if (blockIdx.x == 0) {
+    for (int r = tid; r < nrows; r += LM_THREADS) {
+      double v = a.mu[r0 + r];
+#pragma unroll
+      for (int u = 0; u < M; ++u) v = mu_inc(v, sk[r][2 * u], sk[r][2 * u + 1], a.y[2 * u], a.y[2 * u + 1]);
+      a.mu[r0 + r] = v;
+    }
+  }
+  double* __restrict__ Pblk = a.P + (int64_t)r0 * a.ld;
+  if ((int)blockIdx.x < a.full_tiles) {
+    const int c = (blockIdx.x * LM_THREADS + tid) * 4;
+    double4x w0[M], w1[M];
+#pragma unroll
+    for (int u = 0; u < M; ++u) {
+      w0[u] = ldg256(a.W + (int64_t)(2 * u) * a.ldw + c);
+      w1[u] = ldg256(a.W + (int64_t)(2 * u + 1) * a.ldw + c);
+    }
+    double* p = Pblk + c;
+    int r = 0;
+    for (; r + UNROLL <= nrows; r += UNROLL) {
+      double4x v[UNROLL];
+#pragma unroll
+      for (int q = 0; q < UNROLL; ++q) v[q] = ldg256_stream(p + (int64_t)(r + q) * a.ld);
+#pragma unroll
+      for (int u = 0; u < M; ++u)
+#pragma unroll
+        for (int q = 0; q < UNROLL; ++q) {
+          const double k0 = sk[r + q][2 * u], k1 = sk[r + q][2 * u + 1];
+          v[q].a = rank2e(v[q].a, k0, k1, w0[u].a, w1[u].a);
+          v[q].b = rank2e(v[q].b, k0, k1, w0[u].b, w1[u].b);
+          v[q].c = rank2e(v[q].c, k0, k1, w0[u].c, w1[u].c);
+          v[q].d = rank2e(v[q].d, k0, k1, w0[u].d, w1[u].d);
+        }
+#pragma unroll
+      for (int q = 0; q < UNROLL; ++q) stg256(p + (int64_t)(r + q) * a.ld, v[q]);
+    }
+    for (; r < nrows; ++r) {
+      double4x v = ldg256_stream(p + (int64_t)r * a.ld);
+#pragma unroll
+      for (int u = 0; u < M; ++u) {
+        const double k0 = sk[r][2 * u], k1 = sk[r][2 * u + 1];
+        v.a = rank2e(v.a, k0, k1, w0[u].a, w1[u].a);
+        v.b = rank2e(v.b, k0, k1, w0[u].b, w1[u].b);
+        v.c = rank2e(v.c, k0, k1, w0[u].c, w1[u].c);
+        v.d = rank2e(v.d, k0, k1, w0[u].d, w1[u].d);
+      }
+      stg256(p + (int64_t)r * a.ld, v);
+    }
+  } else {
+    // column tail: a.tail_groups (< LM_THREADS) groups per row, (row, group) mapping
+    const int tg = a.tail_groups;
+    const int cbase = a.full_tiles * LM_THREADS * 4;
+    for (int e = tid; e < nrows * tg; e += LM_THREADS) {
+      const int r = e / tg, c = cbase + (e - r * tg) * 4;
+      double4x v = ldg256_stream(Pblk + (int64_t)r * a.ld + c);
+#pragma unroll
+      for (int u = 0; u < M; ++u) {
+        const double4x w0 = ldg256(a.W + (int64_t)(2 * u) * a.ldw + c);
+        const double4x w1 = ldg256(a.W + (int64_t)(2 * u + 1) * a.ldw + c);
+        const double k0 = sk[r][2 * u], k1 = sk[r][2 * u + 1];
+        v.a = rank2e(v.a, k0, k1, w0.a, w1.a);
+        v.b = rank2e(v.b, k0, k1, w0.b, w1.b);
+        v.c = rank2e(v.c, k0, k1, w0.c, w1.c);
+        v.d = rank2e(v.d, k0, k1, w0.d, w1.d);
+      }
+      stg256(Pblk + (int64_t)r * a.ld + c, v);
+    }
+  }
+}
+
+template <int M>
+static cudaError_t launch_multi_t(const LmMultiArgs& a, cudaStream_t st) {
+  constexpr int RB = 32, UNROLL = 8;
+  dim3 grid(a.full_tiles + (a.tail_groups ? 1 : 0), (a.n + RB - 1) / RB);
+  lm_rank_update_multi_kernel<RB, UNROLL, M><<<grid, LM_THREADS, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t lm_launch_update_multi(const LmMultiArgs& a0, cudaStream_t st) {
+  LmMultiArgs a = a0;
+  if (a.m < 2 || a.m > LM_MAX_FUSED) return cudaErrorInvalidValue;
+  const int groups = (a.n + 3) / 4;
+  a.full_tiles = groups / LM_THREADS;
+  a.tail_groups = groups - a.full_tiles * LM_THREADS;
+  for (int u = 0; u < a.m; ++u) {
+    lm_gather_multi_kernel<<<(a.n + 255) / 256, 256, 0, st>>>(a, u);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
+  switch (a.m) {
+    case 2: return launch_multi_t<2>(a, st);
+    case 3: return launch_multi_t<3>(a, st);
+    default: return launch_multi_t<4>(a, st);
+  }
+}
+
+}  // namespace ekf

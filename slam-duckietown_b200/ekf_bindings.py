@@ -191,6 +191,16 @@ class LargeMapEKF:
     def update(self, slot: int, rng: float, brg: float):
         capi.call("ekf_lm_update", self._h, int(slot), float(rng), float(brg), _stream_ptr(self.torch))
 
+    def update_multi(self, slots, rngs, brgs):
+        """The step's sequential updates (replay_no_ros.py:436-480, given order) in ONE pass over P; bitwise equal
+        to calling update() once per observation."""
+        sl = np.ascontiguousarray(slots, dtype=np.int32)
+        rg = np.ascontiguousarray(rngs, dtype=np.float64)
+        bg = np.ascontiguousarray(brgs, dtype=np.float64)
+        assert sl.shape == rg.shape == bg.shape and sl.ndim == 1
+        capi.call("ekf_lm_update_multi", self._h, int(sl.size), sl.ctypes.data, rg.ctypes.data, bg.ctypes.data,
+                  _stream_ptr(self.torch))
+
     def export_rows(self, slot: int):
         if self.rows5 is None:
             self.rows5 = self.torch.zeros((5, self.ld + 4), dtype=self.torch.float64, device=self.mu.device)
@@ -235,8 +245,8 @@ def EKF_pose_estimation(angular_displacement, linear_displacement, motion_model_
         slot = (i - 3) // 2
         f.augment(slot, tags[slot][0], tags[slot][1])
     f.predict(float(angular_displacement), float(linear_displacement))
-    for slot, rec in tags.items():                        # first-seen-in-window order (:436)
-        f.update(slot, rec[4], rec[5])
+    if tags:                                              # first-seen-in-window order (:436), one pass over P
+        f.update_multi(list(tags.keys()), [rec[4] for rec in tags.values()], [rec[5] for rec in tags.values()])
     mean, cov = f.state(n_new)
     return mean, cov, tags
 

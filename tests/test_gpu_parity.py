@@ -208,6 +208,46 @@ def test_large_map_50_steps_vs_oracle_and_pad(eb):
     assert np.all(full[:, g.n:] == 0.0), "pad columns must stay exactly zero"
 
 
+@pytest.mark.parametrize("n_lm,group", [(700, 3), (700, 6), (256, 2), (1024, 4)])
+def test_large_map_fused_multi_update_bitwise(eb, n_lm, group):
+    """ekf_lm_update_multi (one pass over P for the step's updates) == the same updates applied one at a time,
+    BITWISE, and both match the oracle; groups above 4 are split, repeated slots inside a group are allowed."""
+    import torch
+    from slam_duckietown_b200 import workloads as wl
+    w = wl.make_large_map(n_lm, updates=24)
+    seq, fus = eb.LargeMapEKF(n_lm), eb.LargeMapEKF(n_lm)
+    m_o, c_o = w.mu0.copy(), w.p0()
+    for g in (seq, fus):
+        g.set_noise(0.2, 0.5)
+        g.load(w.mu0, w.p0())
+    fl = eo.Flags(motion_var=0.2, meas_var=0.5)
+    pend = []
+
+    def flush():
+        if pend:
+            fus.update_multi([o[1] for o in pend], [o[2] for o in pend], [o[3] for o in pend])
+            pend.clear()
+    for op in w.ops:
+        if op[0] == "update":
+            seq.update(op[1], op[2], op[3])
+            eo.update_rank(m_o, c_o, op[1], op[2], op[3], 0.5)
+            pend.append(op)
+            if len(pend) == group:
+                flush()
+        elif group <= 4:                                # group > 4: no predicts, so that groups really get split
+            flush()
+            for g in (seq, fus):
+                g.predict(op[1], op[2])
+            dx, dy, th, g0, g1 = eo.motion_step(m_o[2], op[1], op[2], fl)
+            m_o[0] += dx; m_o[1] += dy; m_o[2] = th
+            eo.predict_cov_rank(c_o, g0, g1, 0.2)
+    flush()
+    assert torch.equal(seq.mu, fus.mu), "mu differs between sequential and fused updates"
+    assert torch.equal(seq.P, fus.P), "P differs between sequential and fused updates"
+    mu, p = fus.state()
+    assert_parity(mu, p, m_o, c_o, what=f"fused multi-update n_lm={n_lm} group={group}")
+
+
 def test_large_map_augment_matches_growing_arrays(eb):
     """capacity pre-allocation == the reference's zero-padded growth (:341-360)."""
     g = eb.LargeMapEKF(16)
