@@ -39,11 +39,30 @@ METRIC, UNIT = "EKF filter-steps/s (B=65536, 20 lm)", "filter-steps/s"
 WORKLOAD = "batched Monte Carlo replay: 65536 filters x 20 landmarks (n=43), predict + 3 updates per step"
 
 
+def set_workload(name, world):
+    """--workload M: BASELINE.json configs[3], 1,048,576 filters x 8 landmarks (n=19, 2 updates per step), the
+    filters split contiguously across the ranks (strong scaling). Default B is the contract line's workload."""
+    global BATCH, NLM, M, N_STATE, BYTES_PER_FILTER_STEP, METRIC, WORKLOAD, SCALING
+    if name == "M":
+        total = 1 << 20
+        BATCH, NLM, M = total // world, 8, 2
+        N_STATE = 3 + 2 * NLM
+        BYTES_PER_FILTER_STEP = 16 * (N_STATE * N_STATE + N_STATE) + 8 * (2 + 2 * M) + 4 * M + 16   # 6 152
+        METRIC = "EKF filter-steps/s (B=1048576, 8 lm)"
+        WORKLOAD = (f"batched Monte Carlo replay: 1048576 filters x 8 landmarks (n=19) split over {world} GPU(s), "
+                    "predict + 2 updates per step")
+        SCALING = "strong"
+
+
+SCALING = "weak"
+
+
 def make_config(joseph=False):
     """The `config` object both arms print (same workload, same keys)."""
     return {"workload": WORKLOAD, "filters_per_gpu": BATCH, "landmarks": NLM, "updates_per_step": M,
             "cov_form": "joseph" if joseph else "plain (reference, replay_no_ros.py:480)",
-            "l2": "inputs larger than L2 (0.99 GB of covariance per GPU streamed every step)",
+            "l2": f"inputs larger than L2 ({BATCH * N_STATE * ((N_STATE + 3) & ~3) * 8 / 1e9:.2f} GB of covariance per "
+                  "GPU streamed every step)",
             "sharding": "filters split across ranks, no data-path collective"}
 
 
@@ -340,16 +359,13 @@ def run_own_arm(args, world):
     ach = BYTES_PER_FILTER_STEP * BATCH / (kern_ms * 1e-3) / 1e9
     value = BATCH * world * K / (total_ms * 1e-3)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": SCALING, "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "filters_per_gpu": BATCH, "landmarks": NLM, "updates_per_step": M,
-                       "cov_form": "joseph" if args.joseph else "plain (reference, replay_no_ros.py:480)",
-                       "l2": "inputs larger than L2 (0.99 GB of covariance per GPU streamed every step)",
-                       "sharding": "filters split across ranks, no data-path collective"},
+            "config": make_config(args.joseph),
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "peak_source": which, "unit": "GB/s",
                          "frac": ach / peak, "frac_of_8TBs": ach / 8000.0,
-                         "bytes_per_filter_step": BYTES_PER_FILTER_STEP, "kernel": "batch_step_regw_kernel<20,3,1> (one warp per filter, W in registers)",
-                         "kernel_ms": kern_ms, "traffic": ncu_traffic("batch_step_kernel")},
+                         "bytes_per_filter_step": BYTES_PER_FILTER_STEP, "kernel": f"batch_step_regw_kernel<{NLM},{M},1> (one warp per filter, W in registers)",
+                         "kernel_ms": kern_ms, "traffic": ncu_traffic(f"batch_step_regw_kernel<{NLM},{M}>")},
             "e2e": {"value": BATCH * world * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h,
                     "unpipelined_value": BATCH * world * K / e2e_sync_s,
@@ -377,11 +393,14 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--workload", default="B", choices=["B", "M"],
+                    help="B: 65,536 x 20 lm per GPU (contract line); M: 1,048,576 x 8 lm split over the GPUs")
     ap.add_argument("--joseph", action="store_true", help="one-pass Joseph-form covariance update")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-large-map", action="store_true")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    set_workload(args.workload, world)
     if args.impl == "reference":
         run_reference_arm(args, int(os.environ.get("RANK", "0")), world)
         return
