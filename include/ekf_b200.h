@@ -94,6 +94,23 @@ int ekf_batch_host_sync(ekf_batch_t* h);
 /* number of filters that saw an out-of-order new slot or a non-finite innovation since init            */
 int ekf_batch_fault_count(ekf_batch_t* h, int64_t* count);
 
+/* a3/a4 on the device, per filter (replay_no_ros.py:280-337): gate the window's detections on their per-filter
+ * perturbed camera-frame position (pose_t[0] + noise_tx, pose_t[2] + noise_tz; strict z^2 + x^2 > 2.25 drops),
+ * assign landmark slots in first-seen order in the filter's own slot table, average the window per slot and convert
+ * to range / bearing. Writes the [batch][m] (slot, rng, brg) block ekf_batch_step consumes, in first-seen-in-window
+ * order. det_tag holds compact tag indices in [0, n_tags) (the host maps tag ids and marks IGNORE_TAGS < 0);
+ * noise arrays are [n_det][batch] (or both NULL); tag_slot is [n_tags][batch] (-1 = never seen), n_seen [batch].
+ * Gate decisions, slot tables and update order are bit-exact with the host association.                       */
+int ekf_batch_associate(ekf_batch_t* h, int n_det, const int32_t* det_tag_dev, const double* det_tx_dev,
+                        const double* det_tz_dev, const double* noise_tx_dev, const double* noise_tz_dev,
+                        int n_tags, int32_t* tag_slot_dev, int32_t* n_seen_dev, int32_t* slot_dev, double* rng_dev,
+                        double* brg_dev, int m, void* stream);
+/* windows that held more than m distinct landmarks (the extra ones were dropped) since create              */
+int ekf_batch_associate_overflow_count(ekf_batch_t* h, int64_t* count);
+/* sse_dev[b] += (x_b - gt_x)^2 + (y_b - gt_y)^2 for every filter: absolute trajectory error of the ensemble
+ * against a ground-truth track (the comparison of replay_no_ros.py:519-529 as a number per member)          */
+int ekf_batch_accumulate_ate(ekf_batch_t* h, double gt_x, double gt_y, double* sse_dev, void* stream);
+
 /* ---- large-map mode: ONE filter, P streamed from HBM, optional row-block shard ------------------------- */
 typedef struct ekf_lm ekf_lm_t;
 

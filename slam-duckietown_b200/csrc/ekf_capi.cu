@@ -15,6 +15,7 @@
 #include "ekf_batched.h"
 #include "ekf_common.cuh"
 #include "ekf_largemap.h"
+#include "ekf_ensemble.h"
 
 namespace {
 
@@ -53,7 +54,7 @@ struct ekf_batch {
   // 0 = auto (W-in-registers kernel where it applies: plain form, 1-4 observation slots; else fully staged),
   // 1 = streaming (touched rows/columns staged), 2 = fully staged; EKF_BATCH_KERNEL=auto|stream|staged
   int kernel = 0;
-  unsigned long long* faults = nullptr;  // [0] fault count, [1..2] work / done counters of the persistent kernel
+  unsigned long long* faults = nullptr;  // [0] fault count, [1..2] work / done counters of the persistent kernel, [3] association overflows
   // staging for the host-buffer entry point
   cudaStream_t stream = nullptr;
   double *d_ang = nullptr, *d_lin = nullptr, *d_rng = nullptr, *d_brg = nullptr, *d_pose = nullptr;
@@ -383,6 +384,46 @@ int ekf_batch_fault_count(ekf_batch_t* h, int64_t* count) {
   unsigned long long v = 0;
   CU(cudaMemcpy(&v, h->faults, sizeof(v), cudaMemcpyDeviceToHost));
   *count = (int64_t)v;
+  return EKF_OK;
+}
+
+int ekf_batch_associate(ekf_batch_t* h, int n_det, const int32_t* det_tag_dev, const double* det_tx_dev,
+                        const double* det_tz_dev, const double* noise_tx_dev, const double* noise_tz_dev,
+                        int n_tags, int32_t* tag_slot_dev, int32_t* n_seen_dev, int32_t* slot_dev, double* rng_dev,
+                        double* brg_dev, int m, void* stream) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  if (n_det < 0 || n_tags <= 0) return fail(EKF_EINVAL, "n_det < 0 or n_tags <= 0");
+  if (m < 1 || m > ekf::ASSOC_MAX_M) return fail(EKF_EINVAL, "m must be in [1, %d]", ekf::ASSOC_MAX_M);
+  if ((n_det > 0 && (!det_tag_dev || !det_tx_dev || !det_tz_dev)) || !tag_slot_dev || !n_seen_dev || !slot_dev ||
+      !rng_dev || !brg_dev)
+    return fail(EKF_EINVAL, "null argument");
+  if ((noise_tx_dev == nullptr) != (noise_tz_dev == nullptr)) return fail(EKF_EINVAL, "give both noise arrays or none");
+  CU(cudaSetDevice(h->device));
+  ekf::AssocArgs a{};
+  a.batch = h->batch; a.n_det = n_det; a.n_tags = n_tags; a.m = m;
+  a.det_tag = det_tag_dev; a.det_tx = det_tx_dev; a.det_tz = det_tz_dev;
+  a.noise_tx = noise_tx_dev; a.noise_tz = noise_tz_dev;
+  a.tag_slot = tag_slot_dev; a.n_seen = n_seen_dev;
+  a.slot = slot_dev; a.rng = rng_dev; a.brg = brg_dev;
+  a.overflow = h->faults + 3;
+  CU(ekf::batch_launch_associate(a, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf_batch_associate_overflow_count(ekf_batch_t* h, int64_t* count) {
+  if (!h || !count) return fail(EKF_EINVAL, "null argument");
+  CU(cudaSetDevice(h->device));
+  unsigned long long v = 0;
+  CU(cudaMemcpy(&v, h->faults + 3, sizeof(v), cudaMemcpyDeviceToHost));
+  *count = (int64_t)v;
+  return EKF_OK;
+}
+
+int ekf_batch_accumulate_ate(ekf_batch_t* h, double gt_x, double gt_y, double* sse_dev, void* stream) {
+  if (!h || !sse_dev) return fail(EKF_EINVAL, "null argument");
+  if (!h->mu) return fail(EKF_ESTATE, "state not bound");
+  CU(cudaSetDevice(h->device));
+  CU(ekf::batch_launch_ate(h->mu, h->ld, h->batch, gt_x, gt_y, sse_dev, (cudaStream_t)stream));
   return EKF_OK;
 }
 

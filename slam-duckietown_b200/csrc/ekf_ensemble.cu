@@ -1,0 +1,99 @@
+// ekf_ensemble.cu — the callers' side of the batched Monte Carlo step, on the device (sm_100a):
+//
+//  * batch_associate_kernel — a3/a4 of the reference (src/replay_no_ros.py:280-337) per filter: gate each detection
+//    of the window on its (per-filter perturbed) camera-frame position, assign landmark slots in first-seen order
+//    (the filter's own TAG_INDEX), average the window per slot and convert to range / bearing. Output is exactly the
+//    [B][m] (slot, range, bearing) block the fused step consumes, so per-filter measurement noise needs no host
+//    round trip. Integer bookkeeping (gate decisions, slot tables, update order) is bit-exact
+//    with the host association: the gate and the sums use explicitly rounded IEEE operations (no FMA contraction).
+//  * batch_ate_kernel — accumulates each filter's squared position error against a ground-truth track
+//    (the README's trajectory comparison, replay_no_ros.py:519-529, as a number per ensemble member; §8f-4).
+//
+// One THREAD per filter: the work per filter is a few dozen scalar operations; every per-filter array is laid out
+// [item][B] so that consecutive threads touch consecutive addresses (coalesced), except the [B][m] output block,
+// whose layout is the step kernel's.
+#include "ekf_common.cuh"
+#include "ekf_ensemble.h"
+
+namespace ekf {
+
+__global__ void __launch_bounds__(128) batch_associate_kernel(AssocArgs a) {
+  const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (b >= a.batch) return;
+  const int m = a.m;
+  int bslot[ASSOC_MAX_M];
+  double sx[ASSOC_MAX_M], sz[ASSOC_MAX_M];
+  int cnt[ASSOC_MAX_M];
+  int nb = 0;                      // buckets in use, first-seen-in-window order (:313 iterates the dict in that order)
+  int seen = a.n_seen[b];          // len(TAG_INDEX) of this filter
+  bool overflow = false;
+  for (int d = 0; d < a.n_det; ++d) {
+    const int tag = a.det_tag[d];  // compact tag index; < 0 = ignored tag (IGNORE_TAGS, :286)
+    if (tag < 0 || tag >= a.n_tags) continue;
+    double tx = a.det_tx[d], tz = a.det_tz[d];
+    if (a.noise_tx) {
+      tx = __dadd_rn(tx, a.noise_tx[(int64_t)d * a.batch + b]);
+      tz = __dadd_rn(tz, a.noise_tz[(int64_t)d * a.batch + b]);
+    }
+    // pose_t[2]^2 + pose_t[0]^2 > 1.5^2 drops the detection (:289), strict, on the raw per-detection value
+    if (__dadd_rn(__dmul_rn(tz, tz), __dmul_rn(tx, tx)) > 2.25) continue;
+    int32_t* cell = a.tag_slot + (int64_t)tag * a.batch + b;
+    int s = *cell;
+    if (s < 0) {                   // first sighting ever: slot = len(TAG_INDEX) (:294-295)
+      s = seen++;
+      *cell = s;
+    }
+    int k = 0;
+    while (k < nb && bslot[k] != s) ++k;
+    if (k == nb) {
+      if (nb == m) {               // more distinct landmarks in one window than the step block holds
+        overflow = true;
+        continue;
+      }
+      bslot[nb] = s; sx[nb] = 0.0; sz[nb] = 0.0; cnt[nb] = 0;
+      ++nb;
+    }
+    sx[k] = __dadd_rn(sx[k], tx);  // sequential sums == np.mean over the window axis (:311)
+    sz[k] = __dadd_rn(sz[k], tz);
+    ++cnt[k];
+  }
+  a.n_seen[b] = seen;
+  if (overflow) atomicAdd(a.overflow, 1ULL);
+  for (int k = 0; k < m; ++k) {
+    int s = -1;
+    double r = 0.0, be = 0.0;
+    if (k < nb) {
+      const double n = (double)cnt[k];
+      const double x = sz[k] / n, y = -(sx[k] / n);              // x = t[2], y = -t[0] (:316)
+      r = sqrt(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)));      // :327
+      be = atan2(y, x);                                           // :328
+      s = bslot[k];
+    }
+    a.slot[b * m + k] = s;
+    a.rng[b * m + k] = r;
+    a.brg[b * m + k] = be;
+  }
+}
+
+__global__ void __launch_bounds__(256) batch_ate_kernel(const double* __restrict__ mu, int64_t mu_stride,
+                                                        int64_t batch, double gx, double gy,
+                                                        double* __restrict__ sse) {
+  const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  const double ex = mu[b * mu_stride] - gx, ey = mu[b * mu_stride + 1] - gy;
+  sse[b] += ex * ex + ey * ey;
+}
+
+cudaError_t batch_launch_associate(const AssocArgs& a, cudaStream_t st) {
+  if (a.m < 1 || a.m > ASSOC_MAX_M) return cudaErrorInvalidValue;
+  batch_associate_kernel<<<(unsigned)((a.batch + 127) / 128), 128, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t batch_launch_ate(const double* mu, int64_t mu_stride, int64_t batch, double gx, double gy, double* sse,
+                             cudaStream_t st) {
+  batch_ate_kernel<<<(unsigned)((batch + 255) / 256), 256, 0, st>>>(mu, mu_stride, batch, gx, gy, sse);
+  return cudaGetLastError();
+}
+
+}  // namespace ekf

@@ -1,0 +1,30 @@
+// ekf_ensemble.h — device-side association and ensemble error metrics of the batched mode (internal).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ekf {
+
+constexpr int ASSOC_MAX_M = 8;  // == BATCH_MAX_M: observation slots of one filter-step
+
+struct AssocArgs {
+  int64_t batch;
+  int n_det, n_tags, m;
+  const int32_t* det_tag;   // [n_det] compact tag index (host maps tag ids; < 0 = ignored tag)
+  const double* det_tx;     // [n_det] pose_t[0] of each detection of the window, in window order
+  const double* det_tz;     // [n_det] pose_t[2]
+  const double* noise_tx;   // [n_det][B] per-filter perturbation added to pose_t[0] (null = none)
+  const double* noise_tz;   // [n_det][B]
+  int32_t* tag_slot;        // [n_tags][B] slot of a tag in this filter's TAG_INDEX, -1 = never seen
+  int32_t* n_seen;          // [B] len(TAG_INDEX)
+  int32_t* slot;            // out [B][m], -1 = unused
+  double* rng;              // out [B][m]
+  double* brg;              // out [B][m]
+  unsigned long long* overflow;  // windows that held more than m distinct landmarks
+};
+
+cudaError_t batch_launch_associate(const AssocArgs& a, cudaStream_t st);
+cudaError_t batch_launch_ate(const double* mu, int64_t mu_stride, int64_t batch, double gx, double gy, double* sse,
+                             cudaStream_t st);
+
+}  // namespace ekf

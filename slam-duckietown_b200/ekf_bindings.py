@@ -312,6 +312,38 @@ class BatchedEKF:
                   float(wheel_radius), float(baseline), int(resolution), _ptr(slot) if m else z,
                   _ptr(rng) if m else z, _ptr(brg) if m else z, m, _stream_ptr(self.torch))
 
+    def new_slot_table(self, n_tags: int):
+        """Per-filter TAG_INDEX on the device: (tag_slot int32 [n_tags, B] filled with -1, n_seen int32 [B])."""
+        t = self.torch
+        return (t.full((int(n_tags), self.batch), -1, dtype=t.int32, device=self.dev),
+                t.zeros(self.batch, dtype=t.int32, device=self.dev))
+
+    def associate(self, det_tag, det_tx, det_tz, tag_slot, n_seen, m, noise_tx=None, noise_tz=None):
+        """a3/a4 on the device for every filter (replay_no_ros.py:280-337): the window's detections — compact tag
+        index int32 (D,), pose_t[0] and pose_t[2] (D,), optional per-filter perturbations (D, B) — become the
+        (slot, rng, brg) tensors of shape (B, m) that ``step`` takes; ``tag_slot`` / ``n_seen`` are updated in
+        place. All arguments are DEVICE tensors."""
+        t = self.torch
+        d = int(det_tag.shape[0])
+        slot = t.empty((self.batch, m), dtype=t.int32, device=self.dev)
+        rng = t.empty((self.batch, m), dtype=t.float64, device=self.dev)
+        brg = t.empty((self.batch, m), dtype=t.float64, device=self.dev)
+        z = C.c_void_p(0)
+        capi.call("ekf_batch_associate", self._h, d, _ptr(det_tag) if d else z, _ptr(det_tx) if d else z,
+                  _ptr(det_tz) if d else z, _ptr(noise_tx) if noise_tx is not None else z,
+                  _ptr(noise_tz) if noise_tz is not None else z, int(tag_slot.shape[0]), _ptr(tag_slot),
+                  _ptr(n_seen), _ptr(slot), _ptr(rng), _ptr(brg), int(m), _stream_ptr(t))
+        return slot, rng, brg
+
+    def associate_overflow_count(self) -> int:
+        v = C.c_int64(0)
+        capi.call("ekf_batch_associate_overflow_count", self._h, C.byref(v))
+        return int(v.value)
+
+    def accumulate_ate(self, gt_x: float, gt_y: float, sse):
+        """sse[b] += squared position error of filter b against the ground-truth point (device tensor (B,))."""
+        capi.call("ekf_batch_accumulate_ate", self._h, float(gt_x), float(gt_y), _ptr(sse), _stream_ptr(self.torch))
+
     def step_host(self, ang, lin, slot, rng, brg, pose_out):
         """End-to-end step with HOST (ideally pinned) torch tensors / numpy arrays: H2D, step, D2H of the
         pose (B, 3) into ``pose_out``; synchronous."""

@@ -455,3 +455,75 @@ def test_large_map_full_size_properties(eb):
     d = torch.sqrt(torch.diagonal(outs[0][1]))
     rel = ((outs[0][1] - outs[1][1]).abs() / (d[:, None] * d[None, :])).max()
     assert float(rel) < 1e-9
+
+
+# ---------------------------------------------------------------------------------------------------------
+# device-side association (a3/a4 per filter) and ensemble trajectory error
+# ---------------------------------------------------------------------------------------------------------
+def test_device_association_matches_host_and_feeds_step(eb):
+    """ekf_batch_associate on per-filter perturbed detections == the host association (ekf_bindings.
+    associate_window, itself pinned to replay_no_ros.py:280-337) run filter by filter: gate decisions, slot tables
+    and update order bit-exact, range/bearing to 1e-12; the (slot, rng, brg) block then drives the fused step and
+    the state matches the oracle fed by the host association."""
+    import torch
+    from slam_duckietown_b200.replay import make_detection
+    rs = np.random.default_rng(11)
+    B, L, m, T, n_tags = 40, 12, 8, 12, 10      # m = 8 >= detections per window: no overflow
+    tag_ids = [80, 44, 41, 26, 110, 106, 101, 31, 65, 23]
+    ignore = (41,)
+    world = rs.uniform([-0.2, -1.2], [1.6, 1.2], size=(n_tags, 2))     # camera-frame (x fwd, y left), near the gate
+    f = eb.BatchedEKF(B, L)
+    mv, mm = rs.uniform(0.05, 0.3, B), rs.uniform(0.1, 0.8, B)
+    f.set_noise(mv, mm)
+    f.init(0.1)
+    tag_slot, n_seen = f.new_slot_table(n_tags)
+    host_index = [dict() for _ in range(B)]
+    n = 3 + 2 * L
+    c0 = np.zeros((n, n)); c0[:3, :3] = np.eye(3) * 0.1
+    st = [(np.zeros(n), c0.copy(), 0) for _ in range(B)]
+    sse = torch.zeros(B, dtype=torch.float64, device=f.dev)
+    sse_ref = np.zeros(B)
+    for t in range(T):
+        D = int(rs.integers(0, 9))
+        which = rs.integers(0, n_tags, D)
+        tx = -(world[which, 1] + rs.normal(0, 0.05, D))               # pose_t[0] = -y_rel
+        tz = world[which, 0] + rs.normal(0, 0.05, D)                  # pose_t[2] = x_rel
+        if D:
+            tz[0] = np.sqrt(max(2.25 - tx[0] * tx[0], 0.0))            # a detection sitting right on the 1.5 m gate
+        ntx, ntz = rs.normal(0, 0.03, (D, B)), rs.normal(0, 0.03, (D, B))
+        if D:
+            ntx[0, ::2] = 0.0
+            ntz[0, ::2] = 0.0
+        compact = np.array([-1 if tag_ids[w] in ignore else w for w in which], dtype=np.int32)
+        slot, rng, brg = f.associate(_dev(f.dev, compact), _dev(f.dev, tx), _dev(f.dev, tz), tag_slot, n_seen, m,
+                                     _dev(f.dev, ntx), _dev(f.dev, ntz))
+        ang, lin = rs.normal(0.08, 0.05, B), np.abs(rs.normal(0.05, 0.02, B))
+        slot_h, rng_h, brg_h = slot.cpu().numpy(), rng.cpu().numpy(), brg.cpu().numpy()
+        for b in range(B):
+            dets = [make_detection(tag_ids[which[d]], [tx[d] + ntx[d, b], 0.0, tz[d] + ntz[d, b]]) for d in range(D)]
+            mean, cov, nk = st[b]
+            tags = eb.associate_window(mean, [("0", dets)], host_index[b], ignore)
+            order = list(tags.keys())[:m]
+            assert list(slot_h[b, :len(order)]) == order and np.all(slot_h[b, len(order):] == -1), (t, b)
+            for k, s in enumerate(order):
+                assert abs(rng_h[b, k] - tags[s][4]) <= 1e-12 * max(1.0, abs(tags[s][4]))
+                assert abs(brg_h[b, k] - tags[s][5]) <= 1e-12
+            obs = [(s, tags[s][4], tags[s][5]) for s in order]
+            fl = eo.Flags(motion_var=float(mv[b]), meas_var=float(mm[b]))
+            mean2, cov2, nk = eo.step_from_observations(mean, cov, float(ang[b]), float(lin[b]), obs, fl, nk)
+            st[b] = (mean2, cov2, nk)
+            sse_ref[b] += (mean2[0] - 0.1 * t) ** 2 + (mean2[1] + 0.05 * t) ** 2
+        f.step(_dev(f.dev, ang), _dev(f.dev, lin), slot, rng, brg)
+        f.accumulate_ate(0.1 * t, -0.05 * t, sse)
+    assert f.fault_count() == 0 and f.associate_overflow_count() == 0
+    ts = tag_slot.cpu().numpy()
+    for b in range(B):
+        want = np.full(n_tags, -1)
+        for tid, s in host_index[b].items():
+            want[tag_ids.index(tid)] = s
+        assert np.array_equal(ts[:, b], want), f"slot table of filter {b}"
+        assert int(n_seen[b]) == len(host_index[b])
+    mu, p = f.state()
+    for b in range(B):
+        assert_parity(mu[b], p[b], st[b][0], st[b][1], what=f"device association pipeline b={b}")
+    assert np.allclose(sse.cpu().numpy(), sse_ref, rtol=1e-9, atol=1e-12)
