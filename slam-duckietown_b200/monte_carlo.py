@@ -1,0 +1,76 @@
+"""Batched Monte Carlo replay of ONE decoded bag (BASELINE.json configs[1] fed from events.csv instead of a
+synthetic trajectory): B filters see the same encoder ticks and the same AprilTag detections, each with its own
+process / measurement noise parameters and its own perturbation of the detections, and everything after the
+event parsing runs on the device:
+
+    windows_from_events (host, once)  ->  per step:  associate (a3/a4, per filter)  ->  step_ticks (a1/a2 + fused
+    a5-a11)  ->  accumulate_ate (against the stream's ground_truth events)
+
+This is the README's ablation study (README.md:421-492: sweeps of MOTION_MODEL_VARIANCE / MEASUREMENT_MODEL_VARIANCE
+judged by eye on plots) as numbers: an absolute-trajectory RMSE per ensemble member. With zero perturbation and the
+reference's noise flags every member reproduces the scalar replay (tests/test_gpu_parity.py).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import ekf_bindings as eb
+from .replay import BASELINE, RESOLUTION, WHEEL_RADIUS
+
+
+def compact_tag_table(windows, ignore_tags=()):
+    """tag id -> compact index in first-appearance order over the whole stream; ignored tags are left out."""
+    table = {}
+    for w in windows:
+        for t in w.tag_id:
+            t = int(t)
+            if t not in ignore_tags and t not in table:
+                table[t] = len(table)
+    return table
+
+
+def monte_carlo_replay(windows, batch, n_landmarks, m, motion_var, meas_var, det_sigma=0.0, seed=0,
+                       ignore_tags=None, device=0, joseph=False, on_step=None):
+    """Returns dict(rmse (B,), pose (B,3), n_landmarks_seen (B,), faults, overflows, steps, tag_table (tag id ->
+    compact index), tag_slot (n_tags, B) per-member slot of each compact tag, filter=BatchedEKF).
+
+    motion_var / meas_var: scalars or (B,) arrays (MOTION_MODEL_VARIANCE / MEASUREMENT_MODEL_VARIANCE per member);
+    det_sigma: std-dev (m) of the per-member Gaussian perturbation of each detection's pose_t[0] / pose_t[2]."""
+    import torch
+    ignore = tuple(eb._flag("IGNORE_TAGS")) if ignore_tags is None else tuple(ignore_tags)
+    f = eb.BatchedEKF(batch, n_landmarks, device=device)
+    dev = f.dev
+    f.set_noise(np.broadcast_to(np.asarray(motion_var, dtype=np.float64), (batch,)).copy(),
+                np.broadcast_to(np.asarray(meas_var, dtype=np.float64), (batch,)).copy())
+    f.set_flags(joseph=joseph)
+    f.init(float(np.asarray(motion_var, dtype=np.float64).reshape(-1)[0]))     # replay_no_ros.py:70
+    table = compact_tag_table(windows, ignore)
+    tag_slot, n_seen = f.new_slot_table(max(len(table), 1))
+    sse = torch.zeros(batch, dtype=torch.float64, device=dev)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(int(seed))
+    scored = 0
+
+    def full(v):
+        return torch.full((batch,), int(v), dtype=torch.int32, device=dev)
+    for w in windows:
+        d = len(w.tag_id)
+        compact = torch.tensor([table.get(int(t), -1) for t in w.tag_id], dtype=torch.int32, device=dev)
+        tx = torch.from_numpy(w.tx).to(dev)
+        tz = torch.from_numpy(w.tz).to(dev)
+        ntx = ntz = None
+        if det_sigma > 0.0 and d:
+            ntx = torch.randn((d, batch), dtype=torch.float64, device=dev, generator=gen) * det_sigma
+            ntz = torch.randn((d, batch), dtype=torch.float64, device=dev, generator=gen) * det_sigma
+        slot, rng, brg = f.associate(compact, tx, tz, tag_slot, n_seen, m, ntx, ntz)
+        f.step_ticks(full(w.ticks_l), full(w.ticks_r), full(w.prev_l), full(w.prev_r), WHEEL_RADIUS, BASELINE,
+                     RESOLUTION, slot, rng, brg)
+        if w.ground_truth is not None:
+            f.accumulate_ate(w.ground_truth[0], w.ground_truth[1], sse)
+            scored += 1
+        if on_step:
+            on_step(f, w)
+    rmse = torch.sqrt(sse / max(scored, 1)).cpu().numpy()
+    return dict(rmse=rmse, pose=f.mu[:, :3].cpu().numpy(), n_landmarks_seen=n_seen.cpu().numpy(),
+                faults=f.fault_count(), overflows=f.associate_overflow_count(), steps=len(windows),
+                scored_steps=scored, tag_table=table, tag_slot=tag_slot.cpu().numpy(), filter=f)

@@ -527,3 +527,50 @@ def test_device_association_matches_host_and_feeds_step(eb):
     for b in range(B):
         assert_parity(mu[b], p[b], st[b][0], st[b][1], what=f"device association pipeline b={b}")
     assert np.allclose(sse.cpu().numpy(), sse_ref, rtol=1e-9, atol=1e-12)
+
+
+def test_monte_carlo_replay_of_decoded_bag(eb, surrogate):
+    """events.csv -> windows -> device association -> tick-odometry fused step, 64 ensemble members. With zero
+    perturbation and the reference's noise flags EVERY member must reproduce the reference's own replay() of the
+    same events at each of the 70 steps (state, slot order); with perturbation the members differ, stay finite and
+    fault-free, and the ATE accumulator equals a host recomputation."""
+    import torch
+    from slam_duckietown_b200 import events_io as io, monte_carlo as mc
+    lines, dets, ref = surrogate
+    wins = io.windows_from_events([io.parse_event_line(l) for l in lines], dets)
+    B, L, m = 64, 16, 6
+    step = {"i": 0, "worst": 0.0}
+    track = []
+
+    def check(f, w):
+        i = step["i"]
+        n = int(ref["n"][i])
+        mu, p = f.state(0, B)
+        for b in (0, B - 1):
+            e = assert_parity(mu[b][:n], p[b][:n, :n], ref["mean"][i][:n], ref["cov"][i][:n, :n], what=f"MC step {i} b={b}")
+            step["worst"] = max(step["worst"], *e)
+            assert np.all(mu[b][n:] == 0.0)
+        track.append((mu[:, 0].copy(), mu[:, 1].copy(), w.ground_truth))
+        step["i"] += 1
+    out = mc.monte_carlo_replay(wins, B, L, m, eb._flag("MOTION_MODEL_VARIANCE"), eb._flag("MEASUREMENT_MODEL_VARIANCE"),
+                                det_sigma=0.0, on_step=check)
+    assert step["i"] == 70 and out["faults"] == 0 and out["overflows"] == 0
+    for b in (0, B - 1):                                                           # per-member TAG_INDEX == reference's
+        got = {tid: int(out["tag_slot"][c, b]) for tid, c in out["tag_table"].items() if out["tag_slot"][c, b] >= 0}
+        assert got == {int(t): int(s) for t, s in zip(ref["tag_ids"], ref["tag_slots"])}
+    assert np.all(out["n_landmarks_seen"] == len(ref["tag_ids"]))
+    sse = np.zeros(B)
+    cnt = 0
+    for x, y, gt in track:
+        if gt is not None:
+            sse += (x - gt[0]) ** 2 + (y - gt[1]) ** 2
+            cnt += 1
+    assert cnt == out["scored_steps"] > 0
+    assert np.allclose(out["rmse"], np.sqrt(sse / cnt), rtol=1e-12, atol=0)
+    assert np.all(out["rmse"] == out["rmse"][0])                                   # identical members
+    print(f"monte carlo replay: worst parity {step['worst']:.3e}, ATE rmse {out['rmse'][0]:.4f} m")
+    rs = np.random.default_rng(5)
+    out2 = mc.monte_carlo_replay(wins, B, L, m, np.exp(rs.uniform(np.log(0.05), np.log(1.0), B)),
+                                 np.exp(rs.uniform(np.log(0.05), np.log(1.5), B)), det_sigma=0.02, seed=7)
+    assert out2["faults"] == 0 and np.all(np.isfinite(out2["rmse"])) and np.all(np.isfinite(out2["pose"]))
+    assert len(np.unique(out2["rmse"])) > B // 2
