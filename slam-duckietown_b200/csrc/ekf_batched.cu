@@ -110,8 +110,8 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
         double sb, cb;
         sincos(be + pth, &sb, &cb);
         if (lane == 0) {
-          sMu[j] = px + r * cb;
-          sMu[j + 1] = py + r * sb;
+          sMu[j] = __dadd_rn(px, __dmul_rn(r, cb));
+          sMu[j + 1] = __dadd_rn(py, __dmul_rn(r, sb));
           sP[j * LD + j] = kNewLandmarkVar;
           sP[(j + 1) * LD + j + 1] = kNewLandmarkVar;
         }
@@ -136,8 +136,8 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
       const int t = lane + 32 * p;
       if (t < N) {
         const double p2 = sP[2 * LD + t];
-        sP[0 * LD + t] += g0 * p2;
-        sP[1 * LD + t] += g1 * p2;
+        sP[0 * LD + t] = fma(g0, p2, sP[0 * LD + t]);
+        sP[1 * LD + t] = fma(g1, p2, sP[1 * LD + t]);
       }
     }
     __syncwarp();
@@ -147,12 +147,12 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
       if (i < N) {
         double* row = sP + i * LD;
         const double p2 = row[2];
-        double r0 = row[0] + g0 * p2, r1 = row[1] + g1 * p2;
-        if (i == 0) r0 += mv * mv;           // F^T R F (:421-430)
-        if (i == 1) r1 += mv * mv;
+        double r0 = fma(g0, p2, row[0]), r1 = fma(g1, p2, row[1]);
+        if (i == 0) r0 = __dadd_rn(r0, __dmul_rn(mv, mv));           // F^T R F (:421-430)
+        if (i == 1) r1 = __dadd_rn(r1, __dmul_rn(mv, mv));
         row[0] = r0;
         row[1] = r1;
-        if (i == 2) row[2] = p2 + (mv / 2.0) * (mv / 2.0);
+        if (i == 2) row[2] = __dadd_rn(p2, __dmul_rn(mv / 2.0, mv / 2.0));
       }
     }
     __syncwarp();
@@ -263,8 +263,8 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
       const int t = lane + 32 * p;
       if (t < LD) {
         d2 kk;
-        kk.x = pht0[p] * Si[0][0] + pht1[p] * Si[1][0];
-        kk.y = pht0[p] * Si[0][1] + pht1[p] * Si[1][1];
+        kk.x = dot2(pht0[p], Si[0][0], pht1[p], Si[1][0]);
+        kk.y = dot2(pht0[p], Si[0][1], pht1[p], Si[1][1]);
         *reinterpret_cast<d2*>(ku + 2 * t) = kk;  // zero for the pad row
         if (JOSEPH) {
           wu[t] = hp0[p] - qn * kk.x;
@@ -274,7 +274,7 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
           av.y = pht1[p] - (kk.x * Sq[0][1] + kk.y * Sq[1][1]);
           *reinterpret_cast<d2*>(sA + u * HIST + 2 * t) = av;
         }
-        if (t < N) sMu[t] += kk.x * in.y0 + kk.y * in.y1;
+        if (t < N) sMu[t] = mu_inc(sMu[t], kk.x, kk.y, in.y0, in.y1);
       }
     }
     __syncwarp();

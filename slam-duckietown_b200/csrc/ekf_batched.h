@@ -37,6 +37,10 @@ cudaError_t batch_launch_step_stream(int n_landmarks, const BatchStepArgs& a, in
 bool batch_regw_supported(int m);
 size_t batch_regw_smem_bytes(int n_landmarks, int m);
 cudaError_t batch_launch_step_regw(int n_landmarks, const BatchStepArgs& a, int64_t batch, cudaStream_t st);
+// sub-warp groups for small filters (ekf_batched_group.cu): 8 or 16 lanes per filter, plain form, 1 <= m <= 4
+bool batch_group_supported(int n_landmarks, int m);
+cudaError_t batch_launch_step_group(int n_landmarks, int group_width, const BatchStepArgs& a, int64_t batch,
+                                    cudaStream_t st);
 cudaError_t batch_launch_init(double* mu, double* P, int* n_known, int64_t batch, int n, int ld, double p0,
                               cudaStream_t st);
 cudaError_t batch_launch_pack(double* mu, double* P, const double* mean_ref, const double* cov_ref,

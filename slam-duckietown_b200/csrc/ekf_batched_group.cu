@@ -1,0 +1,384 @@
+// ekf_batched_group.cu — fused EKF-SLAM filter-step for SMALL filters: a GROUP of GW lanes (8 or 16) per filter,
+// 32 / GW filters per warp (sm_100a, fp64).
+//
+// Same reference semantics (src/replay_no_ros.py:341-480), the same algorithm and the same per-element operation
+// sequence as batch_step_regw_kernel (ekf_batched_regw.cu) — results are bitwise equal. What changes is the SIMD
+// mapping. With a whole warp per filter the group-uniform scalar chain of a step (sincos, m x {innovation, atan2,
+// sqrt, reciprocals, S, S^-1}) is issued once per FILTER and computed 32 times redundantly; at n = 19 that chain is
+// ~45 % of the 1 376 warp-instructions of a filter-step and the kernel is issue/latency bound at 47 % of the HBM
+// peak (ncu, profiles/r1h_batchM.*). Here one instruction stream serves 32 / GW filters: lanes of a group own
+// columns t = gl, gl + GW, ... of THEIR filter's covariance (staged in the group's slice of shared memory), the
+// scalar chain of the 32 / GW filters runs in the same instructions, and shuffles / barriers use the group's
+// lane mask, so groups whose observation patterns differ may diverge without deadlock.
+// Plain covariance form, compile-time observation count m <= GW.
+#include "ekf_batched.h"
+#include "ekf_batched_dev.cuh"
+
+namespace ekf {
+
+namespace {
+
+template <int GW>
+__device__ __forceinline__ double gshfl(unsigned gmask, double v, int src) {
+  return __shfl_sync(gmask, v, src, GW);
+}
+template <int GW>
+__device__ __forceinline__ int gshfl(unsigned gmask, int v, int src) {
+  return __shfl_sync(gmask, v, src, GW);
+}
+
+// value of column c (group-uniform) from the lane of the group that owns it (column c lives in lane c % GW, half
+// c / GW): every lane offers its value of that half
+template <int GW, int NT>
+__device__ __forceinline__ double gcol(unsigned gmask, const double (&x)[NT], int c) {
+  const int p = c / GW;
+  double mine = x[0];
+#pragma unroll
+  for (int q = 1; q < NT; ++q)
+    if (p == q) mine = x[q];
+  return gshfl<GW>(gmask, mine, c - p * GW);
+}
+
+}  // namespace
+
+template <int NLM, int MT, int GW>
+__global__ void __launch_bounds__(32) batch_step_group_kernel(BatchStepArgs a, int64_t batch) {
+  constexpr int N = 3 + 2 * NLM;
+  constexpr int LD = (N + 3) & ~3;
+  constexpr int HIST = 2 * LD;          // doubles of one update's K record: [LD][2]
+  constexpr int NT = (LD + GW - 1) / GW;  // lane gl handles indices gl, gl + GW, ...
+  constexpr int FPW = 32 / GW;          // filters per warp
+  constexpr int m = MT;
+  constexpr int SLICE = N * LD + LD + m * HIST + 2;  // doubles of shared memory per filter
+  static_assert(GW == 8 || GW == 16, "group width");
+  static_assert(MT >= 1 && MT <= GW && MT <= BATCH_MAX_M, "observation count");
+  static_assert(SLICE % 2 == 0, "16-byte aligned slices");
+
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int lane = threadIdx.x;
+  const int g = lane / GW, gl = lane - g * GW;
+  const unsigned gmask = (GW == 16 ? 0xffffu : 0xffu) << (g * GW);
+  const int64_t b = (int64_t)blockIdx.x * FPW + g;
+  if (b >= batch) return;  // the whole group leaves; the other groups only ever synchronise among themselves
+  double* sP = reinterpret_cast<double*>(smem_raw) + g * SLICE;  // [N][LD]
+  double* sMu = sP + N * LD;                                     // [LD]
+  double* sK = sMu + LD;                                         // [m][LD][2]  (K_u[i,0], K_u[i,1]) pairs
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sK + m * HIST);    // [2]: mu, P
+  double* __restrict__ gP = a.P + b * (int64_t)(N * LD);
+  double* __restrict__ gMu = a.mu + b * (int64_t)LD;
+
+  // ---- phase 0: TMA bulk loads (mu on its own mbarrier) + per-filter inputs ------------------------------
+  if (gl == 0) {
+    mbar_init(bar, 1);
+    mbar_init(bar + 1, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_expect_tx(bar, (uint32_t)(LD * sizeof(double)));
+    tma_bulk_g2s(sMu, gMu, (uint32_t)(LD * sizeof(double)), bar);
+    mbar_expect_tx(bar + 1, (uint32_t)(N * LD * sizeof(double)));
+    tma_bulk_g2s(sP, gP, (uint32_t)(N * LD * sizeof(double)), bar + 1);
+  }
+  double ang, lin;
+  if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
+    const double dl = delta_phi(a.ticks_l[b], a.prev_l[b], a.resolution);
+    const double dr = delta_phi(a.ticks_r[b], a.prev_r[b], a.resolution);
+    displacement(a.wheel_radius, a.baseline, dl, dr, &ang, &lin);
+  } else {
+    ang = a.ang[b];
+    lin = a.lin[b];
+  }
+  const double mv = a.motion_var[b];
+  const double mm = a.meas_var[b];
+  const double qn = mm * mm;
+  int nk = a.n_known[b];
+  double o_rng = 0.0, o_brg = 0.0;  // observation u lives in lane u of the group
+  int o_slot = -1;
+  if (gl < m) {
+    o_slot = a.slot[b * m + gl];
+    o_rng = a.rng[b * m + gl];
+    o_brg = a.brg[b * m + gl];
+  }
+  __syncwarp(gmask);
+  mbar_wait(bar, 0);
+
+  // robot rows / columns of the CURRENT covariance, lane t: rr[k][p] = P[k][t], rc[k][p] = P[t][k], t = gl + GW p
+  double rr[3][NT], rc[3][NT];
+
+  // ---- phase 1: augment (:355-360) + motion model (:368-417), group-uniform ------------------------------
+  unsigned valid = 0;   // bit u: update u is applied
+  unsigned fresh = 0;   // bit u: update u is the first sighting of its landmark
+  int sl[m];            // slot of observation u (group-uniform)
+  {
+    const double px = sMu[0], py = sMu[1], pth = sMu[2];
+    double sn, cs;  // even lanes sincos(theta), odd lanes sincos(theta + ang): one call instead of two
+    sincos((gl & 1) ? pth + ang : pth, &sn, &cs);
+    const double s1 = gshfl<GW>(gmask, sn, 0), c1 = gshfl<GW>(gmask, cs, 0);
+    const double s2 = gshfl<GW>(gmask, sn, 1), c2 = gshfl<GW>(gmask, cs, 1);
+    int fault = 0;
+#pragma unroll
+    for (int u = 0; u < m; ++u) {
+      const int s = gshfl<GW>(gmask, o_slot, u);
+      sl[u] = s;
+      if (s < 0) continue;
+      if (s >= NLM || s > nk) {  // beyond capacity, or a slot that skips first-seen order (:359 KeyError)
+        fault = 1;
+        continue;
+      }
+      valid |= 1u << u;
+      if (s == nk) {  // first sighting: initialise from the PRE-predict pose (:331-332, :359-360)
+        const int j = 3 + 2 * s;
+        const double r = gshfl<GW>(gmask, o_rng, u), be = gshfl<GW>(gmask, o_brg, u);
+        double sb, cb;
+        sincos(be + pth, &sb, &cb);
+        if (gl == 0) {
+          sMu[j] = __dadd_rn(px, __dmul_rn(r, cb));
+          sMu[j + 1] = __dadd_rn(py, __dmul_rn(r, sb));
+        }
+        fresh |= 1u << u;
+        ++nk;
+      }
+    }
+    if (!(a.flags & kFlagMeasurement)) valid = 0;
+    const Motion mo = motion_from_sincos(pth, ang, lin, a.flags, s1, c1, s2, c2);
+    if (gl == 0) {
+      sMu[0] = px + mo.dx;
+      sMu[1] = py + mo.dy;
+      sMu[2] = mo.theta;
+      a.n_known[b] = nk;
+      if (fault) atomicAdd(a.faults, 1ULL);
+    }
+    mbar_wait(bar + 1, 0);
+    if (fresh && gl == 0) {  // new landmarks' diagonals (:356-357)
+#pragma unroll
+      for (int u = 0; u < m; ++u)
+        if ((fresh >> u) & 1u) {
+          const int j = 3 + 2 * sl[u];
+          sP[j * LD + j] = kNewLandmarkVar;
+          sP[(j + 1) * LD + j + 1] = kNewLandmarkVar;
+        }
+    }
+    __syncwarp(gmask);
+    // predict covariance (:420-430): rows 0-1 += g * row 2 over ALL columns, then columns 0-1 += g * column 2
+    // over ALL rows (using the updated rows 0-1), then the three noise terms
+    const double g0 = mo.g0, g1 = mo.g1;
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      const int t = gl + GW * p;
+      rr[0][p] = rr[1][p] = rr[2][p] = 0.0;
+      if (t < N) {
+        const double p2 = sP[2 * LD + t];
+        rr[0][p] = fma(g0, p2, sP[0 * LD + t]);
+        rr[1][p] = fma(g1, p2, sP[1 * LD + t]);
+        rr[2][p] = p2;
+        sP[0 * LD + t] = rr[0][p];
+        sP[1 * LD + t] = rr[1][p];
+      }
+    }
+    __syncwarp(gmask);
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      const int i = gl + GW * p;
+      rc[0][p] = rc[1][p] = rc[2][p] = 0.0;
+      if (i < N) {
+        double* row = sP + i * LD;
+        const d2 r01 = lds128(row);
+        const double p2 = row[2];
+        double r0 = fma(g0, p2, r01.x), r1 = fma(g1, p2, r01.y), r2 = p2;
+        if (i == 0) r0 = __dadd_rn(r0, __dmul_rn(mv, mv));  // F^T R F (:421-430)
+        if (i == 1) r1 = __dadd_rn(r1, __dmul_rn(mv, mv));
+        if (i == 2) r2 = __dadd_rn(p2, __dmul_rn(mv / 2.0, mv / 2.0));
+        d2 o;
+        o.x = r0; o.y = r1;
+        *reinterpret_cast<d2*>(row) = o;
+        if (i == 2) row[2] = r2;
+        rc[0][p] = r0; rc[1][p] = r1; rc[2][p] = r2;
+      }
+    }
+    __syncwarp(gmask);
+    if (gl < 3) {  // the 3x3 robot block was changed by the column pass: refresh the row registers
+      rr[0][0] = sP[0 * LD + gl];
+      rr[1][0] = sP[1 * LD + gl];
+      rr[2][0] = sP[2 * LD + gl];
+    }
+  }
+
+  // ---- phase 2: sequential updates on the touched rows / columns only ------------------------------------
+  // history in registers: hW[u][.][p] = W_u[:, t], hK[u][p] = K_u[t, :] of this lane's t = gl + GW p
+  double hW0[m][NT], hW1[m][NT];
+  d2 hK[m][NT];
+#pragma unroll
+  for (int u = 0; u < m; ++u) {
+    if (!((valid >> u) & 1u)) continue;  // group-uniform
+    const double z_rng = gshfl<GW>(gmask, o_rng, u), z_brg = gshfl<GW>(gmask, o_brg, u);
+    const int j = 3 + 2 * sl[u];
+    // (a) innovation and H5 (:443-469), group-uniform
+    const Innov in = innovation(sMu[0], sMu[1], sMu[2], sMu[j], sMu[j + 1], z_rng, z_brg);
+    // (b) landmark rows / columns j, j+1 from the staged P0, brought up to date with the earlier updates
+    double lr[2][NT], lc[2][NT];
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      const int t = gl + GW * p;
+      const bool inld = (t < LD), real = (t < N);
+      lr[0][p] = inld ? sP[j * LD + t] : 0.0;
+      lr[1][p] = inld ? sP[(j + 1) * LD + t] : 0.0;
+      lc[0][p] = real ? sP[t * LD + j] : 0.0;
+      lc[1][p] = real ? sP[t * LD + j + 1] : 0.0;
+    }
+#pragma unroll
+    for (int w = 0; w < m - 1; ++w) {  // static trip count keeps the register history statically indexed
+      if (w >= u || !((valid >> w) & 1u)) continue;
+      const d2 kj0 = lds128(sK + w * HIST + 2 * j), kj1 = lds128(sK + w * HIST + 2 * j + 2);
+      const double w0j0 = gcol<GW, NT>(gmask, hW0[w], j), w1j0 = gcol<GW, NT>(gmask, hW1[w], j);
+      const double w0j1 = gcol<GW, NT>(gmask, hW0[w], j + 1), w1j1 = gcol<GW, NT>(gmask, hW1[w], j + 1);
+#pragma unroll
+      for (int p = 0; p < NT; ++p) {
+        lr[0][p] = rank2(lr[0][p], kj0.x, kj0.y, hW0[w][p], hW1[w][p]);
+        lr[1][p] = rank2(lr[1][p], kj1.x, kj1.y, hW0[w][p], hW1[w][p]);
+        lc[0][p] = rank2(lc[0][p], hK[w][p].x, hK[w][p].y, w0j0, w1j0);
+        lc[1][p] = rank2(lc[1][p], hK[w][p].x, hK[w][p].y, w0j1, w1j1);
+      }
+    }
+    // (c) H P (rows) and P H^T (columns) for this lane's t, accumulated in idx5 order
+    double pht0[NT], pht1[NT];
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      double a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const double vr = (k < 3) ? rr[k < 3 ? k : 0][p] : lr[k < 3 ? 0 : k - 3][p];
+        const double vc = (k < 3) ? rc[k < 3 ? k : 0][p] : lc[k < 3 ? 0 : k - 3][p];
+        a0 = fma(in.h[0][k], vr, a0);
+        a1 = fma(in.h[1][k], vr, a1);
+        b0 = fma(vc, in.h[0][k], b0);
+        b1 = fma(vc, in.h[1][k], b1);
+      }
+      hW0[u][p] = a0; hW1[u][p] = a1; pht0[p] = b0; pht1[p] = b1;
+    }
+    // (d) S = (H P) H^T + Q from the five entries idx5 of H P (:473), closed-form inverse; group-uniform
+    double x0[5], x1[5];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      x0[c] = gshfl<GW>(gmask, hW0[u][0], c);
+      x1[c] = gshfl<GW>(gmask, hW1[u][0], c);
+    }
+    x0[3] = gcol<GW, NT>(gmask, hW0[u], j);     x1[3] = gcol<GW, NT>(gmask, hW1[u], j);
+    x0[4] = gcol<GW, NT>(gmask, hW0[u], j + 1); x1[4] = gcol<GW, NT>(gmask, hW1[u], j + 1);
+    double S[2][2], Si[2][2];
+    {
+      double acc00 = 0.0, acc01 = 0.0, acc10 = 0.0, acc11 = 0.0;
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        acc00 = fma(x0[c], in.h[0][c], acc00);
+        acc01 = fma(x0[c], in.h[1][c], acc01);
+        acc10 = fma(x1[c], in.h[0][c], acc10);
+        acc11 = fma(x1[c], in.h[1][c], acc11);
+      }
+      S[0][0] = acc00 + qn; S[0][1] = acc01; S[1][0] = acc10; S[1][1] = acc11 + qn;
+    }
+    inv2(S, Si);
+    // (e) K_u = P H^T S^-1 (:473), mu += K_u y (:476)
+    double* ku = sK + u * HIST;
+#pragma unroll
+    for (int p = 0; p < NT; ++p) {
+      const int t = gl + GW * p;
+      d2 kk;
+      kk.x = dot2(pht0[p], Si[0][0], pht1[p], Si[1][0]);
+      kk.y = dot2(pht0[p], Si[0][1], pht1[p], Si[1][1]);
+      hK[u][p] = kk;  // zero for the pad row and beyond
+      if (t < LD) {
+        *reinterpret_cast<d2*>(ku + 2 * t) = kk;
+        if (t < N) sMu[t] = mu_inc(sMu[t], kk.x, kk.y, in.y0, in.y1);
+      }
+    }
+    __syncwarp(gmask);
+    // (f) bring the robot rows / columns up to date for the next update
+    if (u + 1 < m) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const d2 kr = lds128(ku + 2 * k);
+#pragma unroll
+        for (int p = 0; p < NT; ++p) {
+          rr[k][p] = rank2(rr[k][p], kr.x, kr.y, hW0[u][p], hW1[u][p]);
+          rc[k][p] = rank2(rc[k][p], hK[u][p].x, hK[u][p].y, x0[k], x1[k]);
+        }
+      }
+    }
+  }
+
+  // ---- phase 3: one pass over P, all updates applied in order, streamed to HBM ---------------------------
+  // lane = column gl + GW p of every row of ITS filter (W_u of those columns in registers); K_u of a row is one
+  // 128-bit load per group. Row chunks are compile-time bounded (immediate offsets).
+  {
+    constexpr int CH = (NT >= 3) ? 4 : 8;  // rows in registers per chunk
+    const bool tail_ok = gl + GW * (NT - 1) < LD;
+#pragma unroll
+    for (int r0 = 0; r0 < N; r0 += CH) {
+      double v[CH][NT];
+#pragma unroll
+      for (int q = 0; q < CH; ++q)
+#pragma unroll
+        for (int p = 0; p < NT; ++p)
+          if (r0 + q < N && (p < NT - 1 || tail_ok)) v[q][p] = sP[(r0 + q) * LD + gl + GW * p];
+#pragma unroll
+      for (int u = 0; u < m; ++u) {
+        if (!((valid >> u) & 1u)) continue;
+#pragma unroll
+        for (int q = 0; q < CH; ++q) {
+          if (r0 + q < N) {
+            const d2 k = lds128(sK + u * HIST + 2 * (r0 + q));
+#pragma unroll
+            for (int p = 0; p < NT; ++p) v[q][p] = rank2(v[q][p], k.x, k.y, hW0[u][p], hW1[u][p]);
+          }
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < CH; ++q)
+#pragma unroll
+        for (int p = 0; p < NT; ++p)
+          if (r0 + q < N && (p < NT - 1 || tail_ok)) gP[(r0 + q) * LD + gl + GW * p] = v[q][p];
+    }
+  }
+#pragma unroll
+  for (int p = 0; p < NT; ++p) {
+    const int t = gl + GW * p;
+    if (t < LD) gMu[t] = sMu[t];
+  }
+}
+
+// -------------------------------------------------------------------------------------------------------
+// launchers
+// -------------------------------------------------------------------------------------------------------
+template <int NLM, int MT, int GW>
+static cudaError_t launch_group(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+  constexpr int n = 3 + 2 * NLM, ld = (n + 3) & ~3, fpw = 32 / GW;
+  const size_t smem = (size_t)(n * ld + ld + MT * 2 * ld + 2) * sizeof(double) * fpw;
+  auto kernel = batch_step_group_kernel<NLM, MT, GW>;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  if (e != cudaSuccess) return e;
+  kernel<<<(unsigned)((batch + fpw - 1) / fpw), 32, smem, st>>>(a, batch);
+  return cudaGetLastError();
+}
+
+bool batch_group_supported(int n_landmarks, int m) { return (n_landmarks == 4 || n_landmarks == 8) && m >= 1 && m <= 4; }
+
+template <int NLM, int GW>
+static cudaError_t launch_group_m(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+  switch (a.m) {
+    case 1: return launch_group<NLM, 1, GW>(a, batch, st);
+    case 2: return launch_group<NLM, 2, GW>(a, batch, st);
+    case 3: return launch_group<NLM, 3, GW>(a, batch, st);
+    case 4: return launch_group<NLM, 4, GW>(a, batch, st);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+// group width 8 (four filters per warp) or 16 (two per warp)
+cudaError_t batch_launch_step_group(int n_landmarks, int group_width, const BatchStepArgs& a, int64_t batch,
+                                    cudaStream_t st) {
+  if (n_landmarks == 4) return group_width == 16 ? launch_group_m<4, 16>(a, batch, st) : launch_group_m<4, 8>(a, batch, st);
+  if (n_landmarks == 8) return group_width == 16 ? launch_group_m<8, 16>(a, batch, st) : launch_group_m<8, 8>(a, batch, st);
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace ekf

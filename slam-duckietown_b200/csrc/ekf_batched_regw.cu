@@ -85,8 +85,19 @@ __device__ __forceinline__ void regw_stream_pairs(const double* __restrict__ sp,
 // WPC > 1: ONE persistent CTA per SM whose warps each pull filters from a device-side work counter — the
 // 1 KB of shared memory the system reserves per CTA is then paid once per SM instead of once per filter,
 // which is what lets a 13th filter fit at n = 43 (13 x 17.2 KB + 1 KB <= 228 KB). Opt-in (see launch_regw_mt).
+#ifndef EKF_REGW_MAX_BLOCKS
+#define EKF_REGW_MAX_BLOCKS 24
+#endif
+// resident one-warp CTAs per SM the register allocation should allow: what shared memory admits, at most
+// EKF_REGW_MAX_BLOCKS (small filters are otherwise register-limited to 16 warps: ncu, profiles/r1h_batchM.*)
+__host__ __device__ constexpr int regw_min_blocks(int nlm, int m, int wpc) {
+  const int n = 3 + 2 * nlm, ld = (n + 3) & ~3;
+  const int fit = 233472 / ((n * ld + ld * (1 + 2 * m) + 2) * 8 + 1024);
+  return wpc > 1 ? 1 : (fit < EKF_REGW_MAX_BLOCKS ? fit : EKF_REGW_MAX_BLOCKS);
+}
+
 template <int NLM, int MT, int WPC>
-__global__ void __launch_bounds__(32 * WPC, 1) batch_step_regw_kernel(BatchStepArgs a, int64_t batch) {
+__global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch_step_regw_kernel(BatchStepArgs a, int64_t batch) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
   constexpr int HIST = 2 * LD;        // doubles of one update's K record: [LD][2]
@@ -183,8 +194,8 @@ __global__ void __launch_bounds__(32 * WPC, 1) batch_step_regw_kernel(BatchStepA
         double sb, cb;
         sincos(be + pth, &sb, &cb);
         if (lane == 0) {
-          sMu[j] = px + r * cb;
-          sMu[j + 1] = py + r * sb;
+          sMu[j] = __dadd_rn(px, __dmul_rn(r, cb));
+          sMu[j + 1] = __dadd_rn(py, __dmul_rn(r, sb));
         }
         fresh |= 1u << u;
         ++nk;
@@ -220,8 +231,8 @@ __global__ void __launch_bounds__(32 * WPC, 1) batch_step_regw_kernel(BatchStepA
       rr[0][p] = rr[1][p] = rr[2][p] = 0.0;
       if (t < N) {
         const double p2 = sP[2 * LD + t];
-        rr[0][p] = sP[0 * LD + t] + g0 * p2;
-        rr[1][p] = sP[1 * LD + t] + g1 * p2;
+        rr[0][p] = fma(g0, p2, sP[0 * LD + t]);
+        rr[1][p] = fma(g1, p2, sP[1 * LD + t]);
         rr[2][p] = p2;
         sP[0 * LD + t] = rr[0][p];
         sP[1 * LD + t] = rr[1][p];
@@ -236,10 +247,10 @@ __global__ void __launch_bounds__(32 * WPC, 1) batch_step_regw_kernel(BatchStepA
         double* row = sP + i * LD;
         const d2 r01 = lds128(row);
         const double p2 = row[2];
-        double r0 = r01.x + g0 * p2, r1 = r01.y + g1 * p2, r2 = p2;
-        if (i == 0) r0 += mv * mv;  // F^T R F (:421-430)
-        if (i == 1) r1 += mv * mv;
-        if (i == 2) r2 = p2 + (mv / 2.0) * (mv / 2.0);
+        double r0 = fma(g0, p2, r01.x), r1 = fma(g1, p2, r01.y), r2 = p2;
+        if (i == 0) r0 = __dadd_rn(r0, __dmul_rn(mv, mv));  // F^T R F (:421-430)
+        if (i == 1) r1 = __dadd_rn(r1, __dmul_rn(mv, mv));
+        if (i == 2) r2 = __dadd_rn(p2, __dmul_rn(mv / 2.0, mv / 2.0));
         d2 o;
         o.x = r0; o.y = r1;
         *reinterpret_cast<d2*>(row) = o;
@@ -335,12 +346,12 @@ __global__ void __launch_bounds__(32 * WPC, 1) batch_step_regw_kernel(BatchStepA
     for (int p = 0; p < NT; ++p) {
       const int t = lane + 32 * p;
       d2 kk;
-      kk.x = pht0[p] * Si[0][0] + pht1[p] * Si[1][0];
-      kk.y = pht0[p] * Si[0][1] + pht1[p] * Si[1][1];
+      kk.x = dot2(pht0[p], Si[0][0], pht1[p], Si[1][0]);
+      kk.y = dot2(pht0[p], Si[0][1], pht1[p], Si[1][1]);
       hK[u][p] = kk;  // zero for the pad row and beyond
       if (t < LD) {
         *reinterpret_cast<d2*>(ku + 2 * t) = kk;
-        if (t < N) sMu[t] += kk.x * in.y0 + kk.y * in.y1;
+        if (t < N) sMu[t] = mu_inc(sMu[t], kk.x, kk.y, in.y0, in.y1);
       }
     }
     __syncwarp();

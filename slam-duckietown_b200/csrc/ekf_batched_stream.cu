@@ -177,8 +177,8 @@ __global__ void __launch_bounds__(32) batch_step_stream_kernel(BatchStepArgs a) 
       double sb, cb;
       sincos(be + pth, &sb, &cb);
       if (lane == 0) {
-        sMu[j] = px + r * cb;
-        sMu[j + 1] = py + r * sb;
+        sMu[j] = __dadd_rn(px, __dmul_rn(r, cb));
+        sMu[j + 1] = __dadd_rn(py, __dmul_rn(r, sb));
       }
       // every staged copy of rows / columns j, j+1 gets the new diagonal (a slot may be observed twice)
       if (lane < m && o_slot == s && ((valid >> lane) & 1u)) {
@@ -207,28 +207,28 @@ __global__ void __launch_bounds__(32) batch_step_stream_kernel(BatchStepArgs a) 
       const int t = lane + 32 * p;
       if (t < N) {
         const double p2 = sRow[2 * LD + t];
-        sRow[0 * LD + t] += g0 * p2;
-        sRow[1 * LD + t] += g1 * p2;
+        sRow[0 * LD + t] = fma(g0, p2, sRow[0 * LD + t]);
+        sRow[1 * LD + t] = fma(g1, p2, sRow[1 * LD + t]);
       }
     }
     if (lane < RS) {  // staged column k = lane: elements i = 0, 1 += g * element i = 2
       double* e0 = (lane < 2) ? sC01 + lane : sCol + (lane - 2) * LD;
       const int st = (lane < 2) ? 2 : 1;  // stride between consecutive i
       const double p2 = e0[2 * st];
-      e0[0] += g0 * p2;
-      e0[st] += g1 * p2;
+      e0[0] = fma(g0, p2, e0[0]);
+      e0[st] = fma(g1, p2, e0[st]);
     }
     __syncwarp();
     // column operation P[:,0] += g0 P[:,2], P[:,1] += g1 P[:,2] (with the updated rows 0-1), then F^T R F
     if (lane < RS) {
       double* row = sRow + lane * LD;
       const double p2 = row[2];
-      double r0 = row[0] + g0 * p2, r1 = row[1] + g1 * p2;
-      if (lane == 0) r0 += mv * mv;
-      if (lane == 1) r1 += mv * mv;
+      double r0 = fma(g0, p2, row[0]), r1 = fma(g1, p2, row[1]);
+      if (lane == 0) r0 = __dadd_rn(r0, __dmul_rn(mv, mv));
+      if (lane == 1) r1 = __dadd_rn(r1, __dmul_rn(mv, mv));
       row[0] = r0;
       row[1] = r1;
-      if (lane == 2) row[2] = p2 + (mv / 2.0) * (mv / 2.0);
+      if (lane == 2) row[2] = __dadd_rn(p2, __dmul_rn(mv / 2.0, mv / 2.0));
     }
 #pragma unroll
     for (int p = 0; p < NT; ++p) {
@@ -236,12 +236,12 @@ __global__ void __launch_bounds__(32) batch_step_stream_kernel(BatchStepArgs a) 
       if (i < N) {
         const double p2 = sCol[i];
         d2 c01 = lds128(sC01 + 2 * i);
-        c01.x += g0 * p2;
-        c01.y += g1 * p2;
-        if (i == 0) c01.x += mv * mv;
-        if (i == 1) c01.y += mv * mv;
+        c01.x = fma(g0, p2, c01.x);
+        c01.y = fma(g1, p2, c01.y);
+        if (i == 0) c01.x = __dadd_rn(c01.x, __dmul_rn(mv, mv));
+        if (i == 1) c01.y = __dadd_rn(c01.y, __dmul_rn(mv, mv));
         *reinterpret_cast<d2*>(sC01 + 2 * i) = c01;
-        if (i == 2) sCol[i] = p2 + (mv / 2.0) * (mv / 2.0);
+        if (i == 2) sCol[i] = __dadd_rn(p2, __dmul_rn(mv / 2.0, mv / 2.0));
       }
     }
     __syncwarp();
@@ -339,10 +339,10 @@ __global__ void __launch_bounds__(32) batch_step_stream_kernel(BatchStepArgs a) 
       const int t = lane + 32 * p;
       if (t < LD) {
         d2 kk;
-        kk.x = pht0[p] * Si[0][0] + pht1[p] * Si[1][0];
-        kk.y = pht0[p] * Si[0][1] + pht1[p] * Si[1][1];
+        kk.x = dot2(pht0[p], Si[0][0], pht1[p], Si[1][0]);
+        kk.y = dot2(pht0[p], Si[0][1], pht1[p], Si[1][1]);
         *reinterpret_cast<d2*>(ku + 2 * t) = kk;  // zero for the pad row
-        if (t < N) sMu[t] += kk.x * in.y0 + kk.y * in.y1;
+        if (t < N) sMu[t] = mu_inc(sMu[t], kk.x, kk.y, in.y0, in.y1);
       }
     }
     __syncwarp();

@@ -52,7 +52,9 @@ struct ekf_batch {
   const double *mv = nullptr, *mm = nullptr;
   int flags = ekf::kFlagCircular | ekf::kFlagMeasurement;
   // 0 = auto (W-in-registers kernel where it applies: plain form, 1-4 observation slots; else fully staged),
-  // 1 = streaming (touched rows/columns staged), 2 = fully staged; EKF_BATCH_KERNEL=auto|stream|staged
+  // 1 = streaming (touched rows/columns staged), 2 = fully staged, 3 = warp per filter with W in registers even for
+  // small filters, 8 / 16 = sub-warp groups of that width (capacity <= 8 landmarks; auto picks 8 there);
+  // EKF_BATCH_KERNEL=auto|stream|staged|regw|group8|group16
   int kernel = 0;
   unsigned long long* faults = nullptr;  // [0] fault count, [1..2] work / done counters of the persistent kernel, [3] association overflows
   // staging for the host-buffer entry point
@@ -128,7 +130,8 @@ int ekf_batch_create(int n_landmarks, int64_t batch, int device, ekf_batch_t** o
   h->device = device;
   h->batch = batch;
   if (const char* k = getenv("EKF_BATCH_KERNEL"))
-    h->kernel = (strcmp(k, "stream") == 0) ? 1 : (strcmp(k, "staged") == 0) ? 2 : 0;
+    h->kernel = (strcmp(k, "stream") == 0) ? 1 : (strcmp(k, "staged") == 0) ? 2 : (strcmp(k, "regw") == 0) ? 3 :
+                (strcmp(k, "group8") == 0) ? 8 : (strcmp(k, "group16") == 0) ? 16 : 0;
   cudaError_t e = cudaMalloc(&h->faults, 4 * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaMemset(h->faults, 0, 4 * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
@@ -213,7 +216,9 @@ static int batch_step_common(ekf_batch_t* h, ekf::BatchStepArgs& a, int m, void*
   const bool joseph = (h->flags & ekf::kFlagJoseph) != 0;
   if (!joseph && h->kernel == 1)
     CU(ekf::batch_launch_step_stream(h->nlm, a, h->batch, (cudaStream_t)stream));
-  else if (!joseph && h->kernel == 0 && ekf::batch_regw_supported(m))
+  else if (!joseph && (h->kernel == 0 || h->kernel >= 8) && ekf::batch_group_supported(h->nlm, m))
+    CU(ekf::batch_launch_step_group(h->nlm, h->kernel >= 8 ? h->kernel : 8, a, h->batch, (cudaStream_t)stream));
+  else if (!joseph && (h->kernel == 0 || h->kernel == 3 || h->kernel >= 8) && ekf::batch_regw_supported(m))
     CU(ekf::batch_launch_step_regw(h->nlm, a, h->batch, (cudaStream_t)stream));
   else
     CU(ekf::batch_launch_step(h->nlm, a, h->batch, joseph, (cudaStream_t)stream));

@@ -58,12 +58,15 @@ __device__ __forceinline__ Motion motion_from_sincos(double th, double ang, doub
     return m;
   }
   if ((flags & kFlagCircular) && fabs(ang) > 1e-2) {
+    // every product rounded before the add, as numpy evaluates :391-403 (and so that no kernel's FMA contraction
+    // choice can differ from another's)
     const double r = lin / ang;
-    m.dx = -r * s + r * s2;
-    m.dy = r * c - r * c2;
+    const double rs = __dmul_rn(r, s), rs2 = __dmul_rn(r, s2), rc = __dmul_rn(r, c), rc2 = __dmul_rn(r, c2);
+    m.dx = __dadd_rn(-rs, rs2);
+    m.dy = __dsub_rn(rc, rc2);
     m.theta = wrap_pi(th + ang);
-    m.g0 = -r * c + r * c2;
-    m.g1 = -r * s + r * s2;
+    m.g0 = __dadd_rn(-rc, rc2);
+    m.g1 = __dadd_rn(-rs, rs2);
   } else {
     m.dx = lin * c;
     m.dy = lin * s;
@@ -91,7 +94,7 @@ __device__ __forceinline__ Innov innovation(double mx, double my, double mth, do
                                             double brg) {
   Innov o;
   const double dx = lx - mx, dy = ly - my;
-  const double q = dx * dx + dy * dy;
+  const double q = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
   const double sq = sqrt(q);
   o.q = q;
   o.y0 = rng - sq;
@@ -106,10 +109,15 @@ __device__ __forceinline__ Innov innovation(double mx, double my, double mth, do
 
 // closed-form inverse of the 2x2 innovation covariance (replaces np.linalg.inv, :473)
 __device__ __forceinline__ void inv2(const double s[2][2], double si[2][2]) {
-  const double det = s[0][0] * s[1][1] - s[0][1] * s[1][0];
+  const double det = __dsub_rn(__dmul_rn(s[0][0], s[1][1]), __dmul_rn(s[0][1], s[1][0]));
   const double rd = 1.0 / det;
   si[0][0] = s[1][1] * rd;  si[0][1] = -s[0][1] * rd;
   si[1][0] = -s[1][0] * rd; si[1][1] = s[0][0] * rd;
+}
+
+// a0 b0 + a1 b1 with the rounding sequence spelled out (first product rounded, second fused into the add)
+__device__ __forceinline__ double dot2(double a0, double b0, double a1, double b1) {
+  return fma(a1, b1, __dmul_rn(a0, b0));
 }
 
 // a10 (replay_no_ros.py:476) for one entry: mu + (K[i,0] y0 + K[i,1] y1), with the rounding sequence spelled out so

@@ -167,8 +167,8 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
       ph0 = fma(p, sh[0][k], ph0);
       ph1 = fma(p, sh[1][k], ph1);
     }
-    const double kk0 = ph0 * ssi[0][0] + ph1 * ssi[1][0];
-    const double kk1 = ph0 * ssi[0][1] + ph1 * ssi[1][1];
+    const double kk0 = dot2(ph0, ssi[0][0], ph1, ssi[1][0]);
+    const double kk1 = dot2(ph0, ssi[0][1], ph1, ssi[1][1]);
     a.mu_out[t] = mu_inc(a.mu_out[t], kk0, kk1, sy[0], sy[1]);
   }
   double hp0 = 0.0, hp1 = 0.0;
@@ -188,8 +188,8 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
       pht0 = fma(p, sh[0][k], pht0);
       pht1 = fma(p, sh[1][k], pht1);
     }
-    k0 = pht0 * ssi[0][0] + pht1 * ssi[1][0];
-    k1 = pht0 * ssi[0][1] + pht1 * ssi[1][1];
+    k0 = dot2(pht0, ssi[0][0], pht1, ssi[1][0]);
+    k1 = dot2(pht0, ssi[0][1], pht1, ssi[1][1]);
     a.K0[t] = k0;
     a.K1[t] = k1;
   }

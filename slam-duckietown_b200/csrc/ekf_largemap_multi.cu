@@ -120,8 +120,8 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
     pht0 = fma(pc, sh[0][k], pht0);
     pht1 = fma(pc, sh[1][k], pht1);
   }
-  a.K[(2 * u) * a.ldw + t] = pht0 * ssi[0][0] + pht1 * ssi[1][0];
-  a.K[(2 * u + 1) * a.ldw + t] = pht0 * ssi[0][1] + pht1 * ssi[1][1];
+  a.K[(2 * u) * a.ldw + t] = dot2(pht0, ssi[0][0], pht1, ssi[1][0]);
+  a.K[(2 * u + 1) * a.ldw + t] = dot2(pht0, ssi[0][1], pht1, ssi[1][1]);
   a.W[(2 * u) * a.ldw + t] = hp0;
   a.W[(2 * u + 1) * a.ldw + t] = hp1;
 }

@@ -366,15 +366,17 @@ def test_ekf3_surface(eb):
 
 @pytest.mark.parametrize("name", ["batched_b48_l20.npz", "batched_b32_l8.npz"])
 def test_batched_kernel_variants_bitwise_equal(eb, name, monkeypatch):
-    """The W-in-registers kernel (default), the fully staged kernel and the streaming kernel apply the same
-    per-element operation sequence: their states must be BITWISE equal at every kept step."""
+    """The W-in-registers kernel (default at 20 landmarks), the sub-warp group kernels (default at <= 8 landmarks),
+    the fully staged kernel and the streaming kernel apply the same per-element operation sequence: their states
+    must be BITWISE equal at every kept step."""
     import torch
     z = golden(name)
     outs = {}
-    for variant in ("auto", "staged", "stream"):
+    variants = ("auto", "staged", "stream", "regw", "group8", "group16")
+    for variant in variants:
         monkeypatch.setenv("EKF_BATCH_KERNEL", variant)      # read by ekf_batch_create
         outs[variant], _ = _run_batched(eb, z)
-    for variant in ("staged", "stream"):
+    for variant in variants[1:]:
         for t, (mu, p) in outs["auto"].items():
             mu2, p2 = outs[variant][t]
             assert np.array_equal(mu, mu2), f"{name} {variant} mu differs at t={t}"
