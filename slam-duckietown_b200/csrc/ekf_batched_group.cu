@@ -39,17 +39,26 @@ __device__ __forceinline__ double gcol(unsigned gmask, const double (&x)[NT], in
   return gshfl<GW>(gmask, mine, c - p * GW);
 }
 
+__host__ __device__ constexpr int group_slice_doubles(int nlm, int m, int gw) {
+  const int n = 3 + 2 * nlm, ld = (n + 3) & ~3;
+  const int raw = n * ld + ld + m * 2 * ld + 2;
+  return gw == 8 ? raw + ((8 - raw % 16) + 16) % 16 : raw;
+}
+
 }  // namespace
 
+// 16 resident one-warp CTAs per SM: 128 registers per thread = four warps per scheduler's register file
 template <int NLM, int MT, int GW>
-__global__ void __launch_bounds__(32) batch_step_group_kernel(BatchStepArgs a, int64_t batch) {
+__global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs a, int64_t batch) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
   constexpr int HIST = 2 * LD;          // doubles of one update's K record: [LD][2]
   constexpr int NT = (LD + GW - 1) / GW;  // lane gl handles indices gl, gl + GW, ...
   constexpr int FPW = 32 / GW;          // filters per warp
   constexpr int m = MT;
-  constexpr int SLICE = N * LD + LD + m * HIST + 2;  // doubles of shared memory per filter
+  // doubles of shared memory per filter; with four groups the slices start 64 bytes apart modulo the 128-byte bank
+  // period, so the four 64-byte row segments the groups read in one instruction fall into two full wavefronts
+  constexpr int SLICE = group_slice_doubles(NLM, MT, GW);
   static_assert(GW == 8 || GW == 16, "group width");
   static_assert(MT >= 1 && MT <= GW && MT <= BATCH_MAX_M, "observation count");
   static_assert(SLICE % 2 == 0, "16-byte aligned slices");
@@ -349,8 +358,8 @@ __global__ void __launch_bounds__(32) batch_step_group_kernel(BatchStepArgs a, i
 // -------------------------------------------------------------------------------------------------------
 template <int NLM, int MT, int GW>
 static cudaError_t launch_group(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
-  constexpr int n = 3 + 2 * NLM, ld = (n + 3) & ~3, fpw = 32 / GW;
-  const size_t smem = (size_t)(n * ld + ld + MT * 2 * ld + 2) * sizeof(double) * fpw;
+  constexpr int fpw = 32 / GW;
+  const size_t smem = (size_t)group_slice_doubles(NLM, MT, GW) * sizeof(double) * fpw;
   auto kernel = batch_step_group_kernel<NLM, MT, GW>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
