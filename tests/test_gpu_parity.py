@@ -576,3 +576,34 @@ def test_monte_carlo_replay_of_decoded_bag(eb, surrogate):
                                  np.exp(rs.uniform(np.log(0.05), np.log(1.5), B)), det_sigma=0.02, seed=7)
     assert out2["faults"] == 0 and np.all(np.isfinite(out2["rmse"])) and np.all(np.isfinite(out2["pose"]))
     assert len(np.unique(out2["rmse"])) > B // 2
+
+
+def test_group_kernel_ragged_batch_and_mixed_observations(eb, monkeypatch):
+    """Batch sizes that do not fill the last warp of the sub-warp group kernels (4 or 2 filters per warp), filters
+    of one warp with DIFFERENT observation patterns (some slots -1, so groups diverge), and a predict-only step:
+    group8 / group16 / warp-per-filter must agree bitwise."""
+    import torch
+    from slam_duckietown_b200 import workloads as wl
+    B, L, m = 30, 8, 3
+    w = wl.make_batched(B, n_landmarks=L, m=m, steps=10)
+    slot = w.slot.copy()
+    rs = np.random.default_rng(3)
+    steady = slice(w.warm_steps, None)
+    drop = rs.random(slot[steady].shape) < 0.3          # after every landmark is known: drop observations at random
+    slot[steady][drop] = -1
+    res = {}
+    for variant in ("regw", "group8", "group16"):
+        monkeypatch.setenv("EKF_BATCH_KERNEL", variant)
+        f = eb.BatchedEKF(B, L)
+        f.set_noise(w.motion_var, w.meas_var)
+        f.init(0.1)
+        for t in range(w.steps):
+            f.step(_dev(f.dev, w.ang[t]), _dev(f.dev, w.lin[t]), _dev(f.dev, slot[t]), _dev(f.dev, w.rng[t]),
+                   _dev(f.dev, w.brg[t]))
+        f.step(_dev(f.dev, w.ang[0]), _dev(f.dev, w.lin[0]))                     # m = 0: predict only
+        assert f.fault_count() == 0
+        res[variant] = (f.mu.clone(), f.P.clone(), f.n_known.clone())
+    for variant in ("group8", "group16"):
+        for a, b in zip(res["regw"], res[variant]):
+            assert torch.equal(a, b), variant
+    assert bool(torch.isfinite(res["regw"][0]).all())
