@@ -109,6 +109,17 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
   __shared__ double sy[2];
   const int j = a.j;
   const int idx5[5] = {0, 1, 2, j, j + 1};
+  // this thread's gathers are issued before thread 0's scalar chain (innovation, S^-1) so that the strided column
+  // reads overlap it instead of following it
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = t < a.n;
+  const bool local = live && (t >= a.row_begin && t < a.row_end);
+  double pr[5], pc[5];
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    pr[k] = live ? a.row[k][t] : 0.0;
+    pc[k] = local ? a.P[(int64_t)(t - a.row_begin) * a.ld + idx5[k]] : 0.0;
+  }
   if (threadIdx.x == 0) {
     const Innov in = innovation(*a.mu5[0], *a.mu5[1], *a.mu5[2], *a.mu5[3], *a.mu5[4], a.rng, a.brg);
     double hp5[2][5];
@@ -154,8 +165,7 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
     }
   }
   __syncthreads();
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= a.n) return;
+  if (!live) return;
   if (a.shard && t < 3 && !(t >= a.row_begin && t < a.row_end)) {
     // row-block shard that does not own the robot rows: keep the replicated pose entries of mu current.
     // K[t, :] of rows 0-2 is rebuilt from the exchanged rows (mu5 points into the exchange buffer, so
@@ -174,19 +184,15 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
   double hp0 = 0.0, hp1 = 0.0;
 #pragma unroll
   for (int k = 0; k < 5; ++k) {
-    const double p = a.row[k][t];
-    hp0 = fma(sh[0][k], p, hp0);
-    hp1 = fma(sh[1][k], p, hp1);
+    hp0 = fma(sh[0][k], pr[k], hp0);
+    hp1 = fma(sh[1][k], pr[k], hp1);
   }
   double k0 = 0.0, k1 = 0.0, pht0 = 0.0, pht1 = 0.0;
-  const bool local = (t >= a.row_begin && t < a.row_end);
   if (local) {
-    const double* prow = a.P + (int64_t)(t - a.row_begin) * a.ld;
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
-      const double p = prow[idx5[k]];
-      pht0 = fma(p, sh[0][k], pht0);
-      pht1 = fma(p, sh[1][k], pht1);
+      pht0 = fma(pc[k], sh[0][k], pht0);
+      pht1 = fma(pc[k], sh[1][k], pht1);
     }
     k0 = dot2(pht0, ssi[0][0], pht1, ssi[1][0]);
     k1 = dot2(pht0, ssi[0][1], pht1, ssi[1][1]);

@@ -41,6 +41,37 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
     sww[w][1][k] = a.W[(2 * w + 1) * a.ldw + idx5[k]];
   }
   __syncthreads();
+  // every thread's own gathers (5 row entries, 5 column entries, its entries of the earlier records) and their
+  // rebuild need only the uniform operands staged above: they are issued BEFORE thread 0's scalar chain so that the
+  // strided column reads overlap it instead of following it
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = t < a.n;
+  double pr[5], pc[5];
+  if (live) {
+    double kt0[LM_MAX_FUSED], kt1[LM_MAX_FUSED], wt0[LM_MAX_FUSED], wt1[LM_MAX_FUSED];
+#pragma unroll
+    for (int w = 0; w < LM_MAX_FUSED; ++w)
+      if (w < u) {
+        kt0[w] = a.K[(2 * w) * a.ldw + t];
+        kt1[w] = a.K[(2 * w + 1) * a.ldw + t];
+        wt0[w] = a.W[(2 * w) * a.ldw + t];
+        wt1[w] = a.W[(2 * w + 1) * a.ldw + t];
+      }
+    const double* prow = P + (int64_t)t * a.ld;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      pr[k] = P[(int64_t)idx5[k] * a.ld + t];  // row idx5[k], column t
+      pc[k] = prow[idx5[k]];                   // row t, column idx5[k]
+    }
+#pragma unroll
+    for (int k = 0; k < 5; ++k)
+#pragma unroll
+      for (int w = 0; w < LM_MAX_FUSED; ++w)
+        if (w < u) {
+          pr[k] = rank2e(pr[k], skw[w][k][0], skw[w][k][1], wt0[w], wt1[w]);
+          pc[k] = rank2e(pc[k], kt0[w], kt1[w], sww[w][0][k], sww[w][1][k]);
+        }
+  }
   if (threadIdx.x == 0) {
     double mu5[5];
 #pragma unroll
@@ -91,34 +122,14 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
     }
   }
   __syncthreads();
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= a.n) return;
-  // this thread's entries of the earlier records
-  double kt0[LM_MAX_FUSED], kt1[LM_MAX_FUSED], wt0[LM_MAX_FUSED], wt1[LM_MAX_FUSED];
-#pragma unroll
-  for (int w = 0; w < LM_MAX_FUSED; ++w)
-    if (w < u) {
-      kt0[w] = a.K[(2 * w) * a.ldw + t];
-      kt1[w] = a.K[(2 * w + 1) * a.ldw + t];
-      wt0[w] = a.W[(2 * w) * a.ldw + t];
-      wt1[w] = a.W[(2 * w + 1) * a.ldw + t];
-    }
+  if (!live) return;
   double hp0 = 0.0, hp1 = 0.0, pht0 = 0.0, pht1 = 0.0;
-  const double* prow = P + (int64_t)t * a.ld;
 #pragma unroll
   for (int k = 0; k < 5; ++k) {
-    double pr = P[(int64_t)idx5[k] * a.ld + t];  // row idx5[k], column t
-    double pc = prow[idx5[k]];                   // row t, column idx5[k]
-#pragma unroll
-    for (int w = 0; w < LM_MAX_FUSED; ++w)
-      if (w < u) {
-        pr = rank2e(pr, skw[w][k][0], skw[w][k][1], wt0[w], wt1[w]);
-        pc = rank2e(pc, kt0[w], kt1[w], sww[w][0][k], sww[w][1][k]);
-      }
-    hp0 = fma(sh[0][k], pr, hp0);
-    hp1 = fma(sh[1][k], pr, hp1);
-    pht0 = fma(pc, sh[0][k], pht0);
-    pht1 = fma(pc, sh[1][k], pht1);
+    hp0 = fma(sh[0][k], pr[k], hp0);
+    hp1 = fma(sh[1][k], pr[k], hp1);
+    pht0 = fma(pc[k], sh[0][k], pht0);
+    pht1 = fma(pc[k], sh[1][k], pht1);
   }
   a.K[(2 * u) * a.ldw + t] = dot2(pht0, ssi[0][0], pht1, ssi[1][0]);
   a.K[(2 * u + 1) * a.ldw + t] = dot2(pht0, ssi[0][1], pht1, ssi[1][1]);
