@@ -29,6 +29,8 @@ def main():
     ap.add_argument("--updates", type=int, default=60)
     ap.add_argument("--warmup", type=int, default=6)
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="row exchange: owners push over NVLink peer memory (default) or two NCCL broadcasts")
     args = ap.parse_args()
 
     import torch
@@ -49,7 +51,7 @@ def main():
     L = args.landmarks
     n = 3 + 2 * L
     w = wl.make_large_map(L, updates=args.updates + args.warmup)      # same seeds on every rank
-    f = ShardedLargeMapEKF(L, rank, world, device=local)
+    f = ShardedLargeMapEKF(L, rank, world, device=local, exchange=args.exchange)
     f.set_noise(0.1, 0.7)
     lo, hi = f.ranges[rank]
     a = torch.from_numpy(w.factor).to(dev)                            # (n, 64): P0 = A A^T / 64 + 0.1 I
@@ -91,7 +93,7 @@ def main():
     e1.record()
     sync()
     ms = e0.elapsed_time(e1) / len(timed)
-    # the exchange alone (export + broadcast), same slots
+    # the NCCL exchange alone (export + two broadcasts), same slots, for comparison
     x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     from slam_duckietown_b200.sharded import exchange_rows
     x0.record()
@@ -131,10 +133,13 @@ def main():
         print(json.dumps({
             "metric": f"ms/update @{L} lm", "value": ms, "unit": "ms", "n_gpus": world, "higher_is_better": False,
             "updates": len(timed), "warmup": args.warmup, "dtype": "f64", "data": "synthetic",
-            "scaling": "strong", "exchange_ms": xms, "exchange_share": xms / ms,
+            "scaling": "strong", "exchange": args.exchange, "nccl_exchange_ms": xms,
+            "p2p_error": f.local.p2p_error() if args.exchange == "p2p" else None,
             "config": {"workload": f"single large-map filter, {L} landmarks (n={n}), P {8 * n * n / 1e9:.2f} GB "
                                    f"row-block sharded over {world} GPU(s), one range-bearing update per step",
-                       "exchange": "NCCL broadcast of rows {0,1,2} from rank 0 and {j,j+1} from owner(j), 40 n bytes"},
+                       "exchange": ("owners push rows {0,1,2} / {j,j+1} into every rank's buffer over NVLink peer memory "
+                                    "(cudaIpc), flag wait, no collective" if args.exchange == "p2p" else
+                                    "NCCL broadcast of rows {0,1,2} from rank 0 and {j,j+1} from owner(j)") + ", 40 n bytes"},
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "peak_source": which, "unit": "GB/s",
                          "frac": ach / peak, "frac_of_8TBs": ach / 8000.0, "bytes_per_update_per_gpu": per_gpu_bytes,
                          "bytes_per_update_total": 16 * n * n + 96 * n},

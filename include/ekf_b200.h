@@ -141,6 +141,18 @@ int ekf_lm_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const dou
 int ekf_lm_export_rows(ekf_lm_t* h, int slot, double* rows5_dev, void* stream);
 int ekf_lm_update_from_rows(ekf_lm_t* h, int slot, double rng, double brg, const double* rows5_dev,
                             void* stream);
+/* Row exchange over NVLink peer memory instead of host-driven broadcasts (one process per GPU, all stream-ordered):
+ * ekf_lm_p2p_init allocates this shard's exchange area and returns its cudaIpc handle (handle_bytes >= 64); the host
+ * gathers the handles of all ranks (any transport) and passes them to ekf_lm_p2p_connect ([world][handle_bytes];
+ * local_areas optionally gives device pointers of shards living in the same process). ekf_lm_p2p_update then runs
+ * one sharded update: the owners push rows {0,1,2} / {j,j+1} (+ mu entries) into every rank's area and publish a
+ * sequence number, every rank waits on its own flags, gathers, acknowledges and streams its row block. Every rank
+ * must call it with the same arguments in the same order. ekf_lm_p2p_error reports a spin that ran out of budget. */
+int ekf_lm_p2p_init(ekf_lm_t* h, int world, int rank, unsigned char* handle_out, int64_t handle_bytes);
+int ekf_lm_p2p_connect(ekf_lm_t* h, const unsigned char* handles, int64_t handle_bytes, void* const* local_areas);
+int ekf_lm_p2p_area(ekf_lm_t* h, void** area_dev);
+int ekf_lm_p2p_update(ekf_lm_t* h, int slot, double rng, double brg, int owner, void* stream);
+int ekf_lm_p2p_error(ekf_lm_t* h, int64_t* flag);
 int ekf_lm_sync(ekf_lm_t* h);
 
 /* ---- 3-state localisation EKF of src/EKF-SLAM.py, batched, SoA: state [3][B], cov [9][B] --------------- */

@@ -69,6 +69,11 @@ SIGNATURES = {
     "ekf_lm_update_multi": (_i, [_p, _i, _p, _p, _p, _p]),
     "ekf_lm_export_rows": (_i, [_p, _i, _p, _p]),
     "ekf_lm_update_from_rows": (_i, [_p, _i, _d, _d, _p, _p]),
+    "ekf_lm_p2p_init": (_i, [_p, _i, _i, _p, _l]),
+    "ekf_lm_p2p_connect": (_i, [_p, _p, _l, _p]),
+    "ekf_lm_p2p_area": (_i, [_p, C.POINTER(_p)]),
+    "ekf_lm_p2p_update": (_i, [_p, _i, _d, _d, _i, _p]),
+    "ekf_lm_p2p_error": (_i, [_p, C.POINTER(_l)]),
     "ekf_lm_sync": (_i, [_p]),
     "ekf3_predict": (_i, [_l, _p, _p, _p, _p, _p, _p]),
     "ekf3_update": (_i, [_l, _p, _p, _p, _p, _p, _p, _p]),

@@ -78,6 +78,15 @@ struct ekf_lm {
   double *K0 = nullptr, *K1 = nullptr, *A0 = nullptr, *A1 = nullptr, *W0 = nullptr, *W1 = nullptr,
          *scal = nullptr;
   double *mK = nullptr, *mW = nullptr, *my = nullptr;  // fused multi-update records [LM_MAX_FUSED][2][ldw], y [..][2]
+  // peer-memory row exchange (ekf_lm_p2p_*)
+  int p2p_world = 0, p2p_rank = 0;
+  double* p2p_area = nullptr;                 // this rank's exchange area (cudaMalloc, exported by IPC handle)
+  double* p2p_peer_host[ekf::P2P_MAX_WORLD] = {};
+  bool p2p_opened[ekf::P2P_MAX_WORLD] = {};
+  double** p2p_peers_dev = nullptr;
+  unsigned* p2p_push_count = nullptr;
+  unsigned long long* p2p_err = nullptr;
+  unsigned long long p2p_seq = 0;
   int variant = 0;
 };
 
@@ -481,6 +490,12 @@ int ekf_lm_create(int capacity_landmarks, int device, ekf_lm_t** out) {
 int ekf_lm_destroy(ekf_lm_t* h) {
   if (!h) return EKF_OK;
   cudaSetDevice(h->device);
+  for (int r = 0; r < h->p2p_world; ++r)
+    if (h->p2p_opened[r]) cudaIpcCloseMemHandle(h->p2p_peer_host[r]);
+  cudaFree(h->p2p_area);
+  cudaFree(h->p2p_peers_dev);
+  cudaFree(h->p2p_push_count);
+  cudaFree(h->p2p_err);
   cudaFree(h->K0);
   delete h;
   return EKF_OK;
@@ -534,7 +549,9 @@ int ekf_lm_predict(ekf_lm_t* h, double ang, double lin, void* stream) {
   return EKF_OK;
 }
 
-static int lm_update_impl(ekf_lm_t* h, int slot, double rng, double brg, const double* rows5, void* stream) {
+// p2p: when given, the gather waits on the exchange flags and the streaming kernel acknowledges the buffer
+static int lm_update_impl_split(ekf_lm_t* h, int slot, double rng, double brg, const double* rows5, void* stream,
+                                const ekf::P2PArgs* p2p) {
   if (!h) return fail(EKF_EINVAL, "null handle");
   if (!h->P) return fail(EKF_ESTATE, "state not bound");
   if (slot < 0 || slot >= h->cap) return fail(EKF_EINVAL, "slot %d outside capacity %d", slot, h->cap);
@@ -570,6 +587,11 @@ static int lm_update_impl(ekf_lm_t* h, int slot, double rng, double brg, const d
   g.mm = h->mm;
   g.shard = rows5 ? 1 : 0;
   g.mu_out = h->mu;
+  if (p2p) {
+    g.wait_flags = reinterpret_cast<const unsigned long long*>(h->p2p_area + p2p->flag_off) + (p2p->seq & 1) * 2;
+    g.wait_seq = p2p->seq;
+    g.wait_err = p2p->err;
+  }
   CU(ekf::lm_launch_gather(g, (cudaStream_t)stream));
   ekf::LmUpdateArgs u{};
   u.P = h->P;
@@ -579,8 +601,19 @@ static int lm_update_impl(ekf_lm_t* h, int slot, double rng, double brg, const d
   u.n = h->n;
   u.row_begin = h->row_begin;
   u.row_end = h->row_end;
+  if (p2p) {
+    u.ack_peers = p2p->peers;
+    u.ack_flag_off = p2p->flag_off;
+    u.ack_seq = p2p->seq;
+    u.ack_world = p2p->world;
+    u.ack_rank = p2p->rank;
+  }
   CU(ekf::lm_launch_update(u, joseph, h->variant, (cudaStream_t)stream));
   return EKF_OK;
+}
+
+static int lm_update_impl(ekf_lm_t* h, int slot, double rng, double brg, const double* rows5, void* stream) {
+  return lm_update_impl_split(h, slot, rng, brg, rows5, stream, nullptr);
 }
 
 int ekf_lm_update(ekf_lm_t* h, int slot, double rng, double brg, void* stream) {
@@ -641,6 +674,103 @@ int ekf_lm_update_from_rows(ekf_lm_t* h, int slot, double rng, double brg, const
                             void* stream) {
   if (!rows5_dev) return fail(EKF_EINVAL, "rows5_dev is null");
   return lm_update_impl(h, slot, rng, brg, rows5_dev, stream);
+}
+
+// ---- peer-memory row exchange of the row-block shards ----------------------------------------------------
+static int64_t p2p_area_doubles(const ekf_lm* h) { return 10 * (h->ld + 4) + 4 + ekf::P2P_MAX_WORLD; }
+
+int ekf_lm_p2p_init(ekf_lm_t* h, int world, int rank, unsigned char* handle_out, int64_t handle_bytes) {
+  if (!h || !handle_out) return fail(EKF_EINVAL, "null argument");
+  if (!h->P) return fail(EKF_ESTATE, "state not bound");
+  if (world < 1 || world > ekf::P2P_MAX_WORLD || rank < 0 || rank >= world)
+    return fail(EKF_EINVAL, "world must be in [1, %d] and rank in [0, world)", ekf::P2P_MAX_WORLD);
+  if (handle_bytes < (int64_t)sizeof(cudaIpcMemHandle_t)) return fail(EKF_EINVAL, "handle buffer too small");
+  if (h->p2p_area) return fail(EKF_ESTATE, "p2p already initialised");
+  CU(cudaSetDevice(h->device));
+  const size_t bytes = (size_t)p2p_area_doubles(h) * sizeof(double);
+  CU(cudaMalloc(&h->p2p_area, bytes));
+  CU(cudaMemset(h->p2p_area, 0, bytes));
+  CU(cudaMalloc(&h->p2p_peers_dev, ekf::P2P_MAX_WORLD * sizeof(double*)));
+  CU(cudaMalloc(&h->p2p_push_count, ekf::P2P_MAX_WORLD * sizeof(unsigned)));
+  CU(cudaMemset(h->p2p_push_count, 0, ekf::P2P_MAX_WORLD * sizeof(unsigned)));
+  CU(cudaMalloc(&h->p2p_err, sizeof(unsigned long long)));
+  CU(cudaMemset(h->p2p_err, 0, sizeof(unsigned long long)));
+  cudaIpcMemHandle_t hd;
+  CU(cudaIpcGetMemHandle(&hd, h->p2p_area));
+  memcpy(handle_out, &hd, sizeof(hd));
+  h->p2p_world = world;
+  h->p2p_rank = rank;
+  h->p2p_seq = 0;
+  CU(cudaDeviceSynchronize());
+  return EKF_OK;
+}
+
+// handles: [world][handle_bytes] as gathered from every rank's ekf_lm_p2p_init (own entry ignored).
+// local_areas: optional [world] device pointers for shards living in THIS process (NULL entry = open the handle).
+int ekf_lm_p2p_connect(ekf_lm_t* h, const unsigned char* handles, int64_t handle_bytes, void* const* local_areas) {
+  if (!h || (!handles && !local_areas)) return fail(EKF_EINVAL, "null argument");
+  if (!h->p2p_area) return fail(EKF_ESTATE, "call ekf_lm_p2p_init first");
+  CU(cudaSetDevice(h->device));
+  for (int r = 0; r < h->p2p_world; ++r) {
+    if (r == h->p2p_rank) {
+      h->p2p_peer_host[r] = h->p2p_area;
+    } else if (local_areas && local_areas[r]) {
+      h->p2p_peer_host[r] = (double*)local_areas[r];
+    } else {
+      if (!handles) return fail(EKF_EINVAL, "no handle for rank %d", r);
+      cudaIpcMemHandle_t hd;
+      memcpy(&hd, handles + (size_t)r * handle_bytes, sizeof(hd));
+      void* p = nullptr;
+      CU(cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess));
+      h->p2p_peer_host[r] = (double*)p;
+      h->p2p_opened[r] = true;
+    }
+  }
+  CU(cudaMemcpy(h->p2p_peers_dev, h->p2p_peer_host, h->p2p_world * sizeof(double*), cudaMemcpyHostToDevice));
+  return EKF_OK;
+}
+
+int ekf_lm_p2p_area(ekf_lm_t* h, void** area_dev) {
+  if (!h || !area_dev) return fail(EKF_EINVAL, "null argument");
+  *area_dev = h->p2p_area;
+  return EKF_OK;
+}
+
+int ekf_lm_p2p_update(ekf_lm_t* h, int slot, double rng, double brg, int owner, void* stream) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  if (!h->p2p_peers_dev) return fail(EKF_ESTATE, "p2p exchange not connected");
+  if (slot < 0 || slot >= h->cap) return fail(EKF_EINVAL, "slot %d outside capacity %d", slot, h->cap);
+  if (owner < 0 || owner >= h->p2p_world) return fail(EKF_EINVAL, "owner out of range");
+  if (!(h->flags & ekf::kFlagMeasurement)) return EKF_OK;
+  CU(cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int j = 3 + 2 * slot;
+  ekf::P2PArgs a{};
+  a.P = h->P; a.mu = h->mu; a.peers = h->p2p_peers_dev;
+  a.ld = h->ld; a.ldx = h->ld + 4; a.flag_off = 10 * a.ldx;
+  a.acks = reinterpret_cast<unsigned long long*>(h->p2p_area + a.flag_off) + 4;
+  a.err = h->p2p_err; a.push_count = h->p2p_push_count;
+  a.seq = ++h->p2p_seq;
+  a.world = h->p2p_world; a.rank = h->p2p_rank; a.row_begin = h->row_begin;
+  if (h->p2p_rank == 0) CU(ekf::lm_launch_p2p_push(a, 0, 0, 3, 0, st));
+  if (h->p2p_rank == owner) {
+    if (j < h->row_begin || j + 1 >= h->row_end) return fail(EKF_EINVAL, "rank %d does not own slot %d", owner, slot);
+    CU(ekf::lm_launch_p2p_push(a, j, 3, 2, 1, st));
+  }
+  const double* rows5 = h->p2p_area + (int64_t)(a.seq & 1) * 5 * a.ldx;
+  // gather (waits on the flags, reads the exchange buffer), then the streaming update (acknowledges the buffer)
+  return lm_update_impl_split(h, slot, rng, brg, rows5, stream, &a);
+}
+
+int ekf_lm_p2p_error(ekf_lm_t* h, int64_t* flag) {
+  if (!h || !flag) return fail(EKF_EINVAL, "null argument");
+  *flag = 0;
+  if (!h->p2p_err) return EKF_OK;
+  CU(cudaSetDevice(h->device));
+  unsigned long long v = 0;
+  CU(cudaMemcpy(&v, h->p2p_err, sizeof(v), cudaMemcpyDeviceToHost));
+  *flag = (int64_t)v;
+  return EKF_OK;
 }
 
 int ekf_lm_sync(ekf_lm_t* h) {

@@ -111,6 +111,21 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
   const int idx5[5] = {0, 1, 2, j, j + 1};
   // this thread's gathers are issued before thread 0's scalar chain (innovation, S^-1) so that the strided column
   // reads overlap it instead of following it
+  if (a.wait_flags) {  // rows arrive by peer stores: both parts of the exchange buffer carry this update's number
+    if (threadIdx.x == 0) {
+      const volatile unsigned long long* f = a.wait_flags;
+      const long long t0 = clock64();
+      while (f[0] < a.wait_seq || f[1] < a.wait_seq) {
+        if (clock64() - t0 > 4000000000LL) {
+          atomicExch(a.wait_err, 1ULL);
+          break;
+        }
+        __nanosleep(32);
+      }
+      __threadfence_system();
+    }
+    __syncthreads();
+  }
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = t < a.n;
   const bool local = live && (t >= a.row_begin && t < a.row_end);
@@ -226,6 +241,12 @@ template <int RB, int UNROLL, bool JOSEPH>
 __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs a) {
   __shared__ double sk[RB][4];
   const int tid = threadIdx.x;
+  if (a.ack_peers && blockIdx.x == 0 && blockIdx.y == 0 && tid < a.ack_world) {
+    // this launch follows the gather on the stream: the exchange buffer of update ack_seq is no longer read here
+    volatile unsigned long long* ack =
+        reinterpret_cast<unsigned long long*>(a.ack_peers[tid] + a.ack_flag_off) + 4 + a.ack_rank;
+    *ack = a.ack_seq;
+  }
   const int r0 = a.row_begin + blockIdx.y * RB;          // first global row of this CTA
   const int nrows = min(RB, a.row_end - r0);
   for (int r = tid; r < nrows; r += LM_THREADS) {

@@ -20,6 +20,10 @@ struct LmGatherArgs {
   int shard;              // 1: rows/mu5 come from the exchange buffer of a row-block shard
   double* mu_out;         // shard only: replicated pose entries are refreshed here
   double rng, brg, mm;
+  // peer-memory exchange: wait until both flags of the exchange buffer reached wait_seq before reading `row`
+  const unsigned long long* wait_flags;  // null = no wait
+  unsigned long long wait_seq;
+  unsigned long long* wait_err;
 };
 
 struct LmUpdateArgs {
@@ -29,6 +33,11 @@ struct LmUpdateArgs {
   int64_t ld;
   int n, row_begin, row_end;
   int full_tiles, tail_groups;  // filled by the launcher
+  // peer-memory exchange: the first CTA tells every rank that this rank's gather of update ack_seq is done
+  double* const* ack_peers;     // null = no ack
+  int64_t ack_flag_off;
+  unsigned long long ack_seq;
+  int ack_world, ack_rank;
 };
 
 constexpr int LM_MAX_FUSED = 4;  // updates fused into one pass over P (ekf_largemap_multi.cu)
@@ -48,6 +57,25 @@ struct LmMultiArgs {
   int full_tiles, tail_groups;  // filled by the launcher
 };
 cudaError_t lm_launch_update_multi(const LmMultiArgs& a, cudaStream_t st);
+
+// peer-memory row exchange of the row-block shards (ekf_largemap_p2p.cu). One exchange AREA per rank (doubles):
+//   [2][5][ldx] double-buffered rows {0,1,2,j,j+1} (+ mu entry at column ld), then at flag_off:
+//   u64 flags[2][2] (buffer, part: 0 = robot rows, 1 = landmark rows), u64 acks[P2P_MAX_WORLD]
+constexpr int P2P_MAX_WORLD = 16;
+struct P2PArgs {
+  const double* P;              // local row block
+  const double* mu;
+  double* const* peers;         // device array [world]: every rank's area (own entry = local pointer)
+  unsigned long long* acks;     // local area's ack words
+  unsigned long long* err;      // set to 1 when a spin ran out of budget
+  unsigned* push_count;         // device [world] CTA counters of the push kernel
+  int64_t ld, ldx, flag_off;
+  unsigned long long seq;       // update sequence number, starts at 1
+  int world, rank, row_begin;
+};
+cudaError_t lm_launch_p2p_push(const P2PArgs& a, int first_row, int first_k, int nrows, int part, cudaStream_t st);
+cudaError_t lm_launch_p2p_wait(const P2PArgs& a, cudaStream_t st);
+cudaError_t lm_launch_p2p_ack(const P2PArgs& a, cudaStream_t st);
 
 cudaError_t lm_launch_augment(double* mu, double* P, int64_t ld, int row_begin, int row_end, int j, double gx,
                               double gy, cudaStream_t st);

@@ -212,6 +212,41 @@ class LargeMapEKF:
         capi.call("ekf_lm_update_from_rows", self._h, int(slot), float(rng), float(brg), _ptr(rows5),
                   _stream_ptr(self.torch))
 
+    # ---- row exchange over NVLink peer memory (row-block shards, one process per GPU) ----
+    P2P_HANDLE_BYTES = 64
+
+    def p2p_init(self, world: int, rank: int) -> bytes:
+        """Allocate this shard's exchange area; returns its cudaIpc handle (to be gathered from every rank)."""
+        buf = (C.c_ubyte * self.P2P_HANDLE_BYTES)()
+        capi.call("ekf_lm_p2p_init", self._h, int(world), int(rank), buf, self.P2P_HANDLE_BYTES)
+        return bytes(buf)
+
+    def p2p_area(self) -> int:
+        v = C.c_void_p(0)
+        capi.call("ekf_lm_p2p_area", self._h, C.byref(v))
+        return int(v.value or 0)
+
+    def p2p_connect(self, handles=None, local_areas=None):
+        """handles: list of ``world`` handle byte strings (other processes); local_areas: list of device pointers
+        (ints, 0 = use the handle) for shards living in this process."""
+        hb = None
+        if handles is not None:
+            blob = b"".join(bytes(h).ljust(self.P2P_HANDLE_BYTES, b"\0") for h in handles)
+            hb = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+        la = None
+        if local_areas is not None:
+            la = (C.c_void_p * len(local_areas))(*[C.c_void_p(int(a) or None) for a in local_areas])
+        capi.call("ekf_lm_p2p_connect", self._h, hb, self.P2P_HANDLE_BYTES, la)
+
+    def p2p_update(self, slot: int, rng: float, brg: float, owner: int):
+        capi.call("ekf_lm_p2p_update", self._h, int(slot), float(rng), float(brg), int(owner),
+                  _stream_ptr(self.torch))
+
+    def p2p_error(self) -> int:
+        v = C.c_int64(0)
+        capi.call("ekf_lm_p2p_error", self._h, C.byref(v))
+        return int(v.value)
+
     def sync(self):
         capi.call("ekf_lm_sync", self._h)
 

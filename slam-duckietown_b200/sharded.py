@@ -59,8 +59,12 @@ def exchange_rows(rows5, owner: int, group=None):
 class ShardedLargeMapEKF:
     """One process per GPU; every rank calls the same methods with the same arguments (SPMD)."""
 
-    def __init__(self, capacity: int, rank: int, world: int, device: int | None = None, group=None):
+    def __init__(self, capacity: int, rank: int, world: int, device: int | None = None, group=None,
+                 exchange: str = "nccl"):
+        """exchange: "nccl" — export + two broadcasts per update through torch.distributed; "p2p" — the owners push
+        their rows into every rank's exchange area over NVLink peer memory (cudaIpc), no collective in the update."""
         self.capacity, self.rank, self.world, self.group = int(capacity), int(rank), int(world), group
+        self.exchange = exchange
         self.ranges = row_partition(self.capacity, self.world)
         self.local = eb.LargeMapEKF(self.capacity, device=self.rank if device is None else device,
                                     row_range=self.ranges[self.rank])
@@ -68,6 +72,22 @@ class ShardedLargeMapEKF:
         torch = self.local.torch
         self.rows5 = torch.zeros((5, self.ld + 4), dtype=torch.float64, device=self.local.mu.device)
         self.local.rows5 = self.rows5
+        if exchange == "p2p":
+            self._connect_p2p()
+        elif exchange != "nccl":
+            raise ValueError(f"unknown exchange {exchange!r}")
+
+    def _connect_p2p(self):
+        """torch.distributed is the plumbing only: one all-gather of the 64-byte IPC handles at set-up."""
+        import torch.distributed as dist
+        handle = self.local.p2p_init(self.world, self.rank)
+        if self.world == 1:
+            self.local.p2p_connect(handles=[handle])
+            return
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, handle, group=self.group)
+        self.local.p2p_connect(handles=gathered)
+        dist.barrier(group=self.group)
 
     def close(self):
         self.local.close()
@@ -101,6 +121,9 @@ class ShardedLargeMapEKF:
         self.local.predict(ang, lin)           # no communication
 
     def update(self, slot: int, rng: float, brg: float):
+        if self.exchange == "p2p":
+            self.local.p2p_update(slot, rng, brg, owner_of_slot(slot, self.capacity, self.world))
+            return
         self.local.export_rows(slot)
         exchange_rows(self.rows5, owner_of_slot(slot, self.capacity, self.world), self.group)
         self.local.update_from_rows(slot, rng, brg, self.rows5)

@@ -607,3 +607,35 @@ def test_group_kernel_ragged_batch_and_mixed_observations(eb, monkeypatch):
         for a, b in zip(res["regw"], res[variant]):
             assert torch.equal(a, b), variant
     assert bool(torch.isfinite(res["regw"][0]).all())
+
+
+def test_p2p_row_exchange_two_processes(eb):
+    """Row-block shards in TWO processes (one per rank, both on cuda:0 here; one per GPU on a multi-GPU box) exchange
+    their rows over CUDA IPC peer memory — owners push, consumers wait on flags, no collective: every shard must equal
+    the same rows of an unsharded filter BITWISE and no spin may have timed out."""
+    import json
+    import socket
+    import subprocess
+    import sys
+    import os
+    import torch
+    worker = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_p2p_worker.py")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    world = 2
+    ndev = torch.cuda.device_count()
+    procs = [subprocess.Popen([sys.executable, worker, str(r), str(world), str(port), str(r % ndev)],
+                              stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True) for r in range(world)]
+    outs = []
+    for p in procs:
+        try:
+            o, e = p.communicate(timeout=240)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+        assert p.returncode == 0, e[-2000:]
+        outs.append(json.loads(o.strip().splitlines()[-1]))
+    for o in outs:
+        assert o["same"] and o["p2p_error"] == 0 and o["finite"], o
