@@ -135,6 +135,12 @@ int ekf_lm_update(ekf_lm_t* h, int slot, double rng, double brg, void* stream);
  * form the call falls back to the sequential kernels.                                                   */
 int ekf_lm_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
                         const double* brg_host, void* stream);
+/* Fused step on a row-block shard: export the locally owned ones of the rows {0,1,2} U {j_u, j_u+1 : u < m} (+ mu
+ * entries at column ld) into rows_dev [3 + 2m][ld + 4]; after the owners' rows were exchanged, run the m updates on
+ * the local block with one read + write of it. 2 <= m <= 4. Sharded result == unsharded ekf_lm_update_multi bitwise. */
+int ekf_lm_export_rows_multi(ekf_lm_t* h, int m, const int32_t* slots_host, double* rows_dev, void* stream);
+int ekf_lm_update_multi_from_rows(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
+                                  const double* brg_host, const double* rows_dev, void* stream);
 /* Row-block shards: export this shard's share of rows {0,1,2,j,j+1} (+ mu entries) into rows5_dev
  * [5][ld+4] (rows it does not own are left untouched), then — after the owners' rows were exchanged
  * (NCCL broadcast by the host) — run the update on the local block from the replicated buffer.          */

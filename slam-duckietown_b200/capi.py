@@ -67,6 +67,8 @@ SIGNATURES = {
     "ekf_lm_predict": (_i, [_p, _d, _d, _p]),
     "ekf_lm_update": (_i, [_p, _i, _d, _d, _p]),
     "ekf_lm_update_multi": (_i, [_p, _i, _p, _p, _p, _p]),
+    "ekf_lm_export_rows_multi": (_i, [_p, _i, _p, _p, _p]),
+    "ekf_lm_update_multi_from_rows": (_i, [_p, _i, _p, _p, _p, _p, _p]),
     "ekf_lm_export_rows": (_i, [_p, _i, _p, _p]),
     "ekf_lm_update_from_rows": (_i, [_p, _i, _d, _d, _p, _p]),
     "ekf_lm_p2p_init": (_i, [_p, _i, _i, _p, _l]),

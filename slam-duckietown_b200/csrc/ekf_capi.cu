@@ -78,6 +78,7 @@ struct ekf_lm {
   double *K0 = nullptr, *K1 = nullptr, *A0 = nullptr, *A1 = nullptr, *W0 = nullptr, *W1 = nullptr,
          *scal = nullptr;
   double *mK = nullptr, *mW = nullptr, *my = nullptr;  // fused multi-update records [LM_MAX_FUSED][2][ldw], y [..][2]
+  double* mKR = nullptr;                               // K_u at the exchanged rows [LM_MAX_FUSED][LM_MAX_ROWS][2]
   // peer-memory row exchange (ekf_lm_p2p_*)
   int p2p_world = 0, p2p_rank = 0;
   double* p2p_area = nullptr;                 // this rank's exchange area (cudaMalloc, exported by IPC handle)
@@ -465,7 +466,8 @@ int ekf_lm_create(int capacity_landmarks, int device, ekf_lm_t** out) {
   const char* v = getenv("EKF_LM_VARIANT");
   h->variant = v ? atoi(v) : 0;
   double* ws = nullptr;
-  const size_t ws_doubles = (size_t)(6 + 4 * ekf::LM_MAX_FUSED) * h->ldw + ekf::kScalCount + 2 * ekf::LM_MAX_FUSED;
+  const size_t ws_doubles = (size_t)(6 + 4 * ekf::LM_MAX_FUSED) * h->ldw + ekf::kScalCount + 2 * ekf::LM_MAX_FUSED +
+                            2 * ekf::LM_MAX_FUSED * ekf::LM_MAX_ROWS;
   cudaError_t e = cudaMalloc(&ws, ws_doubles * sizeof(double));
   if (e == cudaSuccess) e = cudaMemset(ws, 0, ws_doubles * sizeof(double));
   if (e != cudaSuccess) {
@@ -483,6 +485,7 @@ int ekf_lm_create(int capacity_landmarks, int device, ekf_lm_t** out) {
   h->my = h->scal + ekf::kScalCount;
   h->mK = h->my + 2 * ekf::LM_MAX_FUSED;
   h->mW = h->mK + 2 * ekf::LM_MAX_FUSED * h->ldw;
+  h->mKR = h->mW + 2 * ekf::LM_MAX_FUSED * h->ldw;
   *out = h;
   return EKF_OK;
 }
@@ -620,17 +623,38 @@ int ekf_lm_update(ekf_lm_t* h, int slot, double rng, double brg, void* stream) {
   return lm_update_impl(h, slot, rng, brg, nullptr, stream);
 }
 
-int ekf_lm_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
-                        const double* brg_host, void* stream) {
+static int lm_multi_check(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
+                          const double* brg_host, bool need_obs = true) {
   if (!h) return fail(EKF_EINVAL, "null handle");
   if (m < 0) return fail(EKF_EINVAL, "m < 0");
-  if (m > 0 && (!slots_host || !rng_host || !brg_host)) return fail(EKF_EINVAL, "observation arrays are null");
+  if (m > 0 && (!slots_host || (need_obs && (!rng_host || !brg_host))))
+    return fail(EKF_EINVAL, "observation arrays are null");
   if (!h->P) return fail(EKF_ESTATE, "state not bound");
-  const bool whole = (h->row_begin == 0 && h->row_end == h->n);
-  const bool joseph = (h->flags & ekf::kFlagJoseph) != 0;
   for (int u = 0; u < m; ++u)
     if (slots_host[u] < 0 || slots_host[u] >= h->cap)
       return fail(EKF_EINVAL, "slot %d outside capacity %d", slots_host[u], h->cap);
+  return EKF_OK;
+}
+
+static void lm_multi_fill(ekf_lm_t* h, ekf::LmMultiArgs& a, int g, const int32_t* slots, const double* rng,
+                          const double* brg, const double* xrows) {
+  a.P = h->P; a.mu = h->mu; a.K = h->mK; a.W = h->mW; a.y = h->my; a.KR = h->mKR;
+  a.xrows = xrows;
+  a.ld = h->ld; a.ldw = h->ldw; a.ldx = h->ld + 4;
+  a.n = h->n; a.m = g; a.row_begin = h->row_begin; a.row_end = h->row_end; a.mm = h->mm;
+  for (int u = 0; u < g; ++u) {
+    a.j[u] = 3 + 2 * slots[u];
+    if (rng) a.rng[u] = rng[u];
+    if (brg) a.brg[u] = brg[u];
+  }
+}
+
+int ekf_lm_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
+                        const double* brg_host, void* stream) {
+  const int rc0 = lm_multi_check(h, m, slots_host, rng_host, brg_host);
+  if (rc0 != EKF_OK) return rc0;
+  const bool whole = (h->row_begin == 0 && h->row_end == h->n);
+  const bool joseph = (h->flags & ekf::kFlagJoseph) != 0;
   if (!(h->flags & ekf::kFlagMeasurement)) return EKF_OK;
   if (!whole || joseph) {  // no fused form there: the sequential path (fails on a shard like ekf_lm_update)
     for (int u = 0; u < m; ++u) {
@@ -648,15 +672,36 @@ int ekf_lm_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const dou
       continue;
     }
     ekf::LmMultiArgs a{};
-    a.P = h->P; a.mu = h->mu; a.K = h->mK; a.W = h->mW; a.y = h->my;
-    a.ld = h->ld; a.ldw = h->ldw; a.n = h->n; a.m = g; a.mm = h->mm;
-    for (int u = 0; u < g; ++u) {
-      a.j[u] = 3 + 2 * slots_host[first + u];
-      a.rng[u] = rng_host[first + u];
-      a.brg[u] = brg_host[first + u];
-    }
+    lm_multi_fill(h, a, g, slots_host + first, rng_host + first, brg_host + first, nullptr);
     CU(ekf::lm_launch_update_multi(a, (cudaStream_t)stream));
   }
+  return EKF_OK;
+}
+
+int ekf_lm_export_rows_multi(ekf_lm_t* h, int m, const int32_t* slots_host, double* rows_dev, void* stream) {
+  const int rc0 = lm_multi_check(h, m, slots_host, nullptr, nullptr, false);
+  if (rc0 != EKF_OK) return rc0;
+  if (!rows_dev) return fail(EKF_EINVAL, "rows_dev is null");
+  if (m < 2 || m > ekf::LM_MAX_FUSED) return fail(EKF_EINVAL, "m must be in [2, %d]", ekf::LM_MAX_FUSED);
+  CU(cudaSetDevice(h->device));
+  ekf::LmMultiArgs a{};
+  lm_multi_fill(h, a, m, slots_host, nullptr, nullptr, nullptr);
+  CU(ekf::lm_launch_export_rows_multi(a, rows_dev, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf_lm_update_multi_from_rows(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
+                                  const double* brg_host, const double* rows_dev, void* stream) {
+  const int rc0 = lm_multi_check(h, m, slots_host, rng_host, brg_host);
+  if (rc0 != EKF_OK) return rc0;
+  if (!rows_dev) return fail(EKF_EINVAL, "rows_dev is null");
+  if (m < 2 || m > ekf::LM_MAX_FUSED) return fail(EKF_EINVAL, "m must be in [2, %d]", ekf::LM_MAX_FUSED);
+  if (h->flags & ekf::kFlagJoseph) return fail(EKF_EINVAL, "Joseph form is not available on a row-block shard");
+  if (!(h->flags & ekf::kFlagMeasurement)) return EKF_OK;
+  CU(cudaSetDevice(h->device));
+  ekf::LmMultiArgs a{};
+  lm_multi_fill(h, a, m, slots_host, rng_host, brg_host, rows_dev);
+  CU(ekf::lm_launch_update_multi(a, (cudaStream_t)stream));
   return EKF_OK;
 }
 

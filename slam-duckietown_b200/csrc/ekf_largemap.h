@@ -41,6 +41,7 @@ struct LmUpdateArgs {
 };
 
 constexpr int LM_MAX_FUSED = 4;  // updates fused into one pass over P (ekf_largemap_multi.cu)
+constexpr int LM_MAX_ROWS = 3 + 2 * LM_MAX_FUSED;  // rows a fused step exchanges
 
 // fused multi-update: m sequential updates of one step, ONE read + write of P (plain form, whole matrix on one GPU)
 struct LmMultiArgs {
@@ -49,14 +50,17 @@ struct LmMultiArgs {
   double* K;    // [m][2][ldw]: K_u[:,0] at K + 2u ldw, K_u[:,1] at K + (2u+1) ldw
   double* W;    // [m][2][ldw]: (H P)_u rows, same indexing
   double* y;    // [m][2] innovations
-  int64_t ld, ldw;
-  int n, m;
+  double* KR;   // [m][LM_MAX_ROWS][2] K_u at the exchanged rows R = {0,1,2} U {j_u, j_u+1} (replicated on every rank)
+  const double* xrows;  // row-block shard: exchanged rows [3 + 2m][ldx] (+ mu entry at column ld); null = read P
+  int64_t ld, ldw, ldx;
+  int n, m, row_begin, row_end;
   int j[LM_MAX_FUSED];
   double rng[LM_MAX_FUSED], brg[LM_MAX_FUSED];
   double mm;
   int full_tiles, tail_groups;  // filled by the launcher
 };
 cudaError_t lm_launch_update_multi(const LmMultiArgs& a, cudaStream_t st);
+cudaError_t lm_launch_export_rows_multi(const LmMultiArgs& a, double* rows, cudaStream_t st);
 
 // peer-memory row exchange of the row-block shards (ekf_largemap_p2p.cu). One exchange AREA per rank (doubles):
 //   [2][5][ldx] double-buffered rows {0,1,2,j,j+1} (+ mu entry at column ld), then at flag_off:

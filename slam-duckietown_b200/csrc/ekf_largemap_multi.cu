@@ -24,7 +24,19 @@ __device__ __forceinline__ double rank2e(double v, double k0, double k1, double 
 
 }  // namespace
 
+// exchanged-row bookkeeping of a fused step: R = {0, 1, 2} U {j_u, j_u + 1 : u < m}; rho indexes R
+__device__ __forceinline__ int rho_row(const LmMultiArgs& a, int rho) {
+  return rho < 3 ? rho : a.j[(rho - 3) >> 1] + ((rho - 3) & 1);
+}
+// row rho of the step's INITIAL covariance: the exchange buffer on a row-block shard, P itself otherwise
+__device__ __forceinline__ const double* rho_ptr(const LmMultiArgs& a, int rho) {
+  return a.xrows ? a.xrows + (int64_t)rho * a.ldx : a.P + (int64_t)rho_row(a, rho) * a.ld;
+}
+
 // a8-a9 for update u of the step, on the covariance as it stands after updates 0..u-1 (never materialised).
+// Every rank computes W_u over all n columns (from the five full rows) and K_u for its local rows (from their five
+// columns); K_u at the exchanged rows R — which later updates need as uniform operands on EVERY rank — is rebuilt
+// from the exchanged rows themselves by block 0 (a.KR), with the operation sequence of the owning thread.
 __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int u) {
   __shared__ double sh[2][5];
   __shared__ double ssi[2][2];
@@ -32,11 +44,12 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
   __shared__ double sww[LM_MAX_FUSED][2][5];  // W_w[:, idx5(u)]
   const int j = a.j[u];
   const int idx5[5] = {0, 1, 2, j, j + 1};
-  const double* __restrict__ P = a.P;
+  const int rho5[5] = {0, 1, 2, 3 + 2 * u, 4 + 2 * u};
+  const int nr = 3 + 2 * a.m;
   if (threadIdx.x < 5 * u) {  // uniform operands of the rebuild
     const int w = threadIdx.x / 5, k = threadIdx.x - 5 * w;
-    skw[w][k][0] = a.K[(2 * w) * a.ldw + idx5[k]];
-    skw[w][k][1] = a.K[(2 * w + 1) * a.ldw + idx5[k]];
+    skw[w][k][0] = a.KR[(w * LM_MAX_ROWS + rho5[k]) * 2];
+    skw[w][k][1] = a.KR[(w * LM_MAX_ROWS + rho5[k]) * 2 + 1];
     sww[w][0][k] = a.W[(2 * w) * a.ldw + idx5[k]];
     sww[w][1][k] = a.W[(2 * w + 1) * a.ldw + idx5[k]];
   }
@@ -46,22 +59,23 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
   // strided column reads overlap it instead of following it
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = t < a.n;
+  const bool local = live && t >= a.row_begin && t < a.row_end;
   double pr[5], pc[5];
   if (live) {
     double kt0[LM_MAX_FUSED], kt1[LM_MAX_FUSED], wt0[LM_MAX_FUSED], wt1[LM_MAX_FUSED];
 #pragma unroll
     for (int w = 0; w < LM_MAX_FUSED; ++w)
       if (w < u) {
-        kt0[w] = a.K[(2 * w) * a.ldw + t];
-        kt1[w] = a.K[(2 * w + 1) * a.ldw + t];
+        kt0[w] = local ? a.K[(2 * w) * a.ldw + t] : 0.0;
+        kt1[w] = local ? a.K[(2 * w + 1) * a.ldw + t] : 0.0;
         wt0[w] = a.W[(2 * w) * a.ldw + t];
         wt1[w] = a.W[(2 * w + 1) * a.ldw + t];
       }
-    const double* prow = P + (int64_t)t * a.ld;
+    const double* prow = a.P + (int64_t)(t - a.row_begin) * a.ld;
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
-      pr[k] = P[(int64_t)idx5[k] * a.ld + t];  // row idx5[k], column t
-      pc[k] = prow[idx5[k]];                   // row t, column idx5[k]
+      pr[k] = rho_ptr(a, rho5[k])[t];            // row idx5[k], column t
+      pc[k] = local ? prow[idx5[k]] : 0.0;       // row t, column idx5[k]
     }
 #pragma unroll
     for (int k = 0; k < 5; ++k)
@@ -76,7 +90,9 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
     double mu5[5];
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
-      double v = a.mu[idx5[k]];  // mu is written by the streaming kernel only: still the step's initial mean
+      // the step's initial mean: riding at column ld of the exchanged row on a shard (local copies of non-local
+      // entries are stale there), mu itself otherwise (it is written by the streaming kernel only)
+      double v = a.xrows ? rho_ptr(a, rho5[k])[a.ld] : a.mu[idx5[k]];
       for (int w = 0; w < u; ++w) v = mu_inc(v, skw[w][k][0], skw[w][k][1], a.y[2 * w], a.y[2 * w + 1]);
       mu5[k] = v;
     }
@@ -87,7 +103,7 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
       double s0 = 0.0, s1 = 0.0;
 #pragma unroll
       for (int k = 0; k < 5; ++k) {
-        double p = P[(int64_t)idx5[k] * a.ld + idx5[c]];
+        double p = rho_ptr(a, rho5[k])[idx5[c]];
         for (int w = 0; w < u; ++w) p = rank2e(p, skw[w][k][0], skw[w][k][1], sww[w][0][c], sww[w][1][c]);
         s0 = fma(in.h[0][k], p, s0);
         s1 = fma(in.h[1][k], p, s1);
@@ -122,6 +138,24 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
     }
   }
   __syncthreads();
+  if (blockIdx.x == 0 && threadIdx.x < nr) {
+    // K_u at exchanged row rho: its five columns idx5(u) come from the exchanged row, rebuilt with the earlier
+    // updates exactly as the thread owning that row rebuilds them
+    const int rho = threadIdx.x;
+    const double* xr = rho_ptr(a, rho);
+    double ph0 = 0.0, ph1 = 0.0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      double p = xr[idx5[k]];
+      for (int w = 0; w < u; ++w)
+        p = rank2e(p, a.KR[(w * LM_MAX_ROWS + rho) * 2], a.KR[(w * LM_MAX_ROWS + rho) * 2 + 1], sww[w][0][k],
+                   sww[w][1][k]);
+      ph0 = fma(p, sh[0][k], ph0);
+      ph1 = fma(p, sh[1][k], ph1);
+    }
+    a.KR[(u * LM_MAX_ROWS + rho) * 2] = dot2(ph0, ssi[0][0], ph1, ssi[1][0]);
+    a.KR[(u * LM_MAX_ROWS + rho) * 2 + 1] = dot2(ph0, ssi[0][1], ph1, ssi[1][1]);
+  }
   if (!live) return;
   double hp0 = 0.0, hp1 = 0.0, pht0 = 0.0, pht1 = 0.0;
 #pragma unroll
@@ -131,8 +165,10 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
     pht0 = fma(pc[k], sh[0][k], pht0);
     pht1 = fma(pc[k], sh[1][k], pht1);
   }
-  a.K[(2 * u) * a.ldw + t] = dot2(pht0, ssi[0][0], pht1, ssi[1][0]);
-  a.K[(2 * u + 1) * a.ldw + t] = dot2(pht0, ssi[0][1], pht1, ssi[1][1]);
+  if (local) {
+    a.K[(2 * u) * a.ldw + t] = dot2(pht0, ssi[0][0], pht1, ssi[1][0]);
+    a.K[(2 * u + 1) * a.ldw + t] = dot2(pht0, ssi[0][1], pht1, ssi[1][1]);
+  }
   a.W[(2 * u) * a.ldw + t] = hp0;
   a.W[(2 * u + 1) * a.ldw + t] = hp1;
 }
@@ -145,8 +181,16 @@ template <int RB, int UNROLL, int M>
 __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMultiArgs a) {
   __shared__ double sk[RB][2 * M];
   const int tid = threadIdx.x;
-  const int r0 = blockIdx.y * RB;
-  const int nrows = min(RB, a.n - r0);
+  const int r0 = a.row_begin + blockIdx.y * RB;  // first global row of this CTA
+  const int nrows = min(RB, a.row_end - r0);
+  if (a.xrows && a.row_begin != 0 && blockIdx.x == 0 && blockIdx.y == 0 && tid < 3) {
+    // row-block shard that does not own the robot rows: keep the replicated pose entries of mu current
+    double v = a.mu[tid];
+#pragma unroll
+    for (int u = 0; u < M; ++u)
+      v = mu_inc(v, a.KR[(u * LM_MAX_ROWS + tid) * 2], a.KR[(u * LM_MAX_ROWS + tid) * 2 + 1], a.y[2 * u], a.y[2 * u + 1]);
+    a.mu[tid] = v;
+  }
   for (int e = tid; e < nrows * 2 * M; e += LM_THREADS) {
     const int r = e / (2 * M), q = e - r * (2 * M);
     sk[r][q] = a.K[(int64_t)q * a.ldw + r0 + r];
@@ -160,7 +204,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
       a.mu[r0 + r] = v;
     }
   }
-  double* __restrict__ Pblk = a.P + (int64_t)r0 * a.ld;
+  double* __restrict__ Pblk = a.P + (int64_t)(r0 - a.row_begin) * a.ld;
   if ((int)blockIdx.x < a.full_tiles) {
     const int c = (blockIdx.x * LM_THREADS + tid) * 4;
     double4x w0[M], w1[M];
@@ -222,10 +266,31 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
   }
 }
 
+// shard export of a fused step: the locally owned ones of the rows R (and their mu entries at column ld) into the
+// exchange buffer rows [3 + 2m][ldx]
+__global__ void lm_export_rows_multi_kernel(LmMultiArgs a, double* __restrict__ rows) {
+  const int rho = blockIdx.y;
+  const int row = rho_row(a, rho);
+  if (row < a.row_begin || row >= a.row_end) return;
+  const double* src = a.P + (int64_t)(row - a.row_begin) * a.ld;
+  double* dst = rows + (int64_t)rho * a.ldx;
+  for (int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; c < a.ld; c += (int64_t)gridDim.x * blockDim.x)
+    dst[c] = src[c];
+  if (blockIdx.x == 0 && threadIdx.x == 0) dst[a.ld] = a.mu[row];
+}
+
+cudaError_t lm_launch_export_rows_multi(const LmMultiArgs& a, double* rows, cudaStream_t st) {
+  dim3 grid(8, 3 + 2 * a.m);
+  lm_export_rows_multi_kernel<<<grid, 256, 0, st>>>(a, rows);
+  return cudaGetLastError();
+}
+
 template <int M>
 static cudaError_t launch_multi_t(const LmMultiArgs& a, cudaStream_t st) {
   constexpr int RB = 32, UNROLL = 8;
-  dim3 grid(a.full_tiles + (a.tail_groups ? 1 : 0), (a.n + RB - 1) / RB);
+  const int rows = a.row_end - a.row_begin;
+  if (rows <= 0) return cudaSuccess;
+  dim3 grid(a.full_tiles + (a.tail_groups ? 1 : 0), (rows + RB - 1) / RB);
   lm_rank_update_multi_kernel<RB, UNROLL, M><<<grid, LM_THREADS, 0, st>>>(a);
   return cudaGetLastError();
 }

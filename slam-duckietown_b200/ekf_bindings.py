@@ -201,6 +201,23 @@ class LargeMapEKF:
         capi.call("ekf_lm_update_multi", self._h, int(sl.size), sl.ctypes.data, rg.ctypes.data, bg.ctypes.data,
                   _stream_ptr(self.torch))
 
+    def export_rows_multi(self, slots, rows=None):
+        """Fused step on a row-block shard: this shard's share of rows {0,1,2} U {j_u, j_u+1} into a
+        (3 + 2m, ld + 4) device buffer (created when not given)."""
+        sl = np.ascontiguousarray(slots, dtype=np.int32)
+        if rows is None:
+            rows = self.torch.zeros((3 + 2 * sl.size, self.ld + 4), dtype=self.torch.float64, device=self.mu.device)
+        capi.call("ekf_lm_export_rows_multi", self._h, int(sl.size), sl.ctypes.data, _ptr(rows),
+                  _stream_ptr(self.torch))
+        return rows
+
+    def update_multi_from_rows(self, slots, rngs, brgs, rows):
+        sl = np.ascontiguousarray(slots, dtype=np.int32)
+        rg = np.ascontiguousarray(rngs, dtype=np.float64)
+        bg = np.ascontiguousarray(brgs, dtype=np.float64)
+        capi.call("ekf_lm_update_multi_from_rows", self._h, int(sl.size), sl.ctypes.data, rg.ctypes.data,
+                  bg.ctypes.data, _ptr(rows), _stream_ptr(self.torch))
+
     def export_rows(self, slot: int):
         if self.rows5 is None:
             self.rows5 = self.torch.zeros((5, self.ld + 4), dtype=self.torch.float64, device=self.mu.device)

@@ -56,6 +56,17 @@ def exchange_rows(rows5, owner: int, group=None):
                    group=group)
 
 
+def exchange_rows_multi(rows, owners, group=None):
+    """Exchange of a fused step: rows 0-2 from rank 0, rows 3+2u, 4+2u (= P rows j_u, j_u+1) from owners[u]."""
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return
+    g = (lambda r: dist.get_global_rank(group, r)) if group is not None else (lambda r: r)
+    dist.broadcast(rows[0:3], src=g(0), group=group)
+    for u, owner in enumerate(owners):
+        dist.broadcast(rows[3 + 2 * u:5 + 2 * u], src=g(owner), group=group)
+
+
 class ShardedLargeMapEKF:
     """One process per GPU; every rank calls the same methods with the same arguments (SPMD)."""
 
@@ -128,6 +139,19 @@ class ShardedLargeMapEKF:
         exchange_rows(self.rows5, owner_of_slot(slot, self.capacity, self.world), self.group)
         self.local.update_from_rows(slot, rng, brg, self.rows5)
 
+    def update_multi(self, slots, rngs, brgs):
+        """The step's sequential updates fused into ONE pass over every shard's row block and ONE exchange of the
+        rows {0,1,2} U {j_u, j_u+1} (groups of at most 4 updates; a single update takes the plain path)."""
+        slots, rngs, brgs = list(slots), list(rngs), list(brgs)
+        for first in range(0, len(slots), 4):
+            sl, rg, bg = slots[first:first + 4], rngs[first:first + 4], brgs[first:first + 4]
+            if len(sl) == 1:
+                self.update(sl[0], rg[0], bg[0])
+                continue
+            rows = self.local.export_rows_multi(sl)
+            exchange_rows_multi(rows, [owner_of_slot(s, self.capacity, self.world) for s in sl], self.group)
+            self.local.update_multi_from_rows(sl, rg, bg, rows)
+
     def local_state(self):
         """(mu slice owned by this rank incl. the replicated pose on rank 0, P row block) as numpy."""
         lo, hi = self.ranges[self.rank]
@@ -176,6 +200,19 @@ class EmulatedShards:
                 bufs[r][3:5].copy_(bufs[owner][3:5])
         for s in self.shards:
             s.update_from_rows(slot, rng, brg)
+
+    def update_multi(self, slots, rngs, brgs):
+        slots = list(slots)
+        owners = [owner_of_slot(s, self.capacity, self.world) for s in slots]
+        bufs = [s.export_rows_multi(slots) for s in self.shards]
+        for r in range(self.world):                   # "broadcast": copy the owners' rows to everyone
+            if r != 0:
+                bufs[r][0:3].copy_(bufs[0][0:3])
+            for u, o in enumerate(owners):
+                if r != o:
+                    bufs[r][3 + 2 * u:5 + 2 * u].copy_(bufs[o][3 + 2 * u:5 + 2 * u])
+        for s, b in zip(self.shards, bufs):
+            s.update_multi_from_rows(slots, rngs, brgs, b)
 
     def state(self):
         import numpy as np

@@ -117,3 +117,54 @@ def test_sharded_equals_unsharded_bitwise(world):
         np.testing.assert_array_equal(s.state()[0][:3], mu1[:3])
     sh.close()
     single.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world,group", [(2, 3), (3, 2), (8, 4)])
+def test_sharded_fused_multi_update_equals_unsharded_bitwise(world, group):
+    """The fused step (m updates, ONE exchange of the rows {0,1,2} U {j_u, j_u+1}, ONE pass over each row block) on
+    row-block shards == the unsharded fused step == the sequential single updates, bitwise; every shard keeps the
+    replicated pose current."""
+    from slam_duckietown_b200 import ekf_bindings as eb, workloads as wl
+    from slam_duckietown_b200.sharded import EmulatedShards
+    n_lm = 300
+    w = wl.make_large_map(n_lm, updates=24)
+    seq, fus = eb.LargeMapEKF(n_lm), eb.LargeMapEKF(n_lm)
+    sh = EmulatedShards(n_lm, world)
+    for g in (seq, fus, sh):
+        g.set_noise(0.1, 0.7)
+        g.load(w.mu0, w.p0())
+    pend = []
+
+    def flush():
+        if pend:
+            args = ([o[1] for o in pend], [o[2] for o in pend], [o[3] for o in pend])
+            fus.update_multi(*args)
+            if len(pend) == 1:
+                sh.update(pend[0][1], pend[0][2], pend[0][3])
+            else:
+                sh.update_multi(*args)
+            pend.clear()
+    for op in w.ops:
+        if op[0] == "update":
+            seq.update(op[1], op[2], op[3])
+            pend.append(op)
+            if len(pend) == group:
+                flush()
+        elif group <= 3:
+            flush()
+            for g in (seq, fus, sh):
+                g.predict(op[1], op[2])
+    flush()
+    mu0, p0 = seq.state()
+    mu1, p1 = fus.state()
+    mu2, p2 = sh.state()
+    np.testing.assert_array_equal(p1, p0)
+    np.testing.assert_array_equal(mu1, mu0)
+    np.testing.assert_array_equal(p2, p0)
+    np.testing.assert_array_equal(mu2, mu0)
+    for s in sh.shards:
+        np.testing.assert_array_equal(s.state()[0][:3], mu0[:3])
+    sh.close()
+    seq.close()
+    fus.close()
