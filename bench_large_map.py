@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--updates", type=int, default=60)
     ap.add_argument("--warmup", type=int, default=6)
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--fused", type=int, default=3, help="also time fused steps of this many updates (0 = skip)")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="row exchange: owners push over NVLink peer memory (default) or two NCCL broadcasts")
     args = ap.parse_args()
@@ -93,6 +94,9 @@ def main():
     e1.record()
     sync()
     ms = e0.elapsed_time(e1) / len(timed)
+    if ref:
+        for o in timed:
+            ref.update(o[1], o[2], o[3])
     # the NCCL exchange alone (export + two broadcasts), same slots, for comparison
     x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     from slam_duckietown_b200.sharded import exchange_rows
@@ -103,15 +107,31 @@ def main():
     x1.record()
     sync()
     xms = x0.elapsed_time(x1) / len(timed)
-    t = torch.tensor([ms, xms], dtype=torch.float64, device=dev)
+    # fused steps: --fused updates with ONE exchange and ONE pass over every row block (ekf_lm_*update_multi)
+    fms = 0.0
+    if args.fused >= 2:
+        groups = [timed[i:i + args.fused] for i in range(0, len(timed) - args.fused + 1, args.fused)]
+        for g3 in groups[:2]:
+            f.update_multi([o[1] for o in g3], [o[2] for o in g3], [o[3] for o in g3])
+        sync()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for g3 in groups[2:]:
+            f.update_multi([o[1] for o in g3], [o[2] for o in g3], [o[3] for o in g3])
+        f1.record()
+        sync()
+        fms = f0.elapsed_time(f1) / max(len(groups) - 2, 1)
+        if ref:
+            for g3 in groups:
+                for o in g3:
+                    ref.update(o[1], o[2], o[3])
+    t = torch.tensor([ms, xms, fms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, xms = float(t[0]), float(t[1])
+    ms, xms, fms = float(t[0]), float(t[1]), float(t[2])
 
     check = None
     if ref:
-        for o in timed:
-            ref.update(o[1], o[2], o[3])
         torch.cuda.synchronize()
         same = bool(torch.equal(f.local.P, ref.P[lo:hi])) and bool(torch.equal(f.local.mu[lo:hi], ref.mu[lo:hi]))
         same &= bool(torch.equal(f.local.mu[:3], ref.mu[:3]))
@@ -133,7 +153,9 @@ def main():
         print(json.dumps({
             "metric": f"ms/update @{L} lm", "value": ms, "unit": "ms", "n_gpus": world, "higher_is_better": False,
             "updates": len(timed), "warmup": args.warmup, "dtype": "f64", "data": "synthetic",
-            "scaling": "strong", "exchange": args.exchange, "nccl_exchange_ms": xms,
+            "scaling": "strong", "exchange": args.exchange,
+            "fused_step": {"updates_per_step": args.fused, "ms_per_step": fms,
+                           "ms_per_update_equiv": fms / args.fused} if args.fused >= 2 else None, "nccl_exchange_ms": xms,
             "p2p_error": f.local.p2p_error() if args.exchange == "p2p" else None,
             "config": {"workload": f"single large-map filter, {L} landmarks (n={n}), P {8 * n * n / 1e9:.2f} GB "
                                    f"row-block sharded over {world} GPU(s), one range-bearing update per step",

@@ -158,6 +158,10 @@ int ekf_lm_p2p_init(ekf_lm_t* h, int world, int rank, unsigned char* handle_out,
 int ekf_lm_p2p_connect(ekf_lm_t* h, const unsigned char* handles, int64_t handle_bytes, void* const* local_areas);
 int ekf_lm_p2p_area(ekf_lm_t* h, void** area_dev);
 int ekf_lm_p2p_update(ekf_lm_t* h, int slot, double rng, double brg, int owner, void* stream);
+/* the fused step (2 <= m <= 4 updates, one pass over the local row block) with its 1 + m row parts pushed by their
+ * owners (owners_host[u] = rank owning rows j_u, j_u+1)                                                        */
+int ekf_lm_p2p_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
+                            const double* brg_host, const int32_t* owners_host, void* stream);
 int ekf_lm_p2p_error(ekf_lm_t* h, int64_t* flag);
 int ekf_lm_sync(ekf_lm_t* h);
 

@@ -75,6 +75,7 @@ SIGNATURES = {
     "ekf_lm_p2p_connect": (_i, [_p, _p, _l, _p]),
     "ekf_lm_p2p_area": (_i, [_p, C.POINTER(_p)]),
     "ekf_lm_p2p_update": (_i, [_p, _i, _d, _d, _i, _p]),
+    "ekf_lm_p2p_update_multi": (_i, [_p, _i, _p, _p, _p, _p, _p]),
     "ekf_lm_p2p_error": (_i, [_p, C.POINTER(_l)]),
     "ekf_lm_sync": (_i, [_p]),
     "ekf3_predict": (_i, [_l, _p, _p, _p, _p, _p, _p]),

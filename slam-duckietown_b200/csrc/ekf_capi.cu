@@ -591,7 +591,9 @@ static int lm_update_impl_split(ekf_lm_t* h, int slot, double rng, double brg, c
   g.shard = rows5 ? 1 : 0;
   g.mu_out = h->mu;
   if (p2p) {
-    g.wait_flags = reinterpret_cast<const unsigned long long*>(h->p2p_area + p2p->flag_off) + (p2p->seq & 1) * 2;
+    g.wait_flags = reinterpret_cast<const unsigned long long*>(h->p2p_area + p2p->flag_off) +
+                   (p2p->seq & 1) * ekf::P2P_PARTS;
+    g.wait_parts = 2;
     g.wait_seq = p2p->seq;
     g.wait_err = p2p->err;
   }
@@ -722,7 +724,8 @@ int ekf_lm_update_from_rows(ekf_lm_t* h, int slot, double rng, double brg, const
 }
 
 // ---- peer-memory row exchange of the row-block shards ----------------------------------------------------
-static int64_t p2p_area_doubles(const ekf_lm* h) { return 10 * (h->ld + 4) + 4 + ekf::P2P_MAX_WORLD; }
+static int64_t p2p_flag_off(const ekf_lm* h) { return 2 * ekf::P2P_ROWS * (h->ld + 4); }
+static int64_t p2p_area_doubles(const ekf_lm* h) { return p2p_flag_off(h) + 2 * ekf::P2P_PARTS + ekf::P2P_MAX_WORLD; }
 
 int ekf_lm_p2p_init(ekf_lm_t* h, int world, int rank, unsigned char* handle_out, int64_t handle_bytes) {
   if (!h || !handle_out) return fail(EKF_EINVAL, "null argument");
@@ -781,6 +784,15 @@ int ekf_lm_p2p_area(ekf_lm_t* h, void** area_dev) {
   return EKF_OK;
 }
 
+static void p2p_fill(ekf_lm_t* h, ekf::P2PArgs& a) {
+  a.P = h->P; a.mu = h->mu; a.peers = h->p2p_peers_dev;
+  a.ld = h->ld; a.ldx = h->ld + 4; a.flag_off = p2p_flag_off(h);
+  a.acks = reinterpret_cast<unsigned long long*>(h->p2p_area + a.flag_off) + 2 * ekf::P2P_PARTS;
+  a.err = h->p2p_err; a.push_count = h->p2p_push_count;
+  a.seq = ++h->p2p_seq;
+  a.world = h->p2p_world; a.rank = h->p2p_rank; a.row_begin = h->row_begin;
+}
+
 int ekf_lm_p2p_update(ekf_lm_t* h, int slot, double rng, double brg, int owner, void* stream) {
   if (!h) return fail(EKF_EINVAL, "null handle");
   if (!h->p2p_peers_dev) return fail(EKF_ESTATE, "p2p exchange not connected");
@@ -790,21 +802,53 @@ int ekf_lm_p2p_update(ekf_lm_t* h, int slot, double rng, double brg, int owner, 
   CU(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;
   const int j = 3 + 2 * slot;
+  if (h->p2p_rank == owner && (j < h->row_begin || j + 1 >= h->row_end))
+    return fail(EKF_EINVAL, "rank %d does not own slot %d", owner, slot);
   ekf::P2PArgs a{};
-  a.P = h->P; a.mu = h->mu; a.peers = h->p2p_peers_dev;
-  a.ld = h->ld; a.ldx = h->ld + 4; a.flag_off = 10 * a.ldx;
-  a.acks = reinterpret_cast<unsigned long long*>(h->p2p_area + a.flag_off) + 4;
-  a.err = h->p2p_err; a.push_count = h->p2p_push_count;
-  a.seq = ++h->p2p_seq;
-  a.world = h->p2p_world; a.rank = h->p2p_rank; a.row_begin = h->row_begin;
+  p2p_fill(h, a);
   if (h->p2p_rank == 0) CU(ekf::lm_launch_p2p_push(a, 0, 0, 3, 0, st));
-  if (h->p2p_rank == owner) {
-    if (j < h->row_begin || j + 1 >= h->row_end) return fail(EKF_EINVAL, "rank %d does not own slot %d", owner, slot);
-    CU(ekf::lm_launch_p2p_push(a, j, 3, 2, 1, st));
-  }
-  const double* rows5 = h->p2p_area + (int64_t)(a.seq & 1) * 5 * a.ldx;
+  if (h->p2p_rank == owner) CU(ekf::lm_launch_p2p_push(a, j, 3, 2, 1, st));
+  const double* rows5 = h->p2p_area + (int64_t)(a.seq & 1) * ekf::P2P_ROWS * a.ldx;
   // gather (waits on the flags, reads the exchange buffer), then the streaming update (acknowledges the buffer)
   return lm_update_impl_split(h, slot, rng, brg, rows5, stream, &a);
+}
+
+// The fused step over peer memory: one push per row part (robot rows by rank 0, rows j_u, j_u+1 by owners[u]), then
+// the m gathers (the first waits on the 1 + m flags) and ONE streaming pass over the local row block.
+int ekf_lm_p2p_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
+                            const double* brg_host, const int32_t* owners_host, void* stream) {
+  const int rc0 = lm_multi_check(h, m, slots_host, rng_host, brg_host);
+  if (rc0 != EKF_OK) return rc0;
+  if (!h->p2p_peers_dev) return fail(EKF_ESTATE, "p2p exchange not connected");
+  if (!owners_host) return fail(EKF_EINVAL, "owners_host is null");
+  if (m < 2 || m > ekf::LM_MAX_FUSED) return fail(EKF_EINVAL, "m must be in [2, %d]", ekf::LM_MAX_FUSED);
+  if (h->flags & ekf::kFlagJoseph) return fail(EKF_EINVAL, "Joseph form is not available on a row-block shard");
+  if (!(h->flags & ekf::kFlagMeasurement)) return EKF_OK;
+  for (int u = 0; u < m; ++u) {
+    const int j = 3 + 2 * slots_host[u];
+    if (owners_host[u] < 0 || owners_host[u] >= h->p2p_world) return fail(EKF_EINVAL, "owner out of range");
+    if (h->p2p_rank == owners_host[u] && (j < h->row_begin || j + 1 >= h->row_end))
+      return fail(EKF_EINVAL, "rank %d does not own slot %d", owners_host[u], slots_host[u]);
+  }
+  CU(cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  ekf::P2PArgs a{};
+  p2p_fill(h, a);
+  if (h->p2p_rank == 0) CU(ekf::lm_launch_p2p_push(a, 0, 0, 3, 0, st));
+  for (int u = 0; u < m; ++u)
+    if (h->p2p_rank == owners_host[u]) CU(ekf::lm_launch_p2p_push(a, 3 + 2 * slots_host[u], 3 + 2 * u, 2, 1 + u, st));
+  ekf::LmMultiArgs g{};
+  lm_multi_fill(h, g, m, slots_host, rng_host, brg_host,
+                h->p2p_area + (int64_t)(a.seq & 1) * ekf::P2P_ROWS * a.ldx);
+  g.wait_flags = reinterpret_cast<const unsigned long long*>(h->p2p_area + a.flag_off) + (a.seq & 1) * ekf::P2P_PARTS;
+  g.wait_seq = a.seq;
+  g.wait_err = a.err;
+  g.ack_peers = a.peers;
+  g.ack_flag_off = a.flag_off;
+  g.ack_world = a.world;
+  g.ack_rank = a.rank;
+  CU(ekf::lm_launch_update_multi(g, st));
+  return EKF_OK;
 }
 
 int ekf_lm_p2p_error(ekf_lm_t* h, int64_t* flag) {

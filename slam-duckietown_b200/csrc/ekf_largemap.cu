@@ -115,13 +115,14 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
     if (threadIdx.x == 0) {
       const volatile unsigned long long* f = a.wait_flags;
       const long long t0 = clock64();
-      while (f[0] < a.wait_seq || f[1] < a.wait_seq) {
-        if (clock64() - t0 > 4000000000LL) {
-          atomicExch(a.wait_err, 1ULL);
-          break;
+      for (int part = 0; part < a.wait_parts; ++part)
+        while (f[part] < a.wait_seq) {
+          if (clock64() - t0 > 4000000000LL) {
+            atomicExch(a.wait_err, 1ULL);
+            break;
+          }
+          __nanosleep(32);
         }
-        __nanosleep(32);
-      }
       __threadfence_system();
     }
     __syncthreads();
@@ -244,7 +245,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs
   if (a.ack_peers && blockIdx.x == 0 && blockIdx.y == 0 && tid < a.ack_world) {
     // this launch follows the gather on the stream: the exchange buffer of update ack_seq is no longer read here
     volatile unsigned long long* ack =
-        reinterpret_cast<unsigned long long*>(a.ack_peers[tid] + a.ack_flag_off) + 4 + a.ack_rank;
+        reinterpret_cast<unsigned long long*>(a.ack_peers[tid] + a.ack_flag_off) + 2 * P2P_PARTS + a.ack_rank;
     *ack = a.ack_seq;
   }
   const int r0 = a.row_begin + blockIdx.y * RB;          // first global row of this CTA

@@ -21,9 +21,10 @@ struct LmGatherArgs {
   double* mu_out;         // shard only: replicated pose entries are refreshed here
   double rng, brg, mm;
   // peer-memory exchange: wait until both flags of the exchange buffer reached wait_seq before reading `row`
-  const unsigned long long* wait_flags;  // null = no wait
+  const unsigned long long* wait_flags;  // null = no wait; else wait_parts consecutive flag words
   unsigned long long wait_seq;
   unsigned long long* wait_err;
+  int wait_parts;
 };
 
 struct LmUpdateArgs {
@@ -54,6 +55,13 @@ struct LmMultiArgs {
   const double* xrows;  // row-block shard: exchanged rows [3 + 2m][ldx] (+ mu entry at column ld); null = read P
   int64_t ld, ldw, ldx;
   int n, m, row_begin, row_end;
+  // peer-memory exchange (see LmGatherArgs / LmUpdateArgs): the first gather waits, the streaming kernel acks
+  const unsigned long long* wait_flags;
+  unsigned long long wait_seq;
+  unsigned long long* wait_err;
+  double* const* ack_peers;
+  int64_t ack_flag_off;
+  int ack_world, ack_rank;
   int j[LM_MAX_FUSED];
   double rng[LM_MAX_FUSED], brg[LM_MAX_FUSED];
   double mm;
@@ -63,9 +71,12 @@ cudaError_t lm_launch_update_multi(const LmMultiArgs& a, cudaStream_t st);
 cudaError_t lm_launch_export_rows_multi(const LmMultiArgs& a, double* rows, cudaStream_t st);
 
 // peer-memory row exchange of the row-block shards (ekf_largemap_p2p.cu). One exchange AREA per rank (doubles):
-//   [2][5][ldx] double-buffered rows {0,1,2,j,j+1} (+ mu entry at column ld), then at flag_off:
-//   u64 flags[2][2] (buffer, part: 0 = robot rows, 1 = landmark rows), u64 acks[P2P_MAX_WORLD]
+//   [2][P2P_ROWS][ldx] double-buffered rows {0,1,2} U {j_u, j_u+1 : u < m} (+ mu entry at column ld), then at
+//   flag_off: u64 flags[2][P2P_PARTS] (buffer, part: 0 = robot rows, 1 + u = landmark rows of update u),
+//   u64 acks[P2P_MAX_WORLD]
 constexpr int P2P_MAX_WORLD = 16;
+constexpr int P2P_ROWS = 11;   // == LM_MAX_ROWS: rows of a fused step of up to 4 updates
+constexpr int P2P_PARTS = 8;   // flag words per buffer (1 + LM_MAX_FUSED used)
 struct P2PArgs {
   const double* P;              // local row block
   const double* mu;
@@ -78,8 +89,6 @@ struct P2PArgs {
   int world, rank, row_begin;
 };
 cudaError_t lm_launch_p2p_push(const P2PArgs& a, int first_row, int first_k, int nrows, int part, cudaStream_t st);
-cudaError_t lm_launch_p2p_wait(const P2PArgs& a, cudaStream_t st);
-cudaError_t lm_launch_p2p_ack(const P2PArgs& a, cudaStream_t st);
 
 cudaError_t lm_launch_augment(double* mu, double* P, int64_t ld, int row_begin, int row_end, int j, double gx,
                               double gy, cudaStream_t st);

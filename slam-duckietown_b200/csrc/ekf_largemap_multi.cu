@@ -10,7 +10,7 @@
 // element in order. HBM traffic per step drops from m x 16 n^2 to 16 n^2 bytes; the per-element operation
 // sequence is that of the sequential kernels (lm_gather_kernel + lm_rank_update_kernel), so the result is bitwise
 // the same (tests/test_gpu_parity.py::test_large_map_fused_multi_update_bitwise).
-// Plain covariance form, whole matrix on one GPU.
+// Plain covariance form; whole matrix on one GPU or a row-block shard fed by exchanged rows.
 #include "ekf_common.cuh"
 #include "ekf_largemap.h"
 
@@ -46,6 +46,22 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
   const int idx5[5] = {0, 1, 2, j, j + 1};
   const int rho5[5] = {0, 1, 2, 3 + 2 * u, 4 + 2 * u};
   const int nr = 3 + 2 * a.m;
+  if (a.wait_flags && u == 0) {  // peer-memory exchange: the step's 1 + m row parts carry this step's number
+    if (threadIdx.x == 0) {
+      const volatile unsigned long long* f = a.wait_flags;
+      const long long t0 = clock64();
+      for (int part = 0; part <= a.m; ++part)
+        while (f[part] < a.wait_seq) {
+          if (clock64() - t0 > 4000000000LL) {
+            atomicExch(a.wait_err, 1ULL);
+            break;
+          }
+          __nanosleep(32);
+        }
+      __threadfence_system();
+    }
+    __syncthreads();
+  }
   if (threadIdx.x < 5 * u) {  // uniform operands of the rebuild
     const int w = threadIdx.x / 5, k = threadIdx.x - 5 * w;
     skw[w][k][0] = a.KR[(w * LM_MAX_ROWS + rho5[k]) * 2];
@@ -181,6 +197,12 @@ template <int RB, int UNROLL, int M>
 __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMultiArgs a) {
   __shared__ double sk[RB][2 * M];
   const int tid = threadIdx.x;
+  if (a.ack_peers && blockIdx.x == 0 && blockIdx.y == 0 && tid < a.ack_world) {
+    // this launch follows the gathers on the stream: the exchange buffer of step wait_seq is no longer read here
+    volatile unsigned long long* ack =
+        reinterpret_cast<unsigned long long*>(a.ack_peers[tid] + a.ack_flag_off) + 2 * P2P_PARTS + a.ack_rank;
+    *ack = a.wait_seq;
+  }
   const int r0 = a.row_begin + blockIdx.y * RB;  // first global row of this CTA
   const int nrows = min(RB, a.row_end - r0);
   if (a.xrows && a.row_begin != 0 && blockIdx.x == 0 && blockIdx.y == 0 && tid < 3) {

@@ -7,7 +7,8 @@
 // stores through peer-mapped pointers (cudaIpc handles, one process per GPU) and publish a sequence number; the
 // consumers wait on a flag in their OWN memory. No collective, no host synchronisation, everything stream-ordered:
 //
-//     push (owners only) -> wait -> gather (lm_gather_kernel reads the exchange buffer) -> ack -> streaming update
+//     push (owners only) -> gather (waits on its own flags, then reads the exchange buffer) -> streaming update
+//     (its first CTA acknowledges the buffer to every rank)
 //
 //  * the exchange buffer is double-buffered on the update's sequence number; a push into buffer s & 1 first waits
 //    until every rank has acknowledged the gather of update s - 2 (acks are tiny peer stores too);
@@ -55,7 +56,7 @@ __global__ void __launch_bounds__(256) lm_p2p_push_kernel(P2PArgs a, int first_r
   if (!ok) return;
   const double* src = a.P + (int64_t)(first_row + k - a.row_begin) * a.ld;
   double* area = a.peers[dest];
-  double* dst = area + ((int64_t)(a.seq & 1) * 5 + first_k + k) * a.ldx;
+  double* dst = area + ((int64_t)(a.seq & 1) * P2P_ROWS + first_k + k) * a.ldx;
   for (int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; c < a.ld; c += (int64_t)gridDim.x * blockDim.x)
     dst[c] = src[c];
   if (blockIdx.x == 0 && threadIdx.x == 0) dst[a.ld] = a.mu[first_row + k];
@@ -67,29 +68,10 @@ __global__ void __launch_bounds__(256) lm_p2p_push_kernel(P2PArgs a, int first_r
       a.push_count[dest] = 0;
       __threadfence_system();
       volatile unsigned long long* flag =
-          reinterpret_cast<unsigned long long*>(area + a.flag_off) + (a.seq & 1) * 2 + part;
+          reinterpret_cast<unsigned long long*>(area + a.flag_off) + (a.seq & 1) * P2P_PARTS + part;
       *flag = a.seq;
     }
   }
-}
-
-// Consumer side: both parts of buffer seq & 1 have arrived.
-__global__ void lm_p2p_wait_kernel(P2PArgs a) {
-  if (threadIdx.x != 0) return;
-  const volatile unsigned long long* flags =
-      reinterpret_cast<unsigned long long*>(a.peers[a.rank] + a.flag_off) + (a.seq & 1) * 2;
-  if (spin_until_ge(flags, a.seq, a.err)) spin_until_ge(flags + 1, a.seq, a.err);
-  __threadfence_system();
-}
-
-// Consumer side, after the gather: tell every rank that this rank no longer reads buffer seq & 1.
-__global__ void lm_p2p_ack_kernel(P2PArgs a) {
-  const int r = threadIdx.x;
-  if (r >= a.world) return;
-  volatile unsigned long long* ack =
-      reinterpret_cast<unsigned long long*>(a.peers[r] + a.flag_off) + 4 + a.rank;
-  *ack = a.seq;
-  __threadfence_system();
 }
 
 cudaError_t lm_launch_p2p_push(const P2PArgs& a, int first_row, int first_k, int nrows, int part, cudaStream_t st) {
@@ -97,13 +79,4 @@ cudaError_t lm_launch_p2p_push(const P2PArgs& a, int first_row, int first_k, int
   lm_p2p_push_kernel<<<grid, 256, 0, st>>>(a, first_row, first_k, nrows, part);
   return cudaGetLastError();
 }
-cudaError_t lm_launch_p2p_wait(const P2PArgs& a, cudaStream_t st) {
-  lm_p2p_wait_kernel<<<1, 32, 0, st>>>(a);
-  return cudaGetLastError();
-}
-cudaError_t lm_launch_p2p_ack(const P2PArgs& a, cudaStream_t st) {
-  lm_p2p_ack_kernel<<<1, 32, 0, st>>>(a);
-  return cudaGetLastError();
-}
-
 }  // namespace ekf

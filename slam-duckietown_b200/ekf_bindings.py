@@ -259,6 +259,14 @@ class LargeMapEKF:
         capi.call("ekf_lm_p2p_update", self._h, int(slot), float(rng), float(brg), int(owner),
                   _stream_ptr(self.torch))
 
+    def p2p_update_multi(self, slots, rngs, brgs, owners):
+        sl = np.ascontiguousarray(slots, dtype=np.int32)
+        rg = np.ascontiguousarray(rngs, dtype=np.float64)
+        bg = np.ascontiguousarray(brgs, dtype=np.float64)
+        ow = np.ascontiguousarray(owners, dtype=np.int32)
+        capi.call("ekf_lm_p2p_update_multi", self._h, int(sl.size), sl.ctypes.data, rg.ctypes.data, bg.ctypes.data,
+                  ow.ctypes.data, _stream_ptr(self.torch))
+
     def p2p_error(self) -> int:
         v = C.c_int64(0)
         capi.call("ekf_lm_p2p_error", self._h, C.byref(v))

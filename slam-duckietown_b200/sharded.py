@@ -148,6 +148,9 @@ class ShardedLargeMapEKF:
             if len(sl) == 1:
                 self.update(sl[0], rg[0], bg[0])
                 continue
+            if self.exchange == "p2p":
+                self.local.p2p_update_multi(sl, rg, bg, [owner_of_slot(s, self.capacity, self.world) for s in sl])
+                continue
             rows = self.local.export_rows_multi(sl)
             exchange_rows_multi(rows, [owner_of_slot(s, self.capacity, self.world) for s in sl], self.group)
             self.local.update_multi_from_rows(sl, rg, bg, rows)

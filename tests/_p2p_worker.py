@@ -17,7 +17,7 @@ def main():
     torch.cuda.set_device(device)
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
     L = 300
-    w = wl.make_large_map(L, updates=14)
+    w = wl.make_large_map(L, updates=20)
     f = ShardedLargeMapEKF(L, rank, world, device=device, exchange="p2p")
     ref = eb.LargeMapEKF(L, device=device)
     for g in (f, ref):
@@ -25,13 +25,24 @@ def main():
     p0 = w.p0()
     f.load(w.mu0, p0)
     ref.load(w.mu0, p0)
-    for op in w.ops:
+    pend = []
+
+    def flush():
+        if pend:                                   # the step's updates fused: one exchange, one pass per shard
+            f.update_multi([o[1] for o in pend], [o[2] for o in pend], [o[3] for o in pend])
+            pend.clear()
+    for i, op in enumerate(w.ops):
         if op[0] == "update":
-            f.update(op[1], op[2], op[3])
             ref.update(op[1], op[2], op[3])
+            if i < len(w.ops) // 2:
+                f.update(op[1], op[2], op[3])      # first half: one exchange per update
+            else:
+                pend.append(op)
         else:
+            flush()
             f.predict(op[1], op[2])
             ref.predict(op[1], op[2])
+    flush()
     torch.cuda.synchronize()
     lo, hi = f.ranges[rank]
     same = bool(torch.equal(f.local.P, ref.P[lo:hi])) and bool(torch.equal(f.local.mu[lo:hi], ref.mu[lo:hi]))
