@@ -53,3 +53,13 @@ def test_unknown_event_raises():
     from slam_duckietown_b200 import events_io as io
     with pytest.raises(ValueError):
         io.parse_event_line("1.0,bogus,3\n")
+
+
+def test_compact_tag_table_first_appearance_and_ignored():
+    """The Monte Carlo driver's tag id -> compact index map: first appearance over the stream, ignored tags left
+    out (they reach the device as -1)."""
+    from slam_duckietown_b200 import events_io as io, monte_carlo as mc
+    w = lambda tags: io.StepWindow(0, 0, 0, 0, np.array(tags, dtype=np.int64), np.zeros(len(tags)), np.zeros(len(tags)), None)
+    wins = [w([44, 80, 44]), w([]), w([26, 80, 300])]
+    assert mc.compact_tag_table(wins) == {44: 0, 80: 1, 26: 2, 300: 3}
+    assert mc.compact_tag_table(wins, ignore_tags=(80,)) == {44: 0, 26: 1, 300: 2}

@@ -60,6 +60,18 @@ def _gloo_worker(rank, world, port, n_lm, slots, out_dir):
         exchange_rows(rows5, owner_of_slot(slot, n_lm, world))
         for k, row in enumerate((0, 1, 2, j, j + 1)):
             ok &= bool(torch.equal(rows5[k, :ld], full[row])) and float(rows5[k, ld]) == 1000.0 + row
+    # the fused step's exchange: rows {0,1,2} U {j_u, j_u+1} with one owner per landmark pair
+    from slam_duckietown_b200.sharded import exchange_rows_multi
+    for group in (slots[:2], slots[1:4], slots[1:5]):
+        rows = torch.full((3 + 2 * len(group), ld + 4), -1.0 - rank, dtype=torch.float64)
+        want = [0, 1, 2] + [r for s_ in group for r in (3 + 2 * s_, 4 + 2 * s_)]
+        for k, row in enumerate(want):
+            if lo <= row < hi:                        # what ekf_lm_export_rows_multi does on the device
+                rows[k, :ld] = full[row]
+                rows[k, ld] = 1000.0 + row
+        exchange_rows_multi(rows, [owner_of_slot(s_, n_lm, world) for s_ in group])
+        for k, row in enumerate(want):
+            ok &= bool(torch.equal(rows[k, :ld], full[row])) and float(rows[k, ld]) == 1000.0 + row
     # the bench's max-over-ranks reduction
     t = torch.tensor([float(rank + 1)], dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
