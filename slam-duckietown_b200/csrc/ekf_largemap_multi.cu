@@ -102,6 +102,21 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
           pc[k] = rank2e(pc[k], kt0[w], kt1[w], sww[w][0][k], sww[w][1][k]);
         }
   }
+  // block 0, threads rho < nr: the five columns idx5(u) of exchanged row rho, rebuilt with the earlier updates exactly
+  // as the thread owning that row rebuilds them (also ahead of the scalar chain)
+  const bool kr_thread = (blockIdx.x == 0 && threadIdx.x < nr);
+  double pk[5];
+  if (kr_thread) {
+    const int rho = threadIdx.x;
+    const double* xr = rho_ptr(a, rho);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) pk[k] = xr[idx5[k]];
+    for (int w = 0; w < u; ++w) {
+      const double kr0 = a.KR[(w * LM_MAX_ROWS + rho) * 2], kr1 = a.KR[(w * LM_MAX_ROWS + rho) * 2 + 1];
+#pragma unroll
+      for (int k = 0; k < 5; ++k) pk[k] = rank2e(pk[k], kr0, kr1, sww[w][0][k], sww[w][1][k]);
+    }
+  }
   if (threadIdx.x == 0) {
     double mu5[5];
 #pragma unroll
@@ -154,20 +169,13 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
     }
   }
   __syncthreads();
-  if (blockIdx.x == 0 && threadIdx.x < nr) {
-    // K_u at exchanged row rho: its five columns idx5(u) come from the exchanged row, rebuilt with the earlier
-    // updates exactly as the thread owning that row rebuilds them
+  if (kr_thread) {  // K_u at exchanged row rho (a.KR): later updates need it as a uniform operand on every rank
     const int rho = threadIdx.x;
-    const double* xr = rho_ptr(a, rho);
     double ph0 = 0.0, ph1 = 0.0;
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
-      double p = xr[idx5[k]];
-      for (int w = 0; w < u; ++w)
-        p = rank2e(p, a.KR[(w * LM_MAX_ROWS + rho) * 2], a.KR[(w * LM_MAX_ROWS + rho) * 2 + 1], sww[w][0][k],
-                   sww[w][1][k]);
-      ph0 = fma(p, sh[0][k], ph0);
-      ph1 = fma(p, sh[1][k], ph1);
+      ph0 = fma(pk[k], sh[0][k], ph0);
+      ph1 = fma(pk[k], sh[1][k], ph1);
     }
     a.KR[(u * LM_MAX_ROWS + rho) * 2] = dot2(ph0, ssi[0][0], ph1, ssi[1][0]);
     a.KR[(u * LM_MAX_ROWS + rho) * 2 + 1] = dot2(ph0, ssi[0][1], ph1, ssi[1][1]);
