@@ -107,6 +107,7 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
   __shared__ double ssi[2][2];
   __shared__ double ssq[2][2];  // S - Q
   __shared__ double sy[2];
+  pdl_wait();
   const int j = a.j;
   const int idx5[5] = {0, 1, 2, j, j + 1};
   // this thread's gathers are issued before thread 0's scalar chain (innovation, S^-1) so that the strided column
@@ -242,6 +243,7 @@ template <int RB, int UNROLL, bool JOSEPH>
 __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs a) {
   __shared__ double sk[RB][4];
   const int tid = threadIdx.x;
+  pdl_wait();
   if (a.ack_peers && blockIdx.x == 0 && blockIdx.y == 0 && tid < a.ack_world) {
     // this launch follows the gather on the stream: the exchange buffer of update ack_seq is no longer read here
     volatile unsigned long long* ack =
@@ -378,8 +380,7 @@ cudaError_t lm_launch_predict(double* mu, double* P, int64_t ld, int n, int row_
 
 cudaError_t lm_launch_gather(const LmGatherArgs& a, cudaStream_t st) {
   const int threads = 256;
-  lm_gather_kernel<<<(a.n + threads - 1) / threads, threads, 0, st>>>(a);
-  return cudaGetLastError();
+  return launch_pdl(lm_gather_kernel, dim3((a.n + threads - 1) / threads), dim3(threads), 0, st, a);
 }
 
 template <int RB, int UNROLL>
@@ -391,11 +392,8 @@ static cudaError_t launch_update_t(const LmUpdateArgs& a0, bool joseph, cudaStre
   const int rows = a.row_end - a.row_begin;
   if (rows <= 0) return cudaSuccess;
   dim3 grid(a.full_tiles + (a.tail_groups ? 1 : 0), (rows + RB - 1) / RB);
-  if (joseph)
-    lm_rank_update_kernel<RB, UNROLL, true><<<grid, LM_THREADS, 0, st>>>(a);
-  else
-    lm_rank_update_kernel<RB, UNROLL, false><<<grid, LM_THREADS, 0, st>>>(a);
-  return cudaGetLastError();
+  if (joseph) return launch_pdl(lm_rank_update_kernel<RB, UNROLL, true>, grid, dim3(LM_THREADS), 0, st, a);
+  return launch_pdl(lm_rank_update_kernel<RB, UNROLL, false>, grid, dim3(LM_THREADS), 0, st, a);
 }
 
 cudaError_t lm_launch_update(const LmUpdateArgs& a, bool joseph, int variant, cudaStream_t st) {

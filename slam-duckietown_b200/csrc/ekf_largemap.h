@@ -3,7 +3,37 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cstdlib>
+
 namespace ekf {
+
+// Programmatic dependent launch (sm_90+): the large-map kernels of one update form a chain on one stream
+// (gather -> streaming update -> next gather ...). Launched with this attribute a kernel's CTAs may be scheduled
+// while its predecessor drains; every such kernel begins with pdl_wait() (griddepcontrol.wait: predecessor complete
+// and its memory visible) before it reads or writes anything, so only launch latency and CTA ramp-up overlap.
+// EKF_LM_PDL=0 switches it off.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args... args) {
+  static const bool on = [] { const char* v = getenv("EKF_LM_PDL"); return !(v && v[0] == '0'); }();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = on ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+#endif
 
 constexpr int LM_THREADS = 128;  // threads per CTA of the streaming update = column groups per tile
 

@@ -46,6 +46,7 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
   const int idx5[5] = {0, 1, 2, j, j + 1};
   const int rho5[5] = {0, 1, 2, 3 + 2 * u, 4 + 2 * u};
   const int nr = 3 + 2 * a.m;
+  pdl_wait();
   if (a.wait_flags && u == 0) {  // peer-memory exchange: the step's 1 + m row parts carry this step's number
     if (threadIdx.x == 0) {
       const volatile unsigned long long* f = a.wait_flags;
@@ -205,6 +206,7 @@ template <int RB, int UNROLL, int M>
 __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMultiArgs a) {
   __shared__ double sk[RB][2 * M];
   const int tid = threadIdx.x;
+  pdl_wait();
   if (a.ack_peers && blockIdx.x == 0 && blockIdx.y == 0 && tid < a.ack_world) {
     // this launch follows the gathers on the stream: the exchange buffer of step wait_seq is no longer read here
     volatile unsigned long long* ack =
@@ -321,8 +323,7 @@ static cudaError_t launch_multi_t(const LmMultiArgs& a, cudaStream_t st) {
   const int rows = a.row_end - a.row_begin;
   if (rows <= 0) return cudaSuccess;
   dim3 grid(a.full_tiles + (a.tail_groups ? 1 : 0), (rows + RB - 1) / RB);
-  lm_rank_update_multi_kernel<RB, UNROLL, M><<<grid, LM_THREADS, 0, st>>>(a);
-  return cudaGetLastError();
+  return launch_pdl(lm_rank_update_multi_kernel<RB, UNROLL, M>, grid, dim3(LM_THREADS), 0, st, a);
 }
 
 cudaError_t lm_launch_update_multi(const LmMultiArgs& a0, cudaStream_t st) {
@@ -332,8 +333,7 @@ cudaError_t lm_launch_update_multi(const LmMultiArgs& a0, cudaStream_t st) {
   a.full_tiles = groups / LM_THREADS;
   a.tail_groups = groups - a.full_tiles * LM_THREADS;
   for (int u = 0; u < a.m; ++u) {
-    lm_gather_multi_kernel<<<(a.n + 255) / 256, 256, 0, st>>>(a, u);
-    cudaError_t e = cudaGetLastError();
+    cudaError_t e = launch_pdl(lm_gather_multi_kernel, dim3((a.n + 255) / 256), dim3(256), 0, st, a, u);
     if (e != cudaSuccess) return e;
   }
   switch (a.m) {
