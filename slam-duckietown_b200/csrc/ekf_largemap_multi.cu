@@ -37,18 +37,29 @@ __device__ __forceinline__ const double* rho_ptr(const LmMultiArgs& a, int rho) 
 // Every rank computes W_u over all n columns (from the five full rows) and K_u for its local rows (from their five
 // columns); K_u at the exchanged rows R — which later updates need as uniform operands on EVERY rank — is rebuilt
 // from the exchanged rows themselves by block 0 (a.KR), with the operation sequence of the owning thread.
+//
+// The O(1) part (five mu entries, innovation, the 5 x 5 block of P_u, S^-1) is on the critical path of the whole
+// step — m of these kernels run back to back before the streaming pass — so it is spread over the CTA instead of
+// being one thread's serial chain of dependent global loads: threads rho < 3 + 2m of warp 0 rebuild the five
+// columns idx5(u) of exchanged row rho (all loads in flight together), lanes 0-4 of warp 1 rebuild the five mu
+// entries and lane 0 of warp 1 runs the innovation meanwhile; thread 0 then only contracts shared-memory values.
+// Every value keeps the operation sequence it had in the one-thread version, so results are unchanged bitwise.
 __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int u) {
   __shared__ double sh[2][5];
   __shared__ double ssi[2][2];
   __shared__ double skw[LM_MAX_FUSED][5][2];  // K_w[idx5(u), :] of the earlier updates
   __shared__ double sww[LM_MAX_FUSED][2][5];  // W_w[:, idx5(u)]
+  __shared__ double syw[LM_MAX_FUSED][2];     // innovations of the earlier updates
+  __shared__ double spk[LM_MAX_ROWS][5];      // P_u[R, idx5(u)]
+  __shared__ double smu[5];
   const int j = a.j[u];
   const int idx5[5] = {0, 1, 2, j, j + 1};
   const int rho5[5] = {0, 1, 2, 3 + 2 * u, 4 + 2 * u};
   const int nr = 3 + 2 * a.m;
+  const int tid = threadIdx.x;
   pdl_wait();
   if (a.wait_flags && u == 0) {  // peer-memory exchange: the step's 1 + m row parts carry this step's number
-    if (threadIdx.x == 0) {
+    if (tid == 0) {
       const volatile unsigned long long* f = a.wait_flags;
       const long long t0 = clock64();
       for (int part = 0; part <= a.m; ++part)
@@ -63,23 +74,22 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
     }
     __syncthreads();
   }
-  if (threadIdx.x < 5 * u) {  // uniform operands of the rebuild
-    const int w = threadIdx.x / 5, k = threadIdx.x - 5 * w;
+  if (tid < 5 * u) {  // uniform operands of the rebuild
+    const int w = tid / 5, k = tid - 5 * w;
     skw[w][k][0] = a.KR[(w * LM_MAX_ROWS + rho5[k]) * 2];
     skw[w][k][1] = a.KR[(w * LM_MAX_ROWS + rho5[k]) * 2 + 1];
     sww[w][0][k] = a.W[(2 * w) * a.ldw + idx5[k]];
     sww[w][1][k] = a.W[(2 * w + 1) * a.ldw + idx5[k]];
+  } else if (tid >= 64 && tid < 64 + 2 * u) {
+    syw[(tid - 64) >> 1][tid & 1] = a.y[tid - 64];
   }
-  __syncthreads();
-  // every thread's own gathers (5 row entries, 5 column entries, its entries of the earlier records) and their
-  // rebuild need only the uniform operands staged above: they are issued BEFORE thread 0's scalar chain so that the
-  // strided column reads overlap it instead of following it
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  // operands that do not depend on the staged values are requested before the barrier
+  const int t = blockIdx.x * blockDim.x + tid;
   const bool live = t < a.n;
   const bool local = live && t >= a.row_begin && t < a.row_end;
   double pr[5], pc[5];
+  double kt0[LM_MAX_FUSED], kt1[LM_MAX_FUSED], wt0[LM_MAX_FUSED], wt1[LM_MAX_FUSED];
   if (live) {
-    double kt0[LM_MAX_FUSED], kt1[LM_MAX_FUSED], wt0[LM_MAX_FUSED], wt1[LM_MAX_FUSED];
 #pragma unroll
     for (int w = 0; w < LM_MAX_FUSED; ++w)
       if (w < u) {
@@ -94,6 +104,30 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
       pr[k] = rho_ptr(a, rho5[k])[t];            // row idx5[k], column t
       pc[k] = local ? prow[idx5[k]] : 0.0;       // row t, column idx5[k]
     }
+  }
+  const bool kr_thread = tid < nr;  // exchanged row rho = tid: its five columns idx5(u)
+  double pk[5], kr0[LM_MAX_FUSED], kr1[LM_MAX_FUSED];
+  if (kr_thread) {
+    const double* xr = rho_ptr(a, tid);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) pk[k] = xr[idx5[k]];
+#pragma unroll
+    for (int w = 0; w < LM_MAX_FUSED; ++w)
+      if (w < u) {
+        kr0[w] = a.KR[(w * LM_MAX_ROWS + tid) * 2];
+        kr1[w] = a.KR[(w * LM_MAX_ROWS + tid) * 2 + 1];
+      }
+  }
+  double mu0 = 0.0;
+  const bool mu_thread = tid >= 32 && tid < 37;
+  if (mu_thread) {
+    // the step's initial mean: riding at column ld of the exchanged row on a shard (local copies of non-local
+    // entries are stale there), mu itself otherwise (it is written by the streaming kernel only)
+    const int k = tid - 32;
+    mu0 = a.xrows ? rho_ptr(a, rho5[k])[a.ld] : a.mu[idx5[k]];
+  }
+  __syncthreads();
+  if (live) {
 #pragma unroll
     for (int k = 0; k < 5; ++k)
 #pragma unroll
@@ -103,42 +137,47 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
           pc[k] = rank2e(pc[k], kt0[w], kt1[w], sww[w][0][k], sww[w][1][k]);
         }
   }
-  // block 0, threads rho < nr: the five columns idx5(u) of exchanged row rho, rebuilt with the earlier updates exactly
-  // as the thread owning that row rebuilds them (also ahead of the scalar chain)
-  const bool kr_thread = (blockIdx.x == 0 && threadIdx.x < nr);
-  double pk[5];
   if (kr_thread) {
-    const int rho = threadIdx.x;
-    const double* xr = rho_ptr(a, rho);
 #pragma unroll
-    for (int k = 0; k < 5; ++k) pk[k] = xr[idx5[k]];
-    for (int w = 0; w < u; ++w) {
-      const double kr0 = a.KR[(w * LM_MAX_ROWS + rho) * 2], kr1 = a.KR[(w * LM_MAX_ROWS + rho) * 2 + 1];
+    for (int w = 0; w < LM_MAX_FUSED; ++w)
+      if (w < u) {
 #pragma unroll
-      for (int k = 0; k < 5; ++k) pk[k] = rank2e(pk[k], kr0, kr1, sww[w][0][k], sww[w][1][k]);
+        for (int k = 0; k < 5; ++k) pk[k] = rank2e(pk[k], kr0[w], kr1[w], sww[w][0][k], sww[w][1][k]);
+      }
+#pragma unroll
+    for (int k = 0; k < 5; ++k) spk[tid][k] = pk[k];
+  }
+  if (tid >= 32 && tid < 64) {  // warp 1: the five mu entries, then the innovation
+    if (mu_thread) {
+      const int k = tid - 32;
+      double v = mu0;
+      for (int w = 0; w < u; ++w) v = mu_inc(v, skw[w][k][0], skw[w][k][1], syw[w][0], syw[w][1]);
+      smu[k] = v;
+    }
+    __syncwarp();
+    if (tid == 32) {
+      const Innov in = innovation(smu[0], smu[1], smu[2], smu[3], smu[4], a.rng[u], a.brg[u]);
+#pragma unroll
+      for (int r = 0; r < 2; ++r)
+#pragma unroll
+        for (int k = 0; k < 5; ++k) sh[r][k] = in.h[r][k];
+      if (blockIdx.x == 0) {
+        a.y[2 * u] = in.y0;
+        a.y[2 * u + 1] = in.y1;
+      }
     }
   }
-  if (threadIdx.x == 0) {
-    double mu5[5];
-#pragma unroll
-    for (int k = 0; k < 5; ++k) {
-      // the step's initial mean: riding at column ld of the exchanged row on a shard (local copies of non-local
-      // entries are stale there), mu itself otherwise (it is written by the streaming kernel only)
-      double v = a.xrows ? rho_ptr(a, rho5[k])[a.ld] : a.mu[idx5[k]];
-      for (int w = 0; w < u; ++w) v = mu_inc(v, skw[w][k][0], skw[w][k][1], a.y[2 * w], a.y[2 * w + 1]);
-      mu5[k] = v;
-    }
-    const Innov in = innovation(mu5[0], mu5[1], mu5[2], mu5[3], mu5[4], a.rng[u], a.brg[u]);
+  __syncthreads();
+  if (tid == 0) {
     double hp5[2][5];
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
       double s0 = 0.0, s1 = 0.0;
 #pragma unroll
       for (int k = 0; k < 5; ++k) {
-        double p = rho_ptr(a, rho5[k])[idx5[c]];
-        for (int w = 0; w < u; ++w) p = rank2e(p, skw[w][k][0], skw[w][k][1], sww[w][0][c], sww[w][1][c]);
-        s0 = fma(in.h[0][k], p, s0);
-        s1 = fma(in.h[1][k], p, s1);
+        const double p = spk[rho5[k]][c];
+        s0 = fma(sh[0][k], p, s0);
+        s1 = fma(sh[1][k], p, s1);
       }
       hp5[0][c] = s0;
       hp5[1][c] = s1;
@@ -150,7 +189,7 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
       for (int b = 0; b < 2; ++b) {
         double acc = 0.0;
 #pragma unroll
-        for (int c = 0; c < 5; ++c) acc = fma(hp5[r][c], in.h[b][c], acc);
+        for (int c = 0; c < 5; ++c) acc = fma(hp5[r][c], sh[b][c], acc);
         s[r][b] = acc;
       }
     const double qn = a.mm * a.mm;
@@ -159,27 +198,20 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
     inv2(s, si);
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
-#pragma unroll
-      for (int k = 0; k < 5; ++k) sh[r][k] = in.h[r][k];
       ssi[r][0] = si[r][0];
       ssi[r][1] = si[r][1];
     }
-    if (blockIdx.x == 0) {
-      a.y[2 * u] = in.y0;
-      a.y[2 * u + 1] = in.y1;
-    }
   }
   __syncthreads();
-  if (kr_thread) {  // K_u at exchanged row rho (a.KR): later updates need it as a uniform operand on every rank
-    const int rho = threadIdx.x;
+  if (kr_thread && blockIdx.x == 0) {  // K_u at exchanged row rho (a.KR), a uniform operand of later updates
     double ph0 = 0.0, ph1 = 0.0;
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
       ph0 = fma(pk[k], sh[0][k], ph0);
       ph1 = fma(pk[k], sh[1][k], ph1);
     }
-    a.KR[(u * LM_MAX_ROWS + rho) * 2] = dot2(ph0, ssi[0][0], ph1, ssi[1][0]);
-    a.KR[(u * LM_MAX_ROWS + rho) * 2 + 1] = dot2(ph0, ssi[0][1], ph1, ssi[1][1]);
+    a.KR[(u * LM_MAX_ROWS + tid) * 2] = dot2(ph0, ssi[0][0], ph1, ssi[1][0]);
+    a.KR[(u * LM_MAX_ROWS + tid) * 2 + 1] = dot2(ph0, ssi[0][1], ph1, ssi[1][1]);
   }
   if (!live) return;
   double hp0 = 0.0, hp1 = 0.0, pht0 = 0.0, pht1 = 0.0;
