@@ -33,36 +33,35 @@ __device__ __forceinline__ const double* rho_ptr(const LmMultiArgs& a, int rho) 
   return a.xrows ? a.xrows + (int64_t)rho * a.ldx : a.P + (int64_t)rho_row(a, rho) * a.ld;
 }
 
-// a8-a9 for update u of the step, on the covariance as it stands after updates 0..u-1 (never materialised).
-// Every rank computes W_u over all n columns (from the five full rows) and K_u for its local rows (from their five
-// columns); K_u at the exchanged rows R — which later updates need as uniform operands on EVERY rank — is rebuilt
-// from the exchanged rows themselves by block 0 (a.KR), with the operation sequence of the owning thread.
-//
-// The O(1) part (five mu entries, innovation, the 5 x 5 block of P_u, S^-1) is on the critical path of the whole
-// step — m of these kernels run back to back before the streaming pass — so it is spread over the CTA instead of
-// being one thread's serial chain of dependent global loads: threads rho < 3 + 2m of warp 0 rebuild the five
-// columns idx5(u) of exchanged row rho (all loads in flight together), lanes 0-4 of warp 1 rebuild the five mu
-// entries and lane 0 of warp 1 runs the innovation meanwhile; thread 0 then only contracts shared-memory values.
-// Every value keeps the operation sequence it had in the one-thread version, so results are unchanged bitwise.
-__global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int u) {
-  __shared__ double sh[2][5];
-  __shared__ double ssi[2][2];
-  __shared__ double skw[LM_MAX_FUSED][5][2];  // K_w[idx5(u), :] of the earlier updates
-  __shared__ double sww[LM_MAX_FUSED][2][5];  // W_w[:, idx5(u)]
-  __shared__ double syw[LM_MAX_FUSED][2];     // innovations of the earlier updates
-  __shared__ double spk[LM_MAX_ROWS][5];      // P_u[R, idx5(u)]
-  __shared__ double smu[5];
-  const int j = a.j[u];
-  const int idx5[5] = {0, 1, 2, j, j + 1};
-  const int rho5[5] = {0, 1, 2, 3 + 2 * u, 4 + 2 * u};
-  const int nr = 3 + 2 * a.m;
+// a8-a9 for ALL M updates of the step in one launch. Update u works on the covariance as it stands after updates
+// 0..u-1 (never materialised). Thread t needs, over the whole step, only column t of the exchanged rows R
+// (P0[R, t], for W_u[:, t]) and, for a local row t, that row's entries in the columns R (P0[t, R], for K_u[t, :]),
+// plus its OWN earlier K_w[t, :], W_w[:, t] — and a handful of uniform operands per update: H5_u, S_u^-1, y_u,
+// K_w[R, :] and W_w[:, R]. Those depend only on the (3 + 2M)^2 block P0[R, R] and mu[R], so every CTA rebuilds
+// them itself in shared memory: lanes rho < 3 + 2M of warp 0 act as the threads owning row / column R[rho]
+// ("virtual threads", same operation sequence as the real thread t = R[rho]), lane 0 runs innovation, S and S^-1
+// between them. No CTA waits for another one, so the m dependent gather launches of the first version (a global
+// round trip and a launch between consecutive updates: 36 us of a 196 us step at 4096 landmarks) collapse into one
+// launch whose serial part is M innovations. Every value keeps its operation sequence: results unchanged bitwise.
+// Block 0 publishes K_u[R, :] (a.KR) and y_u (a.y) for the streaming kernel.
+template <int M>
+__global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
+  constexpr int NR = 3 + 2 * M;
+  __shared__ double sB[NR][NR + 1];  // P0[R, R]
+  __shared__ double smuR[NR];        // mu[R], kept current through the updates
+  __shared__ double sKR[M][NR][2];   // K_u[R, :]
+  __shared__ double sWR[M][2][NR];   // W_u[:, R]
+  __shared__ double sh[M][2][5];
+  __shared__ double ssi[M][2][2];
+  __shared__ double sy[M][2];
+  __shared__ double spk[NR][5];      // P_u[R, idx5(u)] of the update in progress
   const int tid = threadIdx.x;
   pdl_wait();
-  if (a.wait_flags && u == 0) {  // peer-memory exchange: the step's 1 + m row parts carry this step's number
+  if (a.wait_flags) {  // peer-memory exchange: the step's 1 + m row parts carry this step's number
     if (tid == 0) {
       const volatile unsigned long long* f = a.wait_flags;
       const long long t0 = clock64();
-      for (int part = 0; part <= a.m; ++part)
+      for (int part = 0; part <= M; ++part)
         while (f[part] < a.wait_seq) {
           if (clock64() - t0 > 4000000000LL) {
             atomicExch(a.wait_err, 1ULL);
@@ -74,160 +73,162 @@ __global__ void __launch_bounds__(256) lm_gather_multi_kernel(LmMultiArgs a, int
     }
     __syncthreads();
   }
-  if (tid < 5 * u) {  // uniform operands of the rebuild
-    const int w = tid / 5, k = tid - 5 * w;
-    skw[w][k][0] = a.KR[(w * LM_MAX_ROWS + rho5[k]) * 2];
-    skw[w][k][1] = a.KR[(w * LM_MAX_ROWS + rho5[k]) * 2 + 1];
-    sww[w][0][k] = a.W[(2 * w) * a.ldw + idx5[k]];
-    sww[w][1][k] = a.W[(2 * w + 1) * a.ldw + idx5[k]];
-  } else if (tid >= 64 && tid < 64 + 2 * u) {
-    syw[(tid - 64) >> 1][tid & 1] = a.y[tid - 64];
+  if (tid < NR * NR) {
+    const int r = tid / NR, c = tid - r * NR;
+    sB[r][c] = rho_ptr(a, r)[rho_row(a, c)];
+  } else if (tid >= 128 && tid < 128 + NR) {
+    // the step's initial mean: riding at column ld of the exchanged row on a shard (local copies of non-local
+    // entries are stale there), mu itself otherwise (it is written by the streaming kernel only)
+    const int rho = tid - 128;
+    smuR[rho] = a.xrows ? rho_ptr(a, rho)[a.ld] : a.mu[rho_row(a, rho)];
   }
-  // operands that do not depend on the staged values are requested before the barrier
+  // this thread's own operands, requested before the barrier so that they arrive under warp 0's chain
   const int t = blockIdx.x * blockDim.x + tid;
   const bool live = t < a.n;
   const bool local = live && t >= a.row_begin && t < a.row_end;
-  double pr[5], pc[5];
-  double kt0[LM_MAX_FUSED], kt1[LM_MAX_FUSED], wt0[LM_MAX_FUSED], wt1[LM_MAX_FUSED];
+  double pr0[NR], pc0[NR];
   if (live) {
-#pragma unroll
-    for (int w = 0; w < LM_MAX_FUSED; ++w)
-      if (w < u) {
-        kt0[w] = local ? a.K[(2 * w) * a.ldw + t] : 0.0;
-        kt1[w] = local ? a.K[(2 * w + 1) * a.ldw + t] : 0.0;
-        wt0[w] = a.W[(2 * w) * a.ldw + t];
-        wt1[w] = a.W[(2 * w + 1) * a.ldw + t];
-      }
     const double* prow = a.P + (int64_t)(t - a.row_begin) * a.ld;
 #pragma unroll
-    for (int k = 0; k < 5; ++k) {
-      pr[k] = rho_ptr(a, rho5[k])[t];            // row idx5[k], column t
-      pc[k] = local ? prow[idx5[k]] : 0.0;       // row t, column idx5[k]
+    for (int rho = 0; rho < NR; ++rho) {
+      pr0[rho] = rho_ptr(a, rho)[t];                      // row R[rho], column t
+      pc0[rho] = local ? prow[rho_row(a, rho)] : 0.0;     // row t, column R[rho]
     }
   }
-  const bool kr_thread = tid < nr;  // exchanged row rho = tid: its five columns idx5(u)
-  double pk[5], kr0[LM_MAX_FUSED], kr1[LM_MAX_FUSED];
-  if (kr_thread) {
-    const double* xr = rho_ptr(a, tid);
+  __syncthreads();
+  if (tid < 32) {
+    const int rho = tid < NR ? tid : 0;
+    const bool vt = tid < NR;
+    double vK[M][2], vW[M][2];
 #pragma unroll
-    for (int k = 0; k < 5; ++k) pk[k] = xr[idx5[k]];
+    for (int u = 0; u < M; ++u) {
+      const int rho5[5] = {0, 1, 2, 3 + 2 * u, 4 + 2 * u};
+      double pr[5], pc[5];
+      if (vt) {
 #pragma unroll
-    for (int w = 0; w < LM_MAX_FUSED; ++w)
-      if (w < u) {
-        kr0[w] = a.KR[(w * LM_MAX_ROWS + tid) * 2];
-        kr1[w] = a.KR[(w * LM_MAX_ROWS + tid) * 2 + 1];
+        for (int k = 0; k < 5; ++k) {
+          pr[k] = sB[rho5[k]][rho];
+          pc[k] = sB[rho][rho5[k]];
+        }
+#pragma unroll
+        for (int k = 0; k < 5; ++k)
+#pragma unroll
+          for (int w = 0; w < u; ++w) {
+            pr[k] = rank2e(pr[k], sKR[w][rho5[k]][0], sKR[w][rho5[k]][1], vW[w][0], vW[w][1]);
+            pc[k] = rank2e(pc[k], vK[w][0], vK[w][1], sWR[w][0][rho5[k]], sWR[w][1][rho5[k]]);
+          }
+#pragma unroll
+        for (int k = 0; k < 5; ++k) spk[rho][k] = pc[k];
       }
-  }
-  double mu0 = 0.0;
-  const bool mu_thread = tid >= 32 && tid < 37;
-  if (mu_thread) {
-    // the step's initial mean: riding at column ld of the exchanged row on a shard (local copies of non-local
-    // entries are stale there), mu itself otherwise (it is written by the streaming kernel only)
-    const int k = tid - 32;
-    mu0 = a.xrows ? rho_ptr(a, rho5[k])[a.ld] : a.mu[idx5[k]];
+      __syncwarp();
+      if (tid == 0) {
+        const Innov in = innovation(smuR[0], smuR[1], smuR[2], smuR[rho5[3]], smuR[rho5[4]], a.rng[u], a.brg[u]);
+        double hp5[2][5];
+#pragma unroll
+        for (int c = 0; c < 5; ++c) {
+          double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+          for (int k = 0; k < 5; ++k) {
+            const double p = spk[rho5[k]][c];
+            s0 = fma(in.h[0][k], p, s0);
+            s1 = fma(in.h[1][k], p, s1);
+          }
+          hp5[0][c] = s0;
+          hp5[1][c] = s1;
+        }
+        double s[2][2], si[2][2];
+#pragma unroll
+        for (int r = 0; r < 2; ++r)
+#pragma unroll
+          for (int b = 0; b < 2; ++b) {
+            double acc = 0.0;
+#pragma unroll
+            for (int c = 0; c < 5; ++c) acc = fma(hp5[r][c], in.h[b][c], acc);
+            s[r][b] = acc;
+          }
+        const double qn = a.mm * a.mm;
+        s[0][0] += qn;
+        s[1][1] += qn;
+        inv2(s, si);
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+#pragma unroll
+          for (int k = 0; k < 5; ++k) sh[u][r][k] = in.h[r][k];
+          ssi[u][r][0] = si[r][0];
+          ssi[u][r][1] = si[r][1];
+        }
+        sy[u][0] = in.y0;
+        sy[u][1] = in.y1;
+      }
+      __syncwarp();
+      if (vt) {
+        double hp0 = 0.0, hp1 = 0.0, pht0 = 0.0, pht1 = 0.0;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          hp0 = fma(sh[u][0][k], pr[k], hp0);
+          hp1 = fma(sh[u][1][k], pr[k], hp1);
+          pht0 = fma(pc[k], sh[u][0][k], pht0);
+          pht1 = fma(pc[k], sh[u][1][k], pht1);
+        }
+        vK[u][0] = dot2(pht0, ssi[u][0][0], pht1, ssi[u][1][0]);
+        vK[u][1] = dot2(pht0, ssi[u][0][1], pht1, ssi[u][1][1]);
+        vW[u][0] = hp0;
+        vW[u][1] = hp1;
+        sKR[u][rho][0] = vK[u][0];
+        sKR[u][rho][1] = vK[u][1];
+        sWR[u][0][rho] = hp0;
+        sWR[u][1][rho] = hp1;
+        smuR[rho] = mu_inc(smuR[rho], vK[u][0], vK[u][1], sy[u][0], sy[u][1]);
+        if (blockIdx.x == 0) {
+          a.KR[(u * LM_MAX_ROWS + rho) * 2] = vK[u][0];
+          a.KR[(u * LM_MAX_ROWS + rho) * 2 + 1] = vK[u][1];
+        }
+      }
+      if (tid == 0 && blockIdx.x == 0) {
+        a.y[2 * u] = sy[u][0];
+        a.y[2 * u + 1] = sy[u][1];
+      }
+      __syncwarp();
+    }
   }
   __syncthreads();
-  if (live) {
+  if (!live) return;
+  double hK[M][2], hW[M][2];
+#pragma unroll
+  for (int u = 0; u < M; ++u) {
+    const int rho5[5] = {0, 1, 2, 3 + 2 * u, 4 + 2 * u};
+    double pr[5], pc[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      pr[k] = pr0[rho5[k]];
+      pc[k] = pc0[rho5[k]];
+    }
 #pragma unroll
     for (int k = 0; k < 5; ++k)
 #pragma unroll
-      for (int w = 0; w < LM_MAX_FUSED; ++w)
-        if (w < u) {
-          pr[k] = rank2e(pr[k], skw[w][k][0], skw[w][k][1], wt0[w], wt1[w]);
-          pc[k] = rank2e(pc[k], kt0[w], kt1[w], sww[w][0][k], sww[w][1][k]);
-        }
-  }
-  if (kr_thread) {
-#pragma unroll
-    for (int w = 0; w < LM_MAX_FUSED; ++w)
-      if (w < u) {
-#pragma unroll
-        for (int k = 0; k < 5; ++k) pk[k] = rank2e(pk[k], kr0[w], kr1[w], sww[w][0][k], sww[w][1][k]);
+      for (int w = 0; w < u; ++w) {
+        pr[k] = rank2e(pr[k], sKR[w][rho5[k]][0], sKR[w][rho5[k]][1], hW[w][0], hW[w][1]);
+        pc[k] = rank2e(pc[k], hK[w][0], hK[w][1], sWR[w][0][rho5[k]], sWR[w][1][rho5[k]]);
       }
-#pragma unroll
-    for (int k = 0; k < 5; ++k) spk[tid][k] = pk[k];
-  }
-  if (tid >= 32 && tid < 64) {  // warp 1: the five mu entries, then the innovation
-    if (mu_thread) {
-      const int k = tid - 32;
-      double v = mu0;
-      for (int w = 0; w < u; ++w) v = mu_inc(v, skw[w][k][0], skw[w][k][1], syw[w][0], syw[w][1]);
-      smu[k] = v;
-    }
-    __syncwarp();
-    if (tid == 32) {
-      const Innov in = innovation(smu[0], smu[1], smu[2], smu[3], smu[4], a.rng[u], a.brg[u]);
-#pragma unroll
-      for (int r = 0; r < 2; ++r)
-#pragma unroll
-        for (int k = 0; k < 5; ++k) sh[r][k] = in.h[r][k];
-      if (blockIdx.x == 0) {
-        a.y[2 * u] = in.y0;
-        a.y[2 * u + 1] = in.y1;
-      }
-    }
-  }
-  __syncthreads();
-  if (tid == 0) {
-    double hp5[2][5];
-#pragma unroll
-    for (int c = 0; c < 5; ++c) {
-      double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-      for (int k = 0; k < 5; ++k) {
-        const double p = spk[rho5[k]][c];
-        s0 = fma(sh[0][k], p, s0);
-        s1 = fma(sh[1][k], p, s1);
-      }
-      hp5[0][c] = s0;
-      hp5[1][c] = s1;
-    }
-    double s[2][2], si[2][2];
-#pragma unroll
-    for (int r = 0; r < 2; ++r)
-#pragma unroll
-      for (int b = 0; b < 2; ++b) {
-        double acc = 0.0;
-#pragma unroll
-        for (int c = 0; c < 5; ++c) acc = fma(hp5[r][c], sh[b][c], acc);
-        s[r][b] = acc;
-      }
-    const double qn = a.mm * a.mm;
-    s[0][0] += qn;
-    s[1][1] += qn;
-    inv2(s, si);
-#pragma unroll
-    for (int r = 0; r < 2; ++r) {
-      ssi[r][0] = si[r][0];
-      ssi[r][1] = si[r][1];
-    }
-  }
-  __syncthreads();
-  if (kr_thread && blockIdx.x == 0) {  // K_u at exchanged row rho (a.KR), a uniform operand of later updates
-    double ph0 = 0.0, ph1 = 0.0;
+    double hp0 = 0.0, hp1 = 0.0, pht0 = 0.0, pht1 = 0.0;
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
-      ph0 = fma(pk[k], sh[0][k], ph0);
-      ph1 = fma(pk[k], sh[1][k], ph1);
+      hp0 = fma(sh[u][0][k], pr[k], hp0);
+      hp1 = fma(sh[u][1][k], pr[k], hp1);
+      pht0 = fma(pc[k], sh[u][0][k], pht0);
+      pht1 = fma(pc[k], sh[u][1][k], pht1);
     }
-    a.KR[(u * LM_MAX_ROWS + tid) * 2] = dot2(ph0, ssi[0][0], ph1, ssi[1][0]);
-    a.KR[(u * LM_MAX_ROWS + tid) * 2 + 1] = dot2(ph0, ssi[0][1], ph1, ssi[1][1]);
+    hK[u][0] = local ? dot2(pht0, ssi[u][0][0], pht1, ssi[u][1][0]) : 0.0;
+    hK[u][1] = local ? dot2(pht0, ssi[u][0][1], pht1, ssi[u][1][1]) : 0.0;
+    hW[u][0] = hp0;
+    hW[u][1] = hp1;
+    if (local) {
+      a.K[(2 * u) * a.ldw + t] = hK[u][0];
+      a.K[(2 * u + 1) * a.ldw + t] = hK[u][1];
+    }
+    a.W[(2 * u) * a.ldw + t] = hp0;
+    a.W[(2 * u + 1) * a.ldw + t] = hp1;
   }
-  if (!live) return;
-  double hp0 = 0.0, hp1 = 0.0, pht0 = 0.0, pht1 = 0.0;
-#pragma unroll
-  for (int k = 0; k < 5; ++k) {
-    hp0 = fma(sh[0][k], pr[k], hp0);
-    hp1 = fma(sh[1][k], pr[k], hp1);
-    pht0 = fma(pc[k], sh[0][k], pht0);
-    pht1 = fma(pc[k], sh[1][k], pht1);
-  }
-  if (local) {
-    a.K[(2 * u) * a.ldw + t] = dot2(pht0, ssi[0][0], pht1, ssi[1][0]);
-    a.K[(2 * u + 1) * a.ldw + t] = dot2(pht0, ssi[0][1], pht1, ssi[1][1]);
-  }
-  a.W[(2 * u) * a.ldw + t] = hp0;
-  a.W[(2 * u + 1) * a.ldw + t] = hp1;
 }
 
 // a10-a11 for all M updates of the step in one pass: P[i, c] <- P0[i, c] - sum_u K_u[i, :] W_u[:, c] in update
@@ -364,10 +365,14 @@ cudaError_t lm_launch_update_multi(const LmMultiArgs& a0, cudaStream_t st) {
   const int groups = (a.n + 3) / 4;
   a.full_tiles = groups / LM_THREADS;
   a.tail_groups = groups - a.full_tiles * LM_THREADS;
-  for (int u = 0; u < a.m; ++u) {
-    cudaError_t e = launch_pdl(lm_gather_multi_kernel, dim3((a.n + 255) / 256), dim3(256), 0, st, a, u);
-    if (e != cudaSuccess) return e;
+  const dim3 ggrid((a.n + 255) / 256), gblock(256);
+  cudaError_t e;
+  switch (a.m) {
+    case 2: e = launch_pdl(lm_gather_fused_kernel<2>, ggrid, gblock, 0, st, a); break;
+    case 3: e = launch_pdl(lm_gather_fused_kernel<3>, ggrid, gblock, 0, st, a); break;
+    default: e = launch_pdl(lm_gather_fused_kernel<4>, ggrid, gblock, 0, st, a); break;
   }
+  if (e != cudaSuccess) return e;
   switch (a.m) {
     case 2: return launch_multi_t<2>(a, st);
     case 3: return launch_multi_t<3>(a, st);
