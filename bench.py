@@ -296,12 +296,23 @@ def bench_large_map(updates=60, warm=6):
         e1.record()
     torch.cuda.synchronize()
     ms3 = np.array([e0.elapsed_time(e1) for e0, e1 in ev3])
+    # large-map predict (a6-a7 in rank form: rows / columns 0-2 only, ~96 n bytes, latency-bound): microseconds
+    preds = [o for o in w.ops if o[0] == "predict"][:20] or [("predict", 0.05, 0.03)] * 20
+    g.predict(preds[0][1], preds[0][2])
+    torch.cuda.synchronize()
+    evp = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in preds]
+    for (e0, e1), o in zip(evp, preds):
+        e0.record()
+        g.predict(o[1], o[2])
+        e1.record()
+    torch.cuda.synchronize()
+    msp = np.array([e0.elapsed_time(e1) for e0, e1 in evp])
     finite = bool(torch.isfinite(g.mu).all())
     g.close()
     peak, which = measured_peak_gbs()
     ach = LM_BYTES_PER_UPDATE / (float(np.mean(ms)) * 1e-3) / 1e9
     return {"metric": "ms/update @4096 lm", "ms_per_update": float(np.mean(ms)), "ms_min": float(ms.min()),
-            "updates": len(ms), "finite": finite,
+            "updates": len(ms), "finite": finite, "predict_us": float(np.median(msp)) * 1e3,
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "peak_source": which, "unit": "GB/s",
                          "frac": ach / peak, "frac_of_8TBs": ach / 8000.0, "bytes_per_update": LM_BYTES_PER_UPDATE,
                          "traffic": ncu_traffic("lm_rank_update_kernel"),

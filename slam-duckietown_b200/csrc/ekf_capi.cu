@@ -814,7 +814,7 @@ int ekf_lm_p2p_update(ekf_lm_t* h, int slot, double rng, double brg, int owner, 
 }
 
 // The fused step over peer memory: one push per row part (robot rows by rank 0, rows j_u, j_u+1 by owners[u]), then
-// the m gathers (the first waits on the 1 + m flags) and ONE streaming pass over the local row block.
+// the fused gather (waits on the 1 + m flags) and ONE streaming pass over the local row block.
 int ekf_lm_p2p_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
                             const double* brg_host, const int32_t* owners_host, void* stream) {
   const int rc0 = lm_multi_check(h, m, slots_host, rng_host, brg_host);
