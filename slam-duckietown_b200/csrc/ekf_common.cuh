@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include "ekf_fastmath.cuh"
 
 namespace ekf {
 
@@ -95,13 +96,15 @@ __device__ __forceinline__ Innov innovation(double mx, double my, double mth, do
   Innov o;
   const double dx = lx - mx, dy = ly - my;
   const double q = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-  const double sq = sqrt(q);
+  // sqrt, 1/sqrt and atan2 as straight-line code (ekf_fastmath.cuh): the three overlap instead of running as
+  // three library calls with a slow-path branch each; H entries from 1/sqrt(q): sqrt(q) d / q = d / sqrt(q)
+  double sq, isq;
+  fm_sqrt_rsqrt(q, &sq, &isq);
   o.q = q;
   o.y0 = rng - sq;
-  o.y1 = wrap_pi(brg - (atan2(dy, dx) - mth));
-  // one reciprocal instead of the reference's ten divisions by q (:461-469): <= 1 ulp per entry
-  const double rq = 1.0 / q;
-  const double ax = (sq * dx) * rq, ay = (sq * dy) * rq, bx = dx * rq, by = dy * rq;
+  o.y1 = wrap_pi(brg - (fm_atan2(dy, dx) - mth));
+  const double rq = isq * isq;
+  const double ax = dx * isq, ay = dy * isq, bx = dx * rq, by = dy * rq;
   o.h[0][0] = -ax; o.h[0][1] = -ay; o.h[0][2] = 0.0; o.h[0][3] = ax;  o.h[0][4] = ay;
   o.h[1][0] = by;  o.h[1][1] = -bx; o.h[1][2] = -1.0; o.h[1][3] = -by; o.h[1][4] = bx;
   return o;
@@ -110,7 +113,7 @@ __device__ __forceinline__ Innov innovation(double mx, double my, double mth, do
 // closed-form inverse of the 2x2 innovation covariance (replaces np.linalg.inv, :473)
 __device__ __forceinline__ void inv2(const double s[2][2], double si[2][2]) {
   const double det = __dsub_rn(__dmul_rn(s[0][0], s[1][1]), __dmul_rn(s[0][1], s[1][0]));
-  const double rd = 1.0 / det;
+  const double rd = fm_rcp(det);
   si[0][0] = s[1][1] * rd;  si[0][1] = -s[0][1] * rd;
   si[1][0] = -s[1][0] * rd; si[1][1] = s[0][0] * rd;
 }
