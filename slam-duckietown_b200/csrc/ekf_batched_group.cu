@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
   {
     const double px = sMu[0], py = sMu[1], pth = sMu[2];
     double sn, cs;  // even lanes sincos(theta), odd lanes sincos(theta + ang): one call instead of two
-    sincos((gl & 1) ? pth + ang : pth, &sn, &cs);
+    fm_sincos((gl & 1) ? pth + ang : pth, &sn, &cs);
     const double s1 = gshfl<GW>(gmask, sn, 0), c1 = gshfl<GW>(gmask, cs, 0);
     const double s2 = gshfl<GW>(gmask, sn, 1), c2 = gshfl<GW>(gmask, cs, 1);
     int fault = 0;
@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
         const int j = 3 + 2 * s;
         const double r = gshfl<GW>(gmask, o_rng, u), be = gshfl<GW>(gmask, o_brg, u);
         double sb, cb;
-        sincos(be + pth, &sb, &cb);
+        fm_sincos(be + pth, &sb, &cb);
         if (gl == 0) {
           sMu[j] = __dadd_rn(px, __dmul_rn(r, cb));
           sMu[j + 1] = __dadd_rn(py, __dmul_rn(r, sb));

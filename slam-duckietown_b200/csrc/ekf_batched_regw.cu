@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
   {
     const double px = sMu[0], py = sMu[1], pth = sMu[2];
     double sn, cs;  // even lanes sincos(theta), odd lanes sincos(theta + ang): one call instead of two
-    sincos((lane & 1) ? pth + ang : pth, &sn, &cs);
+    fm_sincos((lane & 1) ? pth + ang : pth, &sn, &cs);
     const double s1 = __shfl_sync(kFull, sn, 0), c1 = __shfl_sync(kFull, cs, 0);
     const double s2 = __shfl_sync(kFull, sn, 1), c2 = __shfl_sync(kFull, cs, 1);
     int fault = 0;
@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
         const int j = 3 + 2 * s;
         const double r = __shfl_sync(kFull, o_rng, u), be = __shfl_sync(kFull, o_brg, u);
         double sb, cb;
-        sincos(be + pth, &sb, &cb);
+        fm_sincos(be + pth, &sb, &cb);
         if (lane == 0) {
           sMu[j] = __dadd_rn(px, __dmul_rn(r, cb));
           sMu[j + 1] = __dadd_rn(py, __dmul_rn(r, sb));

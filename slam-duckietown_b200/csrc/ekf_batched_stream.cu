@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(32) batch_step_stream_kernel(BatchStepArgs a) 
   {
     const double px = sMu[0], py = sMu[1], pth = sMu[2];
     double sn, cs;
-    sincos((lane & 1) ? pth + ang : pth, &sn, &cs);
+    fm_sincos((lane & 1) ? pth + ang : pth, &sn, &cs);
     const double s1 = __shfl_sync(kFull, sn, 0), c1 = __shfl_sync(kFull, cs, 0);
     const double s2 = __shfl_sync(kFull, sn, 1), c2 = __shfl_sync(kFull, cs, 1);
     for (int u = 0; u < m; ++u) {
@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(32) batch_step_stream_kernel(BatchStepArgs a) 
       const double r = __shfl_sync(kFull, o_rng, u), be = __shfl_sync(kFull, o_brg, u);
       const int j = 3 + 2 * s;
       double sb, cb;
-      sincos(be + pth, &sb, &cb);
+      fm_sincos(be + pth, &sb, &cb);
       if (lane == 0) {
         sMu[j] = __dadd_rn(px, __dmul_rn(r, cb));
         sMu[j + 1] = __dadd_rn(py, __dmul_rn(r, sb));

@@ -61,7 +61,7 @@ __device__ __forceinline__ Motion motion_from_sincos(double th, double ang, doub
   if ((flags & kFlagCircular) && fabs(ang) > 1e-2) {
     // every product rounded before the add, as numpy evaluates :391-403 (and so that no kernel's FMA contraction
     // choice can differ from another's)
-    const double r = lin / ang;
+    const double r = fm_div(lin, ang);
     const double rs = __dmul_rn(r, s), rs2 = __dmul_rn(r, s2), rc = __dmul_rn(r, c), rc2 = __dmul_rn(r, c2);
     m.dx = __dadd_rn(-rs, rs2);
     m.dy = __dsub_rn(rc, rc2);
@@ -80,8 +80,8 @@ __device__ __forceinline__ Motion motion_from_sincos(double th, double ang, doub
 }
 __device__ __forceinline__ Motion motion_step(double th, double ang, double lin, int flags) {
   double s, c, s2, c2;
-  sincos(th, &s, &c);
-  sincos(th + ang, &s2, &c2);
+  fm_sincos(th, &s, &c);
+  fm_sincos(th + ang, &s2, &c2);
   return motion_from_sincos(th, ang, lin, flags, s, c, s2, c2);
 }
 

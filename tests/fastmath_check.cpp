@@ -32,6 +32,16 @@ int main() {
     worst_s = fmax(worst_s, ulp_err(r, sqrtl((long double)d)));
     worst_is = fmax(worst_is, ulp_err(ir, 1.0L / sqrtl((long double)d)));
   }
+  double worst_sin = 0, worst_cos = 0;
+  std::uniform_real_distribution<double> A(-1, 1);
+  for (long i = 0; i < 2000000; ++i) {
+    double x = A(g) * ((i & 3) == 0 ? 1.0e5 : (i & 3) == 1 ? 100.0 : 3.2);
+    if (i % 1000 == 0) x = (double)(i / 1000 % 64) * 0.78539816339744828 * (1 + 1e-15 * (i % 5 - 2));
+    double s, c; ekf::fm_sincos(x, &s, &c);
+    worst_sin = fmax(worst_sin, fmin(ulp_err(s, sinl((long double)x)), fabs(s - (double)sinl((long double)x)) / 1.1e-16));
+    worst_cos = fmax(worst_cos, fmin(ulp_err(c, cosl((long double)x)), fabs(c - (double)cosl((long double)x)) / 1.1e-16));
+  }
+  printf("sin %.3f cos %.3f ulp\n", worst_sin, worst_cos);
   printf("atan2 %.3f (y=%a x=%a) div %.3f rcp %.3f sqrt %.3f rsqrt %.3f ulp\n", worst_a, wa_y, wa_x, worst_d, worst_r, worst_s, worst_is);
   // special values
   double sp[][2] = {{0.0, 1.0}, {0.0, -1.0}, {-0.0, -1.0}, {1.0, 0.0}, {-1.0, 0.0}, {0.0, 0.0}, {0.0, -0.0}, {-0.0, -0.0}, {1.0, 1.0}, {-1.0, -1.0}, {1.0, -1.0}};
