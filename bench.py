@@ -57,6 +57,19 @@ def set_workload(name, world):
 SCALING = "weak"
 
 
+def kernel_label():
+    """(ncu_traffic key, description) of the kernel the C-ABI dispatches this workload to (ekf_capi.cu: capacities
+    <= 8 landmarks -> group kernel, else the W-in-registers warp kernel), unless EKF_BATCH_KERNEL forces a variant."""
+    forced = os.environ.get("EKF_BATCH_KERNEL", "")
+    if forced:
+        return f"{forced}<{NLM},{M}>", f"EKF_BATCH_KERNEL={forced} variant <{NLM},{M}>"
+    if NLM <= 8:
+        return (f"batch_step_group_kernel<{NLM},{M},8>",
+                f"batch_step_group_kernel<{NLM},{M},8> (8 lanes per filter, four filters per warp)")
+    return (f"batch_step_regw_kernel<{NLM},{M}>",
+            f"batch_step_regw_kernel<{NLM},{M},1> (one warp per filter, W in registers)")
+
+
 def make_config(joseph=False):
     """The `config` object both arms print (same workload, same keys)."""
     return {"workload": WORKLOAD, "filters_per_gpu": BATCH, "landmarks": NLM, "updates_per_step": M,
@@ -407,8 +420,8 @@ def run_own_arm(args, world):
             "config": make_config(args.joseph),
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "peak_source": which, "unit": "GB/s",
                          "frac": ach / peak, "frac_of_8TBs": ach / 8000.0,
-                         "bytes_per_filter_step": BYTES_PER_FILTER_STEP, "kernel": f"batch_step_regw_kernel<{NLM},{M},1> (one warp per filter, W in registers)",
-                         "kernel_ms": kern_ms, "traffic": ncu_traffic(f"batch_step_regw_kernel<{NLM},{M}>")},
+                         "bytes_per_filter_step": BYTES_PER_FILTER_STEP, "kernel": kernel_label()[1],
+                         "kernel_ms": kern_ms, "traffic": ncu_traffic(kernel_label()[0])},
             "e2e": {"value": BATCH * world * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h,
                     "unpipelined_value": BATCH * world * K / e2e_sync_s,
