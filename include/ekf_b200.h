@@ -110,6 +110,12 @@ int ekf_batch_associate_overflow_count(ekf_batch_t* h, int64_t* count);
 /* sse_dev[b] += (x_b - gt_x)^2 + (y_b - gt_y)^2 for every filter: absolute trajectory error of the ensemble
  * against a ground-truth track (the comparison of replay_no_ros.py:519-529 as a number per member)          */
 int ekf_batch_accumulate_ate(ekf_batch_t* h, double gt_x, double gt_y, double* sse_dev, void* stream);
+/* ensemble moments of the state over this handle's filters, fixed summation order (no atomics):
+ * sums_dev[i] = sum_b mu_b[i] (i < n), sums_dev[n + i*n + k] = sum_b mu_b[i] mu_b[k]; n + n*n doubles.
+ * The one optional reduction of the batched mode: ranks all-reduce these n + n*n doubles
+ * (plus the filter count) to get the ensemble mean and covariance that the reference's ablation plots show per
+ * run (README.md:421-492); the filters themselves never interact.                                            */
+int ekf_batch_moments(ekf_batch_t* h, double* sums_dev, void* stream);
 
 /* ---- large-map mode: ONE filter, P streamed from HBM, optional row-block shard ------------------------- */
 typedef struct ekf_lm ekf_lm_t;

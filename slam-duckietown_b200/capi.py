@@ -57,6 +57,7 @@ SIGNATURES = {
     "ekf_batch_associate": (_i, [_p, _i, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _p]),
     "ekf_batch_associate_overflow_count": (_i, [_p, C.POINTER(_l)]),
     "ekf_batch_accumulate_ate": (_i, [_p, _d, _d, _p, _p]),
+    "ekf_batch_moments": (_i, [_p, _p, _p]),
     "ekf_lm_layout": (_i, [_i, C.POINTER(_i), C.POINTER(_l)]),
     "ekf_lm_create": (_i, [_i, _i, C.POINTER(_p)]),
     "ekf_lm_destroy": (_i, [_p]),

@@ -66,6 +66,7 @@ struct ekf_batch {
   cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
   double* p_stage[2] = {nullptr, nullptr};  // per set: ang | lin | rng[M] | brg[M] | pose[3] doubles, slot[M] ints
   int64_t pipe_step = 0;
+  double* mom_partial = nullptr;  // scratch of ekf_batch_moments
 };
 
 struct ekf_lm {
@@ -157,6 +158,7 @@ int ekf_batch_destroy(ekf_batch_t* h) {
   if (!h) return EKF_OK;
   cudaSetDevice(h->device);
   cudaFree(h->faults);
+  cudaFree(h->mom_partial);
   cudaFree(h->d_ang);
   cudaFree(h->d_lin);
   cudaFree(h->d_rng);
@@ -439,6 +441,16 @@ int ekf_batch_accumulate_ate(ekf_batch_t* h, double gt_x, double gt_y, double* s
   if (!h->mu) return fail(EKF_ESTATE, "state not bound");
   CU(cudaSetDevice(h->device));
   CU(ekf::batch_launch_ate(h->mu, h->ld, h->batch, gt_x, gt_y, sse_dev, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf_batch_moments(ekf_batch_t* h, double* sums_dev, void* stream) {
+  if (!h || !sums_dev) return fail(EKF_EINVAL, "null argument");
+  if (!h->mu) return fail(EKF_ESTATE, "state not bound");
+  CU(cudaSetDevice(h->device));
+  if (!h->mom_partial)
+    CU(cudaMalloc(&h->mom_partial, sizeof(double) * ekf::MOM_CTAS * (size_t)(h->n + h->n * h->n)));
+  CU(ekf::batch_launch_moments(h->mu, h->ld, h->batch, h->n, h->mom_partial, sums_dev, (cudaStream_t)stream));
   return EKF_OK;
 }
 

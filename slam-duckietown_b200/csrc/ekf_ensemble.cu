@@ -84,6 +84,75 @@ __global__ void __launch_bounds__(256) batch_ate_kernel(const double* __restrict
   sse[b] += ex * ex + ey * ey;
 }
 
+// Ensemble moments of the state (batched mode: the one optional reduction of the Monte Carlo batch):
+// sums[i] = sum_b mu_b[i], sums[n + i n + k] = sum_b mu_b[i] mu_b[k]. Two passes with a FIXED summation order (no
+// atomics): CTA c reduces its contiguous chunk of filters, staging MOM_TILE mean vectors at a time in shared memory
+// (coalesced rows), thread e owning output element e (and e + 256, ...) with one running sum per element; the
+// second kernel adds the MOM_CTAS partial vectors in index order. mu is 0.35 KB per filter, so the pass costs
+// 1/40th of a filter-step's traffic.
+constexpr int MOM_TILE = 32;
+__global__ void __launch_bounds__(256) batch_moments_partial_kernel(const double* __restrict__ mu, int64_t mu_stride,
+                                                                    int64_t batch, int n, int64_t chunk,
+                                                                    double* __restrict__ partial) {
+  extern __shared__ double tile[];  // [MOM_TILE][n]
+  const int E = n + n * n;
+  const int64_t b0 = blockIdx.x * chunk, b1 = (b0 + chunk < batch) ? b0 + chunk : batch;
+  constexpr int MAXE = 16;  // elements per thread: n <= 63 -> E <= 4032 <= 16 x 256
+  double acc[MAXE];
+#pragma unroll
+  for (int q = 0; q < MAXE; ++q) acc[q] = 0.0;
+  for (int64_t t0 = b0; t0 < b1; t0 += MOM_TILE) {
+    const int nb = (int)((b1 - t0 < MOM_TILE) ? b1 - t0 : MOM_TILE);
+    __syncthreads();
+    for (int x = threadIdx.x; x < nb * n; x += blockDim.x) {
+      const int f = x / n, i = x - f * n;
+      tile[f * n + i] = mu[(t0 + f) * mu_stride + i];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < MAXE; ++q) {
+      const int e = threadIdx.x + q * 256;
+      if (e >= E) break;
+      int i, k;
+      if (e < n) { i = e; k = -1; } else { i = (e - n) / n; k = (e - n) - i * n; }
+      double a = acc[q];
+      for (int f = 0; f < nb; ++f) {
+        const double vi = tile[f * n + i];
+        a = (k < 0) ? __dadd_rn(a, vi) : fma(vi, tile[f * n + k], a);
+      }
+      acc[q] = a;
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < MAXE; ++q) {
+    const int e = threadIdx.x + q * 256;
+    if (e < E) partial[(int64_t)blockIdx.x * E + e] = acc[q];
+  }
+}
+
+__global__ void __launch_bounds__(256) batch_moments_final_kernel(const double* __restrict__ partial, int ctas, int E,
+                                                                  double* __restrict__ sums) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  double a = 0.0;
+  for (int c = 0; c < ctas; ++c) a = __dadd_rn(a, partial[(int64_t)c * E + e]);
+  sums[e] = a;
+}
+
+cudaError_t batch_launch_moments(const double* mu, int64_t mu_stride, int64_t batch, int n, double* partial,
+                                 double* sums, cudaStream_t st) {
+  if (n < 1 || n > 63 || batch < 1) return cudaErrorInvalidValue;
+  const int E = n + n * n;
+  const int64_t chunk = (batch + MOM_CTAS - 1) / MOM_CTAS;
+  const int ctas = (int)((batch + chunk - 1) / chunk);
+  batch_moments_partial_kernel<<<ctas, 256, MOM_TILE * n * sizeof(double), st>>>(mu, mu_stride, batch, n, chunk,
+                                                                                  partial);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  batch_moments_final_kernel<<<(E + 255) / 256, 256, 0, st>>>(partial, ctas, E, sums);
+  return cudaGetLastError();
+}
+
 cudaError_t batch_launch_associate(const AssocArgs& a, cudaStream_t st) {
   if (a.m < 1 || a.m > ASSOC_MAX_M) return cudaErrorInvalidValue;
   batch_associate_kernel<<<(unsigned)((a.batch + 127) / 128), 128, 0, st>>>(a);

@@ -404,6 +404,15 @@ class BatchedEKF:
         """sse[b] += squared position error of filter b against the ground-truth point (device tensor (B,))."""
         capi.call("ekf_batch_accumulate_ate", self._h, float(gt_x), float(gt_y), _ptr(sse), _stream_ptr(self.torch))
 
+    def moments(self, out=None):
+        """(sum_b mu_b, sum_b mu_b mu_b^T) over this handle's filters as one device tensor of n + n*n doubles
+        (fixed summation order). Feed to ``ensemble.allreduce_moments`` for the ensemble mean / covariance."""
+        n = self.n
+        if out is None:
+            out = self.torch.empty(n + n * n, dtype=self.torch.float64, device=self.dev)
+        capi.call("ekf_batch_moments", self._h, _ptr(out), _stream_ptr(self.torch))
+        return out
+
     def step_host(self, ang, lin, slot, rng, brg, pose_out):
         """End-to-end step with HOST (ideally pinned) torch tensors / numpy arrays: H2D, step, D2H of the
         pose (B, 3) into ``pose_out``; synchronous."""

@@ -639,3 +639,32 @@ def test_p2p_row_exchange_two_processes(eb):
         outs.append(json.loads(o.strip().splitlines()[-1]))
     for o in outs:
         assert o["same"] and o["p2p_error"] == 0 and o["finite"], o
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("batch,n_lm", [(5000, 20), (37, 8), (65536, 20)])
+def test_ensemble_moments_match_numpy(eb, batch, n_lm):
+    """ekf_batch_moments (fixed-order device reduction) == numpy sums of mu and mu mu^T over the filters; the
+    ensemble mean / covariance derived from it == numpy's; two calls give bit-identical sums (no atomics)."""
+    import torch
+    from slam_duckietown_b200 import workloads as wl
+    from slam_duckietown_b200.ensemble import ensemble_mean_cov
+    w = wl.make_batched(batch, n_landmarks=n_lm, m=2, steps=4)
+    f = eb.BatchedEKF(batch, n_lm)
+    f.set_noise(w.motion_var, w.meas_var)
+    f.init(0.1)
+    dev = f.dev
+    for t in range(w.steps):
+        f.step(torch.from_numpy(w.ang[t]).to(dev), torch.from_numpy(w.lin[t]).to(dev),
+               torch.from_numpy(w.slot[t]).to(dev), torch.from_numpy(w.rng[t]).to(dev),
+               torch.from_numpy(w.brg[t]).to(dev))
+    mu, _ = f.state()
+    n = f.n
+    s1 = f.moments().cpu().numpy()
+    s2 = f.moments().cpu().numpy()
+    np.testing.assert_array_equal(s1, s2)
+    want = np.concatenate([mu.sum(0), (mu.T @ mu).ravel()])
+    scale = np.abs(want).max()
+    assert np.abs(s1 - want).max() <= 1e-12 * scale * max(1.0, np.log2(batch))
+    mean, cov = ensemble_mean_cov(f)                      # one rank: no process group, identity all-reduce
+    np.testing.assert_allclose(mean.cpu().numpy(), mu.mean(0), rtol=0, atol=1e-12 * max(1.0, np.abs(mu).max()))
+    np.testing.assert_allclose(cov.cpu().numpy(), np.cov(mu.T, bias=True), rtol=0, atol=1e-10 * max(1.0, np.abs(mu).max()) ** 2)

@@ -82,6 +82,46 @@ def _gloo_worker(rank, world, port, n_lm, slots, out_dir):
         fh.write("1" if ok else "0")
 
 
+def _gloo_moments_worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from slam_duckietown_b200.ensemble import allreduce_moments, filter_partition, moments_to_mean_cov
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    batch, n = 101, 7
+    x = np.random.default_rng(5).normal(size=(batch, n)) + np.arange(n)          # the whole ensemble, every rank
+    lo, hi = filter_partition(batch, world)[rank]
+    mine = x[lo:hi]                                                               # what ekf_batch_moments sums on the device
+    sums = torch.from_numpy(np.concatenate([mine.sum(0), (mine[:, :, None] * mine[:, None, :]).sum(0).ravel()]))
+    count, total = allreduce_moments(hi - lo, sums)
+    mean, cov = moments_to_mean_cov(count, total, n)
+    ok = count == batch
+    ok &= bool(np.allclose(mean.numpy(), x.mean(0), rtol=1e-13, atol=1e-13))
+    ok &= bool(np.allclose(cov.numpy(), np.cov(x.T, bias=True), rtol=1e-11, atol=1e-12))
+    dist.barrier()
+    dist.destroy_process_group()
+    with open(os.path.join(out_dir, f"mom{rank}"), "w") as fh:
+        fh.write("1" if ok else "0")
+
+
+@pytest.mark.parametrize("batch,world", [(65536, 8), (1 << 20, 4), (101, 2), (3, 8), (0, 2)])
+def test_filter_partition_is_contiguous_and_balanced(batch, world):
+    from slam_duckietown_b200.ensemble import filter_partition
+    parts = filter_partition(batch, world)
+    assert len(parts) == world and parts[0][0] == 0 and parts[-1][1] == batch
+    assert all(a[1] == b[0] for a, b in zip(parts, parts[1:]))
+    sizes = [e - b for b, e in parts]
+    assert max(sizes) - min(sizes) <= 1 and sizes == sorted(sizes, reverse=True)
+
+
+def test_ensemble_moments_over_gloo_world2(tmp_path):
+    """world_size 2, gloo, CPU: per-rank moment sums + one all_reduce give the whole ensemble's mean / covariance."""
+    import torch.multiprocessing as mp
+    world = 2
+    mp.spawn(_gloo_moments_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    assert [open(tmp_path / f"mom{r}").read() for r in range(world)] == ["1", "1"]
+
+
 def test_row_exchange_over_gloo_world2(tmp_path):
     """world_size 2, gloo, CPU: after the exchange every rank holds the owners' five rows and mu entries."""
     import torch.multiprocessing as mp
