@@ -668,3 +668,58 @@ def test_ensemble_moments_match_numpy(eb, batch, n_lm):
     mean, cov = ensemble_mean_cov(f)                      # one rank: no process group, identity all-reduce
     np.testing.assert_allclose(mean.cpu().numpy(), mu.mean(0), rtol=0, atol=1e-12 * max(1.0, np.abs(mu).max()))
     np.testing.assert_allclose(cov.cpu().numpy(), np.cov(mu.T, bias=True), rtol=0, atol=1e-10 * max(1.0, np.abs(mu).max()) ** 2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("L,m,variants", [(8, 3, ("regw", "group8", "group16", "staged", "stream")),
+                                           (8, 4, ("regw", "group8", "staged")),
+                                           (20, 4, ("regw", "staged", "stream"))])
+def test_batched_random_observation_patterns(eb, monkeypatch, L, m, variants):
+    """Steady-state steps with RANDOM observation blocks per filter: any subset of the m entries empty (-1), the
+    entries in random order, and the SAME landmark observed more than once in one step (the C-ABI takes any slot
+    block; sequential semantics must hold). Every kernel variant must agree bitwise and sampled filters must match
+    the oracle's sequential updates."""
+    import torch
+    from oracle import ekf_oracle as eo
+    from slam_duckietown_b200 import workloads as wl
+    B = 203                                                # not a multiple of the filters per warp
+    w = wl.make_batched(B, n_landmarks=L, m=m, steps=-(-L // m) + 6)
+    rs = np.random.default_rng(11)
+    slot, rng_, brg = w.slot.copy(), w.rng.copy(), w.brg.copy()
+    for t in range(w.warm_steps, w.steps):
+        for b in range(B):
+            k = rs.integers(0, 4)
+            if k == 0:                                     # duplicate: entry 1 re-observes entry 0's landmark
+                slot[t, b, 1] = slot[t, b, 0]
+                rng_[t, b, 1] = rng_[t, b, 0] * (1.0 + 0.01 * rs.normal())
+                brg[t, b, 1] = brg[t, b, 0] + 0.01 * rs.normal()
+            elif k == 1:                                   # random holes
+                slot[t, b, rs.random(m) < 0.5] = -1
+            elif k == 2:                                   # random order
+                perm = rs.permutation(m)
+                slot[t, b], rng_[t, b], brg[t, b] = slot[t, b, perm], rng_[t, b, perm], brg[t, b, perm]
+    res = {}
+    for variant in variants:
+        monkeypatch.setenv("EKF_BATCH_KERNEL", variant)
+        f = eb.BatchedEKF(B, L)
+        f.set_noise(w.motion_var, w.meas_var)
+        f.init(0.1)
+        for t in range(w.steps):
+            f.step(_dev(f.dev, w.ang[t]), _dev(f.dev, w.lin[t]), _dev(f.dev, slot[t]), _dev(f.dev, rng_[t]),
+                   _dev(f.dev, brg[t]))
+        assert f.fault_count() == 0, variant
+        res[variant] = (f.mu.clone(), f.P.clone(), f.n_known.clone())
+        if variant == variants[0]:
+            mu, p = f.state()
+    for variant in variants[1:]:
+        for a, b_ in zip(res[variants[0]], res[variant]):
+            assert torch.equal(a, b_), variant
+    n = 3 + 2 * L
+    for b in (0, 1, 2, 3, 101, B - 1):
+        m_o, c_o, nk = np.zeros(n), np.zeros((n, n)), 0
+        c_o[:3, :3] = np.eye(3) * 0.1
+        fl = eo.Flags(motion_var=float(w.motion_var[b]), meas_var=float(w.meas_var[b]))
+        for t in range(w.steps):
+            obs = [(int(s_), float(r), float(q)) for s_, r, q in zip(slot[t, b], rng_[t, b], brg[t, b]) if s_ >= 0]
+            m_o, c_o, nk = eo.step_from_observations(m_o, c_o, float(w.ang[t, b]), float(w.lin[t, b]), obs, fl, nk)
+        assert_parity(mu[b], p[b], m_o, c_o, what=f"random observation patterns L={L} m={m} b={b}")
