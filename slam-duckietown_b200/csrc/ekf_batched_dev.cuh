@@ -35,6 +35,17 @@ __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_
                : "memory");
 }
 
+// L2 prefetch of the data of the filter that will occupy this CTA's place on the SM one "generation" later. Measured
+// (tools/phase_probe.py, config M): under load a CTA waits ~30 % of its life for its inputs, mu and P to arrive from
+// a saturated HBM; prefetched into L2 about 3/8 of a generation ahead they arrive at L2 latency instead
+// (789 M -> 1 049 M filter-steps/s at config M, the plateau is 1/4 .. 1/2 of a generation).
+__device__ __forceinline__ void l2_prefetch_bulk(const void* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void l2_prefetch(const void* src) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(src));
+}
+
 // one rank-2 (plain) step on a single element; the SAME sequence is used wherever an entry of an
 // intermediate P_u is needed, so phase 2's rebuilt rows/columns equal what phase 3 finally writes.
 __device__ __forceinline__ double rank2(double v, double k0, double k1, double w0, double w1) {

@@ -11,6 +11,7 @@
 // scalar chain of the 32 / GW filters runs in the same instructions, and shuffles / barriers use the group's
 // lane mask, so groups whose observation patterns differ may diverge without deadlock.
 // Plain covariance form, compile-time observation count m <= GW.
+#include <cstdlib>
 #include "ekf_batched.h"
 #include "ekf_batched_dev.cuh"
 
@@ -49,7 +50,7 @@ __host__ __device__ constexpr int group_slice_doubles(int nlm, int m, int gw) {
 
 // 16 resident one-warp CTAs per SM: 128 registers per thread = four warps per scheduler's register file
 template <int NLM, int MT, int GW>
-__global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs a, int64_t batch) {
+__global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs a, int64_t batch, int pf) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
   constexpr int HIST = 2 * LD;          // doubles of one update's K record: [LD][2]
@@ -85,6 +86,31 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
     tma_bulk_g2s(sMu, gMu, (uint32_t)(LD * sizeof(double)), bar);
     mbar_expect_tx(bar + 1, (uint32_t)(N * LD * sizeof(double)));
     tma_bulk_g2s(sP, gP, (uint32_t)(N * LD * sizeof(double)), bar + 1);
+  }
+  // L2 prefetch for the filters that will take this CTA's place on the SM (pf CTAs ahead, ekf_batched_dev.cuh): one
+  // request per array and filter, spread over the lanes of the group
+  if (pf > 0) {
+    const int64_t bn = b + (int64_t)pf * FPW;
+    if (bn < batch) {
+      const void* src = nullptr;
+      switch (gl) {
+        case 1: src = a.ticks_l ? (const void*)(a.ticks_l + bn) : (const void*)(a.ang + bn); break;
+        case 2: src = a.ticks_l ? (const void*)(a.ticks_r + bn) : (const void*)(a.lin + bn); break;
+        case 3: src = a.motion_var + bn; break;
+        case 4: src = a.meas_var + bn; break;
+        case 5: src = a.n_known + bn; break;
+        case 6: src = a.slot + bn * m; break;
+        case 7: src = a.rng + bn * m; break;
+        default: break;
+      }
+      if (gl == 0) {
+        l2_prefetch_bulk(a.P + bn * (int64_t)(N * LD), (uint32_t)(N * LD * sizeof(double)));
+        l2_prefetch_bulk(a.mu + bn * (int64_t)LD, (uint32_t)(LD * sizeof(double)));
+        l2_prefetch(a.brg + bn * m);
+      } else if (src) {
+        l2_prefetch(src);
+      }
+    }
   }
   double ang, lin;
   if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
@@ -365,7 +391,17 @@ static cudaError_t launch_group(const BatchStepArgs& a, int64_t batch, cudaStrea
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   if (e != cudaSuccess) return e;
-  kernel<<<(unsigned)((batch + fpw - 1) / fpw), 32, smem, st>>>(a, batch);
+  // L2-prefetch distance in CTAs: 3/8 of the CTAs resident on the device (EKF_BATCH_PREFETCH overrides, 0 = off)
+  static const int pf = [&] {
+    if (const char* v = getenv("EKF_BATCH_PREFETCH")) return atoi(v);
+    int dev = 0, sms = 0, occ = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, 32, smem) != cudaSuccess)
+      return 0;
+    return sms * occ * 3 / 8;
+  }();
+  kernel<<<(unsigned)((batch + fpw - 1) / fpw), 32, smem, st>>>(a, batch, pf);
   return cudaGetLastError();
 }
 

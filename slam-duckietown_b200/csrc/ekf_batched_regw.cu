@@ -97,7 +97,7 @@ __host__ __device__ constexpr int regw_min_blocks(int nlm, int m, int wpc) {
 }
 
 template <int NLM, int MT, int WPC>
-__global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch_step_regw_kernel(BatchStepArgs a, int64_t batch) {
+__global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch_step_regw_kernel(BatchStepArgs a, int64_t batch, int pf) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
   constexpr int HIST = 2 * LD;        // doubles of one update's K record: [LD][2]
@@ -140,6 +140,30 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
     mbar_expect_tx(bar + 1, (uint32_t)(N * LD * sizeof(double)));
     tma_bulk_g2s(sP, gP, (uint32_t)(N * LD * sizeof(double)), bar + 1);
     if (WPC > 1) b_next = total_warps + (int64_t)atomicAdd(work, 1ULL);  // latency hidden behind this filter
+  }
+  // L2 prefetch for the filter that will take this CTA's place on the SM (pf CTAs ahead, ekf_batched_dev.cuh)
+  if (WPC == 1 && pf > 0) {
+    const int64_t bn = b + pf;
+    if (bn < batch) {
+      const void* src = nullptr;
+      switch (lane) {
+        case 1: src = a.ticks_l ? (const void*)(a.ticks_l + bn) : (const void*)(a.ang + bn); break;
+        case 2: src = a.ticks_l ? (const void*)(a.ticks_r + bn) : (const void*)(a.lin + bn); break;
+        case 3: src = a.motion_var + bn; break;
+        case 4: src = a.meas_var + bn; break;
+        case 5: src = a.n_known + bn; break;
+        case 6: src = a.slot + bn * m; break;
+        case 7: src = a.rng + bn * m; break;
+        case 8: src = a.brg + bn * m; break;
+        default: break;
+      }
+      if (lane == 0) {
+        l2_prefetch_bulk(a.P + bn * (int64_t)(N * LD), (uint32_t)(N * LD * sizeof(double)));
+        l2_prefetch_bulk(a.mu + bn * (int64_t)LD, (uint32_t)(LD * sizeof(double)));
+      } else if (src) {
+        l2_prefetch(src);
+      }
+    }
   }
   double ang, lin;
   if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
@@ -477,7 +501,15 @@ static cudaError_t launch_regw_wpc(const BatchStepArgs& a, int64_t batch, unsign
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   if (e != cudaSuccess) return e;
-  kernel<<<grid, 32 * WPC, smem, st>>>(a, batch);
+  // L2-prefetch distance in CTAs. OFF by default for this kernel: at n = 43 it already runs at 97 % of the device-copy
+  // rate and the prefetch costs 5 % (207.3 -> 197 M filter-steps/s at every distance from 222 to 1332, measured);
+  // EKF_REGW_PREFETCH=<CTAs> turns it on for experiments. The group kernel (small filters) has it on.
+  static const int pf = [] {
+    if (WPC > 1) return 0;
+    const char* v = getenv("EKF_REGW_PREFETCH");
+    return v ? atoi(v) : 0;
+  }();
+  kernel<<<grid, 32 * WPC, smem, st>>>(a, batch, pf);
   return cudaGetLastError();
 }
 
