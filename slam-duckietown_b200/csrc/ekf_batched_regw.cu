@@ -142,8 +142,9 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
     if (WPC > 1) b_next = total_warps + (int64_t)atomicAdd(work, 1ULL);  // latency hidden behind this filter
   }
   // L2 prefetch for the filter that will take this CTA's place on the SM (pf CTAs ahead, ekf_batched_dev.cuh)
-  if (WPC == 1 && pf > 0) {
-    const int64_t bn = b + pf;
+  // pf < 0: the same distance |pf|, but only the per-filter inputs and mu — P is left to the TMA load
+  if (WPC == 1 && pf != 0) {
+    const int64_t bn = b + (pf < 0 ? -pf : pf);
     if (bn < batch) {
       const void* src = nullptr;
       switch (lane) {
@@ -158,7 +159,7 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
         default: break;
       }
       if (lane == 0) {
-        l2_prefetch_bulk(a.P + bn * (int64_t)(N * LD), (uint32_t)(N * LD * sizeof(double)));
+        if (pf > 0) l2_prefetch_bulk(a.P + bn * (int64_t)(N * LD), (uint32_t)(N * LD * sizeof(double)));
         l2_prefetch_bulk(a.mu + bn * (int64_t)LD, (uint32_t)(LD * sizeof(double)));
       } else if (src) {
         l2_prefetch(src);
@@ -503,7 +504,8 @@ static cudaError_t launch_regw_wpc(const BatchStepArgs& a, int64_t batch, unsign
   if (e != cudaSuccess) return e;
   // L2-prefetch distance in CTAs. OFF by default for this kernel: at n = 43 it already runs at 97 % of the device-copy
   // rate and the prefetch costs 5 % (207.3 -> 197 M filter-steps/s at every distance from 222 to 1332, measured);
-  // EKF_REGW_PREFETCH=<CTAs> turns it on for experiments. The group kernel (small filters) has it on.
+  // EKF_REGW_PREFETCH=<CTAs> turns it on for experiments (negative: inputs + mu only, no P). The group kernel (small
+  // filters) has it on.
   static const int pf = [] {
     if (WPC > 1) return 0;
     const char* v = getenv("EKF_REGW_PREFETCH");
