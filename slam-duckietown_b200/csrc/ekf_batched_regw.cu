@@ -96,37 +96,8 @@ __host__ __device__ constexpr int regw_min_blocks(int nlm, int m, int wpc) {
   return wpc > 1 ? 1 : (fit < EKF_REGW_MAX_BLOCKS ? fit : EKF_REGW_MAX_BLOCKS);
 }
 
-// L2 prefetch of the data of filter b + |pf| (ekf_batched_dev.cuh). pf < 0: only the per-filter inputs and mu — P is
-// left to the TMA load.
-template <int NLM>
-__device__ __forceinline__ void prefetch_successor(const BatchStepArgs& a, int64_t b, int64_t batch, int pf, int lane,
-                                                   int m) {
-  constexpr int N = 3 + 2 * NLM;
-  constexpr int LD = (N + 3) & ~3;
-  const int64_t bn = b + (pf < 0 ? -pf : pf);
-  if (bn >= batch) return;
-  const void* src = nullptr;
-  switch (lane) {
-    case 1: src = a.ticks_l ? (const void*)(a.ticks_l + bn) : (const void*)(a.ang + bn); break;
-    case 2: src = a.ticks_l ? (const void*)(a.ticks_r + bn) : (const void*)(a.lin + bn); break;
-    case 3: src = a.motion_var + bn; break;
-    case 4: src = a.meas_var + bn; break;
-    case 5: src = a.n_known + bn; break;
-    case 6: src = a.slot + bn * m; break;
-    case 7: src = a.rng + bn * m; break;
-    case 8: src = a.brg + bn * m; break;
-    default: break;
-  }
-  if (lane == 0) {
-    if (pf > 0) l2_prefetch_bulk(a.P + bn * (int64_t)(N * LD), (uint32_t)(N * LD * sizeof(double)));
-    l2_prefetch_bulk(a.mu + bn * (int64_t)LD, (uint32_t)(LD * sizeof(double)));
-  } else if (src) {
-    l2_prefetch(src);
-  }
-}
-
 template <int NLM, int MT, int WPC>
-__global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch_step_regw_kernel(BatchStepArgs a, int64_t batch, int pf, int pf_tail) {
+__global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch_step_regw_kernel(BatchStepArgs a, int64_t batch, int pf) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
   constexpr int HIST = 2 * LD;        // doubles of one update's K record: [LD][2]
@@ -170,9 +141,31 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
     tma_bulk_g2s(sP, gP, (uint32_t)(N * LD * sizeof(double)), bar + 1);
     if (WPC > 1) b_next = total_warps + (int64_t)atomicAdd(work, 1ULL);  // latency hidden behind this filter
   }
-  // L2 prefetch for the filter that will take this CTA's place on the SM (pf CTAs ahead, ekf_batched_dev.cuh);
-  // pf_tail: issued after the filter's last store instead of here, at the head of its dependent chain
-  if (WPC == 1 && pf != 0 && !pf_tail) prefetch_successor<NLM>(a, b, batch, pf, lane, m);
+  // L2 prefetch for the filter that will take this CTA's place on the SM (pf CTAs ahead, ekf_batched_dev.cuh)
+  // pf < 0: the same distance |pf|, but only the per-filter inputs and mu — P is left to the TMA load
+  if (WPC == 1 && pf != 0) {
+    const int64_t bn = b + (pf < 0 ? -pf : pf);
+    if (bn < batch) {
+      const void* src = nullptr;
+      switch (lane) {
+        case 1: src = a.ticks_l ? (const void*)(a.ticks_l + bn) : (const void*)(a.ang + bn); break;
+        case 2: src = a.ticks_l ? (const void*)(a.ticks_r + bn) : (const void*)(a.lin + bn); break;
+        case 3: src = a.motion_var + bn; break;
+        case 4: src = a.meas_var + bn; break;
+        case 5: src = a.n_known + bn; break;
+        case 6: src = a.slot + bn * m; break;
+        case 7: src = a.rng + bn * m; break;
+        case 8: src = a.brg + bn * m; break;
+        default: break;
+      }
+      if (lane == 0) {
+        if (pf > 0) l2_prefetch_bulk(a.P + bn * (int64_t)(N * LD), (uint32_t)(N * LD * sizeof(double)));
+        l2_prefetch_bulk(a.mu + bn * (int64_t)LD, (uint32_t)(LD * sizeof(double)));
+      } else if (src) {
+        l2_prefetch(src);
+      }
+    }
+  }
   double ang, lin;
   if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
     const double dl = delta_phi(a.ticks_l[b], a.prev_l[b], a.resolution);
@@ -467,7 +460,6 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
     const int t = lane + 32 * p;
     if (t < LD) gMu[t] = sMu[t];
   }
-  if (WPC == 1 && pf != 0 && pf_tail) prefetch_successor<NLM>(a, b, batch, pf, lane, m);
   __syncwarp();  // every lane is done with this filter's shared memory before the next TMA lands
   b = __shfl_sync(kFull, b_next, 0);
   }  // filter loop
@@ -519,11 +511,7 @@ static cudaError_t launch_regw_wpc(const BatchStepArgs& a, int64_t batch, unsign
     const char* v = getenv("EKF_REGW_PREFETCH");
     return v ? atoi(v) : 0;
   }();
-  static const int pf_tail = [] {
-    const char* v = getenv("EKF_REGW_PREFETCH_TAIL");
-    return v ? atoi(v) : 0;
-  }();
-  kernel<<<grid, 32 * WPC, smem, st>>>(a, batch, pf, pf_tail);
+  kernel<<<grid, 32 * WPC, smem, st>>>(a, batch, pf);
   return cudaGetLastError();
 }
 

@@ -1,5 +1,6 @@
 # A/B of the warp-per-filter kernel's opt-in L2 prefetch on config B. EKF_REGW_PREFETCH: distance in CTAs (< 0: inputs +
 # mu only, no P); EKF_REGW_PREFETCH_TAIL=1: issued after the filter's last store instead of at the head of its chain.
+# (EKF_REGW_PREFETCH_TAIL needs the tail-placement build of commit 8a705c7; the shipped kernel ignores it.)
 # AB_LIST: space-separated "distance:tail" pairs
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/r_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r_pytest.log
