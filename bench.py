@@ -1,13 +1,20 @@
 #!/usr/bin/env python
 """bench.py — EKF filter-steps/s on the batched Monte Carlo configuration of BASELINE.json
-(configs[1]: 65,536 independent filters x 20 landmarks, 43-dim state, M = 3 updates per step, 1 B200),
-plus ms/update of the 4096-landmark large-map filter as a secondary figure on the same JSON line.
+(configs[1]: 65,536 independent filters x 20 landmarks, 43-dim state, M = 3 updates per step, 1 B200), with the
+other configurations of BASELINE.json as secondary objects on the same JSON line:
+
+    N = 1 : large_map (configs[2], ms/update @4096 lm), small_filters (configs[3] on one GPU), sustained (>= 2 s of
+            back-to-back launches of the dispatched kernels), bag_ensemble (the decoded-bag-shaped Monte Carlo),
+            config1_replay (configs[0]: the scalar drop-in replay beside the reference's CPU replay), cpu_baseline
+    N > 1 : small_filters (configs[3], 1,048,576 filters split over the ranks: STRONG scaling, with its own e2e) and
+            large_map_sharded (configs[4]: 32,768 landmarks row-block sharded, peer-memory row exchange, with the
+            tracked-rows parity leg; and 4096 landmarks with the sharded == unsharded bitwise flag)
 
     python bench.py [--gpus N] [--steps K] [--warmup W]          # own arm (CUDA core through the C-ABI)
-    python bench.py --impl reference [...]                        # the reference's CPU path (oracle port)
+    python bench.py --impl reference [...]                        # the reference's own CPU path (oracle/_ref)
 
-A "step" is one fused filter-step of every filter on the GPU (one kernel launch). For N > 1 every rank runs
-its own 65,536 filters (filters never interact: weak scaling, no data-path collective).
+A "step" of the headline is one fused filter-step of every filter on the GPU (one kernel launch). For N > 1 every
+rank runs its own 65,536 filters (filters never interact: weak scaling, no data-path collective).
 """
 import os
 import sys
@@ -27,56 +34,62 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-BATCH, NLM, M = 65536, 20, 3
-N_STATE = 3 + 2 * NLM
-# algorithmic bytes per filter-step: one read + one write of mu and P, the per-filter
-# odometry, M x (range, bearing, slot) and the two noise parameters
-BYTES_PER_FILTER_STEP = 16 * (N_STATE * N_STATE + N_STATE) + 8 * (2 + 2 * M) + 4 * M + 16     # 30 364
+UNIT = "filter-steps/s"
 LM_LANDMARKS = 4096
-LM_N = 3 + 2 * LM_LANDMARKS
-LM_BYTES_PER_UPDATE = 16 * LM_N * LM_N + 96 * LM_N                                            # 1 075 315 120
-METRIC, UNIT = "EKF filter-steps/s (B=65536, 20 lm)", "filter-steps/s"
-WORKLOAD = "batched Monte Carlo replay: 65536 filters x 20 landmarks (n=43), predict + 3 updates per step"
+XL_LANDMARKS = 32768
 
 
-def set_workload(name, world):
-    """--workload M: BASELINE.json configs[3], 1,048,576 filters x 8 landmarks (n=19, 2 updates per step), the
-    filters split contiguously across the ranks (strong scaling). Default B is the contract line's workload."""
-    global BATCH, NLM, M, N_STATE, BYTES_PER_FILTER_STEP, METRIC, WORKLOAD, SCALING
-    if name == "M":
-        total = 1 << 20
-        BATCH, NLM, M = total // world, 8, 2
-        N_STATE = 3 + 2 * NLM
-        BYTES_PER_FILTER_STEP = 16 * (N_STATE * N_STATE + N_STATE) + 8 * (2 + 2 * M) + 4 * M + 16   # 6 152
-        METRIC = "EKF filter-steps/s (B=1048576, 8 lm)"
-        WORKLOAD = (f"batched Monte Carlo replay: 1048576 filters x 8 landmarks (n=19) split over {world} GPU(s), "
-                    "predict + 2 updates per step")
-        SCALING = "strong"
+def bytes_per_filter_step(n, m):
+    """Algorithmic bytes of one filter-step: one read + one write of mu and P, the per-filter
+    odometry, m x (range, bearing, slot) and the two noise parameters."""
+    return 16 * (n * n + n) + 8 * (2 + 2 * m) + 4 * m + 16
 
 
-SCALING = "weak"
+def lm_bytes_per_update(n, rows=None):
+    """Algorithmic bytes of one large-map update: read + write of the (local rows of) P, the 5
+    gathered rows + 5 gathered columns, read + write of mu."""
+    rows = n if rows is None else rows
+    return 16 * rows * n + 96 * n
 
 
-def kernel_label():
-    """(ncu_traffic key, description) of the kernel the C-ABI dispatches this workload to (ekf_capi.cu: capacities
-    <= 8 landmarks -> group kernel, else the W-in-registers warp kernel), unless EKF_BATCH_KERNEL forces a variant."""
-    forced = os.environ.get("EKF_BATCH_KERNEL", "")
-    if forced:
-        return f"{forced}<{NLM},{M}>", f"EKF_BATCH_KERNEL={forced} variant <{NLM},{M}>"
-    if NLM <= 8:
-        return (f"batch_step_group_kernel<{NLM},{M},8>",
-                f"batch_step_group_kernel<{NLM},{M},8> (8 lanes per filter, four filters per warp)")
-    return (f"batch_step_regw_kernel<{NLM},{M}>",
-            f"batch_step_regw_kernel<{NLM},{M},1> (one warp per filter, W in registers)")
+class Workload:
+    """B: BASELINE.json configs[1] (the contract line), weak scaling; M: configs[3], split over the ranks."""
 
+    def __init__(self, name, world):
+        self.name = name
+        if name == "M":
+            self.total, self.nlm, self.m, self.scaling = 1 << 20, 8, 2, "strong"
+            self.batch = self.total // world
+            self.metric = "EKF filter-steps/s (B=1048576, 8 lm)"
+            self.text = (f"batched Monte Carlo replay: 1048576 filters x 8 landmarks (n=19) split over {world} GPU(s), "
+                         "predict + 2 updates per step")
+        else:
+            self.batch, self.nlm, self.m, self.scaling = 65536, 20, 3, "weak"
+            self.total = self.batch * world
+            self.metric = "EKF filter-steps/s (B=65536, 20 lm)"
+            self.text = "batched Monte Carlo replay: 65536 filters x 20 landmarks (n=43), predict + 3 updates per step"
+        self.n = 3 + 2 * self.nlm
+        self.bytes = bytes_per_filter_step(self.n, self.m)
 
-def make_config(joseph=False):
-    """The `config` object both arms print (same workload, same keys)."""
-    return {"workload": WORKLOAD, "filters_per_gpu": BATCH, "landmarks": NLM, "updates_per_step": M,
-            "cov_form": "joseph" if joseph else "plain (reference, replay_no_ros.py:480)",
-            "l2": f"inputs larger than L2 ({BATCH * N_STATE * ((N_STATE + 3) & ~3) * 8 / 1e9:.2f} GB of covariance per "
-                  "GPU streamed every step)",
-            "sharding": "filters split across ranks, no data-path collective"}
+    def kernel(self):
+        """(ncu_traffic key, description) of the kernel the C-ABI dispatches this workload to."""
+        forced = os.environ.get("EKF_BATCH_KERNEL", "")
+        if forced:
+            return f"{forced}<{self.nlm},{self.m}>", f"EKF_BATCH_KERNEL={forced} variant <{self.nlm},{self.m}>"
+        if self.nlm <= 8:
+            return (f"batch_step_group_kernel<{self.nlm},{self.m},8>",
+                    f"batch_step_group_kernel<{self.nlm},{self.m},8> (8 lanes per filter, four filters per warp)")
+        return (f"batch_step_regw_kernel<{self.nlm},{self.m}>",
+                f"batch_step_regw_kernel<{self.nlm},{self.m},1> (one warp per filter, W in registers)")
+
+    def config(self, joseph=False):
+        ld = (self.n + 3) & ~3
+        return {"workload": self.text, "filters_per_gpu": self.batch, "landmarks": self.nlm,
+                "updates_per_step": self.m,
+                "cov_form": "joseph" if joseph else "plain (reference, replay_no_ros.py:480)",
+                "l2": f"inputs larger than L2 ({self.batch * self.n * ld * 8 / 1e9:.2f} GB of covariance per "
+                      "GPU streamed every step)",
+                "sharding": "filters split across ranks, no data-path collective"}
 
 
 def measured_peak_gbs():
@@ -88,12 +101,22 @@ def measured_peak_gbs():
 
 
 def ncu_traffic(kernel_key):
-    """dram bytes per launch of the dominant kernel from the committed ncu summary (profiles/), or None."""
+    """dram bytes per launch of the dominant kernel from the committed ncu summary (profiles/ncu_traffic.json: a
+    STATIC figure captured once per kernel change under ncu --set full, never measured inside this run)."""
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
             return json.load(fh).get(kernel_key)
     except Exception:
         return None
+
+
+def roofline_block(bytes_per_launch, ms, **extra):
+    peak, which = measured_peak_gbs()
+    ach = bytes_per_launch / (ms * 1e-3) / 1e9
+    out = {"bound": "hbm", "achieved": ach, "peak": peak, "peak_source": which, "unit": "GB/s", "frac": ach / peak,
+           "frac_of_8TBs": ach / 8000.0}
+    out.update(extra)
+    return out
 
 
 class ClockSampler:
@@ -105,7 +128,7 @@ class ClockSampler:
 
     def __init__(self, index):
         self.index, self.rows, self.proc, self.thread, self.stop_flag = index, [], None, None, False
-        self.sm, self.mx, self.reasons, self.source = [], 0.0, set(), None
+        self.sm, self.mx, self.reasons, self.source, self.power = [], 0.0, set(), None, []
 
     def _nvml_loop(self, nv, h):
         while not self.stop_flag:
@@ -115,6 +138,7 @@ class ClockSampler:
                 for name, bit in self.BITS.items():
                     if mask & bit:
                         self.reasons.add(name)
+                self.power.append(nv.nvmlDeviceGetPowerUsage(h) / 1000.0)
             except Exception:
                 pass
             time.sleep(0.002)
@@ -130,7 +154,7 @@ class ClockSampler:
             self.source = "nvml"
             self.thread = threading.Thread(target=self._nvml_loop, args=(nv, h), daemon=True)
             self.thread.start()
-            return
+            return self
         except Exception:
             self.source = None
         try:
@@ -141,6 +165,7 @@ class ClockSampler:
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
+        return self
 
     def _read(self):
         for line in self.proc.stdout:
@@ -166,74 +191,130 @@ class ClockSampler:
             for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm), "source": self.source}
+        out = {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+               "reasons": sorted(reasons), "samples": len(sm), "source": self.source}
+        if sm:
+            out["sm_mhz_min"] = float(np.min(sm))
+        if self.power:
+            out["power_w_max"] = float(np.max(self.power))
+        return out
 
 
 # ---------------------------------------------------------------------------------------------------------
-# CPU arm: the reference's dense numpy cost profile (oracle port, form="dense"), one filter at a time,
-# parallel over filters on the host cores. This is the ONLY place bench.py executes oracle/ code, and only
-# as the measured baseline — never on the product path.
+# CPU arm. kind "reference": the reference's OWN EKF_pose_estimation (src/replay_no_ros.py:269-482, loaded unmodified
+# from oracle/_ref — bytecode oracle/build_ref.py compiled from /root/reference/src — or from /root/reference itself
+# where that exists), fed detections that reproduce the workload's (slot, range, bearing) blocks. kind "port": the
+# oracle's dense numpy restatement of the same function (same O(n^3) cost profile), used only when the reference
+# cannot be loaded, and reported beside the reference figure at N = 1. One process per host core,
+# OPENBLAS_NUM_THREADS=1. This is the ONLY place bench.py times oracle/ code, and only as the baseline.
 # ---------------------------------------------------------------------------------------------------------
 def _cpu_worker(args):
-    seed, n_filters, n_steps, form = args
+    seed, n_filters, n_steps, kind, nlm, m = args
     from oracle import ekf_oracle as eo
     from slam_duckietown_b200 import workloads as wl
-    w = wl.make_batched(n_filters, NLM, M, steps=-(-NLM // M) + n_steps, perturb_seed=seed)
+    n = 3 + 2 * nlm
+    w = wl.make_batched(n_filters, nlm, m, steps=-(-nlm // m) + n_steps, perturb_seed=seed)
+    ref = None
+    if kind == "reference":
+        from oracle import ref_loader
+        ref = ref_loader.load_replay_module()
+
+    def dets_of(t, b):
+        out = []
+        for k in range(m):
+            s = int(w.slot[t, b, k])
+            if s < 0:
+                continue
+            r, q = w.rng[t, b, k], w.brg[t, b, k]
+            out.append(eo.Detection(100 + s, np.array([[-(r * np.sin(q))], [0.0], [r * np.cos(q)]]), 0.0))
+        return out
     states = []
-    for b in range(n_filters):          # untimed: initialise all landmarks (the 7 augmenting steps)
-        mean = np.zeros(N_STATE)
-        cov = np.zeros((N_STATE, N_STATE))
-        cov[:3, :3] = np.eye(3) * 0.1
-        nk = 0
+    for b in range(n_filters):          # untimed: initialise all landmarks (the augmenting steps)
         fl = eo.Flags(motion_var=float(w.motion_var[b]), meas_var=float(w.meas_var[b]))
-        for t in range(w.warm_steps):
-            obs = [(int(s), float(r), float(q)) for s, r, q in zip(w.slot[t, b], w.rng[t, b], w.brg[t, b]) if s >= 0]
-            mean, cov, nk = eo.step_from_observations(mean, cov, w.ang[t, b], w.lin[t, b], obs, fl, nk)
-        states.append((mean, cov, nk, fl))
+        if ref is not None:
+            ref.MOTION_MODEL_VARIANCE, ref.MEASUREMENT_MODEL_VARIANCE = fl.motion_var, fl.meas_var
+            mean, cov, ti = np.zeros(3), np.eye(3) * 0.1, {}
+            for t in range(w.warm_steps):
+                mean, cov, _ = ref.EKF_pose_estimation(float(w.ang[t, b]), float(w.lin[t, b]), mean, cov, 0.7,
+                                                       [("0", dets_of(t, b))], ti)
+            states.append((mean, cov, ti, fl))
+        else:
+            mean = np.zeros(n)
+            cov = np.zeros((n, n))
+            cov[:3, :3] = np.eye(3) * 0.1
+            nk = 0
+            for t in range(w.warm_steps):
+                obs = [(int(s), float(r), float(q)) for s, r, q in zip(w.slot[t, b], w.rng[t, b], w.brg[t, b]) if s >= 0]
+                mean, cov, nk = eo.step_from_observations(mean, cov, w.ang[t, b], w.lin[t, b], obs, fl, nk)
+            states.append((mean, cov, nk, fl))
+    steady = range(w.warm_steps, w.warm_steps + n_steps)
+    if ref is not None:                 # detections are inputs: built outside the timed region
+        windows = [[[("0", dets_of(t, b))] for t in steady] for b in range(n_filters)]
     t0 = time.perf_counter()
-    for b in range(n_filters):          # timed: steady-state steps, predict + M updates each
-        mean, cov, nk, fl = states[b]
-        for t in range(w.warm_steps, w.warm_steps + n_steps):
-            obs = [(int(s), float(r), float(q)) for s, r, q in zip(w.slot[t, b], w.rng[t, b], w.brg[t, b])]
-            mean, cov, nk = eo.step_from_observations(mean, cov, w.ang[t, b], w.lin[t, b], obs, fl, nk, form=form)
-    return time.perf_counter() - t0, n_filters * n_steps
+    for b in range(n_filters):          # timed: steady-state steps, predict + m updates each
+        mean, cov, aux, fl = states[b]
+        if ref is not None:
+            ref.MOTION_MODEL_VARIANCE, ref.MEASUREMENT_MODEL_VARIANCE = fl.motion_var, fl.meas_var
+            for i, t in enumerate(steady):
+                mean, cov, _ = ref.EKF_pose_estimation(float(w.ang[t, b]), float(w.lin[t, b]), mean, cov, 0.7,
+                                                       windows[b][i], aux)
+        else:
+            for t in steady:
+                obs = [(int(s), float(r), float(q)) for s, r, q in zip(w.slot[t, b], w.rng[t, b], w.brg[t, b])]
+                mean, cov, aux = eo.step_from_observations(mean, cov, w.ang[t, b], w.lin[t, b], obs, fl, aux, form="dense")
+    dt = time.perf_counter() - t0
+    assert len(mean) == n and np.all(np.isfinite(mean))
+    return dt, n_filters * n_steps
 
 
-def cpu_filter_steps_per_s(filters_per_core=48, steps=8, form="dense", cores=None):
-    """Whole-host throughput of the reference's CPU path on a bounded sample of the workload."""
+def cpu_kind():
+    from oracle import ref_loader
+    return "reference" if ref_loader.reference_available() else "port"
+
+
+def cpu_filter_steps_per_s(wk, filters_per_core, steps, kind, cores=None):
+    """Whole-host throughput of the CPU path on a bounded sample of the workload."""
     import multiprocessing as mp
     cores = cores or os.cpu_count() or 1
     ctx = mp.get_context("fork")
     with ctx.Pool(cores) as pool:
         t0 = time.perf_counter()
-        res = pool.map(_cpu_worker, [(100 + i, filters_per_core, steps, form) for i in range(cores)])
+        res = pool.map(_cpu_worker, [(100 + i, filters_per_core, steps, kind, wk.nlm, wk.m) for i in range(cores)])
         wall = time.perf_counter() - t0
     work = sum(r[1] for r in res)
     busy = max(r[0] for r in res)
     return work / busy, cores, work, wall
 
 
-def run_reference_arm(args, rank, world):
+def cpu_sample_text(wk, kind, work, cores, per_core, steps, wall=None):
+    what = ("the reference's own EKF_pose_estimation (src/replay_no_ros.py:269-482, unmodified, loaded from "
+            "oracle/_ref)" if kind == "reference" else
+            "the dense numpy restatement of replay_no_ros.py:269-482 (oracle port)")
+    tail = f", {wall:.1f} s wall" if wall is not None else ""
+    return (f"{work} filter-steps ({cores} processes x {per_core} filters x {steps} steady-state steps) of the "
+            f"{wk.text}, through {what}, OPENBLAS_NUM_THREADS=1{tail}")
+
+
+def run_reference_arm(args, wk, rank, world):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
+    kind = cpu_kind()
+    per_core, steps = 16, 40
     per_step = []
     total = args.warmup + args.steps
     for i in range(total):
-        rate, cores, work, _ = cpu_filter_steps_per_s(filters_per_core=32, steps=60, form="dense", cores=cores)
+        rate, cores, work, _ = cpu_filter_steps_per_s(wk, per_core, steps, kind, cores=cores)
         if i >= args.warmup:
             per_step.append((rate, work))
     value = float(np.mean([r for r, _ in per_step]))
-    sample = (f"{per_step[0][1]} filter-steps per bench step (32 filters x 60 steady-state steps per core) of the "
-              f"{WORKLOAD}; dense numpy restatement of replay_no_ros.py:269-482 (oracle port; the Python reference "
-              "itself cannot travel to the GPU box), one process per core, OPENBLAS_NUM_THREADS=1")
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+    sample = cpu_sample_text(wk, kind, per_step[0][1], cores, per_core, steps) + " per bench step"
+    line = {"impl": "reference", "metric": wk.metric, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * per_step[0][1] / value, "higher_is_better": True, "scaling": "weak",
+            "ms_per_step": 1e3 * per_step[0][1] / value, "higher_is_better": True, "scaling": wk.scaling,
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": make_config(args.joseph),
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "config": wk.config(args.joseph),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -273,10 +354,134 @@ def _max_over_ranks(x, world):
     return float(t.item())
 
 
+def _min_over_ranks(x, world):
+    return -_max_over_ranks(-x, world)
+
+
+class BatchedRun:
+    """One batched workload resident on this rank's GPU, warmed up (every landmark initialised)."""
+
+    def __init__(self, wk, local, rank, joseph=False, distinct=24):
+        import torch
+        from slam_duckietown_b200 import ekf_bindings as eb, workloads as wl
+        self.wk, self.torch, self.distinct = wk, torch, distinct
+        w = wl.make_batched(wk.batch, wk.nlm, wk.m, steps=-(-wk.nlm // wk.m) + distinct, perturb_seed=2 + rank)
+        self.f = f = eb.BatchedEKF(wk.batch, wk.nlm, device=local)
+        f.set_noise(w.motion_var, w.meas_var)
+        f.set_flags(joseph=joseph)
+        f.init(0.1)
+
+        def up(a):
+            return torch.from_numpy(np.ascontiguousarray(a)).to(f.dev)
+        for t in range(w.warm_steps):               # untimed: every landmark gets initialised
+            f.step(up(w.ang[t]), up(w.lin[t]), up(w.slot[t]), up(w.rng[t]), up(w.brg[t]))
+        rng_t = range(w.warm_steps, w.warm_steps + distinct)
+        self.steady = [(up(w.ang[t]), up(w.lin[t]), up(w.slot[t]), up(w.rng[t]), up(w.brg[t])) for t in rng_t]
+        self.pinned = [tuple(torch.from_numpy(np.ascontiguousarray(a[t])).pin_memory()
+                             for a in (w.ang, w.lin, w.slot, w.rng, w.brg)) for t in rng_t]
+        self.poses = [torch.empty((wk.batch, 3), dtype=torch.float64).pin_memory() for _ in range(2)]
+        assert f.fault_count() == 0 and int(f.n_known.min()) == wk.nlm
+        self.h2d = wk.batch * (8 + 8 + wk.m * (4 + 8 + 8))
+        self.d2h = wk.batch * 3 * 8
+
+    def device_resident(self, K, W, world, sampler=None):
+        """K launches, CUDA events on the launching stream; returns (total_ms max over ranks, mean kernel ms)."""
+        torch, f, d = self.torch, self.f, self.distinct
+        for i in range(W):
+            f.step(*self.steady[i % d])
+        _barrier(world)
+        if sampler:
+            sampler.start()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for i in range(K):
+            ev[i][0].record()
+            f.step(*self.steady[(W + i) % d])
+            ev[i][1].record()
+        t1.record()
+        _barrier(world)
+        total_ms = _max_over_ranks(t0.elapsed_time(t1), world)
+        return total_ms, float(np.mean([a.elapsed_time(b) for a, b in ev]))
+
+    def end_to_end(self, K, W, world):
+        """Host buffers in, pose out, through the C-ABI host entry points: (pipelined s, synchronous s)."""
+        f, d = self.f, self.distinct
+        for i in range(W):
+            f.step_host_async(*self.pinned[i % d], self.poses[i & 1])
+        f.host_sync()
+        _barrier(world)
+        t0 = time.perf_counter()
+        for i in range(K):
+            f.step_host_async(*self.pinned[(W + i) % d], self.poses[i & 1])
+        f.host_sync()
+        _barrier(world)
+        e2e_s = _max_over_ranks(time.perf_counter() - t0, world)
+        t0 = time.perf_counter()
+        for i in range(K):
+            f.step_host(*self.pinned[(W + i) % d], self.poses[0])
+        _barrier(world)
+        return e2e_s, _max_over_ranks(time.perf_counter() - t0, world)
+
+    def sustained(self, seconds, local, est_ms):
+        """>= `seconds` of back-to-back launches of the dispatched kernel: ms per launch over chunks of 100 launches
+        (CUDA events), SM clock / power / throttle reasons sampled alongside (VERDICT r1 weak #9)."""
+        torch, f, d = self.torch, self.f, self.distinct
+        chunk = 100
+        n_chunks = max(int(seconds * 1e3 / (est_ms * chunk)) + 1, 4)
+        torch.cuda.synchronize()
+        clk = ClockSampler(local).start()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(n_chunks + 1)]
+        ev[0].record()
+        for c in range(n_chunks):
+            for i in range(chunk):
+                f.step(*self.steady[(c * chunk + i) % d])
+            ev[c + 1].record()
+        torch.cuda.synchronize()
+        c_out = clk.stop()
+        ms = np.array([ev[c].elapsed_time(ev[c + 1]) / chunk for c in range(n_chunks)])
+        med = float(np.median(ms))
+        out = {"seconds": float(ms.sum() * chunk / 1e3), "launches": n_chunks * chunk, "ms_per_step_median": med,
+               "ms_per_step_first_chunk": float(ms[0]), "ms_per_step_last_chunk": float(ms[-1]),
+               "value": self.wk.batch / (med * 1e-3), "unit": UNIT, "clocks": c_out,
+               "roofline": roofline_block(self.wk.bytes * self.wk.batch, med,
+                                          bytes_per_filter_step=self.wk.bytes, kernel=self.wk.kernel()[1])}
+        return out
+
+    def healthy(self):
+        return self.f.fault_count() == 0 and self.f.nonfinite_count() == 0
+
+    def close(self):
+        self.f.close()
+        self.steady = self.pinned = self.poses = None
+        self.torch.cuda.empty_cache()
+
+
+def batched_object(wk, run, K, W, world, with_e2e=True, sustained_s=0.0, local=0):
+    """A secondary object for one batched workload: device-resident value, roofline, optional e2e / sustained."""
+    total_ms, kern_ms = run.device_resident(K, W, world)
+    key, label = wk.kernel()
+    out = {"metric": wk.metric, "value": wk.total * K / (total_ms * 1e-3), "unit": UNIT, "scaling": wk.scaling,
+           "filters_per_gpu": wk.batch, "ms_per_step": total_ms / K, "steps": K,
+           "roofline": roofline_block(wk.bytes * wk.batch, kern_ms, bytes_per_filter_step=wk.bytes, kernel=label,
+                                      kernel_ms=kern_ms, traffic=ncu_traffic(key),
+                                      traffic_source="profiles/ncu_traffic.json (static, one ncu --set full launch)",
+                                      note="per GPU: this rank's filters / this rank's mean launch time")}
+    if with_e2e:
+        e2e_s, sync_s = run.end_to_end(K, W, world)
+        out["e2e"] = {"value": wk.total * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": run.h2d,
+                      "d2h_bytes_per_step": run.d2h, "unpipelined_value": wk.total * K / sync_s}
+    if sustained_s > 0:
+        out["sustained"] = run.sustained(sustained_s, local, kern_ms)
+    out["finite_and_faultless"] = bool(_min_over_ranks(1.0 if run.healthy() else 0.0, world) == 1.0)
+    return out
+
+
 def bench_large_map(updates=60, warm=6):
     """Secondary figure: ms per range-bearing update of the 4096-landmark filter (P = 537 MB > L2)."""
     import torch
     from slam_duckietown_b200 import ekf_bindings as eb, workloads as wl
+    n = 3 + 2 * LM_LANDMARKS
     w = wl.make_large_map(LM_LANDMARKS, updates=updates + warm)
     g = eb.LargeMapEKF(LM_LANDMARKS)
     g.set_noise(0.1, 0.7)
@@ -320,172 +525,271 @@ def bench_large_map(updates=60, warm=6):
         e1.record()
     torch.cuda.synchronize()
     msp = np.array([e0.elapsed_time(e1) for e0, e1 in evp])
-    finite = bool(torch.isfinite(g.mu).all())
+    finite = bool(torch.isfinite(g.mu).all()) and bool(torch.isfinite(g.P).all())
     g.close()
-    peak, which = measured_peak_gbs()
-    ach = LM_BYTES_PER_UPDATE / (float(np.mean(ms)) * 1e-3) / 1e9
+    b1 = lm_bytes_per_update(n)
+    b3 = 16 * n * n + 3 * 96 * n
     return {"metric": "ms/update @4096 lm", "ms_per_update": float(np.mean(ms)), "ms_min": float(ms.min()),
             "updates": len(ms), "finite": finite, "predict_us": float(np.median(msp)) * 1e3,
-            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "peak_source": which, "unit": "GB/s",
-                         "frac": ach / peak, "frac_of_8TBs": ach / 8000.0, "bytes_per_update": LM_BYTES_PER_UPDATE,
-                         "traffic": ncu_traffic("lm_rank_update_kernel"),
-                         "note": "gather + streaming kernels of one update timed together"},
+            "roofline": roofline_block(b1, float(np.mean(ms)), bytes_per_update=b1,
+                                       traffic=ncu_traffic("lm_rank_update_kernel"),
+                                       note="gather + streaming kernels of one update timed together"),
             "fused_step": {"updates_per_step": 3, "ms_per_step": float(np.mean(ms3)),
                            "ms_per_update_equiv": float(np.mean(ms3)) / 3.0, "steps": len(ms3),
-                           "hbm_gbs": (LM_BYTES_PER_UPDATE - 96 * (3 + 2 * LM_LANDMARKS)
-                                       + 3 * 96 * (3 + 2 * LM_LANDMARKS)) / (float(np.mean(ms3)) * 1e-3) / 1e9,
+                           "hbm_gbs": b3 / (float(np.mean(ms3)) * 1e-3) / 1e9,
                            "note": "ekf_lm_update_multi: 3 sequential updates with one read + write of P "
                                    "(16 n^2 + 3 x 96 n bytes per step), bitwise equal to 3 ekf_lm_update calls"}}
 
 
-def bench_config_m(device=0, steps=20, warmup=3):
-    """Secondary figure on the contract line: BASELINE.json configs[3] on ONE GPU — 1,048,576 filters x 8 landmarks
-    (n = 19), predict + 2 updates per step, device-resident, CUDA events around every launch (`--workload M` is the
-    full bench of this configuration, with its end-to-end figure and its split over N GPUs)."""
+def _seed_shard(f, w, dev, chunk_rows=4096):
+    """P0 = A A^T / 64 + 0.1 I, this rank's rows only, built in row chunks (never 34 GB of temporaries)."""
     import torch
+    n = f.n
+    lo, hi = f.ranges[f.rank]
+    a = torch.from_numpy(w.factor).to(dev)
+    at = a.T.contiguous()
+    for r0 in range(lo, hi, chunk_rows):
+        r1 = min(r0 + chunk_rows, hi)
+        blk = a[r0:r1] @ at
+        blk /= 64.0
+        blk[torch.arange(r1 - r0, device=dev), torch.arange(r0, r1, device=dev)] += 0.1
+        f.local.P[r0 - lo:r1 - lo, :n] = blk
+        del blk
+    f.local.mu[:n] = torch.from_numpy(w.mu0).to(dev)
+    return a
+
+
+def bench_large_map_sharded(L, rank, world, local, updates, warm, fused=3, bitwise=False, tracked=False):
+    """One large-map filter row-block sharded over the ranks (BASELINE.json configs[4] at L = 32768), peer-memory row
+    exchange (ekf_lm_p2p_*). ms/update and ms per fused 3-update step (CUDA events, max over ranks), the per-GPU HBM
+    roofline of the largest shard, and parity: `bitwise` — every shard == the same rows of an unsharded filter on the
+    same GPU (n <= 8195); `tracked` — 64 sampled rows per shard + the gathered rows vs the rank-2 restatement of the
+    reference carried on those rows (oracle/sampled_rows.py: the CHECKER, outside every timed region)."""
+    import torch
+    import torch.distributed as dist
     from slam_duckietown_b200 import ekf_bindings as eb, workloads as wl
-    batch, nlm, m = 1 << 20, 8, 2
-    n = 3 + 2 * nlm
-    bytes_per = 16 * (n * n + n) + 8 * (2 + 2 * m) + 4 * m + 16                                  # 6 152
-    distinct = 8
-    w = wl.make_batched(batch, nlm, m, steps=-(-nlm // m) + distinct, perturb_seed=2)
-    f = eb.BatchedEKF(batch, nlm, device=device)
-    f.set_noise(w.motion_var, w.meas_var)
-    f.init(0.1)
+    from slam_duckietown_b200.sharded import ShardedLargeMapEKF, owner_of_slot
+    dev = torch.device("cuda", local)
+    n = 3 + 2 * L
+    w = wl.make_large_map(L, updates=updates + warm)                  # same seeds on every rank
+    f = ShardedLargeMapEKF(L, rank, world, device=local, exchange="p2p")
+    f.set_noise(0.1, 0.7)
+    lo, hi = f.ranges[rank]
+    a = _seed_shard(f, w, dev)
+    ref = None
+    if bitwise:
+        ref = eb.LargeMapEKF(L, device=local)
+        ref.set_noise(0.1, 0.7)
+        full = a @ a.T
+        full /= 64.0
+        full.diagonal().add_(0.1)
+        ref.P[:, :n] = full
+        ref.mu[:n] = torch.from_numpy(w.mu0).to(dev)
+        del full
+    del a
+    ups = [o for o in w.ops if o[0] == "update"]
+    out = {}
 
-    def up(a):
-        return torch.from_numpy(np.ascontiguousarray(a)).to(f.dev)
-    for t in range(w.warm_steps):
-        f.step(up(w.ang[t]), up(w.lin[t]), up(w.slot[t]), up(w.rng[t]), up(w.brg[t]))
-    steady = [(up(w.ang[t]), up(w.lin[t]), up(w.slot[t]), up(w.rng[t]), up(w.brg[t]))
-              for t in range(w.warm_steps, w.warm_steps + distinct)]
-    for i in range(warmup):
-        f.step(*steady[i % distinct])
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
-    for i in range(steps):
-        ev[i][0].record()
-        f.step(*steady[(warmup + i) % distinct])
-        ev[i][1].record()
-    torch.cuda.synchronize()
-    ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
-    ok = bool(torch.isfinite(f.mu).all()) and f.fault_count() == 0
-    peak, which = measured_peak_gbs()
-    ach = bytes_per * batch / (ms * 1e-3) / 1e9
-    key = f"batch_step_group_kernel<{nlm},{m},8>"
-    return {"metric": "EKF filter-steps/s (B=1048576, 8 lm)", "value": batch / (ms * 1e-3), "unit": UNIT,
-            "ms_per_step": ms, "steps": steps, "finite_and_faultless": ok,
-            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "peak_source": which, "unit": "GB/s",
-                         "frac": ach / peak, "frac_of_8TBs": ach / 8000.0, "bytes_per_filter_step": bytes_per,
-                         "kernel": key + " (8 lanes per filter, four filters per warp)", "traffic": ncu_traffic(key)}}
+    # ---- parity leg (iii) first, on the pristine state: 10 updates, tracked rows vs the restatement ----
+    if tracked:
+        from oracle import sampled_rows as sr
+        par = ups[:10]
+        common = sr.required_rows([o[1] for o in par])
+        rs = np.random.default_rng(1000 + rank)
+        mine = [int(r) for r in rs.choice(np.arange(lo, hi), min(64, hi - lo), replace=False)]
+        buf = torch.zeros(f.ld, dtype=torch.float64, device=dev)
+        common_rows0 = np.zeros((len(common), n))
+        for i, r in enumerate(common):                                 # the owners' rows to everyone (set-up plumbing)
+            owner = 0 if r < 3 else owner_of_slot((r - 3) // 2, L, world)
+            if owner == rank:
+                buf.copy_(f.local.P[r - lo])
+            if world > 1:
+                dist.broadcast(buf, src=owner)
+            common_rows0[i] = buf[:n].cpu().numpy()
+        rows = common + [r for r in mine if r not in common]
+        local_rows = [r for r in rows if lo <= r < hi]
+        p_rows0 = np.zeros((len(rows), n))
+        p_rows0[:len(common)] = common_rows0
+        for i, r in enumerate(rows):
+            if i >= len(common):
+                p_rows0[i] = f.local.P[r - lo, :n].cpu().numpy()
+        tr = sr.TrackedRows(w.mu0, rows, p_rows0)
+        for o in par:
+            f.update(o[1], o[2], o[3])
+            tr.update(o[1], o[2], o[3], 0.7)
+        torch.cuda.synchronize()
+        got_p = np.stack([f.local.P[r - lo, :n].cpu().numpy() for r in local_rows])
+        got_mu = f.local.mu[:n].cpu().numpy()
+        # covariance scale of the columns: the diagonal of P lives on its owners -> gather it
+        diag_local = torch.zeros(n, dtype=torch.float64, device=dev)
+        diag_local[lo:hi] = f.local.P[torch.arange(hi - lo, device=dev), torch.arange(lo, hi, device=dev)]
+        if world > 1:
+            dist.all_reduce(diag_local, op=dist.ReduceOp.SUM)
+        e = tr.errors(got_mu[local_rows], got_p, diag_local.cpu().numpy(), subset=local_rows)
+        worst = _max_over_ranks(max(e), world)
+        out["tracked_rows_parity"] = {
+            "worst": worst, "tolerance": 1e-9, "ok": bool(worst <= 1e-9), "updates": len(par),
+            "rows_per_shard": len(mine), "gathered_rows": len(common),
+            "what": "max over ranks of (mu max-norm, P max-norm, P covariance-scaled) between the device rows and the "
+                    "rank-2 restatement of replay_no_ros.py:436-480 carried on those rows (oracle/sampled_rows.py)"}
+        if ref:
+            for o in par:
+                ref.update(o[1], o[2], o[3])
+        ups = ups[10:]
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for o in ups[:warm]:
+        f.update(o[1], o[2], o[3])
+        if ref:
+            ref.update(o[1], o[2], o[3])
+    sync()
+    timed = ups[warm:]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for o in timed:
+        f.update(o[1], o[2], o[3])
+    e1.record()
+    sync()
+    ms = _max_over_ranks(e0.elapsed_time(e1) / len(timed), world)
+    if ref:
+        for o in timed:
+            ref.update(o[1], o[2], o[3])
+    fms = None
+    if fused >= 2:
+        groups = [timed[i:i + fused] for i in range(0, len(timed) - fused + 1, fused)]
+        for g3 in groups[:2]:
+            f.update_multi([o[1] for o in g3], [o[2] for o in g3], [o[3] for o in g3])
+        sync()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for g3 in groups[2:]:
+            f.update_multi([o[1] for o in g3], [o[2] for o in g3], [o[3] for o in g3])
+        f1.record()
+        sync()
+        fms = _max_over_ranks(f0.elapsed_time(f1) / max(len(groups) - 2, 1), world)
+        if ref:
+            for g3 in groups:
+                for o in g3:
+                    ref.update(o[1], o[2], o[3])
+    same = None
+    if ref:
+        torch.cuda.synchronize()
+        ok = bool(torch.equal(f.local.P, ref.P[lo:hi])) and bool(torch.equal(f.local.mu[lo:hi], ref.mu[lo:hi]))
+        ok = ok and bool(torch.equal(f.local.mu[:3], ref.mu[:3]))
+        same = bool(_min_over_ranks(1.0 if ok else 0.0, world) == 1.0)
+        ref.close()
+    finite = bool(torch.isfinite(f.local.mu[:n]).all()) and bool(torch.isfinite(f.local.P).all())
+    finite = bool(_min_over_ranks(1.0 if finite else 0.0, world) == 1.0)
+    p2p_err = int(_max_over_ranks(float(f.local.p2p_error()), world))
+    rows_max = max(h - l for l, h in f.ranges)
+    per_gpu = lm_bytes_per_update(n, rows_max)
+    out.update({
+        "metric": f"ms/update @{L} lm", "landmarks": L, "n": n, "p_gb": 8 * n * n / 1e9, "n_gpus": world,
+        "ms_per_update": ms, "updates": len(timed), "scaling": "strong",
+        "exchange": "owners push rows {0,1,2} / {j,j+1} (+ mu entries) into every rank's buffer over NVLink peer "
+                    "memory (cudaIpc), consumers wait on flags in their own memory; no collective, 40 n bytes",
+        "p2p_error": p2p_err, "finite": finite, "sharded_equals_unsharded_bitwise": same,
+        "roofline": roofline_block(per_gpu, ms, bytes_per_update_per_gpu=per_gpu,
+                                   bytes_per_update_total=lm_bytes_per_update(n),
+                                   note="per GPU: the largest shard's algorithmic bytes / ms per update")})
+    if fms is not None:
+        out["fused_step"] = {"updates_per_step": fused, "ms_per_step": fms, "ms_per_update_equiv": fms / fused,
+                             "hbm_gbs_per_gpu": (16 * rows_max * n + fused * 96 * n) / (fms * 1e-3) / 1e9}
+    f.close()
+    torch.cuda.empty_cache()
+    return out
 
 
-def run_own_arm(args, world):
+def run_own_arm(args, wk, world):
     import torch
-    from slam_duckietown_b200 import capi, ekf_bindings as eb, workloads as wl
+    from slam_duckietown_b200 import capi
     capi.lib()
     rank, local = _dist_setup(world)
     K, W = args.steps, max(args.warmup, 3)
-    distinct = min(K + W, 24)                   # distinct steady-state input sets, cycled
-    w = wl.make_batched(BATCH, NLM, M, steps=-(-NLM // M) + distinct, perturb_seed=2 + rank)
-    f = eb.BatchedEKF(BATCH, NLM, device=local)
-    f.set_noise(w.motion_var, w.meas_var)
-    f.set_flags(joseph=args.joseph)
-    f.init(0.1)
-    dev = f.dev
-
-    def up(a):
-        return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
-    for t in range(w.warm_steps):               # untimed: every landmark gets initialised
-        f.step(up(w.ang[t]), up(w.lin[t]), up(w.slot[t]), up(w.rng[t]), up(w.brg[t]))
-    steady = [(up(w.ang[t]), up(w.lin[t]), up(w.slot[t]), up(w.rng[t]), up(w.brg[t]))
-              for t in range(w.warm_steps, w.warm_steps + distinct)]
-    pinned = [tuple(torch.from_numpy(np.ascontiguousarray(a[t])).pin_memory()
-                    for a in (w.ang, w.lin, w.slot, w.rng, w.brg))
-              for t in range(w.warm_steps, w.warm_steps + distinct)]
-    pose = torch.empty((BATCH, 3), dtype=torch.float64).pin_memory()
-    assert f.fault_count() == 0 and int(f.n_known.min()) == NLM
+    run = BatchedRun(wk, local, rank, joseph=args.joseph, distinct=min(K + W, 24))
 
     # ---- device-resident timing: K launches, CUDA events on the launching stream ----------------------
-    for i in range(W):
-        f.step(*steady[i % distinct])
-    _barrier(world)
-    clocks = ClockSampler(local)
-    if rank == 0:
-        clocks.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    t_all0, t_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t_all0.record()
-    for i in range(K):
-        ev[i][0].record()
-        f.step(*steady[(W + i) % distinct])
-        ev[i][1].record()
-    t_all1.record()
-    _barrier(world)
-    total_ms = _max_over_ranks(t_all0.elapsed_time(t_all1), world)
-    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
-    ok = bool(torch.isfinite(f.mu).all()) and f.fault_count() == 0
-
+    clocks = ClockSampler(local) if rank == 0 else None
+    total_ms, kern_ms = run.device_resident(K, W, world, sampler=clocks)
     # ---- end to end: host buffers in, pose out, through the C-ABI host entry point -----------------------
     # every step: H2D of that step's pinned inputs, the fused step, D2H of every filter's pose; the pipelined
     # entry point overlaps step i's copies with step i-1's kernel (three streams, two staging sets)
-    poses = [pose, torch.empty_like(pose).pin_memory()]
-    for i in range(W):
-        f.step_host_async(*pinned[i % distinct], poses[i & 1])
-    f.host_sync()
-    _barrier(world)
-    t0 = time.perf_counter()
-    for i in range(K):
-        f.step_host_async(*pinned[(W + i) % distinct], poses[i & 1])
-    f.host_sync()
-    _barrier(world)
-    e2e_s = _max_over_ranks(time.perf_counter() - t0, world)
-    # the synchronous call (one step at a time, nothing overlapped), for reference
-    t0 = time.perf_counter()
-    for i in range(K):
-        f.step_host(*pinned[(W + i) % distinct], pose)
-    _barrier(world)
-    e2e_sync_s = _max_over_ranks(time.perf_counter() - t0, world)
-    ok = ok and bool(np.isfinite(poses[0].numpy()).all()) and bool(np.isfinite(poses[1].numpy()).all())
+    e2e_s, e2e_sync_s = run.end_to_end(K, W, world)
+    ok = run.healthy()
+    ok = ok and bool(np.isfinite(run.poses[0].numpy()).all()) and bool(np.isfinite(run.poses[1].numpy()).all())
+    ok = bool(_min_over_ranks(1.0 if ok else 0.0, world) == 1.0)
     clk = clocks.stop() if rank == 0 else None
-    h2d = BATCH * (8 + 8 + M * (4 + 8 + 8))
-    d2h = BATCH * 3 * 8
 
-    if rank != 0:
-        return
-    peak, which = measured_peak_gbs()
-    ach = BYTES_PER_FILTER_STEP * BATCH / (kern_ms * 1e-3) / 1e9
-    value = BATCH * world * K / (total_ms * 1e-3)
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": SCALING, "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic",
-            "config": make_config(args.joseph),
-            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "peak_source": which, "unit": "GB/s",
-                         "frac": ach / peak, "frac_of_8TBs": ach / 8000.0,
-                         "bytes_per_filter_step": BYTES_PER_FILTER_STEP, "kernel": kernel_label()[1],
-                         "kernel_ms": kern_ms, "traffic": ncu_traffic(kernel_label()[0])},
-            "e2e": {"value": BATCH * world * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h,
-                    "unpipelined_value": BATCH * world * K / e2e_sync_s,
+    key, label = wk.kernel()
+    line = {"metric": wk.metric, "value": wk.total * K / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": wk.scaling,
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": wk.config(args.joseph),
+            "roofline": roofline_block(wk.bytes * wk.batch, kern_ms, bytes_per_filter_step=wk.bytes, kernel=label,
+                                       kernel_ms=kern_ms, traffic=ncu_traffic(key),
+                                       traffic_source="profiles/ncu_traffic.json (static: one ncu --set full launch "
+                                                      "of this kernel, not measured in this run)"),
+            "e2e": {"value": wk.total * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": run.h2d,
+                    "d2h_bytes_per_step": run.d2h,
+                    "unpipelined_value": wk.total * K / e2e_sync_s,
                     "note": "ekf_batch_step_host_async + ekf_batch_host_sync: every step copies its pinned host "
                             "odometry+observations in, runs the fused step and copies the robot pose (x,y,theta) of "
                             "every filter out; copies of step i overlap the kernel of step i-1; filter state stays "
                             "resident in HBM. unpipelined_value = the synchronous ekf_batch_step_host"},
             "gpu_launches": K, "clocks": clk, "finite_and_faultless": ok}
+
+    if world == 1 and not args.no_sustained:
+        line["sustained"] = run.sustained(args.sustained_seconds, local, kern_ms)
+    run.close()
+    del run
+
     if world == 1:
-        if not args.no_cpu_baseline:
-            rate, cores, work, wall = cpu_filter_steps_per_s(filters_per_core=192, steps=200, form="dense")
-            line["cpu_baseline"] = {
-                "value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                "sample": f"{work} filter-steps ({cores} processes x 192 filters x 200 steady-state steps) of the same "
-                          "workload through the dense numpy restatement of replay_no_ros.py:269-482 "
-                          f"(oracle port), OPENBLAS_NUM_THREADS=1, {wall:.1f} s wall"}
+        if not args.no_cpu_baseline and rank == 0:
+            kind = cpu_kind()
+            per_core, steps = (96, 100) if kind == "reference" else (192, 200)
+            rate, cores, work, wall = cpu_filter_steps_per_s(wk, per_core, steps, kind)
+            line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": kind,
+                                    "sample": cpu_sample_text(wk, kind, work, cores, per_core, steps, wall)}
+            line["vs_cpu_baseline"] = {"value": line["value"] / rate, "e2e": line["e2e"]["value"] / rate,
+                                       "note": "this run's own GPU / CPU ratio (vs_baseline stays null: the reference "
+                                               "publishes no number for this metric, BASELINE.md §1)"}
+            if kind == "reference":
+                r2, c2, w2, wall2 = cpu_filter_steps_per_s(wk, 96, 100, "port")
+                line["cpu_baseline"]["port_value"] = r2
+                line["cpu_baseline"]["port_sample"] = cpu_sample_text(wk, "port", w2, c2, 96, 100, wall2)
         if not args.no_large_map:
             line["large_map"] = bench_large_map()
             if args.workload == "B":
-                del f, steady                      # 1 GB of covariance back before the 3.4 GB configuration
-                torch.cuda.empty_cache()
-                line["small_filters"] = bench_config_m(local)
-    print(json.dumps(line), flush=True)
+                wm = Workload("M", 1)
+                rm = BatchedRun(wm, local, rank, distinct=8)
+                line["small_filters"] = batched_object(wm, rm, 20, 3, 1, with_e2e=True,
+                                                       sustained_s=0.0 if args.no_sustained else args.sustained_seconds,
+                                                       local=local)
+                rm.close()
+    else:
+        # the sharded modes on the line the driver runs (VERDICT r1 missing #1): strong-split config M with its own
+        # e2e, and the row-block sharded large map (XL: 32,768 landmarks; 4096 landmarks with the bitwise flag)
+        if args.workload == "B" and not args.no_large_map:
+            wm = Workload("M", world)
+            rm = BatchedRun(wm, local, rank, distinct=8)
+            line["small_filters"] = batched_object(wm, rm, 20, 3, world, with_e2e=True)
+            rm.close()
+            del rm
+            torch.cuda.empty_cache()
+            lms = {"l4096": bench_large_map_sharded(LM_LANDMARKS, rank, world, local, updates=60, warm=6,
+                                                    bitwise=True, tracked=True)}
+            try:
+                lms["xl"] = bench_large_map_sharded(XL_LANDMARKS, rank, world, local, updates=30, warm=4,
+                                                    tracked=True)
+            except Exception as exc:                                  # out of memory etc.: say so, keep the line
+                lms["xl"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+            line["large_map_sharded"] = lms
+    if rank == 0:
+        print(json.dumps(line), flush=True)
 
 
 def main():
@@ -498,14 +802,16 @@ def main():
                     help="B: 65,536 x 20 lm per GPU (contract line); M: 1,048,576 x 8 lm split over the GPUs")
     ap.add_argument("--joseph", action="store_true", help="one-pass Joseph-form covariance update")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-large-map", action="store_true")
+    ap.add_argument("--no-large-map", action="store_true", help="skip the secondary objects")
+    ap.add_argument("--no-sustained", action="store_true")
+    ap.add_argument("--sustained-seconds", type=float, default=2.0)
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    set_workload(args.workload, world)
+    wk = Workload(args.workload, world)
     if args.impl == "reference":
-        run_reference_arm(args, int(os.environ.get("RANK", "0")), world)
+        run_reference_arm(args, wk, int(os.environ.get("RANK", "0")), world)
         return
-    run_own_arm(args, world)
+    run_own_arm(args, wk, world)
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()

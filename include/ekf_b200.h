@@ -32,7 +32,6 @@ extern "C" {
 #define EKF_EINVAL (-1)  /* bad argument */
 #define EKF_ECUDA (-2)   /* CUDA runtime error (message has cudaGetErrorString) */
 #define EKF_ESTATE (-3)  /* handle not bound / wrong mode */
-#define EKF_ENCCL (-4)   /* NCCL error */
 
 /* covariance update forms */
 #define EKF_COV_PLAIN 0  /* P <- P - K (H P): the reference, replay_no_ros.py:480 */
@@ -80,19 +79,27 @@ int ekf_batch_pack(ekf_batch_t* h, const double* mean_ref_dev, const double* cov
 int ekf_batch_unpack(ekf_batch_t* h, double* mean_ref_dev, double* cov_ref_dev, int64_t first, int64_t count,
                      void* stream);
 /* End-to-end call with HOST buffers: pinned staging + H2D of this step's inputs, the fused step, D2H of the
- * robot pose (x, y, theta) of every filter into pose_host [batch][3]; synchronous.                       */
+ * robot pose (x, y, theta) of every filter into pose_host [batch][3]; synchronous.
+ * Stream contract (both host entry points): the work runs on the handle's own streams; `stream` is the caller's
+ * stream that last touched the bound state (ekf_batch_init / step / pack ...). On entry the handle's streams wait
+ * for everything enqueued on it so far; on exit `stream` is made to wait for this step's kernel, so later calls
+ * on it (ekf_batch_step, unpack, moments) see the state this call produced.                                 */
 int ekf_batch_step_host(ekf_batch_t* h, const double* ang_host, const double* lin_host,
                         const int32_t* slot_host, const double* rng_host, const double* brg_host, int m,
-                        double* pose_host);
+                        double* pose_host, void* stream);
 /* Pipelined form of the same call: returns once the work is enqueued; step i's H2D copies overlap step i-1's
  * kernel and step i-2's D2H (three streams, two staging sets). Host buffers must stay valid and pose_host
  * unread until ekf_batch_host_sync returns.                                                             */
 int ekf_batch_step_host_async(ekf_batch_t* h, const double* ang_host, const double* lin_host,
                               const int32_t* slot_host, const double* rng_host, const double* brg_host, int m,
-                              double* pose_host);
+                              double* pose_host, void* stream);
 int ekf_batch_host_sync(ekf_batch_t* h);
-/* number of filters that saw an out-of-order new slot or a non-finite innovation since init            */
+/* number of filter-steps since init that were handed a slot beyond the capacity or one that skips first-seen
+ * order (the reference raises KeyError there, replay_no_ros.py:359); those observations are not applied       */
 int ekf_batch_fault_count(ekf_batch_t* h, int64_t* count);
+/* health check on demand: number of filters whose mu or P currently holds a non-finite value (the reference
+ * carries inf / nan silently, e.g. q = 0 at :446-469); scans the whole state once, synchronous on `stream`   */
+int ekf_batch_nonfinite_count(ekf_batch_t* h, int64_t* count, void* stream);
 
 /* a3/a4 on the device, per filter (replay_no_ros.py:280-337): gate the window's detections on their per-filter
  * perturbed camera-frame position (pose_t[0] + noise_tx, pose_t[2] + noise_tz; strict z^2 + x^2 > 2.25 drops),
@@ -105,7 +112,8 @@ int ekf_batch_associate(ekf_batch_t* h, int n_det, const int32_t* det_tag_dev, c
                         const double* det_tz_dev, const double* noise_tx_dev, const double* noise_tz_dev,
                         int n_tags, int32_t* tag_slot_dev, int32_t* n_seen_dev, int32_t* slot_dev, double* rng_dev,
                         double* brg_dev, int m, void* stream);
-/* windows that held more than m distinct landmarks (the extra ones were dropped) since create              */
+/* windows that held more than m distinct landmarks since create: the extra detections are dropped BEFORE a slot
+ * is handed out, so a dropped new tag is first-seen in a later window and slot order stays gap-free            */
 int ekf_batch_associate_overflow_count(ekf_batch_t* h, int64_t* count);
 /* sse_dev[b] += (x_b - gt_x)^2 + (y_b - gt_y)^2 for every filter: absolute trajectory error of the ensemble
  * against a ground-truth track (the comparison of replay_no_ros.py:519-529 as a number per member)          */

@@ -17,10 +17,30 @@ import sys
 import types
 
 REFERENCE_ROOT = os.environ.get("EKF_REFERENCE_ROOT", "/root/reference")
+# build outputs of oracle/build_ref.py: the reference's own code byte-compiled (travels to the GPU box)
+REF_BUILD_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+def source_available() -> bool:
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "src", "replay_no_ros.py"))
+
+
+def compiled_available() -> bool:
+    """oracle/_ref holds bytecode of THIS interpreter version (a .pyc of another version cannot be loaded)."""
+    pyc = os.path.join(REF_BUILD_DIR, "replay_no_ros.pyc")
+    if not (os.path.isfile(pyc) and os.path.isfile(os.path.join(REF_BUILD_DIR, "ekf_slam_functions.pyc"))):
+        return False
+    with open(pyc, "rb") as fh:
+        return fh.read(4) == importlib.util.MAGIC_NUMBER
 
 
 def reference_available() -> bool:
-    return os.path.isfile(os.path.join(REFERENCE_ROOT, "src", "replay_no_ros.py"))
+    return source_available() or compiled_available()
+
+
+def reference_kind() -> str:
+    """"source": /root/reference is here; "compiled": oracle/_ref bytecode; "absent"."""
+    return "source" if source_available() else ("compiled" if compiled_available() else "absent")
 
 
 def _stub(name: str, **attrs) -> types.ModuleType:
@@ -83,10 +103,15 @@ def load_replay_module():
     if "replay" in _cache:
         return _cache["replay"]
     if not reference_available():
-        raise FileNotFoundError(f"reference not found under {REFERENCE_ROOT}")
+        raise FileNotFoundError(f"reference not found under {REFERENCE_ROOT} and no oracle/_ref build")
     _install_stubs()
-    path = os.path.join(REFERENCE_ROOT, "src", "replay_no_ros.py")
-    spec = importlib.util.spec_from_file_location("_ref_replay_no_ros", path)
+    if source_available():
+        path = os.path.join(REFERENCE_ROOT, "src", "replay_no_ros.py")
+        spec = importlib.util.spec_from_file_location("_ref_replay_no_ros", path)
+    else:
+        from importlib.machinery import SourcelessFileLoader
+        path = os.path.join(REF_BUILD_DIR, "replay_no_ros.pyc")
+        spec = importlib.util.spec_from_loader("_ref_replay_no_ros", SourcelessFileLoader("_ref_replay_no_ros", path))
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     _cache["replay"] = mod
@@ -104,19 +129,25 @@ def load_ekf3_functions():
     import numpy as np
     from typing import Tuple
 
-    path = os.path.join(REFERENCE_ROOT, "src", "EKF-SLAM.py")
-    with open(path, "r") as fh:
-        tree = ast.parse(fh.read(), filename=path)
-    keep = []
-    for node in tree.body:
-        if isinstance(node, ast.FunctionDef) and node.name in ("predict", "update", "delta_phi", "displacement"):
-            keep.append(node)
-        elif isinstance(node, ast.Assign) and any(
-            isinstance(t, ast.Name) and t.id in ("motion_noise", "observation_noise") for t in node.targets
-        ):
-            keep.append(node)
     ns = {"np": np, "Tuple": Tuple}
-    exec(compile(ast.Module(body=keep, type_ignores=[]), path, "exec"), ns)
+    if source_available():
+        path = os.path.join(REFERENCE_ROOT, "src", "EKF-SLAM.py")
+        with open(path, "r") as fh:
+            tree = ast.parse(fh.read(), filename=path)
+        keep = []
+        for node in tree.body:
+            if isinstance(node, ast.FunctionDef) and node.name in ("predict", "update", "delta_phi", "displacement"):
+                keep.append(node)
+            elif isinstance(node, ast.Assign) and any(
+                isinstance(t, ast.Name) and t.id in ("motion_noise", "observation_noise") for t in node.targets
+            ):
+                keep.append(node)
+        exec(compile(ast.Module(body=keep, type_ignores=[]), path, "exec"), ns)
+    else:
+        import marshal
+        with open(os.path.join(REF_BUILD_DIR, "ekf_slam_functions.pyc"), "rb") as fh:
+            fh.read(16)
+            exec(marshal.load(fh), ns)
     out = types.SimpleNamespace(**{k: ns[k] for k in
                                    ("predict", "update", "delta_phi", "displacement",
                                     "motion_noise", "observation_noise")})

@@ -50,10 +50,11 @@ SIGNATURES = {
     "ekf_batch_step_ticks": (_i, [_p, _p, _p, _p, _p, _d, _d, _i, _p, _p, _p, _i, _p]),
     "ekf_batch_pack": (_i, [_p, _p, _p, _l, _l, _p]),
     "ekf_batch_unpack": (_i, [_p, _p, _p, _l, _l, _p]),
-    "ekf_batch_step_host": (_i, [_p, _p, _p, _p, _p, _p, _i, _p]),
-    "ekf_batch_step_host_async": (_i, [_p, _p, _p, _p, _p, _p, _i, _p]),
+    "ekf_batch_step_host": (_i, [_p, _p, _p, _p, _p, _p, _i, _p, _p]),
+    "ekf_batch_step_host_async": (_i, [_p, _p, _p, _p, _p, _p, _i, _p, _p]),
     "ekf_batch_host_sync": (_i, [_p]),
     "ekf_batch_fault_count": (_i, [_p, C.POINTER(_l)]),
+    "ekf_batch_nonfinite_count": (_i, [_p, C.POINTER(_l), _p]),
     "ekf_batch_associate": (_i, [_p, _i, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _p]),
     "ekf_batch_associate_overflow_count": (_i, [_p, C.POINTER(_l)]),
     "ekf_batch_accumulate_ate": (_i, [_p, _d, _d, _p, _p]),

@@ -56,7 +56,7 @@ struct ekf_batch {
   // small filters, 8 / 16 = sub-warp groups of that width (capacity <= 8 landmarks; auto picks 8 there);
   // EKF_BATCH_KERNEL=auto|stream|staged|regw|group8|group16
   int kernel = 0;
-  unsigned long long* faults = nullptr;  // [0] fault count, [1..2] work / done counters of the persistent kernel, [3] association overflows
+  unsigned long long* faults = nullptr;  // [0] fault count, [1..2] work / done counters of the persistent kernel, [3] association overflows, [4] scratch of ekf_batch_nonfinite_count
   // staging for the host-buffer entry point
   cudaStream_t stream = nullptr;
   double *d_ang = nullptr, *d_lin = nullptr, *d_rng = nullptr, *d_brg = nullptr, *d_pose = nullptr;
@@ -66,6 +66,7 @@ struct ekf_batch {
   cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
   double* p_stage[2] = {nullptr, nullptr};  // per set: ang | lin | rng[M] | brg[M] | pose[3] doubles, slot[M] ints
   int64_t pipe_step = 0;
+  cudaEvent_t ev_caller = nullptr;  // orders the handle's streams after the caller's stream
   double* mom_partial = nullptr;  // scratch of ekf_batch_moments
 };
 
@@ -143,8 +144,8 @@ int ekf_batch_create(int n_landmarks, int64_t batch, int device, ekf_batch_t** o
   if (const char* k = getenv("EKF_BATCH_KERNEL"))
     h->kernel = (strcmp(k, "stream") == 0) ? 1 : (strcmp(k, "staged") == 0) ? 2 : (strcmp(k, "regw") == 0) ? 3 :
                 (strcmp(k, "group8") == 0) ? 8 : (strcmp(k, "group16") == 0) ? 16 : 0;
-  cudaError_t e = cudaMalloc(&h->faults, 4 * sizeof(unsigned long long));
-  if (e == cudaSuccess) e = cudaMemset(h->faults, 0, 4 * sizeof(unsigned long long));
+  cudaError_t e = cudaMalloc(&h->faults, 8 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMemset(h->faults, 0, 8 * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) {
     ekf_batch_destroy(h);
@@ -171,6 +172,7 @@ int ekf_batch_destroy(ekf_batch_t* h) {
     if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
     if (h->ev_out[i]) cudaEventDestroy(h->ev_out[i]);
   }
+  if (h->ev_caller) cudaEventDestroy(h->ev_caller);
   if (h->s_in) cudaStreamDestroy(h->s_in);
   if (h->s_out) cudaStreamDestroy(h->s_out);
   if (h->stream) cudaStreamDestroy(h->stream);
@@ -294,9 +296,21 @@ int ekf_batch_unpack(ekf_batch_t* h, double* mean_ref_dev, double* cov_ref_dev, 
   return EKF_OK;
 }
 
+// Stream contract of the host entry points: the fused step runs on the handle's own non-blocking streams (copy-in /
+// compute / copy-out). `stream` is the caller's stream that last touched the bound state (init, step, pack, ...):
+// on entry the handle's streams wait for everything enqueued on it so far, on exit it is made to wait for the
+// step's kernel, so that a later ekf_batch_step / unpack / moments on `stream` sees the state this call produced.
+static int host_order_in(ekf_batch_t* h, cudaStream_t caller, cudaStream_t first, cudaStream_t second) {
+  if (!h->ev_caller) CU(cudaEventCreateWithFlags(&h->ev_caller, cudaEventDisableTiming));
+  CU(cudaEventRecord(h->ev_caller, caller));
+  CU(cudaStreamWaitEvent(first, h->ev_caller, 0));
+  if (second) CU(cudaStreamWaitEvent(second, h->ev_caller, 0));
+  return EKF_OK;
+}
+
 int ekf_batch_step_host(ekf_batch_t* h, const double* ang_host, const double* lin_host,
                         const int32_t* slot_host, const double* rng_host, const double* brg_host, int m,
-                        double* pose_host) {
+                        double* pose_host, void* stream) {
   if (!h || !ang_host || !lin_host || !pose_host) return fail(EKF_EINVAL, "null argument");
   if (m < 0 || m > ekf::BATCH_MAX_M) return fail(EKF_EINVAL, "m must be in [0, %d]", ekf::BATCH_MAX_M);
   if (m > 0 && (!slot_host || !rng_host || !brg_host)) return fail(EKF_EINVAL, "observation arrays are null");
@@ -311,6 +325,12 @@ int ekf_batch_step_host(ekf_batch_t* h, const double* ang_host, const double* li
     CU(cudaMalloc(&h->d_pose, B * 3 * sizeof(double)));
   }
   cudaStream_t st = h->stream;
+  if (h->s_in) {  // an earlier pipelined call may still be in flight on the other two streams
+    CU(cudaStreamSynchronize(h->s_in));
+    CU(cudaStreamSynchronize(h->s_out));
+  }
+  int rc = host_order_in(h, (cudaStream_t)stream, st, nullptr);
+  if (rc != EKF_OK) return rc;
   CU(cudaMemcpyAsync(h->d_ang, ang_host, B * sizeof(double), cudaMemcpyHostToDevice, st));
   CU(cudaMemcpyAsync(h->d_lin, lin_host, B * sizeof(double), cudaMemcpyHostToDevice, st));
   if (m > 0) {
@@ -318,11 +338,11 @@ int ekf_batch_step_host(ekf_batch_t* h, const double* ang_host, const double* li
     CU(cudaMemcpyAsync(h->d_rng, rng_host, B * m * sizeof(double), cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(h->d_brg, brg_host, B * m * sizeof(double), cudaMemcpyHostToDevice, st));
   }
-  int rc = ekf_batch_step(h, h->d_ang, h->d_lin, h->d_slot, h->d_rng, h->d_brg, m, st);
+  rc = ekf_batch_step(h, h->d_ang, h->d_lin, h->d_slot, h->d_rng, h->d_brg, m, st);
   if (rc != EKF_OK) return rc;
   CU(ekf::batch_launch_pose(h->mu, h->d_pose, B, h->ld, st));
   CU(cudaMemcpyAsync(pose_host, h->d_pose, B * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
+  CU(cudaStreamSynchronize(st));  // synchronous: the caller's stream needs no further ordering
   return EKF_OK;
 }
 
@@ -332,7 +352,7 @@ int ekf_batch_step_host(ekf_batch_t* h, const double* ang_host, const double* li
 // until ekf_batch_host_sync returns.
 int ekf_batch_step_host_async(ekf_batch_t* h, const double* ang_host, const double* lin_host,
                               const int32_t* slot_host, const double* rng_host, const double* brg_host, int m,
-                              double* pose_host) {
+                              double* pose_host, void* stream) {
   if (!h || !ang_host || !lin_host || !pose_host) return fail(EKF_EINVAL, "null argument");
   if (m < 0 || m > ekf::BATCH_MAX_M) return fail(EKF_EINVAL, "m must be in [0, %d]", ekf::BATCH_MAX_M);
   if (m > 0 && (!slot_host || !rng_host || !brg_host)) return fail(EKF_EINVAL, "observation arrays are null");
@@ -357,6 +377,9 @@ int ekf_batch_step_host_async(ekf_batch_t* h, const double* ang_host, const doub
   double* d_brg = d_rng + B * M;
   double* d_pose = d_brg + B * M;
   int32_t* d_slot = reinterpret_cast<int32_t*>(d_pose + B * 3);
+  // the state may have been touched on the caller's stream (init / step / pack) since the last host step
+  int rc = host_order_in(h, (cudaStream_t)stream, h->stream, nullptr);
+  if (rc != EKF_OK) return rc;
   // copy-in: the set is free once the kernel of step i-2 (its last reader) is done
   if (h->pipe_step >= 2) CU(cudaStreamWaitEvent(h->s_in, h->ev_done[set], 0));
   CU(cudaMemcpyAsync(d_ang, ang_host, B * sizeof(double), cudaMemcpyHostToDevice, h->s_in));
@@ -370,10 +393,12 @@ int ekf_batch_step_host_async(ekf_batch_t* h, const double* ang_host, const doub
   // compute: after this step's inputs have landed and the pose buffer of step i-2 has drained
   CU(cudaStreamWaitEvent(h->stream, h->ev_in[set], 0));
   if (h->pipe_step >= 2) CU(cudaStreamWaitEvent(h->stream, h->ev_out[set], 0));
-  int rc = ekf_batch_step(h, d_ang, d_lin, d_slot, d_rng, d_brg, m, h->stream);
+  rc = ekf_batch_step(h, d_ang, d_lin, d_slot, d_rng, d_brg, m, h->stream);
   if (rc != EKF_OK) return rc;
   CU(ekf::batch_launch_pose(h->mu, d_pose, B, h->ld, h->stream));
   CU(cudaEventRecord(h->ev_done[set], h->stream));
+  // the caller's stream sees the state of this step from here on
+  CU(cudaStreamWaitEvent((cudaStream_t)stream, h->ev_done[set], 0));
   // copy-out
   CU(cudaStreamWaitEvent(h->s_out, h->ev_done[set], 0));
   CU(cudaMemcpyAsync(pose_host, d_pose, B * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->s_out));
@@ -400,6 +425,20 @@ int ekf_batch_fault_count(ekf_batch_t* h, int64_t* count) {
   CU(cudaSetDevice(h->device));
   unsigned long long v = 0;
   CU(cudaMemcpy(&v, h->faults, sizeof(v), cudaMemcpyDeviceToHost));
+  *count = (int64_t)v;
+  return EKF_OK;
+}
+
+int ekf_batch_nonfinite_count(ekf_batch_t* h, int64_t* count, void* stream) {
+  if (!h || !count) return fail(EKF_EINVAL, "null argument");
+  if (!h->mu) return fail(EKF_ESTATE, "state not bound");
+  CU(cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  CU(cudaMemsetAsync(h->faults + 4, 0, sizeof(unsigned long long), st));
+  CU(ekf::batch_launch_nonfinite(h->mu, h->P, h->ld, (int64_t)h->n * h->ld, h->batch, h->faults + 4, st));
+  unsigned long long v = 0;
+  CU(cudaMemcpyAsync(&v, h->faults + 4, sizeof(v), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
   *count = (int64_t)v;
   return EKF_OK;
 }
@@ -560,7 +599,7 @@ int ekf_lm_predict(ekf_lm_t* h, double ang, double lin, void* stream) {
   if (!h->P) return fail(EKF_ESTATE, "state not bound");
   CU(cudaSetDevice(h->device));
   CU(ekf::lm_launch_predict(h->mu, h->P, h->ld, h->n, h->row_begin, h->row_end, h->scal, ang, lin, h->mv,
-                            h->flags, true, (cudaStream_t)stream));
+                            h->flags, (cudaStream_t)stream));
   return EKF_OK;
 }
 
@@ -811,6 +850,8 @@ int ekf_lm_p2p_update(ekf_lm_t* h, int slot, double rng, double brg, int owner, 
   if (slot < 0 || slot >= h->cap) return fail(EKF_EINVAL, "slot %d outside capacity %d", slot, h->cap);
   if (owner < 0 || owner >= h->p2p_world) return fail(EKF_EINVAL, "owner out of range");
   if (!(h->flags & ekf::kFlagMeasurement)) return EKF_OK;
+  if (h->p2p_world == 1)  // nobody to exchange with: the plain single-GPU update, no push / flag / ack protocol
+    return lm_update_impl(h, slot, rng, brg, nullptr, stream);
   CU(cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;
   const int j = 3 + 2 * slot;
@@ -834,6 +875,7 @@ int ekf_lm_p2p_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const
   if (!h->p2p_peers_dev) return fail(EKF_ESTATE, "p2p exchange not connected");
   if (!owners_host) return fail(EKF_EINVAL, "owners_host is null");
   if (m < 2 || m > ekf::LM_MAX_FUSED) return fail(EKF_EINVAL, "m must be in [2, %d]", ekf::LM_MAX_FUSED);
+  if (h->p2p_world == 1) return ekf_lm_update_multi(h, m, slots_host, rng_host, brg_host, stream);
   if (h->flags & ekf::kFlagJoseph) return fail(EKF_EINVAL, "Joseph form is not available on a row-block shard");
   if (!(h->flags & ekf::kFlagMeasurement)) return EKF_OK;
   for (int u = 0; u < m; ++u) {

@@ -39,16 +39,19 @@ __global__ void __launch_bounds__(128) batch_associate_kernel(AssocArgs a) {
     if (__dadd_rn(__dmul_rn(tz, tz), __dmul_rn(tx, tx)) > 2.25) continue;
     int32_t* cell = a.tag_slot + (int64_t)tag * a.batch + b;
     int s = *cell;
-    if (s < 0) {                   // first sighting ever: slot = len(TAG_INDEX) (:294-295)
-      s = seen++;
-      *cell = s;
-    }
     int k = 0;
-    while (k < nb && bslot[k] != s) ++k;
+    if (s >= 0)
+      while (k < nb && bslot[k] != s) ++k;
+    else
+      k = nb;                      // a tag never seen before cannot have a bucket yet
     if (k == nb) {
-      if (nb == m) {               // more distinct landmarks in one window than the step block holds
-        overflow = true;
-        continue;
+      if (nb == m) {               // more distinct landmarks in one window than the step block holds: the
+        overflow = true;           // detection is dropped BEFORE a slot is handed out, so a dropped new tag is
+        continue;                  // simply "first seen" in a later window and slot order stays gap-free
+      }
+      if (s < 0) {                 // first sighting ever: slot = len(TAG_INDEX) (:294-295)
+        s = seen++;
+        *cell = s;
       }
       bslot[nb] = s; sx[nb] = 0.0; sz[nb] = 0.0; cnt[nb] = 0;
       ++nb;
@@ -137,6 +140,28 @@ __global__ void __launch_bounds__(256) batch_moments_final_kernel(const double* 
   double a = 0.0;
   for (int c = 0; c < ctas; ++c) a = __dadd_rn(a, partial[(int64_t)c * E + e]);
   sums[e] = a;
+}
+
+// Health check on demand (not on the hot path): counts[0] = filters whose mu or P holds a non-finite value (the
+// reference would carry inf / nan silently, e.g. q = 0 when a landmark estimate coincides with the pose, :446-469).
+// One warp per filter, coalesced reads of its record.
+__global__ void __launch_bounds__(256) batch_nonfinite_kernel(const double* __restrict__ mu, const double* __restrict__ P,
+                                                              int64_t mu_stride, int64_t p_stride, int64_t batch,
+                                                              unsigned long long* __restrict__ count) {
+  const int64_t b = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (b >= batch) return;
+  bool bad = false;
+  for (int64_t i = lane; i < mu_stride; i += 32) bad |= !isfinite(mu[b * mu_stride + i]);
+  for (int64_t i = lane; i < p_stride; i += 32) bad |= !isfinite(P[b * p_stride + i]);
+  if (__any_sync(0xffffffffu, bad) && lane == 0) atomicAdd(count, 1ULL);
+}
+
+cudaError_t batch_launch_nonfinite(const double* mu, const double* P, int64_t mu_stride, int64_t p_stride,
+                                   int64_t batch, unsigned long long* count, cudaStream_t st) {
+  const int64_t threads = batch * 32;
+  batch_nonfinite_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(mu, P, mu_stride, p_stride, batch, count);
+  return cudaGetLastError();
 }
 
 cudaError_t batch_launch_moments(const double* mu, int64_t mu_stride, int64_t batch, int n, double* partial,

@@ -28,6 +28,8 @@ constexpr int MOM_CTAS = 592;  // 4 x 148 SMs: partial sums of the ensemble mome
 // sums[n + n*n] = (sum_b mu_b, sum_b mu_b mu_b^T) in a fixed order; partial: scratch [MOM_CTAS][n + n*n]
 cudaError_t batch_launch_moments(const double* mu, int64_t mu_stride, int64_t batch, int n, double* partial,
                                  double* sums, cudaStream_t st);
+cudaError_t batch_launch_nonfinite(const double* mu, const double* P, int64_t mu_stride, int64_t p_stride,
+                                   int64_t batch, unsigned long long* count, cudaStream_t st);
 cudaError_t batch_launch_ate(const double* mu, int64_t mu_stride, int64_t batch, double gx, double gy, double* sse,
                              cudaStream_t st);
 

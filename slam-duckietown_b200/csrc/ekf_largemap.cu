@@ -35,28 +35,32 @@ __global__ void lm_augment_kernel(double* __restrict__ mu, double* __restrict__ 
 }
 
 // -------------------------------------------------------------------------------------------------------
-// a6 predict mean (:368-417): one thread; leaves g0, g1 in the workspace for the covariance kernel.
+// a6-a7 predict (:368-430) in ONE launch. Mean: every CTA's thread 0 evaluates the motion model from the
+// pre-predict heading mu[2] (a few hundred cycles, redundant per CTA) and shares g0 = G[0,2], g1 = G[1,2]
+// through shared memory. Covariance: P <- G_F P G_F^T + F^T R F touches rows 0-1, columns 0-1 and three
+// diagonal entries; thread t >= 3 does column t of rows 0-1 and row t of columns 0-1, thread 0 the 3x3 robot
+// block in the same order (rows first, then columns with the updated rows, then the noise).
+// mu[0..2] is written by CTA 0 only AFTER every CTA has read the old heading: each CTA bumps an arrival counter
+// once it holds g0/g1, CTA 0's thread 0 waits for gridDim.x arrivals (nobody waits on CTA 0, so this cannot
+// deadlock whatever the residency) and re-arms the counter. Round 1 used two plain launches (mean, covariance):
+// 22 us per predict at 4096 landmarks, of which 8 us were kernels.
 // -------------------------------------------------------------------------------------------------------
-__global__ void lm_predict_mean_kernel(double* __restrict__ mu, double* __restrict__ scal, double ang,
-                                       double lin, int flags) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  const Motion m = motion_step(mu[2], ang, lin, flags);
-  mu[0] += m.dx;
-  mu[1] += m.dy;
-  mu[2] = m.theta;
-  scal[kScalG0] = m.g0;
-  scal[kScalG1] = m.g1;
-}
-
-// -------------------------------------------------------------------------------------------------------
-// a7 predict covariance (:420-430): P <- G_F P G_F^T + F^T R F touches rows 0-1, columns 0-1 and three
-// diagonal entries. Thread t >= 3 does column t of rows 0-1 and row t of columns 0-1; thread 0 does the
-// 3x3 robot block in the same order (rows first, then columns with the updated rows, then the noise).
-// -------------------------------------------------------------------------------------------------------
-__global__ void lm_predict_cov_kernel(double* __restrict__ P, int64_t ld, int n, int row_begin, int row_end,
-                                      const double* __restrict__ scal, double mv) {
+__global__ void __launch_bounds__(256) lm_predict_kernel(double* __restrict__ mu, double* __restrict__ P, int64_t ld,
+                                                         int n, int row_begin, int row_end,
+                                                         unsigned long long* __restrict__ arrive, double ang,
+                                                         double lin, double mv, int flags) {
+  __shared__ double sg[5];
+  pdl_wait();
+  if (threadIdx.x == 0) {
+    const double th = *reinterpret_cast<volatile double*>(mu + 2);
+    const Motion m = motion_step(th, ang, lin, flags);
+    sg[0] = m.g0; sg[1] = m.g1; sg[2] = m.dx; sg[3] = m.dy; sg[4] = m.theta;
+    __threadfence();
+    atomicAdd(arrive, 1ULL);
+  }
+  __syncthreads();
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const double g0 = scal[kScalG0], g1 = scal[kScalG1];
+  const double g0 = sg[0], g1 = sg[1];
   const bool own_robot = (row_begin == 0);
   if (t >= 3 && t < n) {
     if (own_robot) {  // rows 0-1, column t
@@ -70,29 +74,41 @@ __global__ void lm_predict_cov_kernel(double* __restrict__ P, int64_t ld, int n,
       row[0] += g0 * p2;
       row[1] += g1 * p2;
     }
-  } else if (t == 0 && own_robot) {
-    double b[3][3];
+  } else if (t == 0) {
+    if (own_robot) {
+      double b[3][3];
 #pragma unroll
-    for (int i = 0; i < 3; ++i)
+      for (int i = 0; i < 3; ++i)
 #pragma unroll
-      for (int c = 0; c < 3; ++c) b[i][c] = P[i * ld + c];
+        for (int c = 0; c < 3; ++c) b[i][c] = P[i * ld + c];
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      b[0][c] += g0 * b[2][c];
-      b[1][c] += g1 * b[2][c];
+      for (int c = 0; c < 3; ++c) {
+        b[0][c] += g0 * b[2][c];
+        b[1][c] += g1 * b[2][c];
+      }
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        b[i][0] += g0 * b[i][2];
+        b[i][1] += g1 * b[i][2];
+      }
+      b[0][0] += mv * mv;
+      b[1][1] += mv * mv;
+      b[2][2] += (mv / 2.0) * (mv / 2.0);
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) P[i * ld + c] = b[i][c];
     }
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      b[i][0] += g0 * b[i][2];
-      b[i][1] += g1 * b[i][2];
+    // the mean, last: every CTA has taken its copy of the old heading
+    const long long t0 = clock64();
+    while (*reinterpret_cast<volatile unsigned long long*>(arrive) < (unsigned long long)gridDim.x) {
+      if (clock64() - t0 > 4000000000LL) break;  // cannot happen (no CTA waits on another); never hang the GPU
+      __nanosleep(20);
     }
-    b[0][0] += mv * mv;
-    b[1][1] += mv * mv;
-    b[2][2] += (mv / 2.0) * (mv / 2.0);
-#pragma unroll
-    for (int i = 0; i < 3; ++i)
-#pragma unroll
-      for (int c = 0; c < 3; ++c) P[i * ld + c] = b[i][c];
+    *arrive = 0ULL;
+    mu[0] += sg[2];
+    mu[1] += sg[3];
+    mu[2] = sg[4];
   }
 }
 
@@ -369,13 +385,11 @@ cudaError_t lm_launch_augment(double* mu, double* P, int64_t ld, int row_begin, 
 }
 
 cudaError_t lm_launch_predict(double* mu, double* P, int64_t ld, int n, int row_begin, int row_end,
-                              double* scal, double ang, double lin, double mv, int flags, bool update_mean,
-                              cudaStream_t st) {
-  if (update_mean) lm_predict_mean_kernel<<<1, 32, 0, st>>>(mu, scal, ang, lin, flags);
+                              double* scal, double ang, double lin, double mv, int flags, cudaStream_t st) {
   const int threads = 256;
-  lm_predict_cov_kernel<<<(n + threads - 1) / threads, threads, 0, st>>>(P, ld, n, row_begin, row_end, scal,
-                                                                         mv);
-  return cudaGetLastError();
+  unsigned long long* arrive = reinterpret_cast<unsigned long long*>(scal + kScalArrive);
+  return launch_pdl(lm_predict_kernel, dim3((n + threads - 1) / threads), dim3(threads), 0, st, mu, P, ld, n,
+                    row_begin, row_end, arrive, ang, lin, mv, flags);
 }
 
 cudaError_t lm_launch_gather(const LmGatherArgs& a, cudaStream_t st) {

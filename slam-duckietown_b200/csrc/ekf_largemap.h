@@ -38,7 +38,7 @@ __device__ __forceinline__ void pdl_wait() {
 constexpr int LM_THREADS = 128;  // threads per CTA of the streaming update = column groups per tile
 
 // slots of the small scalar workspace (device doubles)
-enum : int { kScalG0 = 0, kScalG1 = 1, kScalY0 = 2, kScalY1 = 3, kScalCount = 8 };
+enum : int { kScalG0 = 0, kScalG1 = 1, kScalY0 = 2, kScalY1 = 3, kScalArrive = 6 /* u64 arrival counter of the predict */, kScalCount = 8 };
 
 struct LmGatherArgs {
   const double* P;        // local row block
@@ -123,8 +123,7 @@ cudaError_t lm_launch_p2p_push(const P2PArgs& a, int first_row, int first_k, int
 cudaError_t lm_launch_augment(double* mu, double* P, int64_t ld, int row_begin, int row_end, int j, double gx,
                               double gy, cudaStream_t st);
 cudaError_t lm_launch_predict(double* mu, double* P, int64_t ld, int n, int row_begin, int row_end,
-                              double* scal, double ang, double lin, double mv, int flags, bool update_mean,
-                              cudaStream_t st);
+                              double* scal, double ang, double lin, double mv, int flags, cudaStream_t st);
 cudaError_t lm_launch_gather(const LmGatherArgs& a, cudaStream_t st);
 cudaError_t lm_launch_update(const LmUpdateArgs& a, bool joseph, int variant, cudaStream_t st);
 cudaError_t lm_launch_export_rows(const double* P, const double* mu, int64_t ld, int row_begin, int row_end,

@@ -421,7 +421,7 @@ class BatchedEKF:
         m = 0 if slot is None else int(slot.shape[1])
         z = C.c_void_p(0)
         capi.call("ekf_batch_step_host", self._h, hp(ang), hp(lin), hp(slot) if m else z, hp(rng) if m else z,
-                  hp(brg) if m else z, m, hp(pose_out))
+                  hp(brg) if m else z, m, hp(pose_out), _stream_ptr(self.torch))
 
     def step_host_async(self, ang, lin, slot, rng, brg, pose_out):
         """Pipelined ``step_host``: enqueue only. Keep the (pinned) host buffers alive and do not read
@@ -431,7 +431,7 @@ class BatchedEKF:
         m = 0 if slot is None else int(slot.shape[1])
         z = C.c_void_p(0)
         capi.call("ekf_batch_step_host_async", self._h, hp(ang), hp(lin), hp(slot) if m else z,
-                  hp(rng) if m else z, hp(brg) if m else z, m, hp(pose_out))
+                  hp(rng) if m else z, hp(brg) if m else z, m, hp(pose_out), _stream_ptr(self.torch))
 
     def host_sync(self):
         capi.call("ekf_batch_host_sync", self._h)
@@ -459,6 +459,12 @@ class BatchedEKF:
     def fault_count(self) -> int:
         v = C.c_int64()
         capi.call("ekf_batch_fault_count", self._h, C.byref(v))
+        return v.value
+
+    def nonfinite_count(self) -> int:
+        """Filters whose mu or P holds a non-finite value right now (a full scan on the device)."""
+        v = C.c_int64()
+        capi.call("ekf_batch_nonfinite_count", self._h, C.byref(v), _stream_ptr(self.torch))
         return v.value
 
 

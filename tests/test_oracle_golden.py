@@ -1,5 +1,6 @@
 """CPU: the oracle restatement against the golden vectors dumped from the unmodified reference."""
 import numpy as np
+import pytest
 
 from conftest import assert_parity, golden
 from oracle import ekf_oracle as eo
@@ -128,3 +129,31 @@ def test_odometry_helpers():
     ang, lin = eo.displacement(0.0318, 0.1, 0.2, 0.5)
     assert ang == (0.0318 * 0.5 - 0.0318 * 0.2) / 0.1 and lin == (0.0318 * 0.2 + 0.0318 * 0.5) / 2
     assert eo.wrap_pi(np.pi) == -np.pi and abs(eo.wrap_pi(-np.pi) + np.pi) < 1e-15
+
+
+def test_tracked_rows_oracle_equals_full_oracle():
+    """oracle/sampled_rows.TrackedRows (the XL leg: the rank-2 restatement on a subset of rows) == the full rank-2
+    oracle restricted to those rows, through a mixed sequence of updates and predicts."""
+    from oracle import sampled_rows as sr
+    from slam_duckietown_b200 import workloads as wl
+    w = wl.make_large_map(100, updates=30)
+    m_o, c_o = w.mu0.copy(), w.p0()
+    fl = eo.Flags(motion_var=0.2, meas_var=0.5)
+    slots = [op[1] for op in w.ops if op[0] == "update"]
+    rs = np.random.default_rng(0)
+    rows = sr.required_rows(slots)
+    rows += [int(r) for r in rs.permutation(w.n) if r not in rows][:17]
+    tr = sr.TrackedRows(w.mu0, rows, c_o[rows, :])
+    for op in w.ops:
+        if op[0] == "update":
+            eo.update_rank(m_o, c_o, op[1], op[2], op[3], 0.5)
+            tr.update(op[1], op[2], op[3], 0.5)
+        else:
+            dx, dy, th, g0, g1 = eo.motion_step(m_o[2], op[1], op[2], fl)
+            m_o[0] += dx; m_o[1] += dy; m_o[2] = th
+            eo.predict_cov_rank(c_o, g0, g1, 0.2)
+            tr.predict(op[1], op[2], fl)
+    e = tr.errors(m_o[rows], c_o[rows, :], np.diag(c_o))
+    assert max(e) <= 1e-12, e
+    with pytest.raises(KeyError):
+        sr.TrackedRows(w.mu0, [0, 1, 2], w.p0()[[0, 1, 2], :]).update(5, 1.0, 0.1, 0.5)
