@@ -124,6 +124,32 @@ int ekf_batch_accumulate_ate(ekf_batch_t* h, double gt_x, double gt_y, double* s
  * (plus the filter count) to get the ensemble mean and covariance that the reference's ablation plots show per
  * run (README.md:421-492); the filters themselves never interact.                                            */
 int ekf_batch_moments(ekf_batch_t* h, double* sums_dev, void* stream);
+/* the same for the robot pose only: sums_dev[0..2] = sum_b (x, y, theta), sums_dev[3 + 3 i + k] = sum_b pose_i pose_k
+ * (12 doubles) — the per-step result of a Monte Carlo replay (mean trajectory and its spread)                  */
+int ekf_batch_pose_moments(ekf_batch_t* h, double* sums_dev, void* stream);
+
+/* ---- Monte Carlo perturbations generated ON the device ---------------------------------------------------------
+ * The batched mode replays ONE common trajectory per ensemble member with member-specific perturbations (north star:
+ * "Monte Carlo noise replays of the same bag"). Every perturbation is a pure function of (seed, GLOBAL filter index
+ * first_filter + b, step, stream): Philox4x32-10 -> inverse normal CDF evaluated with separately rounded IEEE
+ * operations, so the host can regenerate any member's inputs bit for bit (oracle/mc_noise.py) whatever the sharding.
+ * The common step record is: doubles [ang, lin, rng[0..m), brg[0..m)] followed by int32 slot[0..m)
+ * (ekf_batch_mc_record_doubles(m) doubles in all). sigma4 = std-dev of the perturbation of (ang, lin, rng, brg).  */
+int ekf_batch_mc_record_doubles(int m, int64_t* doubles);
+/* writes the [batch] / [batch][m] blocks ekf_batch_step consumes from a DEVICE record                            */
+int ekf_batch_perturb(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int m,
+                      const double* record_dev, const double* sigma4, double* ang_dev, double* lin_dev,
+                      int32_t* slot_dev, double* rng_dev, double* brg_dev, void* stream);
+/* per-filter perturbation of the window's detections for ekf_batch_associate: noise_tx / noise_tz [n_det][batch]  */
+int ekf_batch_detection_noise(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int n_det,
+                              double sigma, double* noise_tx_dev, double* noise_tz_dev, void* stream);
+/* One pipelined Monte Carlo step from a HOST record (same pipeline, stream contract and ekf_batch_host_sync as
+ * ekf_batch_step_host_async): H2D of the record (< 200 bytes), perturbation generator, fused step, optionally
+ * sse_dev[b] += squared position error against (gt_x, gt_y) when score != 0, and the 12 pose moments copied to
+ * pose_moments_host (may be NULL). Per step the host sends the common record and receives 96 bytes.             */
+int ekf_batch_mc_step_host_async(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int m,
+                                 const double* record_host, const double* sigma4, int score, double gt_x, double gt_y,
+                                 double* sse_dev, double* pose_moments_host, void* stream);
 
 /* ---- large-map mode: ONE filter, P streamed from HBM, optional row-block shard ------------------------- */
 typedef struct ekf_lm ekf_lm_t;

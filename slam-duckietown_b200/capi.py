@@ -31,6 +31,7 @@ _p = C.c_void_p
 _i = C.c_int
 _l = C.c_int64
 _d = C.c_double
+_u64 = C.c_uint64
 
 # name -> (restype, argtypes); every symbol include/ekf_b200.h declares
 SIGNATURES = {
@@ -59,6 +60,11 @@ SIGNATURES = {
     "ekf_batch_associate_overflow_count": (_i, [_p, C.POINTER(_l)]),
     "ekf_batch_accumulate_ate": (_i, [_p, _d, _d, _p, _p]),
     "ekf_batch_moments": (_i, [_p, _p, _p]),
+    "ekf_batch_pose_moments": (_i, [_p, _p, _p]),
+    "ekf_batch_mc_record_doubles": (_i, [_i, C.POINTER(_l)]),
+    "ekf_batch_perturb": (_i, [_p, _u64, _u64, _u64, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "ekf_batch_detection_noise": (_i, [_p, _u64, _u64, _u64, _i, _d, _p, _p, _p]),
+    "ekf_batch_mc_step_host_async": (_i, [_p, _u64, _u64, _u64, _i, _p, _p, _i, _d, _d, _p, _p, _p]),
     "ekf_lm_layout": (_i, [_i, C.POINTER(_i), C.POINTER(_l)]),
     "ekf_lm_create": (_i, [_i, _i, C.POINTER(_p)]),
     "ekf_lm_destroy": (_i, [_p]),

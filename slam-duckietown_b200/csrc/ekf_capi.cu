@@ -68,6 +68,8 @@ struct ekf_batch {
   int64_t pipe_step = 0;
   cudaEvent_t ev_caller = nullptr;  // orders the handle's streams after the caller's stream
   double* mom_partial = nullptr;  // scratch of ekf_batch_moments
+  double* pose_partial = nullptr;  // scratch of ekf_batch_pose_moments
+  double* mc_record[2] = {nullptr, nullptr};  // device copies of the common step record (one per staging set)
 };
 
 struct ekf_lm {
@@ -160,6 +162,9 @@ int ekf_batch_destroy(ekf_batch_t* h) {
   cudaSetDevice(h->device);
   cudaFree(h->faults);
   cudaFree(h->mom_partial);
+  cudaFree(h->pose_partial);
+  cudaFree(h->mc_record[0]);
+  cudaFree(h->mc_record[1]);
   cudaFree(h->d_ang);
   cudaFree(h->d_lin);
   cudaFree(h->d_rng);
@@ -346,16 +351,20 @@ int ekf_batch_step_host(ekf_batch_t* h, const double* ang_host, const double* li
   return EKF_OK;
 }
 
-// Pipelined variant of ekf_batch_step_host: returns as soon as the work is enqueued. Step i's H2D copies run on
-// a copy-in stream while step i-1's kernel runs on the compute stream and step i-2's poses drain on a copy-out
-// stream (two staging sets, ordered by events). Host buffers must stay valid, and pose_host must not be read,
-// until ekf_batch_host_sync returns.
-int ekf_batch_step_host_async(ekf_batch_t* h, const double* ang_host, const double* lin_host,
-                              const int32_t* slot_host, const double* rng_host, const double* brg_host, int m,
-                              double* pose_host, void* stream) {
-  if (!h || !ang_host || !lin_host || !pose_host) return fail(EKF_EINVAL, "null argument");
-  if (m < 0 || m > ekf::BATCH_MAX_M) return fail(EKF_EINVAL, "m must be in [0, %d]", ekf::BATCH_MAX_M);
-  if (m > 0 && (!slot_host || !rng_host || !brg_host)) return fail(EKF_EINVAL, "observation arrays are null");
+// The pipeline behind both pipelined host entry points. Step i: `fill` puts the step's per-filter inputs into staging
+// set i & 1 on the copy-in stream (H2D copies, or one small copy + the on-device perturbation generator); the fused
+// step then runs on the compute stream; `post` turns the new state into the step's result in the set's result area
+// (every filter's pose, or the ensemble's pose moments) on the compute stream; the result drains to `out_host` on the
+// copy-out stream. Two staging sets ordered by events: fill(i) overlaps step(i-1) and drain(i-2).
+}  // extern "C" (templates cannot have C linkage)
+
+struct PipeSet {
+  double *ang, *lin, *rng, *brg, *result;
+  int32_t* slot;
+};
+
+template <typename Fill, typename Post>
+static int pipe_step(ekf_batch_t* h, int m, void* caller, void* out_host, size_t out_bytes, Fill fill, Post post) {
   CU(cudaSetDevice(h->device));
   const int64_t B = h->batch;
   const int M = ekf::BATCH_MAX_M;
@@ -371,40 +380,148 @@ int ekf_batch_step_host_async(ekf_batch_t* h, const double* ang_host, const doub
     }
   }
   const int set = (int)(h->pipe_step & 1);
-  double* d_ang = h->p_stage[set];
-  double* d_lin = d_ang + B;
-  double* d_rng = d_lin + B;
-  double* d_brg = d_rng + B * M;
-  double* d_pose = d_brg + B * M;
-  int32_t* d_slot = reinterpret_cast<int32_t*>(d_pose + B * 3);
+  PipeSet ps;
+  ps.ang = h->p_stage[set];
+  ps.lin = ps.ang + B;
+  ps.rng = ps.lin + B;
+  ps.brg = ps.rng + B * M;
+  ps.result = ps.brg + B * M;  // [B][3] doubles
+  ps.slot = reinterpret_cast<int32_t*>(ps.result + B * 3);
   // the state may have been touched on the caller's stream (init / step / pack) since the last host step
-  int rc = host_order_in(h, (cudaStream_t)stream, h->stream, nullptr);
+  int rc = host_order_in(h, (cudaStream_t)caller, h->stream, nullptr);
   if (rc != EKF_OK) return rc;
   // copy-in: the set is free once the kernel of step i-2 (its last reader) is done
   if (h->pipe_step >= 2) CU(cudaStreamWaitEvent(h->s_in, h->ev_done[set], 0));
-  CU(cudaMemcpyAsync(d_ang, ang_host, B * sizeof(double), cudaMemcpyHostToDevice, h->s_in));
-  CU(cudaMemcpyAsync(d_lin, lin_host, B * sizeof(double), cudaMemcpyHostToDevice, h->s_in));
-  if (m > 0) {
-    CU(cudaMemcpyAsync(d_slot, slot_host, B * m * sizeof(int32_t), cudaMemcpyHostToDevice, h->s_in));
-    CU(cudaMemcpyAsync(d_rng, rng_host, B * m * sizeof(double), cudaMemcpyHostToDevice, h->s_in));
-    CU(cudaMemcpyAsync(d_brg, brg_host, B * m * sizeof(double), cudaMemcpyHostToDevice, h->s_in));
-  }
+  rc = fill(ps, h->s_in);
+  if (rc != EKF_OK) return rc;
   CU(cudaEventRecord(h->ev_in[set], h->s_in));
-  // compute: after this step's inputs have landed and the pose buffer of step i-2 has drained
+  // compute: after this step's inputs have landed and the result area of step i-2 has drained
   CU(cudaStreamWaitEvent(h->stream, h->ev_in[set], 0));
   if (h->pipe_step >= 2) CU(cudaStreamWaitEvent(h->stream, h->ev_out[set], 0));
-  rc = ekf_batch_step(h, d_ang, d_lin, d_slot, d_rng, d_brg, m, h->stream);
+  rc = ekf_batch_step(h, ps.ang, ps.lin, ps.slot, ps.rng, ps.brg, m, h->stream);
   if (rc != EKF_OK) return rc;
-  CU(ekf::batch_launch_pose(h->mu, d_pose, B, h->ld, h->stream));
+  rc = post(ps, h->stream);
+  if (rc != EKF_OK) return rc;
   CU(cudaEventRecord(h->ev_done[set], h->stream));
   // the caller's stream sees the state of this step from here on
-  CU(cudaStreamWaitEvent((cudaStream_t)stream, h->ev_done[set], 0));
+  CU(cudaStreamWaitEvent((cudaStream_t)caller, h->ev_done[set], 0));
   // copy-out
   CU(cudaStreamWaitEvent(h->s_out, h->ev_done[set], 0));
-  CU(cudaMemcpyAsync(pose_host, d_pose, B * 3 * sizeof(double), cudaMemcpyDeviceToHost, h->s_out));
+  if (out_host && out_bytes)
+    CU(cudaMemcpyAsync(out_host, ps.result, out_bytes, cudaMemcpyDeviceToHost, h->s_out));
   CU(cudaEventRecord(h->ev_out[set], h->s_out));
   ++h->pipe_step;
   return EKF_OK;
+}
+
+extern "C" {
+
+// Pipelined variant of ekf_batch_step_host: returns as soon as the work is enqueued. Host buffers must stay valid,
+// and pose_host must not be read, until ekf_batch_host_sync returns.
+int ekf_batch_step_host_async(ekf_batch_t* h, const double* ang_host, const double* lin_host,
+                              const int32_t* slot_host, const double* rng_host, const double* brg_host, int m,
+                              double* pose_host, void* stream) {
+  if (!h || !ang_host || !lin_host || !pose_host) return fail(EKF_EINVAL, "null argument");
+  if (m < 0 || m > ekf::BATCH_MAX_M) return fail(EKF_EINVAL, "m must be in [0, %d]", ekf::BATCH_MAX_M);
+  if (m > 0 && (!slot_host || !rng_host || !brg_host)) return fail(EKF_EINVAL, "observation arrays are null");
+  const int64_t B = h->batch;
+  return pipe_step(
+      h, m, stream, pose_host, (size_t)B * 3 * sizeof(double),
+      [&](const PipeSet& ps, cudaStream_t st) -> int {
+        CU(cudaMemcpyAsync(ps.ang, ang_host, B * sizeof(double), cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(ps.lin, lin_host, B * sizeof(double), cudaMemcpyHostToDevice, st));
+        if (m > 0) {
+          CU(cudaMemcpyAsync(ps.slot, slot_host, B * m * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+          CU(cudaMemcpyAsync(ps.rng, rng_host, B * m * sizeof(double), cudaMemcpyHostToDevice, st));
+          CU(cudaMemcpyAsync(ps.brg, brg_host, B * m * sizeof(double), cudaMemcpyHostToDevice, st));
+        }
+        return EKF_OK;
+      },
+      [&](const PipeSet& ps, cudaStream_t st) -> int {
+        CU(ekf::batch_launch_pose(h->mu, ps.result, B, h->ld, st));
+        return EKF_OK;
+      });
+}
+
+// ---- Monte Carlo replay with the perturbations generated on the device --------------------------------------
+int ekf_batch_mc_record_doubles(int m, int64_t* doubles) {
+  if (m < 0 || m > ekf::BATCH_MAX_M || !doubles) return fail(EKF_EINVAL, "m out of range or null argument");
+  *doubles = 2 + 2 * m + (m + 1) / 2;
+  return EKF_OK;
+}
+
+static int mc_fill_args(ekf_batch_t* h, ekf::PerturbArgs& a, uint64_t seed, uint64_t step, uint64_t first_filter, int m,
+                        const double* sigma4) {
+  if (m < 0 || m > ekf::BATCH_MAX_M) return fail(EKF_EINVAL, "m must be in [0, %d]", ekf::BATCH_MAX_M);
+  if (!sigma4) return fail(EKF_EINVAL, "sigma4 is null");
+  if (step > 0xffffffffull) return fail(EKF_EINVAL, "step must fit 32 bits");
+  a.batch = h->batch; a.seed = seed; a.first_filter = first_filter; a.step = (uint32_t)step; a.m = m;
+  a.s_ang = sigma4[0]; a.s_lin = sigma4[1]; a.s_rng = sigma4[2]; a.s_brg = sigma4[3];
+  return EKF_OK;
+}
+
+int ekf_batch_perturb(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int m,
+                      const double* record_dev, const double* sigma4, double* ang_dev, double* lin_dev,
+                      int32_t* slot_dev, double* rng_dev, double* brg_dev, void* stream) {
+  if (!h || !record_dev || !ang_dev || !lin_dev) return fail(EKF_EINVAL, "null argument");
+  if (m > 0 && (!slot_dev || !rng_dev || !brg_dev)) return fail(EKF_EINVAL, "observation arrays are null");
+  ekf::PerturbArgs a{};
+  const int rc = mc_fill_args(h, a, seed, step, first_filter, m, sigma4);
+  if (rc != EKF_OK) return rc;
+  a.record = record_dev; a.ang = ang_dev; a.lin = lin_dev; a.slot = slot_dev; a.rng = rng_dev; a.brg = brg_dev;
+  CU(cudaSetDevice(h->device));
+  CU(ekf::batch_launch_perturb(a, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf_batch_detection_noise(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int n_det,
+                              double sigma, double* noise_tx_dev, double* noise_tz_dev, void* stream) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  if (n_det < 0 || step > 0xffffffffull) return fail(EKF_EINVAL, "n_det < 0 or step beyond 32 bits");
+  if (n_det > 0 && (!noise_tx_dev || !noise_tz_dev)) return fail(EKF_EINVAL, "null argument");
+  CU(cudaSetDevice(h->device));
+  CU(ekf::batch_launch_detection_noise(h->batch, seed, first_filter, (uint32_t)step, n_det, sigma, noise_tx_dev,
+                                       noise_tz_dev, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf_batch_pose_moments(ekf_batch_t* h, double* sums_dev, void* stream) {
+  if (!h || !sums_dev) return fail(EKF_EINVAL, "null argument");
+  if (!h->mu) return fail(EKF_ESTATE, "state not bound");
+  CU(cudaSetDevice(h->device));
+  if (!h->pose_partial) CU(cudaMalloc(&h->pose_partial, sizeof(double) * ekf::POSE_MOM_CTAS * 9));
+  CU(ekf::batch_launch_pose_moments(h->mu, h->ld, h->batch, h->pose_partial, sums_dev, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf_batch_mc_step_host_async(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int m,
+                                 const double* record_host, const double* sigma4, int score, double gt_x, double gt_y,
+                                 double* sse_dev, double* pose_moments_host, void* stream) {
+  if (!h || !record_host) return fail(EKF_EINVAL, "null argument");
+  if (score && !sse_dev) return fail(EKF_EINVAL, "score requested without an sse buffer");
+  ekf::PerturbArgs a{};
+  const int rc0 = mc_fill_args(h, a, seed, step, first_filter, m, sigma4);
+  if (rc0 != EKF_OK) return rc0;
+  CU(cudaSetDevice(h->device));
+  if (!h->pose_partial) CU(cudaMalloc(&h->pose_partial, sizeof(double) * ekf::POSE_MOM_CTAS * 9));
+  if (!h->mc_record[0])
+    for (int i = 0; i < 2; ++i) CU(cudaMalloc(&h->mc_record[i], sizeof(double) * 32));
+  const int set = (int)(h->pipe_step & 1);
+  const size_t rec_bytes = sizeof(double) * (size_t)(2 + 2 * m + (m + 1) / 2);
+  return pipe_step(
+      h, m, stream, pose_moments_host, pose_moments_host ? 12 * sizeof(double) : 0,
+      [&](const PipeSet& ps, cudaStream_t st) -> int {
+        CU(cudaMemcpyAsync(h->mc_record[set], record_host, rec_bytes, cudaMemcpyHostToDevice, st));
+        a.record = h->mc_record[set];
+        a.ang = ps.ang; a.lin = ps.lin; a.slot = ps.slot; a.rng = ps.rng; a.brg = ps.brg;
+        CU(ekf::batch_launch_perturb(a, st));
+        return EKF_OK;
+      },
+      [&](const PipeSet& ps, cudaStream_t st) -> int {
+        if (score) CU(ekf::batch_launch_ate(h->mu, h->ld, h->batch, gt_x, gt_y, sse_dev, st));
+        if (pose_moments_host) CU(ekf::batch_launch_pose_moments(h->mu, h->ld, h->batch, h->pose_partial, ps.result, st));
+        return EKF_OK;
+      });
 }
 
 int ekf_batch_host_sync(ekf_batch_t* h) {

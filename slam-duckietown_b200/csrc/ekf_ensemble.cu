@@ -14,6 +14,7 @@
 // whose layout is the step kernel's.
 #include "ekf_common.cuh"
 #include "ekf_ensemble.h"
+#include "ekf_philox.cuh"
 
 namespace ekf {
 
@@ -175,6 +176,131 @@ cudaError_t batch_launch_moments(const double* mu, int64_t mu_stride, int64_t ba
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   batch_moments_final_kernel<<<(E + 255) / 256, 256, 0, st>>>(partial, ctas, E, sums);
+  return cudaGetLastError();
+}
+
+
+// -------------------------------------------------------------------------------------------------------
+// Monte Carlo perturbations on the device. One thread per (filter, stream): stream 0 -> (ang, lin), stream 1 + k ->
+// (rng_k, brg_k). ~60 integer + ~50 fp64 instructions per normal, no memory traffic besides the outputs
+// (16 + 20 m bytes per filter, < 1 % of a filter-step's bytes).
+// -------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) batch_perturb_kernel(PerturbArgs a) {
+  const int per = 1 + a.m;
+  const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t b = tid / per;
+  if (b >= a.batch) return;
+  const int q = (int)(tid - b * per);
+  double z0, z1;
+  normal_pair(a.seed, a.first_filter + (uint64_t)b, a.step, q == 0 ? kStreamOdometry : kStreamObservation0 + (q - 1),
+              &z0, &z1);
+  if (q == 0) {
+    a.ang[b] = __dadd_rn(a.record[0], __dmul_rn(a.s_ang, z0));
+    a.lin[b] = __dadd_rn(a.record[1], __dmul_rn(a.s_lin, z1));
+  } else {
+    const int k = q - 1;
+    const int32_t* slots = reinterpret_cast<const int32_t*>(a.record + 2 + 2 * a.m);
+    a.slot[b * a.m + k] = slots[k];
+    a.rng[b * a.m + k] = __dadd_rn(a.record[2 + k], __dmul_rn(a.s_rng, z0));
+    a.brg[b * a.m + k] = __dadd_rn(a.record[2 + a.m + k], __dmul_rn(a.s_brg, z1));
+  }
+}
+
+cudaError_t batch_launch_perturb(const PerturbArgs& a, cudaStream_t st) {
+  if (a.m < 0 || a.m > ASSOC_MAX_M) return cudaErrorInvalidValue;
+  const int64_t threads = a.batch * (1 + a.m);
+  batch_perturb_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) batch_detection_noise_kernel(int64_t batch, uint64_t seed, uint64_t first_filter,
+                                                                    uint32_t step, int n_det, double sigma,
+                                                                    double* __restrict__ ntx, double* __restrict__ ntz) {
+  const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int d = blockIdx.y;
+  if (b >= batch || d >= n_det) return;
+  double z0, z1;
+  normal_pair(seed, first_filter + (uint64_t)b, step, kStreamDetection0 + d, &z0, &z1);
+  ntx[(int64_t)d * batch + b] = __dmul_rn(sigma, z0);
+  ntz[(int64_t)d * batch + b] = __dmul_rn(sigma, z1);
+}
+
+cudaError_t batch_launch_detection_noise(int64_t batch, uint64_t seed, uint64_t first_filter, uint32_t step, int n_det,
+                                         double sigma, double* noise_tx, double* noise_tz, cudaStream_t st) {
+  if (n_det <= 0) return cudaSuccess;
+  dim3 grid((unsigned)((batch + 255) / 256), (unsigned)n_det);
+  batch_detection_noise_kernel<<<grid, 256, 0, st>>>(batch, seed, first_filter, step, n_det, sigma, noise_tx, noise_tz);
+  return cudaGetLastError();
+}
+
+// -------------------------------------------------------------------------------------------------------
+// Ensemble moments of the robot pose (the per-step result of a Monte Carlo replay: mean trajectory + its spread).
+// Pass 1: thread per filter (grid-stride), 9 running sums (3 first, 6 distinct second moments), fixed-order warp
+// shuffle tree, then the warps of the CTA in index order. Pass 2: one CTA adds the per-CTA partials, lane-strided
+// then by the same shuffle tree. No atomics: two calls give identical bits.
+// -------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_tree_sum(double v) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v = __dadd_rn(v, __shfl_down_sync(0xffffffffu, v, off));
+  return v;
+}
+
+__global__ void __launch_bounds__(256) batch_pose_moments_partial_kernel(const double* __restrict__ mu, int64_t mu_stride,
+                                                                         int64_t batch, double* __restrict__ partial) {
+  __shared__ double sw[8][9];
+  double acc[9];
+#pragma unroll
+  for (int q = 0; q < 9; ++q) acc[q] = 0.0;
+  for (int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; b < batch; b += (int64_t)gridDim.x * blockDim.x) {
+    const double x = mu[b * mu_stride], y = mu[b * mu_stride + 1], t = mu[b * mu_stride + 2];
+    acc[0] = __dadd_rn(acc[0], x);
+    acc[1] = __dadd_rn(acc[1], y);
+    acc[2] = __dadd_rn(acc[2], t);
+    acc[3] = fma(x, x, acc[3]);
+    acc[4] = fma(x, y, acc[4]);
+    acc[5] = fma(x, t, acc[5]);
+    acc[6] = fma(y, y, acc[6]);
+    acc[7] = fma(y, t, acc[7]);
+    acc[8] = fma(t, t, acc[8]);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int q = 0; q < 9; ++q) {
+    const double v = warp_tree_sum(acc[q]);
+    if (lane == 0) sw[warp][q] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 9) {
+    double v = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) v = __dadd_rn(v, sw[w][threadIdx.x]);
+    partial[(int64_t)blockIdx.x * 9 + threadIdx.x] = v;
+  }
+}
+
+__global__ void __launch_bounds__(288) batch_pose_moments_final_kernel(const double* __restrict__ partial, int ctas,
+                                                                       double* __restrict__ sums) {
+  const int q = threadIdx.x >> 5, lane = threadIdx.x & 31;  // warp q sums element q
+  double v = 0.0;
+  for (int c = lane; c < ctas; c += 32) v = __dadd_rn(v, partial[(int64_t)c * 9 + q]);
+  v = warp_tree_sum(v);
+  if (lane == 0) {
+    // sums[0..2] first moments; sums[3 + 3 i + k] the symmetric 3x3 second-moment block
+    static const int where[9][2] = {{0, -1}, {1, -1}, {2, -1}, {3, 3}, {4, 6}, {5, 9}, {7, 7}, {8, 10}, {11, 11}};
+    sums[where[q][0]] = v;
+    if (where[q][1] >= 0) sums[where[q][1]] = v;
+  }
+}
+
+cudaError_t batch_launch_pose_moments(const double* mu, int64_t mu_stride, int64_t batch, double* partial, double* sums,
+                                      cudaStream_t st) {
+  if (batch < 1) return cudaErrorInvalidValue;
+  const int64_t want = (batch + 255) / 256;
+  const int ctas = (int)(want < POSE_MOM_CTAS ? want : POSE_MOM_CTAS);
+  batch_pose_moments_partial_kernel<<<ctas, 256, 0, st>>>(mu, mu_stride, batch, partial);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  batch_pose_moments_final_kernel<<<1, 288, 0, st>>>(partial, ctas, sums);
   return cudaGetLastError();
 }
 

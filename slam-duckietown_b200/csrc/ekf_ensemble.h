@@ -24,6 +24,30 @@ struct AssocArgs {
 };
 
 cudaError_t batch_launch_associate(const AssocArgs& a, cudaStream_t st);
+
+// Monte Carlo inputs generated on the device (ekf_philox.cuh): every filter gets the step's COMMON odometry /
+// observations plus its own perturbation, a pure function of (seed, first_filter + b, step, stream).
+// record (device): doubles [ang, lin, rng[0..m), brg[0..m)] followed by int32 slot[0..m)
+struct PerturbArgs {
+  int64_t batch;
+  uint64_t seed, first_filter;
+  uint32_t step;
+  int m;
+  const double* record;
+  double s_ang, s_lin, s_rng, s_brg;  // standard deviations of the four perturbations
+  double *ang, *lin;                  // out [B]
+  int32_t* slot;                      // out [B][m]
+  double *rng, *brg;                  // out [B][m]
+};
+cudaError_t batch_launch_perturb(const PerturbArgs& a, cudaStream_t st);
+// noise_tx / noise_tz [n_det][B] = sigma * the normal pair of stream kStreamDetection0 + d (per-filter detection noise)
+cudaError_t batch_launch_detection_noise(int64_t batch, uint64_t seed, uint64_t first_filter, uint32_t step, int n_det,
+                                         double sigma, double* noise_tx, double* noise_tz, cudaStream_t st);
+// ensemble moments of the robot pose only: sums[0..2] = sum_b (x, y, theta), sums[3 + 3 i + k] = sum_b pose_i pose_k;
+// two passes, fixed summation order; partial: scratch [POSE_MOM_CTAS][12]
+constexpr int POSE_MOM_CTAS = 1184;  // 8 x 148 SMs
+cudaError_t batch_launch_pose_moments(const double* mu, int64_t mu_stride, int64_t batch, double* partial, double* sums,
+                                      cudaStream_t st);
 constexpr int MOM_CTAS = 592;  // 4 x 148 SMs: partial sums of the ensemble moments
 // sums[n + n*n] = (sum_b mu_b, sum_b mu_b mu_b^T) in a fixed order; partial: scratch [MOM_CTAS][n + n*n]
 cudaError_t batch_launch_moments(const double* mu, int64_t mu_stride, int64_t batch, int n, double* partial,

@@ -413,6 +413,69 @@ class BatchedEKF:
         capi.call("ekf_batch_moments", self._h, _ptr(out), _stream_ptr(self.torch))
         return out
 
+    def pose_moments(self, out=None):
+        """(sum_b pose_b, sum_b pose_b pose_b^T) of the robot pose over this handle's filters: 12 doubles on the device."""
+        if out is None:
+            out = self.torch.empty(12, dtype=self.torch.float64, device=self.dev)
+        capi.call("ekf_batch_pose_moments", self._h, _ptr(out), _stream_ptr(self.torch))
+        return out
+
+    # ---- Monte Carlo perturbations generated on the device (counter-based: seed, global filter index, step) ----
+    @staticmethod
+    def mc_record(ang, lin, slots=(), rngs=(), brgs=(), out=None):
+        """Pack one step's COMMON inputs: doubles [ang, lin, rng[0..m), brg[0..m)] followed by int32 slot[0..m).
+        Returns a numpy float64 array (or fills ``out``, e.g. a pinned torch tensor's numpy view)."""
+        m = len(slots)
+        n = 2 + 2 * m + (m + 1) // 2
+        rec = np.zeros(n) if out is None else out
+        assert rec.dtype == np.float64 and rec.size >= n
+        rec[0], rec[1] = float(ang), float(lin)
+        rec[2:2 + m] = np.asarray(rngs, dtype=np.float64)
+        rec[2 + m:2 + 2 * m] = np.asarray(brgs, dtype=np.float64)
+        rec[2 + 2 * m:n].view(np.int32)[:m] = np.asarray(slots, dtype=np.int32)
+        return rec
+
+    def perturb(self, seed, step, record_dev, m, sigma4, first_filter=0):
+        """Per-filter (ang, lin, slot, rng, brg) DEVICE tensors for ``step`` from a device-resident common record."""
+        t = self.torch
+        ang = t.empty(self.batch, dtype=t.float64, device=self.dev)
+        lin = t.empty(self.batch, dtype=t.float64, device=self.dev)
+        slot = t.empty((self.batch, m), dtype=t.int32, device=self.dev)
+        rng = t.empty((self.batch, m), dtype=t.float64, device=self.dev)
+        brg = t.empty((self.batch, m), dtype=t.float64, device=self.dev)
+        sg = (C.c_double * 4)(*[float(x) for x in sigma4])
+        z = C.c_void_p(0)
+        capi.call("ekf_batch_perturb", self._h, int(seed), int(step), int(first_filter), int(m), _ptr(record_dev), sg,
+                  _ptr(ang), _ptr(lin), _ptr(slot) if m else z, _ptr(rng) if m else z, _ptr(brg) if m else z,
+                  _stream_ptr(t))
+        return ang, lin, slot, rng, brg
+
+    def detection_noise(self, seed, step, n_det, sigma, first_filter=0):
+        """(noise_tx, noise_tz) device tensors (n_det, B) for ``associate``."""
+        t = self.torch
+        ntx = t.empty((int(n_det), self.batch), dtype=t.float64, device=self.dev)
+        ntz = t.empty((int(n_det), self.batch), dtype=t.float64, device=self.dev)
+        if n_det:
+            capi.call("ekf_batch_detection_noise", self._h, int(seed), int(step), int(first_filter), int(n_det),
+                      float(sigma), _ptr(ntx), _ptr(ntz), _stream_ptr(t))
+        return ntx, ntz
+
+    def mc_step_host_async(self, seed, step, record_host, m, sigma4, first_filter=0, gt=None, sse=None,
+                           pose_moments_out=None):
+        """One pipelined Monte Carlo step from a HOST record (``mc_record``; ideally pinned): the perturbations are
+        generated on the device, the fused step runs, ``sse`` (device, (B,)) accumulates the squared position error
+        against ``gt`` when given, and the 12 pose moments land in ``pose_moments_out`` (host, pinned) after
+        ``host_sync()``."""
+        def hp(a):
+            return C.c_void_p(a.data_ptr() if hasattr(a, "data_ptr") else a.ctypes.data)
+        sg = (C.c_double * 4)(*[float(x) for x in sigma4])
+        z = C.c_void_p(0)
+        score = gt is not None and sse is not None
+        capi.call("ekf_batch_mc_step_host_async", self._h, int(seed), int(step), int(first_filter), int(m),
+                  hp(record_host), sg, int(score), float(gt[0]) if score else 0.0, float(gt[1]) if score else 0.0,
+                  _ptr(sse) if score else z, hp(pose_moments_out) if pose_moments_out is not None else z,
+                  _stream_ptr(self.torch))
+
     def step_host(self, ang, lin, slot, rng, brg, pose_out):
         """End-to-end step with HOST (ideally pinned) torch tensors / numpy arrays: H2D, step, D2H of the
         pose (B, 3) into ``pose_out``; synchronous."""

@@ -30,12 +30,16 @@ def compact_tag_table(windows, ignore_tags=()):
 
 
 def monte_carlo_replay(windows, batch, n_landmarks, m, motion_var, meas_var, det_sigma=0.0, seed=0,
-                       ignore_tags=None, device=0, joseph=False, on_step=None):
+                       ignore_tags=None, device=0, joseph=False, on_step=None, first_filter=0):
     """Returns dict(rmse (B,), pose (B,3), n_landmarks_seen (B,), faults, overflows, steps, tag_table (tag id ->
     compact index), tag_slot (n_tags, B) per-member slot of each compact tag, filter=BatchedEKF).
 
     motion_var / meas_var: scalars or (B,) arrays (MOTION_MODEL_VARIANCE / MEASUREMENT_MODEL_VARIANCE per member);
-    det_sigma: std-dev (m) of the per-member Gaussian perturbation of each detection's pose_t[0] / pose_t[2]."""
+    det_sigma: std-dev (m) of the per-member Gaussian perturbation of each detection's pose_t[0] / pose_t[2], drawn
+    ON the device by the counter-based generator (ekf_batch_detection_noise): a pure function of (seed, first_filter +
+    b, window index, detection index), so a member's inputs are the same whatever the sharding and can be regenerated
+    on the host (oracle/mc_noise.py:detection_noise) for per-member parity checks.
+    first_filter: global index of this handle's filter 0 (rank r of a filter-sharded ensemble passes its range start)."""
     import torch
     ignore = tuple(eb._flag("IGNORE_TAGS")) if ignore_tags is None else tuple(ignore_tags)
     f = eb.BatchedEKF(batch, n_landmarks, device=device)
@@ -47,21 +51,18 @@ def monte_carlo_replay(windows, batch, n_landmarks, m, motion_var, meas_var, det
     table = compact_tag_table(windows, ignore)
     tag_slot, n_seen = f.new_slot_table(max(len(table), 1))
     sse = torch.zeros(batch, dtype=torch.float64, device=dev)
-    gen = torch.Generator(device=dev)
-    gen.manual_seed(int(seed))
     scored = 0
 
     def full(v):
         return torch.full((batch,), int(v), dtype=torch.int32, device=dev)
-    for w in windows:
+    for step, w in enumerate(windows):
         d = len(w.tag_id)
         compact = torch.tensor([table.get(int(t), -1) for t in w.tag_id], dtype=torch.int32, device=dev)
         tx = torch.from_numpy(w.tx).to(dev)
         tz = torch.from_numpy(w.tz).to(dev)
         ntx = ntz = None
         if det_sigma > 0.0 and d:
-            ntx = torch.randn((d, batch), dtype=torch.float64, device=dev, generator=gen) * det_sigma
-            ntz = torch.randn((d, batch), dtype=torch.float64, device=dev, generator=gen) * det_sigma
+            ntx, ntz = f.detection_noise(seed, step, d, det_sigma, first_filter)
         slot, rng, brg = f.associate(compact, tx, tz, tag_slot, n_seen, m, ntx, ntz)
         f.step_ticks(full(w.ticks_l), full(w.ticks_r), full(w.prev_l), full(w.prev_r), WHEEL_RADIUS, BASELINE,
                      RESOLUTION, slot, rng, brg)

@@ -1,0 +1,162 @@
+"""The counter-based Monte Carlo perturbation generator: numpy twin (oracle/mc_noise.py) on CPU — Random123 known
+answers, accuracy of the inverse CDF — and, on the GPU, the device generator == the twin BIT FOR BIT, per-member
+parity of a generated Monte Carlo replay against the oracle fed the same generated numbers, and invariance of every
+member under re-sharding of the ensemble."""
+import numpy as np
+import pytest
+
+from conftest import assert_parity
+from oracle import ekf_oracle as eo, mc_noise as mn
+
+
+def test_philox4x32_10_known_answers():
+    """Random123 kat_vectors (philox4x32, 10 rounds)."""
+    kat = [((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+           ((0xffffffff,) * 4, (0xffffffff,) * 2, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+           ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0),
+            (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]
+    for ctr, key, want in kat:
+        got = mn.philox4x32_10(*ctr, *key)
+        assert tuple(int(x) for x in got) == want
+
+
+def test_uniforms_strictly_inside_unit_interval():
+    lo = mn.uniform52(np.array([0], dtype=np.uint32), np.array([0], dtype=np.uint32))
+    hi = mn.uniform52(np.array([0xffffffff], dtype=np.uint32), np.array([0xffffffff], dtype=np.uint32))
+    assert 0.0 < lo[0] == 2.0 ** -53 and hi[0] == 1.0 - 2.0 ** -53 < 1.0
+
+
+def test_inverse_cdf_and_log_accuracy():
+    from scipy.special import ndtri
+    u = np.concatenate([np.linspace(1e-10, 0.999999, 200001), 1 - np.logspace(-16, -1, 1000), np.logspace(-300, -1, 3000),
+                        [2.0 ** -53, 1 - 2.0 ** -53, 0.5, 0.075, 0.925]])
+    u = u[(u > 0) & (u < 1)]
+    z, zr = mn.normal_icdf(u), ndtri(u)
+    assert np.max(np.abs(z - zr) / np.maximum(np.abs(zr), 1e-3)) < 5e-15
+    x = np.concatenate([np.logspace(-300, 0, 5000), np.linspace(1e-3, 0.5, 5000)])
+    assert np.max(np.abs(mn.det_log(x) - np.log(x)) / np.maximum(np.abs(np.log(x)), 1e-3)) < 1e-15
+
+
+def test_normal_pairs_look_normal_and_streams_are_independent():
+    f = np.arange(400000)
+    z0, z1 = mn.normal_pair(11, f, 5, 0)
+    y0, _ = mn.normal_pair(11, f, 5, 1)
+    w0, _ = mn.normal_pair(11, f, 6, 0)
+    for z in (z0, z1, y0, w0):
+        assert abs(z.mean()) < 0.01 and abs(z.std() - 1.0) < 0.01
+        assert abs(np.mean(z ** 4) - 3.0) < 0.1
+    for a, b in ((z0, z1), (z0, y0), (z0, w0)):
+        assert abs(np.corrcoef(a, b)[0, 1]) < 0.01
+    a0, _ = mn.normal_pair(11, f + (1 << 33), 5, 0)          # the high word of the filter index is part of the counter
+    assert not np.array_equal(a0, z0)
+
+
+@pytest.fixture(scope="module")
+def eb():
+    import torch
+    assert torch.cuda.is_available()
+    from slam_duckietown_b200 import capi, ekf_bindings
+    capi.lib()
+    return ekf_bindings
+
+
+@pytest.mark.gpu
+def test_device_generator_equals_numpy_twin_bitwise(eb):
+    import torch
+    B, m = 50021, 3
+    f = eb.BatchedEKF(B, 8)
+    sigma = (0.01, 0.003, 0.02, 0.025)
+    for seed, step, first in ((7, 0, 0), (2 ** 40 + 5, 123456, 3 * 2 ** 32 + 17)):
+        rec = f.mc_record(0.08, 0.05, [4, -1, 2], [0.9, 0.0, 1.2], [0.3, 0.0, -0.4])
+        ang, lin, slot, rng, brg = f.perturb(seed, step, torch.from_numpy(rec).to(f.dev), m, sigma, first)
+        a, l_, s_, r_, b_ = mn.perturb_step(seed, first, B, step, 0.08, 0.05, [4, -1, 2], [0.9, 0.0, 1.2], [0.3, 0.0, -0.4], sigma)
+        assert np.array_equal(ang.cpu().numpy(), a) and np.array_equal(lin.cpu().numpy(), l_)
+        assert np.array_equal(slot.cpu().numpy(), s_)
+        assert np.array_equal(rng.cpu().numpy(), r_) and np.array_equal(brg.cpu().numpy(), b_)
+        ntx, ntz = f.detection_noise(seed, step, 5, 0.02, first)
+        tx, tz = mn.detection_noise(seed, first, B, step, 5, 0.02)
+        assert np.array_equal(ntx.cpu().numpy(), tx) and np.array_equal(ntz.cpu().numpy(), tz)
+
+
+@pytest.mark.gpu
+def test_pose_moments_match_numpy_and_are_deterministic(eb):
+    import torch
+    from slam_duckietown_b200 import workloads as wl
+    for B in (37, 70001, 400000):
+        w = wl.make_batched(B, 8, 2, steps=3)
+        f = eb.BatchedEKF(B, 8)
+        f.set_noise(w.motion_var, w.meas_var)
+        f.init(0.1)
+        for t in range(3):
+            f.step(*(torch.from_numpy(np.ascontiguousarray(a[t])).to(f.dev) for a in (w.ang, w.lin, w.slot, w.rng, w.brg)))
+        s1, s2 = f.pose_moments().cpu().numpy(), f.pose_moments().cpu().numpy()
+        assert np.array_equal(s1, s2)
+        pose = f.mu[:, :3].cpu().numpy()
+        want = np.concatenate([pose.sum(0), (pose.T @ pose).ravel()])
+        assert np.max(np.abs(s1 - want)) <= 1e-12 * max(1.0, np.abs(want).max()) * np.log2(B + 1)
+        full = f.moments().cpu().numpy()
+        n = f.n
+        np.testing.assert_allclose(s1[:3], full[:3], rtol=1e-12, atol=1e-12)
+        np.testing.assert_allclose(s1[3:].reshape(3, 3), full[n:].reshape(n, n)[:3, :3], rtol=1e-12, atol=1e-12)
+
+
+@pytest.mark.gpu
+def test_generated_monte_carlo_replay_per_member_parity_and_sharding_invariance(eb):
+    """B members replay one common trajectory through ekf_batch_mc_step_host_async (record H2D, on-device
+    perturbations, fused step, ATE, pose moments). (1) sampled members == the oracle fed the numbers the numpy twin
+    generates for them; (2) the same ensemble split into two handles with first_filter offsets gives every member the
+    identical bits; (3) ATE and the per-step pose moments agree with host recomputation."""
+    import torch
+    from slam_duckietown_b200 import workloads as wl
+    B, L, m, seed = 6000, 8, 2, 20261105
+    sigma = (0.01, 0.003, 0.02, 0.02)
+    base = wl.make_batched(1, L, m, steps=24)                       # the common trajectory: filter 0's unperturbed inputs
+    rs = np.random.default_rng(1)
+    mv, mm = np.exp(rs.uniform(np.log(0.05), np.log(1.0), B)), np.exp(rs.uniform(np.log(0.05), np.log(1.5), B))
+    gts = [(0.01 * t, -0.005 * t) for t in range(base.steps)]
+
+    def run(lo, hi):
+        f = eb.BatchedEKF(hi - lo, L)
+        f.set_noise(mv[lo:hi], mm[lo:hi])
+        f.init(0.1)
+        sse = torch.zeros(hi - lo, dtype=torch.float64, device=f.dev)
+        recs = [torch.from_numpy(f.mc_record(base.ang[t, 0], base.lin[t, 0], base.slot[t, 0], base.rng[t, 0],
+                                             base.brg[t, 0])).pin_memory() for t in range(base.steps)]
+        moms = [torch.zeros(12, dtype=torch.float64).pin_memory() for _ in range(base.steps)]
+        for t in range(base.steps):
+            f.mc_step_host_async(seed, t, recs[t], m, sigma, first_filter=lo, gt=gts[t], sse=sse, pose_moments_out=moms[t])
+        f.host_sync()
+        assert f.fault_count() == 0 and f.nonfinite_count() == 0
+        mu, p = f.state()
+        return mu, p, sse.cpu().numpy(), np.stack([x.numpy().copy() for x in moms]), f
+    mu, p, sse, moms, f = run(0, B)
+    # (1) per-member parity against the oracle fed the twin's numbers
+    n = 3 + 2 * L
+    gen = [mn.perturb_step(seed, 0, B, t, base.ang[t, 0], base.lin[t, 0], base.slot[t, 0], base.rng[t, 0],
+                           base.brg[t, 0], sigma) for t in range(base.steps)]
+    sse_ref = np.zeros(B)
+    for b in list(range(0, B, 97)) + [B - 1]:
+        m_o, c_o, nk = np.zeros(n), np.zeros((n, n)), 0
+        c_o[:3, :3] = np.eye(3) * 0.1
+        fl = eo.Flags(motion_var=float(mv[b]), meas_var=float(mm[b]))
+        for t in range(base.steps):
+            a, l_, s_, r_, b_ = gen[t]
+            obs = [(int(s_[b, k]), float(r_[b, k]), float(b_[b, k])) for k in range(m) if s_[b, k] >= 0]
+            m_o, c_o, nk = eo.step_from_observations(m_o, c_o, float(a[b]), float(l_[b]), obs, fl, nk)
+            sse_ref[b] += (m_o[0] - gts[t][0]) ** 2 + (m_o[1] - gts[t][1]) ** 2
+        assert_parity(mu[b], p[b], m_o, c_o, what=f"generated MC member {b}")
+        assert abs(sse[b] - sse_ref[b]) <= 1e-9 * max(1.0, sse_ref[b])
+    # (3) the last step's pose moments == numpy over the final state
+    pose = mu[:, :3]
+    want = np.concatenate([pose.sum(0), (pose.T @ pose).ravel()])
+    assert np.max(np.abs(moms[-1] - want)) <= 1e-11 * max(1.0, np.abs(want).max())
+    assert np.all(np.isfinite(moms)) and not np.array_equal(moms[0], moms[-1])
+    f.close()
+    # (2) re-sharded: two handles, global filter indices preserved
+    half = B // 2 + 7
+    mu_a, p_a, sse_a, _, fa = run(0, half)
+    mu_b, p_b, sse_b, _, fb = run(half, B)
+    assert np.array_equal(np.concatenate([mu_a, mu_b]), mu) and np.array_equal(np.concatenate([p_a, p_b]), p)
+    assert np.array_equal(np.concatenate([sse_a, sse_b]), sse)
+    fa.close()
+    fb.close()
