@@ -579,6 +579,117 @@ def bench_large_map(updates=60, warm=6):
                                    "(16 n^2 + 3 x 96 n bytes per step), bitwise equal to 3 ekf_lm_update calls"}}
 
 
+def _surrogate():
+    """The decoded-bag fixture (tests/golden/surrogate: events.csv + detections sidecar synthesised from the bundled
+    Vicon ground truth; the real .bag is not in the container)."""
+    import gzip
+    from slam_duckietown_b200 import events_io as io
+    d = os.path.join(ROOT, "tests", "golden", "surrogate")
+    with gzip.open(os.path.join(d, "events.csv.gz"), "rt") as fh:
+        lines = fh.readlines()
+    return lines, io.load_detections(os.path.join(d, "detections.npz"))
+
+
+def bench_bag_ensemble(local, members=65536, capacity=16, m=6):
+    """The workload north_star (3) describes — Monte Carlo noise replays of the SAME bag: 65,536 ensemble members
+    replay the decoded (surrogate) bag, 70 EKF steps, 13 landmarks (capacity 16, n = 35), up to 6 updates per step;
+    every member has its own MOTION / MEASUREMENT variance and its own perturbation of every detection (generated on
+    the device). Per step: detection noise -> association (a3/a4 per member) -> tick odometry + fused step
+    (batch_step_regw_kernel<16,6>) -> ATE. e2e = the whole monte_carlo_replay call from parsed windows to the
+    per-member RMSE on the host."""
+    import torch
+    from slam_duckietown_b200 import events_io as io, monte_carlo as mc
+    lines, dets = _surrogate()
+    wins = io.windows_from_events([io.parse_event_line(x) for x in lines], dets)
+    rs = np.random.default_rng(5)
+    mv = np.exp(rs.uniform(np.log(0.05), np.log(1.0), members))
+    mm = np.exp(rs.uniform(np.log(0.05), np.log(1.5), members))
+    out = None
+    secs = []
+    for rep in range(2):                                   # first pass warms allocations / module loads
+        if out is not None:
+            out["filter"].close()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        out = mc.monte_carlo_replay(wins, members, capacity, m, mv, mm, det_sigma=0.02, seed=7, device=local)
+        torch.cuda.synchronize()
+        secs.append(time.perf_counter() - t0)
+    f = out["filter"]
+    n = f.n
+    steps = out["steps"]
+    upd = float(np.mean([min(len(set(w.tag_id.tolist())), m) for w in wins]))
+    # the fused step alone, steady state: the last window's inputs re-launched (ticks odometry, m = 6 block)
+    args = out["last_step_args"]
+    for _ in range(3):
+        f.step_ticks_common(*args)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(20)]
+    for e0, e1 in ev:
+        e0.record()
+        f.step_ticks_common(*args)
+        e1.record()
+    torch.cuda.synchronize()
+    kms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    m_last = int((args[7][0] >= 0).sum())
+    bytes_step = bytes_per_filter_step(n, m)
+    res = {"metric": "EKF filter-steps/s (decoded-bag Monte Carlo, 65536 members, 13 landmarks)",
+           "value": members * steps / secs[-1], "unit": UNIT, "members": members, "steps": steps,
+           "capacity_landmarks": capacity, "landmarks_seen": int(out["n_landmarks_seen"].max()),
+           "updates_per_step_mean": upd, "observation_slots": m, "seconds": secs[-1], "first_pass_seconds": secs[0],
+           "faults": int(out["faults"]), "overflows": int(out["overflows"]),
+           "rmse_m": {"min": float(out["rmse"].min()), "median": float(np.median(out["rmse"])),
+                      "max": float(out["rmse"].max())},
+           "finite": bool(np.isfinite(out["rmse"]).all()) and f.nonfinite_count() == 0,
+           "e2e": {"value": members * steps / secs[-1], "unit": UNIT,
+                   "note": "whole monte_carlo_replay: per window the detections (a few hundred bytes) go to the "
+                           "device, everything per member stays there; the per-member RMSE (0.5 MB) comes back once"},
+           "step_kernel": {"ms": kms, "updates_in_timed_step": m_last,
+                           "roofline": roofline_block(bytes_step * members, kms, bytes_per_filter_step=bytes_step,
+                                                      kernel=f"batch_step_regw_kernel<{capacity},{m},1> (tick odometry)")}}
+    f.close()
+    torch.cuda.empty_cache()
+    return res
+
+
+def bench_config1():
+    """BASELINE.json configs[0]: the single-filter replay of the (surrogate) bag. Three drivers of the SAME 70 steps:
+    the restated event loop over the CUDA drop-in, the reference's UNCHANGED replay() over the CUDA drop-in, and the
+    reference's own replay() with its own numpy EKF on this host's CPU (one core). At n <= 29 the filter-step is a few
+    thousand flops: the scalar drop-in is bound by launch + PCIe round trips per call, the CPU by Python overhead."""
+    import tempfile
+    from oracle import ref_loader
+    from slam_duckietown_b200 import replay
+    lines, dets = _surrogate()
+    out = {"metric": "EKF steps/s, single-filter replay of the decoded (surrogate) bag", "steps": None}
+    replay.replay_events(lines, dets)                      # warm-up (allocations, kernels loaded)
+    t0 = time.perf_counter()
+    recs = replay.replay_events(lines, dets)
+    dt = time.perf_counter() - t0
+    out["steps"] = len(recs)
+    out["cuda_dropin_restated_loop"] = {"steps_per_s": len(recs) / dt, "ms_per_step": 1e3 * dt / len(recs)}
+    if ref_loader.reference_available():
+        mod = ref_loader.load_replay_module()
+        with tempfile.TemporaryDirectory() as tmp:
+            with open(os.path.join(tmp, "events.csv"), "w") as fh:
+                fh.writelines(lines)
+            t0 = time.perf_counter()
+            r2 = replay.drive_reference_replay(mod, tmp, dets)
+            dt2 = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            r3 = ref_loader.run_reference_replay(tmp, dets)
+            dt3 = time.perf_counter() - t0
+        out["cuda_dropin_unchanged_replay"] = {"steps_per_s": len(r2) / dt2, "ms_per_step": 1e3 * dt2 / len(r2)}
+        out["reference_cpu"] = {"steps_per_s": len(r3) / dt3, "ms_per_step": 1e3 * dt3 / len(r3), "cores": 1,
+                                "kind": "reference", "loaded_from": ref_loader.reference_kind()}
+        err = 0.0
+        for a, b in zip(r2, r3):
+            err = max(err, float(np.max(np.abs(a["mean"] - b["mean"])) / max(np.max(np.abs(b["mean"])), 1e-300)))
+        out["max_rel_mean_difference_vs_reference"] = err
+        out["final_state_dim"] = int(len(r3[-1]["mean"]))
+    else:
+        out["reference_cpu"] = {"unavailable": "reference neither at /root/reference nor compiled into oracle/_ref"}
+    return out
+
+
 def _seed_shard(f, w, dev, chunk_rows=4096):
     """P0 = A A^T / 64 + 0.1 I, this rank's rows only, built in row chunks (never 34 GB of temporaries)."""
     import torch
@@ -807,6 +918,8 @@ def run_own_arm(args, wk, world):
         if not args.no_large_map:
             line["large_map"] = bench_large_map()
             if args.workload == "B":
+                line["bag_ensemble"] = bench_bag_ensemble(local)
+                line["config1_replay"] = bench_config1()
                 wm = Workload("M", 1)
                 rm = BatchedRun(wm, local, rank, distinct=8)
                 line["small_filters"] = batched_object(wm, rm, 20, 3, 1, rank=0, with_e2e=True,

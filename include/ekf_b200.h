@@ -73,6 +73,11 @@ int ekf_batch_step_ticks(ekf_batch_t* h, const int32_t* ticks_left_dev, const in
                          const int32_t* prev_left_dev, const int32_t* prev_right_dev, double wheel_radius,
                          double baseline, int resolution, const int32_t* slot_dev, const double* rng_dev,
                          const double* brg_dev, int m, void* stream);
+/* Same, every filter sees the SAME encoder ticks (Monte Carlo replays of one bag): four scalars, no per-filter arrays */
+int ekf_batch_step_ticks_common(ekf_batch_t* h, int32_t ticks_left, int32_t ticks_right, int32_t prev_left,
+                                int32_t prev_right, double wheel_radius, double baseline, int resolution,
+                                const int32_t* slot_dev, const double* rng_dev, const double* brg_dev, int m,
+                                void* stream);
 /* Reference layout (mean (n,), covariance (n,n) C-order per filter, device memory) <-> device layout.   */
 int ekf_batch_pack(ekf_batch_t* h, const double* mean_ref_dev, const double* cov_ref_dev, int64_t first,
                    int64_t count, void* stream);
@@ -112,6 +117,13 @@ int ekf_batch_associate(ekf_batch_t* h, int n_det, const int32_t* det_tag_dev, c
                         const double* det_tz_dev, const double* noise_tx_dev, const double* noise_tz_dev,
                         int n_tags, int32_t* tag_slot_dev, int32_t* n_seen_dev, int32_t* slot_dev, double* rng_dev,
                         double* brg_dev, int m, void* stream);
+/* ekf_batch_associate with the per-filter detection noise generated INSIDE the kernel: detection d of filter b is
+ * perturbed by sigma x the normal pair of (seed, first_filter + b, step, detection stream d) — the numbers
+ * ekf_batch_detection_noise would write, without the two [n_det][batch] arrays                                 */
+int ekf_batch_associate_generated(ekf_batch_t* h, int n_det, const int32_t* det_tag_dev, const double* det_tx_dev,
+                                  const double* det_tz_dev, uint64_t seed, uint64_t step, uint64_t first_filter,
+                                  double sigma, int n_tags, int32_t* tag_slot_dev, int32_t* n_seen_dev,
+                                  int32_t* slot_dev, double* rng_dev, double* brg_dev, int m, void* stream);
 /* windows that held more than m distinct landmarks since create: the extra detections are dropped BEFORE a slot
  * is handed out, so a dropped new tag is first-seen in a later window and slot order stays gap-free            */
 int ekf_batch_associate_overflow_count(ekf_batch_t* h, int64_t* count);
@@ -191,17 +203,21 @@ int ekf_lm_update_from_rows(ekf_lm_t* h, int slot, double rng, double brg, const
  * ekf_lm_p2p_init allocates this shard's exchange area and returns its cudaIpc handle (handle_bytes >= 64); the host
  * gathers the handles of all ranks (any transport) and passes them to ekf_lm_p2p_connect ([world][handle_bytes];
  * local_areas optionally gives device pointers of shards living in the same process). ekf_lm_p2p_update then runs
- * one sharded update: the owners push rows {0,1,2} / {j,j+1} (+ mu entries) into every rank's area and publish a
- * sequence number, every rank waits on its own flags, gathers, acknowledges and streams its row block. Every rank
- * must call it with the same arguments in the same order. ekf_lm_p2p_error reports a spin that ran out of budget. */
+ * one sharded update in the SAME two launches as on one GPU: at the head of the gather kernel the owner of rows
+ * {j,j+1} stores them (+ mu entries) into every peer's area and publishes a sequence number, the other ranks wait on
+ * flags in their own memory; rank 0's streaming kernel pushes the rows {0,1,2} it has just updated into the buffer of
+ * the NEXT update (a predict, or ekf_lm_p2p_invalidate after an external write to P, makes rank 0's next gather push
+ * them instead). With world = 1 the call is ekf_lm_update. Every rank must make the same calls in the same order.
+ * ekf_lm_p2p_error reports a spin that ran out of budget.                                                       */
 int ekf_lm_p2p_init(ekf_lm_t* h, int world, int rank, unsigned char* handle_out, int64_t handle_bytes);
 int ekf_lm_p2p_connect(ekf_lm_t* h, const unsigned char* handles, int64_t handle_bytes, void* const* local_areas);
 int ekf_lm_p2p_area(ekf_lm_t* h, void** area_dev);
 int ekf_lm_p2p_update(ekf_lm_t* h, int slot, double rng, double brg, int owner, void* stream);
-/* the fused step (2 <= m <= 4 updates, one pass over the local row block) with its 1 + m row parts pushed by their
- * owners (owners_host[u] = rank owning rows j_u, j_u+1)                                                        */
+/* the fused step (2 <= m <= 4 updates, one pass over the local row block): the fused gather pushes / waits for its
+ * 1 + m row parts (owners_host[u] = rank owning rows j_u, j_u+1), the streaming kernel pre-pushes rows {0,1,2}   */
 int ekf_lm_p2p_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
                             const double* brg_host, const int32_t* owners_host, void* stream);
+int ekf_lm_p2p_invalidate(ekf_lm_t* h);
 int ekf_lm_p2p_error(ekf_lm_t* h, int64_t* flag);
 int ekf_lm_sync(ekf_lm_t* h);
 

@@ -27,8 +27,8 @@ def source_available() -> bool:
 
 def compiled_available() -> bool:
     """oracle/_ref holds bytecode of THIS interpreter version (a .pyc of another version cannot be loaded)."""
-    pyc = os.path.join(REF_BUILD_DIR, "replay_no_ros.pyc")
-    if not (os.path.isfile(pyc) and os.path.isfile(os.path.join(REF_BUILD_DIR, "ekf_slam_functions.pyc"))):
+    pyc = os.path.join(REF_BUILD_DIR, "replay_no_ros.bytecode")
+    if not (os.path.isfile(pyc) and os.path.isfile(os.path.join(REF_BUILD_DIR, "ekf_slam_functions.bytecode"))):
         return False
     with open(pyc, "rb") as fh:
         return fh.read(4) == importlib.util.MAGIC_NUMBER
@@ -110,7 +110,7 @@ def load_replay_module():
         spec = importlib.util.spec_from_file_location("_ref_replay_no_ros", path)
     else:
         from importlib.machinery import SourcelessFileLoader
-        path = os.path.join(REF_BUILD_DIR, "replay_no_ros.pyc")
+        path = os.path.join(REF_BUILD_DIR, "replay_no_ros.bytecode")
         spec = importlib.util.spec_from_loader("_ref_replay_no_ros", SourcelessFileLoader("_ref_replay_no_ros", path))
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
@@ -145,7 +145,7 @@ def load_ekf3_functions():
         exec(compile(ast.Module(body=keep, type_ignores=[]), path, "exec"), ns)
     else:
         import marshal
-        with open(os.path.join(REF_BUILD_DIR, "ekf_slam_functions.pyc"), "rb") as fh:
+        with open(os.path.join(REF_BUILD_DIR, "ekf_slam_functions.bytecode"), "rb") as fh:
             fh.read(16)
             exec(marshal.load(fh), ns)
     out = types.SimpleNamespace(**{k: ns[k] for k in

@@ -32,6 +32,7 @@ _i = C.c_int
 _l = C.c_int64
 _d = C.c_double
 _u64 = C.c_uint64
+_i32 = C.c_int32
 
 # name -> (restype, argtypes); every symbol include/ekf_b200.h declares
 SIGNATURES = {
@@ -49,6 +50,7 @@ SIGNATURES = {
     "ekf_batch_init": (_i, [_p, _d, _p]),
     "ekf_batch_step": (_i, [_p, _p, _p, _p, _p, _p, _i, _p]),
     "ekf_batch_step_ticks": (_i, [_p, _p, _p, _p, _p, _d, _d, _i, _p, _p, _p, _i, _p]),
+    "ekf_batch_step_ticks_common": (_i, [_p, _i32, _i32, _i32, _i32, _d, _d, _i, _p, _p, _p, _i, _p]),
     "ekf_batch_pack": (_i, [_p, _p, _p, _l, _l, _p]),
     "ekf_batch_unpack": (_i, [_p, _p, _p, _l, _l, _p]),
     "ekf_batch_step_host": (_i, [_p, _p, _p, _p, _p, _p, _i, _p, _p]),
@@ -57,6 +59,7 @@ SIGNATURES = {
     "ekf_batch_fault_count": (_i, [_p, C.POINTER(_l)]),
     "ekf_batch_nonfinite_count": (_i, [_p, C.POINTER(_l), _p]),
     "ekf_batch_associate": (_i, [_p, _i, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _p]),
+    "ekf_batch_associate_generated": (_i, [_p, _i, _p, _p, _p, _u64, _u64, _u64, _d, _i, _p, _p, _p, _p, _p, _i, _p]),
     "ekf_batch_associate_overflow_count": (_i, [_p, C.POINTER(_l)]),
     "ekf_batch_accumulate_ate": (_i, [_p, _d, _d, _p, _p]),
     "ekf_batch_moments": (_i, [_p, _p, _p]),
@@ -84,6 +87,7 @@ SIGNATURES = {
     "ekf_lm_p2p_area": (_i, [_p, C.POINTER(_p)]),
     "ekf_lm_p2p_update": (_i, [_p, _i, _d, _d, _i, _p]),
     "ekf_lm_p2p_update_multi": (_i, [_p, _i, _p, _p, _p, _p, _p]),
+    "ekf_lm_p2p_invalidate": (_i, [_p]),
     "ekf_lm_p2p_error": (_i, [_p, C.POINTER(_l)]),
     "ekf_lm_sync": (_i, [_p]),
     "ekf3_predict": (_i, [_l, _p, _p, _p, _p, _p, _p]),

@@ -63,7 +63,11 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
     tma_bulk_g2s(sMu, gMu, (uint32_t)(LD * sizeof(double)), bar);
   }
   double ang, lin;
-  if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
+  if (a.ticks_common) {  // a1/a2 on the device from ticks every filter shares (Monte Carlo replay of one bag)
+    const double dl = delta_phi(a.c_tl, a.c_pl, a.resolution);
+    const double dr = delta_phi(a.c_tr, a.c_pr, a.resolution);
+    displacement(a.wheel_radius, a.baseline, dl, dr, &ang, &lin);
+  } else if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
     const double dl = delta_phi(a.ticks_l[b], a.prev_l[b], a.resolution);
     const double dr = delta_phi(a.ticks_r[b], a.prev_r[b], a.resolution);
     displacement(a.wheel_radius, a.baseline, dl, dr, &ang, &lin);

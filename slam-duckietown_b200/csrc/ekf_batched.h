@@ -16,6 +16,8 @@ struct BatchStepArgs {
   const double* ang;             // [B] (or null when ticks are given)
   const double* lin;             // [B]
   const int32_t *ticks_l, *ticks_r, *prev_l, *prev_r;  // [B] each, or null
+  int ticks_common;              // 1: every filter sees the SAME encoder ticks c_tl / c_tr / c_pl / c_pr (one bag)
+  int32_t c_tl, c_tr, c_pl, c_pr;
   double wheel_radius, baseline;
   long long resolution;
   const int32_t* slot;           // [B][m]
@@ -30,10 +32,7 @@ bool batch_capacity_supported(int n_landmarks);
 size_t batch_step_smem_bytes(int n_landmarks, int m, bool joseph);
 cudaError_t batch_launch_step(int n_landmarks, const BatchStepArgs& a, int64_t batch, bool joseph,
                               cudaStream_t st);
-// streaming variant (ekf_batched_stream.cu): stages only the touched rows/columns; plain covariance form
-size_t batch_stream_smem_bytes(int n_landmarks, int m);
-cudaError_t batch_launch_step_stream(int n_landmarks, const BatchStepArgs& a, int64_t batch, cudaStream_t st);
-// W-in-registers variant (ekf_batched_regw.cu): plain covariance form, 1 <= m <= 4 observation slots
+// W-in-registers variant (ekf_batched_regw.cu): plain covariance form, 1 <= m <= 6 observation slots
 bool batch_regw_supported(int m);
 size_t batch_regw_smem_bytes(int n_landmarks, int m);
 cudaError_t batch_launch_step_regw(int n_landmarks, const BatchStepArgs& a, int64_t batch, cudaStream_t st);

@@ -94,8 +94,8 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
     if (bn < batch) {
       const void* src = nullptr;
       switch (gl) {
-        case 1: src = a.ticks_l ? (const void*)(a.ticks_l + bn) : (const void*)(a.ang + bn); break;
-        case 2: src = a.ticks_l ? (const void*)(a.ticks_r + bn) : (const void*)(a.lin + bn); break;
+        case 1: src = a.ticks_l ? (const void*)(a.ticks_l + bn) : (a.ang ? (const void*)(a.ang + bn) : nullptr); break;
+        case 2: src = a.ticks_l ? (const void*)(a.ticks_r + bn) : (a.lin ? (const void*)(a.lin + bn) : nullptr); break;
         case 3: src = a.motion_var + bn; break;
         case 4: src = a.meas_var + bn; break;
         case 5: src = a.n_known + bn; break;
@@ -113,7 +113,11 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
     }
   }
   double ang, lin;
-  if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
+  if (a.ticks_common) {  // a1/a2 on the device from ticks every filter shares (Monte Carlo replay of one bag)
+    const double dl = delta_phi(a.c_tl, a.c_pl, a.resolution);
+    const double dr = delta_phi(a.c_tr, a.c_pr, a.resolution);
+    displacement(a.wheel_radius, a.baseline, dl, dr, &ang, &lin);
+  } else if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
     const double dl = delta_phi(a.ticks_l[b], a.prev_l[b], a.resolution);
     const double dr = delta_phi(a.ticks_r[b], a.prev_r[b], a.resolution);
     displacement(a.wheel_radius, a.baseline, dl, dr, &ang, &lin);

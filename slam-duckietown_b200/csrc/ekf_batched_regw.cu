@@ -93,7 +93,11 @@ __device__ __forceinline__ void regw_stream_pairs(const double* __restrict__ sp,
 __host__ __device__ constexpr int regw_min_blocks(int nlm, int m, int wpc) {
   const int n = 3 + 2 * nlm, ld = (n + 3) & ~3;
   const int fit = 233472 / ((n * ld + ld * (1 + 2 * m) + 2) * 8 + 1024);
-  return wpc > 1 ? 1 : (fit < EKF_REGW_MAX_BLOCKS ? fit : EKF_REGW_MAX_BLOCKS);
+  // m > 4 (the decoded-bag-shaped steps with up to 6 updates): the W history alone is 4 m registers per lane, so the
+  // register allocation is given room (<= 10 resident warps) instead of being squeezed into spills
+  // capacities >= 12 landmarks at m <= 4: at most 16 resident warps, i.e. 128 registers (17+ forced spills)
+  const int cap = (m > 4) ? 10 : (nlm >= 12 ? 16 : EKF_REGW_MAX_BLOCKS);
+  return wpc > 1 ? 1 : (fit < cap ? fit : cap);
 }
 
 template <int NLM, int MT, int WPC>
@@ -104,6 +108,9 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
   constexpr int NT = (LD + 31) / 32;  // lane t handles indices t, t + 32
   constexpr int m = MT;
   constexpr int SLICE = N * LD + LD + m * HIST + 2;  // doubles of shared memory per warp
+  // K history of this lane's rows: in registers for m <= 4; for longer steps it is re-read from the K records in
+  // shared memory (one LDS.128 per earlier update and half), which frees 4 m registers per lane
+  constexpr bool KREG = (MT <= 4);
   static_assert(NT <= 2, "lane owns at most two columns");
   static_assert(MT >= 1 && MT <= BATCH_MAX_M, "observation count");
   static_assert(SLICE % 2 == 0, "16-byte aligned slices");
@@ -148,8 +155,8 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
     if (bn < batch) {
       const void* src = nullptr;
       switch (lane) {
-        case 1: src = a.ticks_l ? (const void*)(a.ticks_l + bn) : (const void*)(a.ang + bn); break;
-        case 2: src = a.ticks_l ? (const void*)(a.ticks_r + bn) : (const void*)(a.lin + bn); break;
+        case 1: src = a.ticks_l ? (const void*)(a.ticks_l + bn) : (a.ang ? (const void*)(a.ang + bn) : nullptr); break;
+        case 2: src = a.ticks_l ? (const void*)(a.ticks_r + bn) : (a.lin ? (const void*)(a.lin + bn) : nullptr); break;
         case 3: src = a.motion_var + bn; break;
         case 4: src = a.meas_var + bn; break;
         case 5: src = a.n_known + bn; break;
@@ -167,7 +174,11 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
     }
   }
   double ang, lin;
-  if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
+  if (a.ticks_common) {  // a1/a2 on the device from ticks every filter shares (Monte Carlo replay of one bag)
+    const double dl = delta_phi(a.c_tl, a.c_pl, a.resolution);
+    const double dr = delta_phi(a.c_tr, a.c_pr, a.resolution);
+    displacement(a.wheel_radius, a.baseline, dl, dr, &ang, &lin);
+  } else if (a.ticks_l) {  // a1/a2 on the device (replay_no_ros.py:262-266, :491-497)
     const double dl = delta_phi(a.ticks_l[b], a.prev_l[b], a.resolution);
     const double dr = delta_phi(a.ticks_r[b], a.prev_r[b], a.resolution);
     displacement(a.wheel_radius, a.baseline, dl, dr, &ang, &lin);
@@ -294,7 +305,17 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
   // ---- phase 2: sequential updates on the touched rows / columns only --------------------------------
   // history in registers: hW[u][.][p] = W_u[:, t], hK[u][p] = K_u[t, :] of this lane's t = lane + 32 p
   double hW0[m][NT], hW1[m][NT];
-  d2 hK[m][NT];
+  d2 hK[KREG ? m : 1][NT];
+  auto k_hist = [&](int w, int p) -> d2 {
+    if constexpr (KREG) {
+      return hK[w][p];
+    } else {
+      const int t = lane + 32 * p;
+      d2 z;
+      z.x = 0.0; z.y = 0.0;
+      return (t < LD) ? lds128(sK + w * HIST + 2 * t) : z;
+    }
+  };
 #pragma unroll
   for (int u = 0; u < m; ++u) {
     if (!((valid >> u) & 1u)) continue;  // warp-uniform
@@ -321,10 +342,11 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
       const double w0j1 = col_bcast<NT>(hW0[w], j + 1), w1j1 = col_bcast<NT>(hW1[w], j + 1);
 #pragma unroll
       for (int p = 0; p < NT; ++p) {
+        const d2 kw = k_hist(w, p);
         lr[0][p] = rank2(lr[0][p], kj0.x, kj0.y, hW0[w][p], hW1[w][p]);
         lr[1][p] = rank2(lr[1][p], kj1.x, kj1.y, hW0[w][p], hW1[w][p]);
-        lc[0][p] = rank2(lc[0][p], hK[w][p].x, hK[w][p].y, w0j0, w1j0);
-        lc[1][p] = rank2(lc[1][p], hK[w][p].x, hK[w][p].y, w0j1, w1j1);
+        lc[0][p] = rank2(lc[0][p], kw.x, kw.y, w0j0, w1j0);
+        lc[1][p] = rank2(lc[1][p], kw.x, kw.y, w0j1, w1j1);
       }
     }
     // (c) H P (rows) and P H^T (columns) for this lane's t, accumulated in idx5 order
@@ -367,13 +389,15 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
     inv2(S, Si);
     // (e) K_u = P H^T S^-1 (:473), mu += K_u y (:476)
     double* ku = sK + u * HIST;
+    d2 kcur[NT];
 #pragma unroll
     for (int p = 0; p < NT; ++p) {
       const int t = lane + 32 * p;
       d2 kk;
       kk.x = dot2(pht0[p], Si[0][0], pht1[p], Si[1][0]);
       kk.y = dot2(pht0[p], Si[0][1], pht1[p], Si[1][1]);
-      hK[u][p] = kk;  // zero for the pad row and beyond
+      if constexpr (KREG) hK[u][p] = kk;  // zero for the pad row and beyond
+      kcur[p] = kk;
       if (t < LD) {
         *reinterpret_cast<d2*>(ku + 2 * t) = kk;
         if (t < N) sMu[t] = mu_inc(sMu[t], kk.x, kk.y, in.y0, in.y1);
@@ -388,7 +412,7 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
 #pragma unroll
         for (int p = 0; p < NT; ++p) {
           rr[k][p] = rank2(rr[k][p], kr.x, kr.y, hW0[u][p], hW1[u][p]);
-          rc[k][p] = rank2(rc[k][p], hK[u][p].x, hK[u][p].y, x0[k], x1[k]);
+          rc[k][p] = rank2(rc[k][p], kcur[p].x, kcur[p].y, x0[k], x1[k]);
         }
       }
     }
@@ -480,7 +504,7 @@ size_t batch_regw_smem_bytes(int n_landmarks, int m) {
   return ((size_t)n * ld + ld + (size_t)m * 2 * ld + 2) * sizeof(double);
 }
 
-bool batch_regw_supported(int m) { return m >= 1 && m <= 4; }
+bool batch_regw_supported(int m) { return m >= 1 && m <= 6; }
 
 // warps of one persistent CTA that fit an SM (shared memory: 227 KB per CTA; registers: <= 16 warps), and
 // resident one-warp CTAs (each also pays the 1 KB system reservation; <= 32 CTAs per SM)
@@ -540,6 +564,8 @@ static cudaError_t launch_regw_t(const BatchStepArgs& a, int64_t batch, cudaStre
     case 2: return launch_regw_mt<NLM, 2>(a, batch, st);
     case 3: return launch_regw_mt<NLM, 3>(a, batch, st);
     case 4: return launch_regw_mt<NLM, 4>(a, batch, st);
+    case 5: return launch_regw_mt<NLM, 5>(a, batch, st);
+    case 6: return launch_regw_mt<NLM, 6>(a, batch, st);
     default: return cudaErrorInvalidValue;
   }
 }

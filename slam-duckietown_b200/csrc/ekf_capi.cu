@@ -51,10 +51,9 @@ struct ekf_batch {
   int32_t* n_known = nullptr;
   const double *mv = nullptr, *mm = nullptr;
   int flags = ekf::kFlagCircular | ekf::kFlagMeasurement;
-  // 0 = auto (W-in-registers kernel where it applies: plain form, 1-4 observation slots; else fully staged),
-  // 1 = streaming (touched rows/columns staged), 2 = fully staged, 3 = warp per filter with W in registers even for
-  // small filters, 8 / 16 = sub-warp groups of that width (capacity <= 8 landmarks; auto picks 8 there);
-  // EKF_BATCH_KERNEL=auto|stream|staged|regw|group8|group16
+  // 0 = auto (W-in-registers kernel where it applies: plain form, 1-6 observation slots; else fully staged),
+  // 2 = fully staged, 3 = warp per filter with W in registers even for small filters, 8 / 16 = sub-warp groups of
+  // that width (capacity <= 8 landmarks; auto picks 8 there); EKF_BATCH_KERNEL=auto|staged|regw|group8|group16
   int kernel = 0;
   unsigned long long* faults = nullptr;  // [0] fault count, [1..2] work / done counters of the persistent kernel, [3] association overflows, [4] scratch of ekf_batch_nonfinite_count
   // staging for the host-buffer entry point
@@ -92,6 +91,7 @@ struct ekf_lm {
   unsigned* p2p_push_count = nullptr;
   unsigned long long* p2p_err = nullptr;
   unsigned long long p2p_seq = 0;
+  unsigned long long p2p_robot_seq = 0;  // update number whose buffer already holds rows 0-2 (pre-pushed by rank 0)
   int variant = 0;
 };
 
@@ -144,7 +144,7 @@ int ekf_batch_create(int n_landmarks, int64_t batch, int device, ekf_batch_t** o
   h->device = device;
   h->batch = batch;
   if (const char* k = getenv("EKF_BATCH_KERNEL"))
-    h->kernel = (strcmp(k, "stream") == 0) ? 1 : (strcmp(k, "staged") == 0) ? 2 : (strcmp(k, "regw") == 0) ? 3 :
+    h->kernel = (strcmp(k, "staged") == 0) ? 2 : (strcmp(k, "regw") == 0) ? 3 :
                 (strcmp(k, "group8") == 0) ? 8 : (strcmp(k, "group16") == 0) ? 16 : 0;
   cudaError_t e = cudaMalloc(&h->faults, 8 * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaMemset(h->faults, 0, 8 * sizeof(unsigned long long));
@@ -233,9 +233,7 @@ static int batch_step_common(ekf_batch_t* h, ekf::BatchStepArgs& a, int m, void*
   a.flags = h->flags;
   CU(cudaSetDevice(h->device));
   const bool joseph = (h->flags & ekf::kFlagJoseph) != 0;
-  if (!joseph && h->kernel == 1)
-    CU(ekf::batch_launch_step_stream(h->nlm, a, h->batch, (cudaStream_t)stream));
-  else if (!joseph && (h->kernel == 0 || h->kernel >= 8) && ekf::batch_group_supported(h->nlm, m))
+  if (!joseph && (h->kernel == 0 || h->kernel >= 8) && ekf::batch_group_supported(h->nlm, m))
     CU(ekf::batch_launch_step_group(h->nlm, h->kernel >= 8 ? h->kernel : 8, a, h->batch, (cudaStream_t)stream));
   else if (!joseph && (h->kernel == 0 || h->kernel == 3 || h->kernel >= 8) && ekf::batch_regw_supported(m))
     CU(ekf::batch_launch_step_regw(h->nlm, a, h->batch, (cudaStream_t)stream));
@@ -268,6 +266,24 @@ int ekf_batch_step_ticks(ekf_batch_t* h, const int32_t* ticks_left_dev, const in
   a.ticks_r = ticks_right_dev;
   a.prev_l = prev_left_dev;
   a.prev_r = prev_right_dev;
+  a.wheel_radius = wheel_radius;
+  a.baseline = baseline;
+  a.resolution = resolution;
+  a.slot = slot_dev;
+  a.rng = rng_dev;
+  a.brg = brg_dev;
+  return batch_step_common(h, a, m, stream);
+}
+
+int ekf_batch_step_ticks_common(ekf_batch_t* h, int32_t ticks_left, int32_t ticks_right, int32_t prev_left,
+                                int32_t prev_right, double wheel_radius, double baseline, int resolution,
+                                const int32_t* slot_dev, const double* rng_dev, const double* brg_dev, int m,
+                                void* stream) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  if (resolution == 0 || baseline == 0.0) return fail(EKF_EINVAL, "resolution / baseline must be non-zero");
+  ekf::BatchStepArgs a{};
+  a.ticks_common = 1;
+  a.c_tl = ticks_left; a.c_tr = ticks_right; a.c_pl = prev_left; a.c_pr = prev_right;
   a.wheel_radius = wheel_radius;
   a.baseline = baseline;
   a.resolution = resolution;
@@ -583,6 +599,29 @@ int ekf_batch_associate(ekf_batch_t* h, int n_det, const int32_t* det_tag_dev, c
   return EKF_OK;
 }
 
+int ekf_batch_associate_generated(ekf_batch_t* h, int n_det, const int32_t* det_tag_dev, const double* det_tx_dev,
+                                  const double* det_tz_dev, uint64_t seed, uint64_t step, uint64_t first_filter,
+                                  double sigma, int n_tags, int32_t* tag_slot_dev, int32_t* n_seen_dev,
+                                  int32_t* slot_dev, double* rng_dev, double* brg_dev, int m, void* stream) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  if (n_det < 0 || n_tags <= 0) return fail(EKF_EINVAL, "n_det < 0 or n_tags <= 0");
+  if (m < 1 || m > ekf::ASSOC_MAX_M) return fail(EKF_EINVAL, "m must be in [1, %d]", ekf::ASSOC_MAX_M);
+  if ((n_det > 0 && (!det_tag_dev || !det_tx_dev || !det_tz_dev)) || !tag_slot_dev || !n_seen_dev || !slot_dev ||
+      !rng_dev || !brg_dev)
+    return fail(EKF_EINVAL, "null argument");
+  if (step > 0xffffffffull) return fail(EKF_EINVAL, "step must fit 32 bits");
+  CU(cudaSetDevice(h->device));
+  ekf::AssocArgs a{};
+  a.batch = h->batch; a.n_det = n_det; a.n_tags = n_tags; a.m = m;
+  a.det_tag = det_tag_dev; a.det_tx = det_tx_dev; a.det_tz = det_tz_dev;
+  a.gen = 1; a.gen_seed = seed; a.gen_step = (uint32_t)step; a.gen_first = first_filter; a.gen_sigma = sigma;
+  a.tag_slot = tag_slot_dev; a.n_seen = n_seen_dev;
+  a.slot = slot_dev; a.rng = rng_dev; a.brg = brg_dev;
+  a.overflow = h->faults + 3;
+  CU(ekf::batch_launch_associate(a, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
 int ekf_batch_associate_overflow_count(ekf_batch_t* h, int64_t* count) {
   if (!h || !count) return fail(EKF_EINVAL, "null argument");
   CU(cudaSetDevice(h->device));
@@ -717,32 +756,70 @@ int ekf_lm_predict(ekf_lm_t* h, double ang, double lin, void* stream) {
   CU(cudaSetDevice(h->device));
   CU(ekf::lm_launch_predict(h->mu, h->P, h->ld, h->n, h->row_begin, h->row_end, h->scal, ang, lin, h->mv,
                             h->flags, (cudaStream_t)stream));
+  h->p2p_robot_seq = 0;  // rows 0-1 and the pose changed: the robot rows pre-pushed by the last update are stale
   return EKF_OK;
 }
 
-// p2p: when given, the gather waits on the exchange flags and the streaming kernel acknowledges the buffer
+// exchange descriptor of update / step number `seq` of this handle's peer-memory exchange
+static int64_t p2p_flag_off(const ekf_lm* h) { return 2 * ekf::P2P_ROWS * (h->ld + 4); }
+static int64_t p2p_area_doubles(const ekf_lm* h) { return p2p_flag_off(h) + 2 * ekf::P2P_PARTS + ekf::P2P_MAX_WORLD; }
+
+static ekf::LmExchange p2p_exchange(ekf_lm_t* h, unsigned long long seq) {
+  ekf::LmExchange x{};
+  x.peers = h->p2p_peers_dev;
+  x.ldx = h->ld + 4;
+  x.flag_off = p2p_flag_off(h);
+  x.acks = reinterpret_cast<unsigned long long*>(h->p2p_area + x.flag_off) + 2 * ekf::P2P_PARTS;
+  x.err = h->p2p_err;
+  x.count = h->p2p_push_count;
+  x.seq = seq;
+  x.world = h->p2p_world;
+  x.rank = h->p2p_rank;
+  return x;
+}
+
+// One range-bearing update. rows5: replicated 5-row buffer of a row-block shard whose rows were exchanged by the host
+// (NCCL path / emulated shards); owner >= 0: peer-memory exchange inside the kernels (ekf_lm_p2p_update).
 static int lm_update_impl_split(ekf_lm_t* h, int slot, double rng, double brg, const double* rows5, void* stream,
-                                const ekf::P2PArgs* p2p) {
+                                int owner) {
   if (!h) return fail(EKF_EINVAL, "null handle");
   if (!h->P) return fail(EKF_ESTATE, "state not bound");
   if (slot < 0 || slot >= h->cap) return fail(EKF_EINVAL, "slot %d outside capacity %d", slot, h->cap);
   if (!(h->flags & ekf::kFlagMeasurement)) return EKF_OK;  // ENABLE_MEASUREMENT_MODEL = False (:435)
   const bool whole = (h->row_begin == 0 && h->row_end == h->n);
-  if (!rows5 && !whole) return fail(EKF_ESTATE, "row-block shard: use ekf_lm_update_from_rows");
+  const bool p2p = owner >= 0;
+  if (!rows5 && !whole && !p2p) return fail(EKF_ESTATE, "row-block shard: use ekf_lm_update_from_rows");
   const bool joseph = (h->flags & ekf::kFlagJoseph) != 0;
   if (joseph && !whole) return fail(EKF_EINVAL, "Joseph form is not available on a row-block shard");
   CU(cudaSetDevice(h->device));
   const int j = 3 + 2 * slot;
   const int idx5[5] = {0, 1, 2, j, j + 1};
   ekf::LmGatherArgs g{};
+  ekf::LmUpdateArgs u{};
   g.P = h->P;
   const int64_t ldx = h->ld + 4;
+  if (p2p) {
+    const unsigned long long seq = ++h->p2p_seq;
+    g.x = u.x = p2p_exchange(h, seq);
+    rows5 = h->p2p_area + (int64_t)(seq & 1) * ekf::P2P_ROWS * ldx;
+    g.wait_flags = reinterpret_cast<const unsigned long long*>(h->p2p_area + g.x.flag_off) + (seq & 1) * ekf::P2P_PARTS;
+    const bool robot_there = (h->p2p_robot_seq == seq);  // pre-pushed by rank 0's previous streaming kernel
+    if (h->p2p_rank == 0) {
+      if (!robot_there) g.push_mask |= 1;
+    } else {
+      g.wait_mask |= 1;
+    }
+    if (h->p2p_rank == owner) g.push_mask |= 2; else g.wait_mask |= 2;
+    u.prepush = (h->p2p_rank == 0);
+    h->p2p_robot_seq = seq + 1;                          // every rank: the streaming kernels of this update pre-push
+  }
   for (int k = 0; k < 5; ++k) {
-    if (rows5) {
+    const bool own = idx5[k] >= h->row_begin && idx5[k] < h->row_end;
+    if (rows5 && !(p2p && own)) {
       g.row[k] = rows5 + k * ldx;
       g.mu5[k] = rows5 + k * ldx + h->ld;
     } else {
-      g.row[k] = h->P + (int64_t)idx5[k] * h->ld;
+      g.row[k] = h->P + (int64_t)(idx5[k] - h->row_begin) * h->ld;
       g.mu5[k] = h->mu + idx5[k];
     }
   }
@@ -758,15 +835,7 @@ static int lm_update_impl_split(ekf_lm_t* h, int slot, double rng, double brg, c
   g.mm = h->mm;
   g.shard = rows5 ? 1 : 0;
   g.mu_out = h->mu;
-  if (p2p) {
-    g.wait_flags = reinterpret_cast<const unsigned long long*>(h->p2p_area + p2p->flag_off) +
-                   (p2p->seq & 1) * ekf::P2P_PARTS;
-    g.wait_parts = 2;
-    g.wait_seq = p2p->seq;
-    g.wait_err = p2p->err;
-  }
   CU(ekf::lm_launch_gather(g, (cudaStream_t)stream));
-  ekf::LmUpdateArgs u{};
   u.P = h->P;
   u.mu = h->mu;
   u.K0 = h->K0; u.K1 = h->K1; u.A0 = h->A0; u.A1 = h->A1; u.W0 = h->W0; u.W1 = h->W1; u.scal = h->scal;
@@ -774,19 +843,12 @@ static int lm_update_impl_split(ekf_lm_t* h, int slot, double rng, double brg, c
   u.n = h->n;
   u.row_begin = h->row_begin;
   u.row_end = h->row_end;
-  if (p2p) {
-    u.ack_peers = p2p->peers;
-    u.ack_flag_off = p2p->flag_off;
-    u.ack_seq = p2p->seq;
-    u.ack_world = p2p->world;
-    u.ack_rank = p2p->rank;
-  }
   CU(ekf::lm_launch_update(u, joseph, h->variant, (cudaStream_t)stream));
   return EKF_OK;
 }
 
 static int lm_update_impl(ekf_lm_t* h, int slot, double rng, double brg, const double* rows5, void* stream) {
-  return lm_update_impl_split(h, slot, rng, brg, rows5, stream, nullptr);
+  return lm_update_impl_split(h, slot, rng, brg, rows5, stream, -1);
 }
 
 int ekf_lm_update(ekf_lm_t* h, int slot, double rng, double brg, void* stream) {
@@ -806,8 +868,10 @@ static int lm_multi_check(ekf_lm_t* h, int m, const int32_t* slots_host, const d
   return EKF_OK;
 }
 
+// xrows: exchanged rows of a row-block shard ([3 + 2g][ldx]); own_local: rows this rank owns are read from its own P
+// (peer-memory exchange: owners do not push to themselves), otherwise every row comes from xrows (replicated buffer)
 static void lm_multi_fill(ekf_lm_t* h, ekf::LmMultiArgs& a, int g, const int32_t* slots, const double* rng,
-                          const double* brg, const double* xrows) {
+                          const double* brg, const double* xrows, bool own_local = false) {
   a.P = h->P; a.mu = h->mu; a.K = h->mK; a.W = h->mW; a.y = h->my; a.KR = h->mKR;
   a.xrows = xrows;
   a.ld = h->ld; a.ldw = h->ldw; a.ldx = h->ld + 4;
@@ -816,6 +880,17 @@ static void lm_multi_fill(ekf_lm_t* h, ekf::LmMultiArgs& a, int g, const int32_t
     a.j[u] = 3 + 2 * slots[u];
     if (rng) a.rng[u] = rng[u];
     if (brg) a.brg[u] = brg[u];
+  }
+  for (int rho = 0; rho < 3 + 2 * g; ++rho) {
+    const int row = rho < 3 ? rho : a.j[(rho - 3) >> 1] + ((rho - 3) & 1);
+    const bool own = row >= h->row_begin && row < h->row_end;
+    if (xrows && !(own_local && own)) {
+      a.rowp[rho] = xrows + (int64_t)rho * a.ldx;
+      a.mup[rho] = a.rowp[rho] + h->ld;
+    } else {
+      a.rowp[rho] = h->P + (int64_t)(row - h->row_begin) * h->ld;
+      a.mup[rho] = h->mu + row;
+    }
   }
 }
 
@@ -892,9 +967,6 @@ int ekf_lm_update_from_rows(ekf_lm_t* h, int slot, double rng, double brg, const
 }
 
 // ---- peer-memory row exchange of the row-block shards ----------------------------------------------------
-static int64_t p2p_flag_off(const ekf_lm* h) { return 2 * ekf::P2P_ROWS * (h->ld + 4); }
-static int64_t p2p_area_doubles(const ekf_lm* h) { return p2p_flag_off(h) + 2 * ekf::P2P_PARTS + ekf::P2P_MAX_WORLD; }
-
 int ekf_lm_p2p_init(ekf_lm_t* h, int world, int rank, unsigned char* handle_out, int64_t handle_bytes) {
   if (!h || !handle_out) return fail(EKF_EINVAL, "null argument");
   if (!h->P) return fail(EKF_ESTATE, "state not bound");
@@ -952,15 +1024,6 @@ int ekf_lm_p2p_area(ekf_lm_t* h, void** area_dev) {
   return EKF_OK;
 }
 
-static void p2p_fill(ekf_lm_t* h, ekf::P2PArgs& a) {
-  a.P = h->P; a.mu = h->mu; a.peers = h->p2p_peers_dev;
-  a.ld = h->ld; a.ldx = h->ld + 4; a.flag_off = p2p_flag_off(h);
-  a.acks = reinterpret_cast<unsigned long long*>(h->p2p_area + a.flag_off) + 2 * ekf::P2P_PARTS;
-  a.err = h->p2p_err; a.push_count = h->p2p_push_count;
-  a.seq = ++h->p2p_seq;
-  a.world = h->p2p_world; a.rank = h->p2p_rank; a.row_begin = h->row_begin;
-}
-
 int ekf_lm_p2p_update(ekf_lm_t* h, int slot, double rng, double brg, int owner, void* stream) {
   if (!h) return fail(EKF_EINVAL, "null handle");
   if (!h->p2p_peers_dev) return fail(EKF_ESTATE, "p2p exchange not connected");
@@ -969,22 +1032,16 @@ int ekf_lm_p2p_update(ekf_lm_t* h, int slot, double rng, double brg, int owner, 
   if (!(h->flags & ekf::kFlagMeasurement)) return EKF_OK;
   if (h->p2p_world == 1)  // nobody to exchange with: the plain single-GPU update, no push / flag / ack protocol
     return lm_update_impl(h, slot, rng, brg, nullptr, stream);
-  CU(cudaSetDevice(h->device));
-  cudaStream_t st = (cudaStream_t)stream;
   const int j = 3 + 2 * slot;
   if (h->p2p_rank == owner && (j < h->row_begin || j + 1 >= h->row_end))
     return fail(EKF_EINVAL, "rank %d does not own slot %d", owner, slot);
-  ekf::P2PArgs a{};
-  p2p_fill(h, a);
-  if (h->p2p_rank == 0) CU(ekf::lm_launch_p2p_push(a, 0, 0, 3, 0, st));
-  if (h->p2p_rank == owner) CU(ekf::lm_launch_p2p_push(a, j, 3, 2, 1, st));
-  const double* rows5 = h->p2p_area + (int64_t)(a.seq & 1) * ekf::P2P_ROWS * a.ldx;
-  // gather (waits on the flags, reads the exchange buffer), then the streaming update (acknowledges the buffer)
-  return lm_update_impl_split(h, slot, rng, brg, rows5, stream, &a);
+  // two launches, as on one GPU: the gather (owners push their rows at its head, everyone else waits on the flags in
+  // its own memory) and the streaming update (acknowledges the buffer; rank 0 pre-pushes rows 0-2 for the next update)
+  return lm_update_impl_split(h, slot, rng, brg, nullptr, stream, owner);
 }
 
-// The fused step over peer memory: one push per row part (robot rows by rank 0, rows j_u, j_u+1 by owners[u]), then
-// the fused gather (waits on the 1 + m flags) and ONE streaming pass over the local row block.
+// The fused step over peer memory: the fused gather pushes / waits for the step's 1 + m row parts, then ONE streaming
+// pass over the local row block.
 int ekf_lm_p2p_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
                             const double* brg_host, const int32_t* owners_host, void* stream) {
   const int rc0 = lm_multi_check(h, m, slots_host, rng_host, brg_host);
@@ -1002,23 +1059,30 @@ int ekf_lm_p2p_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const
       return fail(EKF_EINVAL, "rank %d does not own slot %d", owners_host[u], slots_host[u]);
   }
   CU(cudaSetDevice(h->device));
-  cudaStream_t st = (cudaStream_t)stream;
-  ekf::P2PArgs a{};
-  p2p_fill(h, a);
-  if (h->p2p_rank == 0) CU(ekf::lm_launch_p2p_push(a, 0, 0, 3, 0, st));
-  for (int u = 0; u < m; ++u)
-    if (h->p2p_rank == owners_host[u]) CU(ekf::lm_launch_p2p_push(a, 3 + 2 * slots_host[u], 3 + 2 * u, 2, 1 + u, st));
+  const unsigned long long seq = ++h->p2p_seq;
   ekf::LmMultiArgs g{};
   lm_multi_fill(h, g, m, slots_host, rng_host, brg_host,
-                h->p2p_area + (int64_t)(a.seq & 1) * ekf::P2P_ROWS * a.ldx);
-  g.wait_flags = reinterpret_cast<const unsigned long long*>(h->p2p_area + a.flag_off) + (a.seq & 1) * ekf::P2P_PARTS;
-  g.wait_seq = a.seq;
-  g.wait_err = a.err;
-  g.ack_peers = a.peers;
-  g.ack_flag_off = a.flag_off;
-  g.ack_world = a.world;
-  g.ack_rank = a.rank;
-  CU(ekf::lm_launch_update_multi(g, st));
+                h->p2p_area + (int64_t)(seq & 1) * ekf::P2P_ROWS * (h->ld + 4), /*own_local=*/true);
+  g.x = p2p_exchange(h, seq);
+  g.wait_flags = reinterpret_cast<const unsigned long long*>(h->p2p_area + g.x.flag_off) + (seq & 1) * ekf::P2P_PARTS;
+  const bool robot_there = (h->p2p_robot_seq == seq);
+  if (h->p2p_rank == 0) {
+    if (!robot_there) g.push_mask |= 1;
+  } else {
+    g.wait_mask |= 1;
+  }
+  for (int u = 0; u < m; ++u) {
+    if (h->p2p_rank == owners_host[u]) g.push_mask |= 2 << u; else g.wait_mask |= 2 << u;
+  }
+  g.prepush = (h->p2p_rank == 0);
+  h->p2p_robot_seq = seq + 1;
+  CU(ekf::lm_launch_update_multi(g, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
+int ekf_lm_p2p_invalidate(ekf_lm_t* h) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  h->p2p_robot_seq = 0;
   return EKF_OK;
 }
 

@@ -32,7 +32,12 @@ __global__ void __launch_bounds__(128) batch_associate_kernel(AssocArgs a) {
     const int tag = a.det_tag[d];  // compact tag index; < 0 = ignored tag (IGNORE_TAGS, :286)
     if (tag < 0 || tag >= a.n_tags) continue;
     double tx = a.det_tx[d], tz = a.det_tz[d];
-    if (a.noise_tx) {
+    if (a.gen) {  // the same numbers ekf_batch_detection_noise would have written: sigma * z, added with one rounding
+      double z0, z1;
+      normal_pair(a.gen_seed, a.gen_first + (uint64_t)b, a.gen_step, kStreamDetection0 + d, &z0, &z1);
+      tx = __dadd_rn(tx, __dmul_rn(a.gen_sigma, z0));
+      tz = __dadd_rn(tz, __dmul_rn(a.gen_sigma, z1));
+    } else if (a.noise_tx) {
       tx = __dadd_rn(tx, a.noise_tx[(int64_t)d * a.batch + b]);
       tz = __dadd_rn(tz, a.noise_tz[(int64_t)d * a.batch + b]);
     }

@@ -15,6 +15,12 @@ struct AssocArgs {
   const double* det_tz;     // [n_det] pose_t[2]
   const double* noise_tx;   // [n_det][B] per-filter perturbation added to pose_t[0] (null = none)
   const double* noise_tz;   // [n_det][B]
+  // gen != 0: no noise arrays — detection d of filter b is perturbed by gen_sigma x the normal pair of
+  // (gen_seed, gen_first + b, gen_step, kStreamDetection0 + d), generated in the kernel (ekf_philox.cuh)
+  int gen;
+  uint64_t gen_seed, gen_first;
+  uint32_t gen_step;
+  double gen_sigma;
   int32_t* tag_slot;        // [n_tags][B] slot of a tag in this filter's TAG_INDEX, -1 = never seen
   int32_t* n_seen;          // [B] len(TAG_INDEX)
   int32_t* slot;            // out [B][m], -1 = unused

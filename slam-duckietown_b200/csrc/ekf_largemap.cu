@@ -19,6 +19,7 @@
 // streaming kernel `lm_rank_update_kernel` moves the 16 n^2 with 256-bit loads/stores.
 #include "ekf_common.cuh"
 #include "ekf_largemap.h"
+#include "ekf_largemap_p2p.cuh"
 
 namespace ekf {
 
@@ -126,33 +127,41 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
   pdl_wait();
   const int j = a.j;
   const int idx5[5] = {0, 1, 2, j, j + 1};
-  // this thread's gathers are issued before thread 0's scalar chain (innovation, S^-1) so that the strided column
-  // reads overlap it instead of following it
-  if (a.wait_flags) {  // rows arrive by peer stores: both parts of the exchange buffer carry this update's number
-    if (threadIdx.x == 0) {
-      const volatile unsigned long long* f = a.wait_flags;
-      const long long t0 = clock64();
-      for (int part = 0; part < a.wait_parts; ++part)
-        while (f[part] < a.wait_seq) {
-          if (clock64() - t0 > 4000000000LL) {
-            atomicExch(a.wait_err, 1ULL);
-            break;
-          }
-          __nanosleep(32);
-        }
-      __threadfence_system();
-    }
-    __syncthreads();
-  }
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = t < a.n;
   const bool local = live && (t >= a.row_begin && t < a.row_end);
+  // this thread's column gathers touch only the local block: issued first, they fly under the exchange below and
+  // under thread 0's scalar chain (innovation, S^-1)
   double pr[5], pc[5];
 #pragma unroll
-  for (int k = 0; k < 5; ++k) {
-    pr[k] = live ? a.row[k][t] : 0.0;
-    pc[k] = local ? a.P[(int64_t)(t - a.row_begin) * a.ld + idx5[k]] : 0.0;
+  for (int k = 0; k < 5; ++k) pc[k] = local ? a.P[(int64_t)(t - a.row_begin) * a.ld + idx5[k]] : 0.0;
+  if (a.x.peers) {
+    // peer-memory exchange inside this kernel (LmExchange, ekf_largemap.h): owners push their rows first ...
+    if (a.push_mask) {
+      if (threadIdx.x == 0) x_wait_acks(a.x, a.x.seq > 2 ? a.x.seq - 2 : 0);
+      __syncthreads();
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        if (!((a.push_mask >> (k < 3 ? 0 : 1)) & 1)) continue;
+        const double v = live ? a.row[k][t] : 0.0;                     // a.row[k] points into this rank's own P
+        const double m = (t == 0) ? *a.mu5[k] : 0.0;
+        for (int d = 0; d < a.x.world; ++d) {
+          if (d == a.x.rank) continue;
+          double* dst = x_row(a.x.peers[d], a.x, a.x.seq, k);
+          if (live) dst[t] = v;
+          if (t == 0) dst[a.ld] = m;
+        }
+      }
+      x_publish(a.x, a.x.count, gridDim.x, a.x.seq, (unsigned)a.push_mask);
+    }
+    // ... then everyone waits for the parts that come from a peer
+    if (a.wait_mask) {
+      if (threadIdx.x == 0) x_wait_parts(a.x, a.wait_flags, (unsigned)a.wait_mask);
+      __syncthreads();
+    }
   }
+#pragma unroll
+  for (int k = 0; k < 5; ++k) pr[k] = live ? a.row[k][t] : 0.0;
   if (threadIdx.x == 0) {
     const Innov in = innovation(*a.mu5[0], *a.mu5[1], *a.mu5[2], *a.mu5[3], *a.mu5[4], a.rng, a.brg);
     double hp5[2][5];
@@ -255,16 +264,24 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
 // are done by an extra column of CTAs with a (row, group) mapping. CTAs of column tile 0 also apply
 // mu += K y for their rows.
 // -------------------------------------------------------------------------------------------------------
-template <int RB, int UNROLL, bool JOSEPH>
+// push of rows 0-2 (just updated, still in registers) into every peer's buffer of the NEXT update: 256-bit stores
+__device__ __forceinline__ void x_prepush4(const LmExchange& x, int row, int c, const double4x& v) {
+  for (int d = 0; d < x.world; ++d)
+    if (d != x.rank) stg256(x_row(x.peers[d], x, x.seq + 1, row) + c, v);
+}
+
+// PRE: rank 0 of a peer-memory exchange — row tile 0 also pushes the updated robot rows (see LmExchange)
+template <int RB, int UNROLL, bool JOSEPH, bool PRE>
 __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs a) {
   __shared__ double sk[RB][4];
   const int tid = threadIdx.x;
   pdl_wait();
-  if (a.ack_peers && blockIdx.x == 0 && blockIdx.y == 0 && tid < a.ack_world) {
-    // this launch follows the gather on the stream: the exchange buffer of update ack_seq is no longer read here
-    volatile unsigned long long* ack =
-        reinterpret_cast<unsigned long long*>(a.ack_peers[tid] + a.ack_flag_off) + 2 * P2P_PARTS + a.ack_rank;
-    *ack = a.ack_seq;
+  // this launch follows the gather on the stream: the exchange buffer of update x.seq is no longer read here
+  if (a.x.peers && blockIdx.x == 0 && blockIdx.y == 0) x_ack(a.x);
+  const bool pre = PRE && blockIdx.y == 0;
+  if (pre) {  // the buffer of update seq + 1 was last read by the gathers of update seq - 1
+    if (tid == 0) x_wait_acks(a.x, a.x.seq > 1 ? a.x.seq - 1 : 0);
+    __syncthreads();
   }
   const int r0 = a.row_begin + blockIdx.y * RB;          // first global row of this CTA
   const int nrows = min(RB, a.row_end - r0);
@@ -279,7 +296,13 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs
   __syncthreads();
   if (blockIdx.x == 0) {  // a10: mu += K y for this CTA's rows
     const double y0 = a.scal[kScalY0], y1 = a.scal[kScalY1];
-    for (int r = tid; r < nrows; r += LM_THREADS) a.mu[r0 + r] = mu_inc(a.mu[r0 + r], sk[r][0], sk[r][1], y0, y1);
+    for (int r = tid; r < nrows; r += LM_THREADS) {
+      const double m = mu_inc(a.mu[r0 + r], sk[r][0], sk[r][1], y0, y1);
+      a.mu[r0 + r] = m;
+      if (pre && r < 3)  // r0 == 0 here: the pose entries ride at column ld of the pushed rows
+        for (int d = 0; d < a.x.world; ++d)
+          if (d != a.x.rank) x_row(a.x.peers[d], a.x, a.x.seq + 1, r)[a.ld] = m;
+    }
   }
   double* __restrict__ Pblk = a.P + (int64_t)(r0 - a.row_begin) * a.ld;
   if ((int)blockIdx.x < a.full_tiles) {
@@ -313,6 +336,10 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs
       }
 #pragma unroll
       for (int u = 0; u < UNROLL; ++u) stg256(p + (int64_t)(r + u) * a.ld, v[u]);
+      if (pre && r == 0) {
+#pragma unroll
+        for (int u = 0; u < 3 && u < UNROLL; ++u) x_prepush4(a.x, u, c, v[u]);
+      }
     }
     for (; r < nrows; ++r) {
       double4x v = ldg256_stream(p + (int64_t)r * a.ld);
@@ -329,6 +356,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs
         v.d = fma(a1, kc1.d, fma(a0, kc0.d, v.d));
       }
       stg256(p + (int64_t)r * a.ld, v);
+      if (pre && r < 3 && nrows < UNROLL) x_prepush4(a.x, r, c, v);
     }
   } else {
     // column tail: a.tail_groups (< LM_THREADS) groups per row, (row, group) mapping
@@ -352,8 +380,10 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs
         v.d = fma(a1, kc1.d, fma(a0, kc0.d, v.d));
       }
       stg256(Pblk + (int64_t)r * a.ld + c, v);
+      if (pre && r < 3) x_prepush4(a.x, r, c, v);
     }
   }
+  if (pre) x_publish(a.x, a.x.count + kPrepushCounter, gridDim.x, a.x.seq + 1, 1u);
 }
 
 // shard export: copy the locally owned ones of rows {0,1,2,j,j+1} (and their mu entries, stashed at column
@@ -406,8 +436,10 @@ static cudaError_t launch_update_t(const LmUpdateArgs& a0, bool joseph, cudaStre
   const int rows = a.row_end - a.row_begin;
   if (rows <= 0) return cudaSuccess;
   dim3 grid(a.full_tiles + (a.tail_groups ? 1 : 0), (rows + RB - 1) / RB);
-  if (joseph) return launch_pdl(lm_rank_update_kernel<RB, UNROLL, true>, grid, dim3(LM_THREADS), 0, st, a);
-  return launch_pdl(lm_rank_update_kernel<RB, UNROLL, false>, grid, dim3(LM_THREADS), 0, st, a);
+  if (a.prepush && a.x.peers && !joseph)
+    return launch_pdl(lm_rank_update_kernel<RB, UNROLL, false, true>, grid, dim3(LM_THREADS), 0, st, a);
+  if (joseph) return launch_pdl(lm_rank_update_kernel<RB, UNROLL, true, false>, grid, dim3(LM_THREADS), 0, st, a);
+  return launch_pdl(lm_rank_update_kernel<RB, UNROLL, false, false>, grid, dim3(LM_THREADS), 0, st, a);
 }
 
 cudaError_t lm_launch_update(const LmUpdateArgs& a, bool joseph, int variant, cudaStream_t st) {

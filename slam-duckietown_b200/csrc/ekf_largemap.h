@@ -40,6 +40,26 @@ constexpr int LM_THREADS = 128;  // threads per CTA of the streaming update = co
 // slots of the small scalar workspace (device doubles)
 enum : int { kScalG0 = 0, kScalG1 = 1, kScalY0 = 2, kScalY1 = 3, kScalArrive = 6 /* u64 arrival counter of the predict */, kScalCount = 8 };
 
+// Peer-memory row exchange, folded into the update's own kernels (round 2; round 1 launched a separate push kernel
+// per row part: 14.8 us per update against a 17 us streaming pass at 8 GPUs, profiles/r1o_lm_launches.summary.txt).
+//   * landmark rows {j, j+1}: the OWNER's gather kernel pushes them (+ their mu entries) to every peer at its head
+//     (CTA b = column chunk b), publishes the part's flag from its last CTA, and itself reads the rows from its own P;
+//   * robot rows {0, 1, 2}: rank 0's STREAMING kernel of update s pushes the rows it has just brought up to date
+//     (row tile 0, from registers) into the buffer of update s + 1 and publishes that flag — the next gather finds
+//     three of its five rows already there. A predict (or an external write to P) in between invalidates the
+//     pre-push; rank 0's next gather then pushes the robot rows itself, like a landmark part.
+// The buffer of update s is s & 1; a push into it first waits (in the pushing CTA) until every rank has acknowledged
+// the gather of update s - 2 (landmark part) resp. s - 1 (pre-push into the buffer of s + 1).
+struct LmExchange {
+  double* const* peers;          // device array [world]: every rank's exchange area; null = no exchange
+  unsigned long long* acks;      // this rank's ack words [world] (local memory)
+  unsigned long long* err;       // set to 1 when a spin ran out of budget
+  unsigned* count;               // device CTA counters [P2P_PARTS] of the in-kernel pushes
+  int64_t ldx, flag_off;
+  unsigned long long seq;        // sequence number of THIS update (starts at 1)
+  int world, rank;
+};
+
 struct LmGatherArgs {
   const double* P;        // local row block
   const double* row[5];   // rows {0,1,2,j,j+1}: into P itself (single GPU) or the exchanged buffer (shard)
@@ -50,11 +70,11 @@ struct LmGatherArgs {
   int shard;              // 1: rows/mu5 come from the exchange buffer of a row-block shard
   double* mu_out;         // shard only: replicated pose entries are refreshed here
   double rng, brg, mm;
-  // peer-memory exchange: wait until both flags of the exchange buffer reached wait_seq before reading `row`
-  const unsigned long long* wait_flags;  // null = no wait; else wait_parts consecutive flag words
-  unsigned long long wait_seq;
-  unsigned long long* wait_err;
-  int wait_parts;
+  // peer-memory exchange (x.peers != null): bit k of push_mask = this rank pushes part k (0: rows 0-2, 1: rows j, j+1)
+  // at the head of the kernel; bit k of wait_mask = part k arrives from a peer: wait for its flag before reading it
+  LmExchange x;
+  const unsigned long long* wait_flags;  // this rank's flag words of buffer seq & 1
+  int push_mask, wait_mask;
 };
 
 struct LmUpdateArgs {
@@ -64,11 +84,10 @@ struct LmUpdateArgs {
   int64_t ld;
   int n, row_begin, row_end;
   int full_tiles, tail_groups;  // filled by the launcher
-  // peer-memory exchange: the first CTA tells every rank that this rank's gather of update ack_seq is done
-  double* const* ack_peers;     // null = no ack
-  int64_t ack_flag_off;
-  unsigned long long ack_seq;
-  int ack_world, ack_rank;
+  // peer-memory exchange (x.peers != null): the first CTA tells every rank that this rank's gather of update x.seq is
+  // done; with prepush set (rank 0), row tile 0 pushes the updated rows 0-2 (+ mu) into the buffer of update seq + 1
+  LmExchange x;
+  int prepush;
 };
 
 constexpr int LM_MAX_FUSED = 4;  // updates fused into one pass over P (ekf_largemap_multi.cu)
@@ -85,13 +104,15 @@ struct LmMultiArgs {
   const double* xrows;  // row-block shard: exchanged rows [3 + 2m][ldx] (+ mu entry at column ld); null = read P
   int64_t ld, ldw, ldx;
   int n, m, row_begin, row_end;
-  // peer-memory exchange (see LmGatherArgs / LmUpdateArgs): the first gather waits, the streaming kernel acks
+  // peer-memory exchange (see LmExchange): part 0 = rows 0-2, part 1 + u = rows j_u, j_u + 1. The fused gather pushes
+  // the parts in push_mask at its head and waits for those in wait_mask; the streaming kernel acks and (prepush, rank
+  // 0) pushes the updated rows 0-2 for the next step. rowp / mup: where row R[rho] of the step's initial covariance and
+  // its mu entry are read from — this rank's own P / mu when it owns the row, the exchange buffer otherwise.
+  LmExchange x;
   const unsigned long long* wait_flags;
-  unsigned long long wait_seq;
-  unsigned long long* wait_err;
-  double* const* ack_peers;
-  int64_t ack_flag_off;
-  int ack_world, ack_rank;
+  int push_mask, wait_mask, prepush;
+  const double* rowp[LM_MAX_ROWS];
+  const double* mup[LM_MAX_ROWS];
   int j[LM_MAX_FUSED];
   double rng[LM_MAX_FUSED], brg[LM_MAX_FUSED];
   double mm;
@@ -107,18 +128,7 @@ cudaError_t lm_launch_export_rows_multi(const LmMultiArgs& a, double* rows, cuda
 constexpr int P2P_MAX_WORLD = 16;
 constexpr int P2P_ROWS = 11;   // == LM_MAX_ROWS: rows of a fused step of up to 4 updates
 constexpr int P2P_PARTS = 8;   // flag words per buffer (1 + LM_MAX_FUSED used)
-struct P2PArgs {
-  const double* P;              // local row block
-  const double* mu;
-  double* const* peers;         // device array [world]: every rank's area (own entry = local pointer)
-  unsigned long long* acks;     // local area's ack words
-  unsigned long long* err;      // set to 1 when a spin ran out of budget
-  unsigned* push_count;         // device [world] CTA counters of the push kernel
-  int64_t ld, ldx, flag_off;
-  unsigned long long seq;       // update sequence number, starts at 1
-  int world, rank, row_begin;
-};
-cudaError_t lm_launch_p2p_push(const P2PArgs& a, int first_row, int first_k, int nrows, int part, cudaStream_t st);
+// in-kernel push helpers (ekf_largemap_p2p.cuh) are shared by the gather and streaming kernels
 
 cudaError_t lm_launch_augment(double* mu, double* P, int64_t ld, int row_begin, int row_end, int j, double gx,
                               double gy, cudaStream_t st);

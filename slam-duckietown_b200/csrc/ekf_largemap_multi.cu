@@ -13,6 +13,7 @@
 // Plain covariance form; whole matrix on one GPU or a row-block shard fed by exchanged rows.
 #include "ekf_common.cuh"
 #include "ekf_largemap.h"
+#include "ekf_largemap_p2p.cuh"
 
 namespace ekf {
 
@@ -28,10 +29,9 @@ __device__ __forceinline__ double rank2e(double v, double k0, double k1, double 
 __device__ __forceinline__ int rho_row(const LmMultiArgs& a, int rho) {
   return rho < 3 ? rho : a.j[(rho - 3) >> 1] + ((rho - 3) & 1);
 }
-// row rho of the step's INITIAL covariance: the exchange buffer on a row-block shard, P itself otherwise
-__device__ __forceinline__ const double* rho_ptr(const LmMultiArgs& a, int rho) {
-  return a.xrows ? a.xrows + (int64_t)rho * a.ldx : a.P + (int64_t)rho_row(a, rho) * a.ld;
-}
+// row rho of the step's INITIAL covariance: this rank's own P where it owns the row, the exchange buffer otherwise
+// (a.rowp / a.mup are filled by the host; the whole matrix on one GPU: all of them point into P / mu)
+__device__ __forceinline__ const double* rho_ptr(const LmMultiArgs& a, int rho) { return a.rowp[rho]; }
 
 // a8-a9 for ALL M updates of the step in one launch. Update u works on the covariance as it stands after updates
 // 0..u-1 (never materialised). Thread t needs, over the whole step, only column t of the exchanged rows R
@@ -57,21 +57,40 @@ __global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
   __shared__ double spk[NR][5];      // P_u[R, idx5(u)] of the update in progress
   const int tid = threadIdx.x;
   pdl_wait();
-  if (a.wait_flags) {  // peer-memory exchange: the step's 1 + m row parts carry this step's number
-    if (tid == 0) {
-      const volatile unsigned long long* f = a.wait_flags;
-      const long long t0 = clock64();
-      for (int part = 0; part <= M; ++part)
-        while (f[part] < a.wait_seq) {
-          if (clock64() - t0 > 4000000000LL) {
-            atomicExch(a.wait_err, 1ULL);
-            break;
-          }
-          __nanosleep(32);
+  const int t = blockIdx.x * blockDim.x + tid;
+  const bool live = t < a.n;
+  const bool local = live && t >= a.row_begin && t < a.row_end;
+  // this thread's column operands touch only the local block: requested first, they fly under the exchange and
+  // under warp 0's chain
+  double pr0[NR], pc0[NR];
+  if (live) {
+    const double* prow = a.P + (int64_t)(t - a.row_begin) * a.ld;
+#pragma unroll
+    for (int rho = 0; rho < NR; ++rho) pc0[rho] = local ? prow[rho_row(a, rho)] : 0.0;  // row t, column R[rho]
+  }
+  if (a.x.peers) {  // peer-memory exchange inside this kernel: part 0 = rows 0-2, part 1 + u = rows j_u, j_u + 1
+    if (a.push_mask) {
+      if (tid == 0) x_wait_acks(a.x, a.x.seq > 2 ? a.x.seq - 2 : 0);
+      __syncthreads();
+#pragma unroll
+      for (int rho = 0; rho < NR; ++rho) {
+        const int part = rho < 3 ? 0 : 1 + ((rho - 3) >> 1);
+        if (!((a.push_mask >> part) & 1)) continue;
+        const double v = live ? a.rowp[rho][t] : 0.0;  // this rank's own P
+        const double m = (t == 0) ? *a.mup[rho] : 0.0;
+        for (int d = 0; d < a.x.world; ++d) {
+          if (d == a.x.rank) continue;
+          double* dst = x_row(a.x.peers[d], a.x, a.x.seq, rho);
+          if (live) dst[t] = v;
+          if (t == 0) dst[a.ld] = m;
         }
-      __threadfence_system();
+      }
+      x_publish(a.x, a.x.count, gridDim.x, a.x.seq, (unsigned)a.push_mask);
     }
-    __syncthreads();
+    if (a.wait_mask) {
+      if (tid == 0) x_wait_parts(a.x, a.wait_flags, (unsigned)a.wait_mask);
+      __syncthreads();
+    }
   }
   if (tid < NR * NR) {
     const int r = tid / NR, c = tid - r * NR;
@@ -80,20 +99,11 @@ __global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
     // the step's initial mean: riding at column ld of the exchanged row on a shard (local copies of non-local
     // entries are stale there), mu itself otherwise (it is written by the streaming kernel only)
     const int rho = tid - 128;
-    smuR[rho] = a.xrows ? rho_ptr(a, rho)[a.ld] : a.mu[rho_row(a, rho)];
+    smuR[rho] = *a.mup[rho];
   }
-  // this thread's own operands, requested before the barrier so that they arrive under warp 0's chain
-  const int t = blockIdx.x * blockDim.x + tid;
-  const bool live = t < a.n;
-  const bool local = live && t >= a.row_begin && t < a.row_end;
-  double pr0[NR], pc0[NR];
   if (live) {
-    const double* prow = a.P + (int64_t)(t - a.row_begin) * a.ld;
 #pragma unroll
-    for (int rho = 0; rho < NR; ++rho) {
-      pr0[rho] = rho_ptr(a, rho)[t];                      // row R[rho], column t
-      pc0[rho] = local ? prow[rho_row(a, rho)] : 0.0;     // row t, column R[rho]
-    }
+    for (int rho = 0; rho < NR; ++rho) pr0[rho] = rho_ptr(a, rho)[t];  // row R[rho], column t
   }
   __syncthreads();
   if (tid < 32) {
@@ -235,16 +245,23 @@ __global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
 // order, mu[i] += K_u[i, :] y_u in update order. Tiling as lm_rank_update_kernel: a CTA owns LM_THREADS column
 // groups of 4 doubles x RB rows; W_u of a thread's 4 columns stays in registers (8 M doubles), K_u of the RB rows
 // in shared memory, UNROLL rows of P in flight per thread (256-bit streaming loads, in-place 256-bit stores).
-template <int RB, int UNROLL, int M>
+__device__ __forceinline__ void xm_prepush4(const LmExchange& x, int row, int c, const double4x& v) {
+  for (int d = 0; d < x.world; ++d)
+    if (d != x.rank) stg256(x_row(x.peers[d], x, x.seq + 1, row) + c, v);
+}
+
+// PRE: rank 0 of a peer-memory exchange — row tile 0 also pushes the updated robot rows for the NEXT step
+template <int RB, int UNROLL, int M, bool PRE>
 __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMultiArgs a) {
   __shared__ double sk[RB][2 * M];
   const int tid = threadIdx.x;
   pdl_wait();
-  if (a.ack_peers && blockIdx.x == 0 && blockIdx.y == 0 && tid < a.ack_world) {
-    // this launch follows the gathers on the stream: the exchange buffer of step wait_seq is no longer read here
-    volatile unsigned long long* ack =
-        reinterpret_cast<unsigned long long*>(a.ack_peers[tid] + a.ack_flag_off) + 2 * P2P_PARTS + a.ack_rank;
-    *ack = a.wait_seq;
+  // this launch follows the gather on the stream: the exchange buffer of step x.seq is no longer read here
+  if (a.x.peers && blockIdx.x == 0 && blockIdx.y == 0) x_ack(a.x);
+  const bool pre = PRE && blockIdx.y == 0;
+  if (pre) {
+    if (tid == 0) x_wait_acks(a.x, a.x.seq > 1 ? a.x.seq - 1 : 0);
+    __syncthreads();
   }
   const int r0 = a.row_begin + blockIdx.y * RB;  // first global row of this CTA
   const int nrows = min(RB, a.row_end - r0);
@@ -267,6 +284,9 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
 #pragma unroll
       for (int u = 0; u < M; ++u) v = mu_inc(v, sk[r][2 * u], sk[r][2 * u + 1], a.y[2 * u], a.y[2 * u + 1]);
       a.mu[r0 + r] = v;
+      if (pre && r < 3)
+        for (int d = 0; d < a.x.world; ++d)
+          if (d != a.x.rank) x_row(a.x.peers[d], a.x, a.x.seq + 1, r)[a.ld] = v;
     }
   }
   double* __restrict__ Pblk = a.P + (int64_t)(r0 - a.row_begin) * a.ld;
@@ -296,6 +316,10 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
         }
 #pragma unroll
       for (int q = 0; q < UNROLL; ++q) stg256(p + (int64_t)(r + q) * a.ld, v[q]);
+      if (pre && r == 0) {
+#pragma unroll
+        for (int q = 0; q < 3 && q < UNROLL; ++q) xm_prepush4(a.x, q, c, v[q]);
+      }
     }
     for (; r < nrows; ++r) {
       double4x v = ldg256_stream(p + (int64_t)r * a.ld);
@@ -308,6 +332,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
         v.d = rank2e(v.d, k0, k1, w0[u].d, w1[u].d);
       }
       stg256(p + (int64_t)r * a.ld, v);
+      if (pre && r < 3 && nrows < UNROLL) xm_prepush4(a.x, r, c, v);
     }
   } else {
     // column tail: a.tail_groups (< LM_THREADS) groups per row, (row, group) mapping
@@ -327,8 +352,10 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
         v.d = rank2e(v.d, k0, k1, w0.d, w1.d);
       }
       stg256(Pblk + (int64_t)r * a.ld + c, v);
+      if (pre && r < 3) xm_prepush4(a.x, r, c, v);
     }
   }
+  if (pre) x_publish(a.x, a.x.count + kPrepushCounter, gridDim.x, a.x.seq + 1, 1u);
 }
 
 // shard export of a fused step: the locally owned ones of the rows R (and their mu entries at column ld) into the
@@ -356,7 +383,9 @@ static cudaError_t launch_multi_t(const LmMultiArgs& a, cudaStream_t st) {
   const int rows = a.row_end - a.row_begin;
   if (rows <= 0) return cudaSuccess;
   dim3 grid(a.full_tiles + (a.tail_groups ? 1 : 0), (rows + RB - 1) / RB);
-  return launch_pdl(lm_rank_update_multi_kernel<RB, UNROLL, M>, grid, dim3(LM_THREADS), 0, st, a);
+  if (a.prepush && a.x.peers)
+    return launch_pdl(lm_rank_update_multi_kernel<RB, UNROLL, M, true>, grid, dim3(LM_THREADS), 0, st, a);
+  return launch_pdl(lm_rank_update_multi_kernel<RB, UNROLL, M, false>, grid, dim3(LM_THREADS), 0, st, a);
 }
 
 cudaError_t lm_launch_update_multi(const LmMultiArgs& a0, cudaStream_t st) {

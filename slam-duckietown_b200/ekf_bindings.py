@@ -167,11 +167,11 @@ class LargeMapEKF:
         mu = np.zeros(self.ld)
         mu[:m] = mean
         self.mu.copy_(torch.from_numpy(mu))
-        blk = np.zeros((self.row_end - self.row_begin, self.ld))
         lo, hi = self.row_begin, min(self.row_end, m)
+        # only the live block travels: the rest of the device buffer is zeroed in place (no host staging of the pad)
+        self.P.zero_()
         if hi > lo:
-            blk[: hi - lo, :m] = cov[lo:hi, :]
-        self.P.copy_(torch.from_numpy(blk))
+            self.P[: hi - lo, :m].copy_(torch.from_numpy(np.ascontiguousarray(cov[lo:hi, :])))
 
     def state(self, m: int | None = None):
         """Download (mean[:m], cov block[:, :m]) as numpy float64."""
@@ -267,6 +267,10 @@ class LargeMapEKF:
         capi.call("ekf_lm_p2p_update_multi", self._h, int(sl.size), sl.ctypes.data, rg.ctypes.data, bg.ctypes.data,
                   ow.ctypes.data, _stream_ptr(self.torch))
 
+    def p2p_invalidate(self):
+        """P was written from outside the library (torch): the robot rows pre-pushed by the last update are stale."""
+        capi.call("ekf_lm_p2p_invalidate", self._h)
+
     def p2p_error(self) -> int:
         v = C.c_int64(0)
         capi.call("ekf_lm_p2p_error", self._h, C.byref(v))
@@ -277,6 +281,7 @@ class LargeMapEKF:
 
 
 _scalar_cache = {}
+_scalar_last = {"filter": None}     # what the last EKF_pose_estimation call returned (device-resident fast path)
 
 
 def _scalar_filter(n_landmarks: int) -> LargeMapEKF:
@@ -287,12 +292,34 @@ def _scalar_filter(n_landmarks: int) -> LargeMapEKF:
     return f
 
 
+def _still_resident(f, mean_in, cov_in) -> bool:
+    """True when (mean_in, cov_in) are the very arrays the previous call returned from filter ``f`` and still hold
+    what was returned: the state is then already on the device and the upload (2 x 537 MB of PCIe per call at 4096
+    landmarks) is skipped. Identity of the two array objects, plus a content check of the whole mean and of a strided
+    sample of the covariance against copies kept from the previous call (an in-place edit by the caller falls back
+    to the upload)."""
+    last = _scalar_last
+    if last["filter"] is not f or mean_in is not last.get("mean") or cov_in is not last.get("cov"):
+        return False
+    if not np.array_equal(mean_in, last["mean_copy"]):
+        return False
+    return np.array_equal(cov_in.reshape(-1)[last["sample_idx"]], last["cov_sample"])
+
+
 def EKF_pose_estimation(angular_displacement, linear_displacement, motion_model_mean, motion_model_covariance,
                         delta_t, timestamp_detectedTags_pair_list, TAG_INDEX):
     """Drop-in for replay_no_ros.py:269-482: NEW (mean, covariance) arrays come back, TAG_INDEX is mutated in
-    place, ``tags_positions`` is the reference's dict of 6-element lists. ``delta_t`` is unused (as there)."""
-    mean_in = np.asarray(motion_model_mean, dtype=np.float64)
-    cov_in = np.asarray(motion_model_covariance, dtype=np.float64)
+    place, ``tags_positions`` is the reference's dict of 6-element lists. ``delta_t`` is unused (as there).
+    When the caller hands back exactly what the previous call returned (what ``replay()`` does, :229), the state is
+    still resident on the device and is not uploaded again."""
+    if isinstance(motion_model_mean, np.ndarray) and motion_model_mean.dtype == np.float64:
+        mean_in = motion_model_mean
+    else:
+        mean_in = np.asarray(motion_model_mean, dtype=np.float64)
+    if isinstance(motion_model_covariance, np.ndarray) and motion_model_covariance.dtype == np.float64:
+        cov_in = motion_model_covariance
+    else:
+        cov_in = np.asarray(motion_model_covariance, dtype=np.float64)
     tags = associate_window(mean_in, timestamp_detectedTags_pair_list, TAG_INDEX, tuple(_flag("IGNORE_TAGS")))
     n_old = len(mean_in)
     n_new = max(n_old, 3 + 2 * len(TAG_INDEX))
@@ -300,7 +327,8 @@ def EKF_pose_estimation(angular_displacement, linear_displacement, motion_model_
     f.set_noise(_flag("MOTION_MODEL_VARIANCE"), _flag("MEASUREMENT_MODEL_VARIANCE"))
     f.set_flags(_flag("ENABLE_CIRCULAR_INTERPOLATION"), _flag("ENABLE_MEASUREMENT_MODEL"),
                 _flag("DISABLE_MOTION_MODEL"), JOSEPH_FORM)
-    f.load(mean_in, cov_in)
+    if not _still_resident(f, mean_in, cov_in):
+        f.load(mean_in, cov_in)
     for i in range(n_old, n_new, 2):                      # :355-360 (KeyError like the reference at :359)
         slot = (i - 3) // 2
         f.augment(slot, tags[slot][0], tags[slot][1])
@@ -308,6 +336,9 @@ def EKF_pose_estimation(angular_displacement, linear_displacement, motion_model_
     if tags:                                              # first-seen-in-window order (:436), one pass over P
         f.update_multi(list(tags.keys()), [rec[4] for rec in tags.values()], [rec[5] for rec in tags.values()])
     mean, cov = f.state(n_new)
+    idx = np.linspace(0, cov.size - 1, num=min(cov.size, 257), dtype=np.int64)
+    _scalar_last.update(filter=f, mean=mean, cov=cov, mean_copy=mean.copy(), sample_idx=idx,
+                        cov_sample=cov.reshape(-1)[idx].copy())
     return mean, cov, tags
 
 
@@ -372,23 +403,45 @@ class BatchedEKF:
                   float(wheel_radius), float(baseline), int(resolution), _ptr(slot) if m else z,
                   _ptr(rng) if m else z, _ptr(brg) if m else z, m, _stream_ptr(self.torch))
 
+    def step_ticks_common(self, ticks_l, ticks_r, prev_l, prev_r, wheel_radius, baseline, resolution, slot=None,
+                          rng=None, brg=None):
+        """``step_ticks`` when every filter sees the same encoder ticks (four Python ints, no per-filter tensors)."""
+        m = 0 if slot is None else int(slot.shape[1])
+        z = C.c_void_p(0)
+        capi.call("ekf_batch_step_ticks_common", self._h, int(ticks_l), int(ticks_r), int(prev_l), int(prev_r),
+                  float(wheel_radius), float(baseline), int(resolution), _ptr(slot) if m else z,
+                  _ptr(rng) if m else z, _ptr(brg) if m else z, m, _stream_ptr(self.torch))
+
     def new_slot_table(self, n_tags: int):
         """Per-filter TAG_INDEX on the device: (tag_slot int32 [n_tags, B] filled with -1, n_seen int32 [B])."""
         t = self.torch
         return (t.full((int(n_tags), self.batch), -1, dtype=t.int32, device=self.dev),
                 t.zeros(self.batch, dtype=t.int32, device=self.dev))
 
-    def associate(self, det_tag, det_tx, det_tz, tag_slot, n_seen, m, noise_tx=None, noise_tz=None):
+    def associate(self, det_tag, det_tx, det_tz, tag_slot, n_seen, m, noise_tx=None, noise_tz=None, generated=None,
+                  out=None):
         """a3/a4 on the device for every filter (replay_no_ros.py:280-337): the window's detections — compact tag
         index int32 (D,), pose_t[0] and pose_t[2] (D,), optional per-filter perturbations (D, B) — become the
         (slot, rng, brg) tensors of shape (B, m) that ``step`` takes; ``tag_slot`` / ``n_seen`` are updated in
-        place. All arguments are DEVICE tensors."""
+        place. All arguments are DEVICE tensors. ``generated=(seed, step, first_filter, sigma)``: the perturbations
+        are generated inside the kernel (the numbers ``detection_noise`` would write) instead of read from arrays.
+        ``out=(slot, rng, brg)`` reuses output tensors."""
         t = self.torch
         d = int(det_tag.shape[0])
-        slot = t.empty((self.batch, m), dtype=t.int32, device=self.dev)
-        rng = t.empty((self.batch, m), dtype=t.float64, device=self.dev)
-        brg = t.empty((self.batch, m), dtype=t.float64, device=self.dev)
+        if out is None:
+            slot = t.empty((self.batch, m), dtype=t.int32, device=self.dev)
+            rng = t.empty((self.batch, m), dtype=t.float64, device=self.dev)
+            brg = t.empty((self.batch, m), dtype=t.float64, device=self.dev)
+        else:
+            slot, rng, brg = out
         z = C.c_void_p(0)
+        if generated is not None:
+            seed, step, first, sigma = generated
+            capi.call("ekf_batch_associate_generated", self._h, d, _ptr(det_tag) if d else z, _ptr(det_tx) if d else z,
+                      _ptr(det_tz) if d else z, int(seed), int(step), int(first), float(sigma),
+                      int(tag_slot.shape[0]), _ptr(tag_slot), _ptr(n_seen), _ptr(slot), _ptr(rng), _ptr(brg), int(m),
+                      _stream_ptr(t))
+            return slot, rng, brg
         capi.call("ekf_batch_associate", self._h, d, _ptr(det_tag) if d else z, _ptr(det_tx) if d else z,
                   _ptr(det_tz) if d else z, _ptr(noise_tx) if noise_tx is not None else z,
                   _ptr(noise_tz) if noise_tz is not None else z, int(tag_slot.shape[0]), _ptr(tag_slot),

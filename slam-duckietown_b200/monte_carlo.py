@@ -3,8 +3,9 @@ synthetic trajectory): B filters see the same encoder ticks and the same AprilTa
 process / measurement noise parameters and its own perturbation of the detections, and everything after the
 event parsing runs on the device:
 
-    windows_from_events (host, once)  ->  per step:  associate (a3/a4, per filter)  ->  step_ticks (a1/a2 + fused
-    a5-a11)  ->  accumulate_ate (against the stream's ground_truth events)
+    windows_from_events (host, once; all detections uploaded in one copy)  ->  per step:  associate (a3/a4 per
+    filter, the per-member detection noise generated inside the kernel)  ->  step_ticks_common (a1/a2 from the shared
+    encoder ticks + fused a5-a11)  ->  accumulate_ate (against the stream's ground_truth events)
 
 This is the README's ablation study (README.md:421-492: sweeps of MOTION_MODEL_VARIANCE / MEASUREMENT_MODEL_VARIANCE
 judged by eye on plots) as numbers: an absolute-trajectory RMSE per ensemble member. With zero perturbation and the
@@ -32,7 +33,8 @@ def compact_tag_table(windows, ignore_tags=()):
 def monte_carlo_replay(windows, batch, n_landmarks, m, motion_var, meas_var, det_sigma=0.0, seed=0,
                        ignore_tags=None, device=0, joseph=False, on_step=None, first_filter=0):
     """Returns dict(rmse (B,), pose (B,3), n_landmarks_seen (B,), faults, overflows, steps, tag_table (tag id ->
-    compact index), tag_slot (n_tags, B) per-member slot of each compact tag, filter=BatchedEKF).
+    compact index), tag_slot (n_tags, B) per-member slot of each compact tag, filter=BatchedEKF, last_step_args = the
+    arguments of the last ``step_ticks_common`` call).
 
     motion_var / meas_var: scalars or (B,) arrays (MOTION_MODEL_VARIANCE / MEASUREMENT_MODEL_VARIANCE per member);
     det_sigma: std-dev (m) of the per-member Gaussian perturbation of each detection's pose_t[0] / pose_t[2], drawn
@@ -52,20 +54,31 @@ def monte_carlo_replay(windows, batch, n_landmarks, m, motion_var, meas_var, det
     tag_slot, n_seen = f.new_slot_table(max(len(table), 1))
     sse = torch.zeros(batch, dtype=torch.float64, device=dev)
     scored = 0
-
-    def full(v):
-        return torch.full((batch,), int(v), dtype=torch.int32, device=dev)
+    last_args = None
+    # every window's detections go to the device in ONE copy (compact tag index, pose_t[0], pose_t[2] of all windows
+    # back to back); a window is then three views into those arrays
+    counts = [len(w.tag_id) for w in windows]
+    offs = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    if offs[-1]:
+        all_tag = np.concatenate([[table.get(int(t), -1) for t in w.tag_id] for w in windows if len(w.tag_id)])
+        packed = np.concatenate([all_tag.astype(np.float64), np.concatenate([w.tx for w in windows]),
+                                 np.concatenate([w.tz for w in windows])])
+    else:
+        packed = np.zeros(3)
+    dpk = torch.from_numpy(packed).to(dev)
+    total = int(offs[-1])
+    d_tag = dpk[:total].to(torch.int32)
+    d_tx, d_tz = dpk[total:2 * total], dpk[2 * total:3 * total]
+    out_bufs = (torch.empty((batch, m), dtype=torch.int32, device=dev),
+                torch.empty((batch, m), dtype=torch.float64, device=dev),
+                torch.empty((batch, m), dtype=torch.float64, device=dev))
     for step, w in enumerate(windows):
-        d = len(w.tag_id)
-        compact = torch.tensor([table.get(int(t), -1) for t in w.tag_id], dtype=torch.int32, device=dev)
-        tx = torch.from_numpy(w.tx).to(dev)
-        tz = torch.from_numpy(w.tz).to(dev)
-        ntx = ntz = None
-        if det_sigma > 0.0 and d:
-            ntx, ntz = f.detection_noise(seed, step, d, det_sigma, first_filter)
-        slot, rng, brg = f.associate(compact, tx, tz, tag_slot, n_seen, m, ntx, ntz)
-        f.step_ticks(full(w.ticks_l), full(w.ticks_r), full(w.prev_l), full(w.prev_r), WHEEL_RADIUS, BASELINE,
-                     RESOLUTION, slot, rng, brg)
+        lo, hi = int(offs[step]), int(offs[step + 1])
+        gen = (seed, step, first_filter, det_sigma) if (det_sigma > 0.0 and hi > lo) else None
+        slot, rng, brg = f.associate(d_tag[lo:hi], d_tx[lo:hi], d_tz[lo:hi], tag_slot, n_seen, m, generated=gen,
+                                     out=out_bufs)
+        last_args = (w.ticks_l, w.ticks_r, w.prev_l, w.prev_r, WHEEL_RADIUS, BASELINE, RESOLUTION, slot, rng, brg)
+        f.step_ticks_common(*last_args)
         if w.ground_truth is not None:
             f.accumulate_ate(w.ground_truth[0], w.ground_truth[1], sse)
             scored += 1
@@ -74,4 +87,5 @@ def monte_carlo_replay(windows, batch, n_landmarks, m, motion_var, meas_var, det
     rmse = torch.sqrt(sse / max(scored, 1)).cpu().numpy()
     return dict(rmse=rmse, pose=f.mu[:, :3].cpu().numpy(), n_landmarks_seen=n_seen.cpu().numpy(),
                 faults=f.fault_count(), overflows=f.associate_overflow_count(), steps=len(windows),
-                scored_steps=scored, tag_table=table, tag_slot=tag_slot.cpu().numpy(), filter=f)
+                scored_steps=scored, tag_table=table, tag_slot=tag_slot.cpu().numpy(), filter=f,
+                last_step_args=last_args)

@@ -73,7 +73,8 @@ class ShardedLargeMapEKF:
     def __init__(self, capacity: int, rank: int, world: int, device: int | None = None, group=None,
                  exchange: str = "nccl"):
         """exchange: "nccl" — export + two broadcasts per update through torch.distributed; "p2p" — the owners push
-        their rows into every rank's exchange area over NVLink peer memory (cudaIpc), no collective in the update."""
+        their rows into every rank's exchange area over NVLink peer memory (cudaIpc) from INSIDE the update's own two
+        kernels (gather: rows j, j+1; streaming: rows 0-2 for the next update), no collective and no extra launch."""
         self.capacity, self.rank, self.world, self.group = int(capacity), int(rank), int(world), group
         self.exchange = exchange
         self.ranges = row_partition(self.capacity, self.world)
@@ -124,6 +125,7 @@ class ShardedLargeMapEKF:
         self.local.P.zero_()
         if hi > lo:
             self.local.P[: hi - lo, :m] = torch.from_numpy(np.ascontiguousarray(blk)).to(self.local.P.device)
+        self.local.p2p_invalidate()
 
     def augment(self, slot: int, gx: float, gy: float):
         self.local.augment(slot, gx, gy)       # mu entries everywhere, diagonal on the owner only

@@ -367,12 +367,12 @@ def test_ekf3_surface(eb):
 @pytest.mark.parametrize("name", ["batched_b48_l20.npz", "batched_b32_l8.npz"])
 def test_batched_kernel_variants_bitwise_equal(eb, name, monkeypatch):
     """The W-in-registers kernel (default at 20 landmarks), the sub-warp group kernels (default at <= 8 landmarks),
-    the fully staged kernel and the streaming kernel apply the same per-element operation sequence: their states
+    and the fully staged kernel apply the same per-element operation sequence: their states
     must be BITWISE equal at every kept step."""
     import torch
     z = golden(name)
     outs = {}
-    variants = ("auto", "staged", "stream", "regw", "group8", "group16")
+    variants = ("auto", "staged", "regw", "group8", "group16")
     for variant in variants:
         monkeypatch.setenv("EKF_BATCH_KERNEL", variant)      # read by ekf_batch_create
         outs[variant], _ = _run_batched(eb, z)
@@ -609,7 +609,8 @@ def test_group_kernel_ragged_batch_and_mixed_observations(eb, monkeypatch):
     assert bool(torch.isfinite(res["regw"][0]).all())
 
 
-def test_p2p_row_exchange_two_processes(eb):
+@pytest.mark.parametrize("world", [2, 3])
+def test_p2p_row_exchange_two_processes(eb, world):
     """Row-block shards in TWO processes (one per rank, both on cuda:0 here; one per GPU on a multi-GPU box) exchange
     their rows over CUDA IPC peer memory — owners push, consumers wait on flags, no collective: every shard must equal
     the same rows of an unsharded filter BITWISE and no spin may have timed out."""
@@ -623,7 +624,6 @@ def test_p2p_row_exchange_two_processes(eb):
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
-    world = 2
     ndev = torch.cuda.device_count()
     procs = [subprocess.Popen([sys.executable, worker, str(r), str(world), str(port), str(r % ndev)],
                               stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True) for r in range(world)]
@@ -671,9 +671,11 @@ def test_ensemble_moments_match_numpy(eb, batch, n_lm):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("L,m,variants", [(8, 3, ("regw", "group8", "group16", "staged", "stream")),
+@pytest.mark.parametrize("L,m,variants", [(8, 3, ("regw", "group8", "group16", "staged")),
                                            (8, 4, ("regw", "group8", "staged")),
-                                           (20, 4, ("regw", "staged", "stream"))])
+                                           (20, 4, ("regw", "staged")),
+                                           (16, 6, ("auto", "regw", "staged")),      # the decoded-bag shape: K history re-read
+                                           (20, 5, ("regw", "staged"))])             # from shared memory for m > 4
 def test_batched_random_observation_patterns(eb, monkeypatch, L, m, variants):
     """Steady-state steps with RANDOM observation blocks per filter: any subset of the m entries empty (-1), the
     entries in random order, and the SAME landmark observed more than once in one step (the C-ABI takes any slot

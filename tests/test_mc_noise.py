@@ -160,3 +160,38 @@ def test_generated_monte_carlo_replay_per_member_parity_and_sharding_invariance(
     assert np.array_equal(np.concatenate([sse_a, sse_b]), sse)
     fa.close()
     fb.close()
+
+
+@pytest.mark.gpu
+def test_generated_association_and_common_ticks_equal_array_forms_bitwise(eb):
+    """ekf_batch_associate_generated (noise drawn inside the kernel) == ekf_batch_detection_noise arrays fed to
+    ekf_batch_associate; ekf_batch_step_ticks_common == ekf_batch_step_ticks with four constant tick arrays."""
+    import torch
+    B, L, m, D = 3001, 16, 6, 9
+    rs = np.random.default_rng(4)
+    res = []
+    for mode in ("arrays", "generated"):
+        f = eb.BatchedEKF(B, L)
+        f.init(0.1)
+        tag_slot, n_seen = f.new_slot_table(12)
+        for step in range(5):
+            st = np.random.default_rng(100 + step)
+            tags = torch.from_numpy(st.integers(0, 12, D).astype(np.int32)).to(f.dev)
+            tx = torch.from_numpy(st.normal(0, 0.3, D)).to(f.dev)
+            tz = torch.from_numpy(st.uniform(0.4, 1.45, D)).to(f.dev)
+            if mode == "arrays":
+                ntx, ntz = f.detection_noise(99, step, D, 0.03, first_filter=12345)
+                slot, rng, brg = f.associate(tags, tx, tz, tag_slot, n_seen, m, ntx, ntz)
+                full = [torch.full((B,), v, dtype=torch.int32, device=f.dev) for v in (1010 + 7 * step, 1012 + 6 * step,
+                                                                                      1003 + 7 * step, 1006 + 6 * step)]
+                f.step_ticks(*full, 0.0318, 0.1, 135, slot, rng, brg)
+            else:
+                slot, rng, brg = f.associate(tags, tx, tz, tag_slot, n_seen, m, generated=(99, step, 12345, 0.03))
+                f.step_ticks_common(1010 + 7 * step, 1012 + 6 * step, 1003 + 7 * step, 1006 + 6 * step, 0.0318, 0.1, 135,
+                                    slot, rng, brg)
+        assert f.fault_count() == 0
+        res.append((f.mu.clone(), f.P.clone(), tag_slot.clone(), n_seen.clone(), f.associate_overflow_count()))
+    for a, b in zip(res[0][:4], res[1][:4]):
+        assert torch.equal(a, b)
+    assert res[0][4] == res[1][4]
+    del rs

@@ -134,12 +134,12 @@ def test_golden_fixtures_regenerate_identically(ref, tmp_path, monkeypatch):
 @pytest.mark.skipif(not (ref_loader.source_available() and ref_loader.compiled_available()),
                     reason="needs both /root/reference and oracle/_ref")
 def test_compiled_reference_is_the_unmodified_source():
-    """oracle/_ref/replay_no_ros.pyc == compile(/root/reference/src/replay_no_ros.py): the travelling build output
+    """oracle/_ref/replay_no_ros.bytecode == compile(/root/reference/src/replay_no_ros.py): the travelling build output
     is the reference's own code, nothing added or removed."""
     src = os.path.join(ref_loader.REFERENCE_ROOT, "src", "replay_no_ros.py")
     with open(src) as fh:
         want = compile(fh.read(), src, "exec", dont_inherit=True)
-    with open(os.path.join(ref_loader.REF_BUILD_DIR, "replay_no_ros.pyc"), "rb") as fh:
+    with open(os.path.join(ref_loader.REF_BUILD_DIR, "replay_no_ros.bytecode"), "rb") as fh:
         fh.read(16)
         got = marshal.load(fh)
     assert marshal.dumps(got) == marshal.dumps(want)
