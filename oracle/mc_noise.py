@@ -10,10 +10,12 @@ place and this module reproduces it on the host for the per-member parity tests:
     implementation's known-answer vectors are checked in tests/test_mc_noise.py): key = (seed lo, seed hi),
     counter = (filter lo, filter hi, step, stream) -> four 32-bit words;
   * two uniforms in (0, 1): u = (k + 0.5) 2^-52 with k = (w0 >> 6) 2^26 + (w1 >> 6) (and w2, w3) — exact in float64;
-  * standard normals by the inverse CDF, Wichura's AS241 PPND16 (Appl. Statist. 37 (1988) 477-484), evaluated
-    with IEEE add / multiply / divide / sqrt ONLY, each rounded separately and in one fixed order (the device uses
-    __dadd_rn / __dmul_rn / __ddiv_rn / __dsqrt_rn: no FMA contraction), and a logarithm built from the same
-    operations (frexp + atanh series), so host and device agree in every bit.
+  * a PAIR of standard normals by Box-Muller, r = sqrt(-2 log u1), (r cos 2 pi u2, r sin 2 pi u2), with the logarithm
+    (frexp + atanh series) and the sine / cosine (octant reduction + Taylor polynomials on [0, pi/4]) built from IEEE
+    add / multiply / divide / sqrt ONLY, each rounded separately and in one fixed order (the device uses __dadd_rn /
+    __dmul_rn / __ddiv_rn / __dsqrt_rn: no FMA contraction), so host and device agree in every bit. Straight-line code:
+    a warp never diverges (the first cut used the inverse CDF AS241, whose tail branch almost every warp took:
+    89 us per 1 M filter-steps against 0.99 ms for the step itself, tools/mc_probe.py).
 """
 from __future__ import annotations
 
@@ -68,46 +70,44 @@ def det_log(x):
     return e * LN2 + (2.0 * s) * p
 
 
-A = [3.3871328727963666080, 1.3314166789178437745e+2, 1.9715909503065514427e+3, 1.3731693765509461125e+4,
-     4.5921953931549871457e+4, 6.7265770927008700853e+4, 3.3430575583588128105e+4, 2.5090809287301226727e+3]
-B = [1.0, 4.2313330701600911252e+1, 6.8718700749205790830e+2, 5.3941960214247511077e+3, 2.1213794301586595867e+4,
-     3.9307895800092710610e+4, 2.8729085735721942674e+4, 5.2264952788528545610e+3]
-C = [1.42343711074968357734, 4.63033784615654529590, 5.76949722146069140550, 3.64784832476320460504,
-     1.27045825245236838258, 2.41780725177450611770e-1, 2.27238449892691845833e-2, 7.74545014278341407640e-4]
-D = [1.0, 2.05319162663775882187, 1.67638483018380384940, 6.89767334985100004550e-1, 1.48103976427480074590e-1,
-     1.51986665636164571966e-2, 5.47593808499534494600e-4, 1.05075007164441684324e-9]
-E = [6.65790464350110377720, 5.46378491116411436990, 1.78482653991729133580, 2.96560571828504891230e-1,
-     2.65321895265761230930e-2, 1.24266094738807843860e-3, 2.71155556874348757815e-5, 2.01033439929228813265e-7]
-F = [1.0, 5.99832206555887937690e-1, 1.36929880922735805310e-1, 1.48753612908506148525e-2,
-     7.86869131145613259100e-4, 1.84631831751005468180e-5, 1.42151175831644588870e-7, 2.04426310338993978564e-15]
+PIO4 = 0.7853981633974483
+SIN_COEF = [-1.0 / 6.0, 1.0 / 120.0, -1.0 / 5040.0, 1.0 / 362880.0, -1.0 / 39916800.0, 1.0 / 6227020800.0,
+            -1.0 / 1307674368000.0, 1.0 / 355687428096000.0]
+COS_COEF = [-1.0 / 2.0, 1.0 / 24.0, -1.0 / 720.0, 1.0 / 40320.0, -1.0 / 3628800.0, 1.0 / 479001600.0,
+            -1.0 / 87178291200.0, 1.0 / 20922789888000.0]
 
 
-def _horner(coef, r):
-    p = np.full_like(r, coef[7])
-    for k in range(6, -1, -1):
-        p = p * r + coef[k]
-    return p
+def sincos_2pi(t):
+    """(sin, cos) of 2 pi t for t in [0, 1): octant k = floor(8 t) (exact), Taylor polynomials on [0, pi/4] in a fixed
+    IEEE add / mul order, octant symmetries by selection and sign."""
+    t = np.asarray(t, dtype=np.float64)
+    x = t * 8.0
+    k = np.floor(x)
+    f = x - k
+    ki = k.astype(np.int64)
+    g = np.where((ki & 1) == 1, 1.0 - f, f)
+    a = g * PIO4
+    a2 = a * a
+    ps = np.full_like(a, SIN_COEF[7])
+    pc = np.full_like(a, COS_COEF[7])
+    for i in range(6, -1, -1):
+        ps = ps * a2 + SIN_COEF[i]
+        pc = pc * a2 + COS_COEF[i]
+    sa = a + a * (a2 * ps)
+    ca = 1.0 + a2 * pc
+    swap = (((ki + 1) >> 1) & 1) == 1
+    s = np.where(swap, ca, sa)
+    c = np.where(swap, sa, ca)
+    s = np.where(ki >= 4, -s, s)
+    c = np.where((ki >= 2) & (ki <= 5), -c, c)
+    return s, c
 
 
-def normal_icdf(u):
-    """Standard-normal quantile of u in (0, 1): AS241 PPND16, fixed operation order (see module docstring)."""
-    u = np.asarray(u, dtype=np.float64)
-    q = u - 0.5
-    out = np.empty_like(u)
-    central = np.abs(q) <= 0.425
-    r = 0.180625 - q * q
-    with np.errstate(invalid="ignore", divide="ignore"):
-        out_c = q * _horner(A, r) / _horner(B, r)
-        rt = np.where(q < 0.0, u, 1.0 - u)
-        rt = np.sqrt(-det_log(np.where(central, 0.25, rt)))
-        r1 = rt - 1.6
-        v1 = _horner(C, r1) / _horner(D, r1)
-        r2 = rt - 5.0
-        v2 = _horner(E, r2) / _horner(F, r2)
-    tail = np.where(rt <= 5.0, v1, v2)
-    tail = np.where(q < 0.0, -tail, tail)
-    out = np.where(central, out_c, tail)
-    return out
+def box_muller(u1, u2):
+    """Two independent standard normals from two uniforms in (0, 1): r = sqrt(-2 log u1), (r cos 2 pi u2, r sin 2 pi u2)."""
+    r = np.sqrt(-2.0 * det_log(u1))
+    s, c = sincos_2pi(u2)
+    return r * c, r * s
 
 
 def normal_pair(seed, filt, step, stream):
@@ -117,7 +117,7 @@ def normal_pair(seed, filt, step, stream):
     w = philox4x32_10((filt & MASK32).astype(np.uint32), (filt >> np.uint64(32)).astype(np.uint32),
                       np.asarray(step, dtype=np.uint32), np.asarray(stream, dtype=np.uint32),
                       np.uint32(seed & 0xFFFFFFFF), np.uint32((seed >> 32) & 0xFFFFFFFF))
-    return normal_icdf(uniform52(w[0], w[1])), normal_icdf(uniform52(w[2], w[3]))
+    return box_muller(uniform52(w[0], w[1]), uniform52(w[2], w[3]))
 
 
 # streams of one filter-step (ekf_philox.cuh: kStreamOdometry, kStreamObservation0, kStreamDetection0)

@@ -750,13 +750,22 @@ int ekf_lm_augment(ekf_lm_t* h, int slot, double gx, double gy, void* stream) {
   return EKF_OK;
 }
 
+// The robot rows pre-pushed for update p2p_seq + 1 have gone stale (predict, external write to P). Their flag already
+// carries the number p2p_seq + 1, so that number is BURNT: the next update takes p2p_seq + 2 and rank 0's gather pushes
+// fresh rows under it — a waiter can never mistake the stale push for the fresh one. Every rank makes the same calls
+// in the same order, so the numbering stays in step; acks and flags are compared with >=, so a skipped number is fine.
+static void p2p_drop_prepush(ekf_lm_t* h) {
+  if (h->p2p_robot_seq != 0 && h->p2p_robot_seq == h->p2p_seq + 1) ++h->p2p_seq;
+  h->p2p_robot_seq = 0;
+}
+
 int ekf_lm_predict(ekf_lm_t* h, double ang, double lin, void* stream) {
   if (!h) return fail(EKF_EINVAL, "null handle");
   if (!h->P) return fail(EKF_ESTATE, "state not bound");
   CU(cudaSetDevice(h->device));
   CU(ekf::lm_launch_predict(h->mu, h->P, h->ld, h->n, h->row_begin, h->row_end, h->scal, ang, lin, h->mv,
                             h->flags, (cudaStream_t)stream));
-  h->p2p_robot_seq = 0;  // rows 0-1 and the pose changed: the robot rows pre-pushed by the last update are stale
+  p2p_drop_prepush(h);  // rows 0-1 and the pose changed: the robot rows pre-pushed by the last update are stale
   return EKF_OK;
 }
 
@@ -1082,7 +1091,7 @@ int ekf_lm_p2p_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const
 
 int ekf_lm_p2p_invalidate(ekf_lm_t* h) {
   if (!h) return fail(EKF_EINVAL, "null handle");
-  h->p2p_robot_seq = 0;
+  p2p_drop_prepush(h);
   return EKF_OK;
 }
 

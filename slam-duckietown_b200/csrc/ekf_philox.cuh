@@ -4,8 +4,8 @@
 // Every perturbation of the batched Monte Carlo mode is a pure function of (seed, GLOBAL filter index, step, stream):
 //   Philox4x32-10 (Salmon et al., SC'11), key = (seed lo, seed hi), counter = (filter lo, filter hi, step, stream)
 //   -> two uniforms u = (k + 0.5) 2^-52, k = (w0 >> 6) 2^26 + (w1 >> 6)   (exact in fp64, strictly inside (0, 1))
-//   -> two standard normals by the inverse CDF (Wichura's AS241 PPND16).
-// The inverse CDF and its logarithm use ONLY IEEE add / multiply / divide / sqrt, each rounded separately in a fixed
+//   -> a pair of standard normals by Box-Muller: r = sqrt(-2 log u1), (r cos 2 pi u2, r sin 2 pi u2).
+// The logarithm and the sine / cosine use ONLY IEEE add / multiply / divide / sqrt, each rounded separately in a fixed
 // order (__dadd_rn / __dmul_rn / __ddiv_rn / __dsqrt_rn: the compiler may not contract them into FMAs), which is
 // what numpy does on the host — so an ensemble member's inputs can be regenerated off the device and replayed through
 // the oracle, whatever the sharding (the counter holds the global filter index, not the rank-local one).
@@ -73,46 +73,32 @@ __device__ __forceinline__ double det_log(double x) {
   return pn_add(pn_mul((double)e, 0.6931471805599453), pn_mul(pn_mul(2.0, s), p));
 }
 
-#define EKF_PN_HORNER(r, c0, c1, c2, c3, c4, c5, c6, c7)                                                        \
-  pn_add(pn_mul(pn_add(pn_mul(pn_add(pn_mul(pn_add(pn_mul(pn_add(pn_mul(pn_add(pn_mul(pn_add(pn_mul((c7), (r)), \
-  (c6)), (r)), (c5)), (r)), (c4)), (r)), (c3)), (r)), (c2)), (r)), (c1)), (r)), (c0))
-
-// standard-normal quantile of u in (0, 1): AS241 PPND16, operation order == oracle/mc_noise.py:normal_icdf
-__device__ __forceinline__ double normal_icdf(double u) {
-  const double q = pn_sub(u, 0.5);
-  if (fabs(q) <= 0.425) {
-    const double r = pn_sub(0.180625, pn_mul(q, q));
-    const double num = EKF_PN_HORNER(r, 3.3871328727963666080, 1.3314166789178437745e+2, 1.9715909503065514427e+3,
-                                     1.3731693765509461125e+4, 4.5921953931549871457e+4, 6.7265770927008700853e+4,
-                                     3.3430575583588128105e+4, 2.5090809287301226727e+3);
-    const double den = EKF_PN_HORNER(r, 1.0, 4.2313330701600911252e+1, 6.8718700749205790830e+2,
-                                     5.3941960214247511077e+3, 2.1213794301586595867e+4, 3.9307895800092710610e+4,
-                                     2.8729085735721942674e+4, 5.2264952788528545610e+3);
-    return pn_div(pn_mul(q, num), den);
-  }
-  double r = (q < 0.0) ? u : pn_sub(1.0, u);
-  r = __dsqrt_rn(-det_log(r));
-  double v;
-  if (r <= 5.0) {
-    r = pn_sub(r, 1.6);
-    const double num = EKF_PN_HORNER(r, 1.42343711074968357734, 4.63033784615654529590, 5.76949722146069140550,
-                                     3.64784832476320460504, 1.27045825245236838258, 2.41780725177450611770e-1,
-                                     2.27238449892691845833e-2, 7.74545014278341407640e-4);
-    const double den = EKF_PN_HORNER(r, 1.0, 2.05319162663775882187, 1.67638483018380384940,
-                                     6.89767334985100004550e-1, 1.48103976427480074590e-1, 1.51986665636164571966e-2,
-                                     5.47593808499534494600e-4, 1.05075007164441684324e-9);
-    v = pn_div(num, den);
-  } else {
-    r = pn_sub(r, 5.0);
-    const double num = EKF_PN_HORNER(r, 6.65790464350110377720, 5.46378491116411436990, 1.78482653991729133580,
-                                     2.96560571828504891230e-1, 2.65321895265761230930e-2, 1.24266094738807843860e-3,
-                                     2.71155556874348757815e-5, 2.01033439929228813265e-7);
-    const double den = EKF_PN_HORNER(r, 1.0, 5.99832206555887937690e-1, 1.36929880922735805310e-1,
-                                     1.48753612908506148525e-2, 7.86869131145613259100e-4, 1.84631831751005468180e-5,
-                                     1.42151175831644588870e-7, 2.04426310338993978564e-15);
-    v = pn_div(num, den);
-  }
-  return (q < 0.0) ? -v : v;
+// (sin, cos) of 2 pi t, t in [0, 1): octant k = floor(8 t) (exact), Taylor polynomials on [0, pi/4], octant symmetries
+// by selection and sign — operation order == oracle/mc_noise.py:sincos_2pi. Straight-line.
+__device__ __forceinline__ void sincos_2pi(double t, double* s, double* c) {
+  const double x = pn_mul(t, 8.0);
+  const double kf = floor(x);
+  const double f = pn_sub(x, kf);
+  const int k = (int)kf;
+  const double g = (k & 1) ? pn_sub(1.0, f) : f;
+  const double a = pn_mul(g, 0.7853981633974483);
+  const double a2 = pn_mul(a, a);
+  double ps = 1.0 / 355687428096000.0, pc = 1.0 / 20922789888000.0;
+  ps = pn_add(pn_mul(ps, a2), -1.0 / 1307674368000.0); pc = pn_add(pn_mul(pc, a2), -1.0 / 87178291200.0);
+  ps = pn_add(pn_mul(ps, a2), 1.0 / 6227020800.0);     pc = pn_add(pn_mul(pc, a2), 1.0 / 479001600.0);
+  ps = pn_add(pn_mul(ps, a2), -1.0 / 39916800.0);      pc = pn_add(pn_mul(pc, a2), -1.0 / 3628800.0);
+  ps = pn_add(pn_mul(ps, a2), 1.0 / 362880.0);         pc = pn_add(pn_mul(pc, a2), 1.0 / 40320.0);
+  ps = pn_add(pn_mul(ps, a2), -1.0 / 5040.0);          pc = pn_add(pn_mul(pc, a2), -1.0 / 720.0);
+  ps = pn_add(pn_mul(ps, a2), 1.0 / 120.0);            pc = pn_add(pn_mul(pc, a2), 1.0 / 24.0);
+  ps = pn_add(pn_mul(ps, a2), -1.0 / 6.0);             pc = pn_add(pn_mul(pc, a2), -1.0 / 2.0);
+  const double sa = pn_add(a, pn_mul(a, pn_mul(a2, ps)));
+  const double ca = pn_add(1.0, pn_mul(a2, pc));
+  const bool swap = ((k + 1) >> 1) & 1;
+  double ss = swap ? ca : sa, cc = swap ? sa : ca;
+  if (k >= 4) ss = -ss;
+  if (k >= 2 && k <= 5) cc = -cc;
+  *s = ss;
+  *c = cc;
 }
 
 // the two standard normals of (seed, global filter index, step, stream)
@@ -120,8 +106,12 @@ __device__ __forceinline__ void normal_pair(uint64_t seed, uint64_t filter, uint
                                             double* z1) {
   const Philox4 w = philox4x32_10((uint32_t)filter, (uint32_t)(filter >> 32), step, stream, (uint32_t)seed,
                                   (uint32_t)(seed >> 32));
-  *z0 = normal_icdf(uniform52(w.x, w.y));
-  *z1 = normal_icdf(uniform52(w.z, w.w));
+  // Box-Muller: r = sqrt(-2 log u1), (r cos 2 pi u2, r sin 2 pi u2)
+  const double r = __dsqrt_rn(pn_mul(-2.0, det_log(uniform52(w.x, w.y))));
+  double sn, cs;
+  sincos_2pi(uniform52(w.z, w.w), &sn, &cs);
+  *z0 = pn_mul(r, cs);
+  *z1 = pn_mul(r, sn);
 }
 #endif  // __CUDACC__
 

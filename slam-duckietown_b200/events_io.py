@@ -70,7 +70,7 @@ def read_events(path) -> list[Event]:
 def format_event(ev: Event) -> str:
     """The writer's formatting (decode_bag_file.py:337-347): non-string data goes through repr()."""
     if ev.kind == "ground_truth":
-        data = f"{ev.data[0]!r},{ev.data[1]!r}"
+        data = f"{ev.data[0]!r}, {ev.data[1]!r}"          # "x, y" with the decoder's blank (decode_bag_file.py:178)
     elif isinstance(ev.data, str):
         data = ev.data
     else:
@@ -162,4 +162,79 @@ def windows_from_events(events: Iterable[Event], detections: dict) -> list[StepW
                                   frames))
             prev_l, prev_r = cur_l, cur_r
             tag, tx, tz, frames = [], [], [], []
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# ground-truth alignment (scripts/decode_bag_file.py:111-253 `get_ground_truth`)
+# ---------------------------------------------------------------------------------------------------------
+def capture_window_from_xcp(path) -> tuple[float, float]:
+    """(start, end) of the Vicon capture as POSIX seconds from the system file's ``Camera/Capture`` element, with the
+    decoder's fixed UTC-5 correction (decode_bag_file.py:128-133)."""
+    import xml.etree.ElementTree as ET
+    from datetime import datetime, timedelta
+    cap = ET.parse(path).getroot().find("Camera/Capture")
+    shift = timedelta(hours=5).total_seconds()
+    return (datetime.fromisoformat(cap.get("START_TIME")).timestamp() + shift,
+            datetime.fromisoformat(cap.get("END_TIME")).timestamp() + shift)
+
+
+def _vicon_rows(path, skip=5):
+    with open(path, "r") as fh:
+        for _ in range(skip):
+            fh.readline()
+        return [line.split(",") for line in fh.read().strip().splitlines()]
+
+
+def _into_start_frame(ax, ay, x, y, theta):
+    """The decoder's ``rotate_around`` (decode_bag_file.py:107-109): (x, y) turned by +theta about (ax, ay)."""
+    from math import cos, sin
+    return ax + (x - ax) * cos(theta) - (y - ay) * sin(theta), ay + (x - ax) * sin(theta) + (y - ay) * cos(theta)
+
+
+def ground_truth_events(first_timestamp: float, robot_csv, trajectories_csv, start_capture_time: float,
+                        end_capture_time: float, delay: float = 0.0) -> list[Event]:
+    """Vicon exports -> the ``landmarks`` event (at ``first_timestamp``) and one ``ground_truth`` event per valid robot
+    frame, in the frame of the robot pose closest in time to the bag's first event, metres. Semantics of the decoder,
+    including its quirks:
+
+    * frame -> time: ``frame / framerate + start + delay`` with ``framerate = round(all rows / capture length)``
+      (:151-157); only rows with exactly 8 fields are poses (:150);
+    * the start pose is the one closest in time to ``first_timestamp``; more than 2 s away is an error (:160-167,
+      raised here where the decoder exits);
+    * every position is turned about the start position by +RZ of the start pose, shifted to it and divided by 1000
+      (:170-181) — positions only, no heading;
+    * landmarks: per marker the midpoint of the min / max of its x and y over the capture (:199-229), a coordinate of
+      exactly 0 counting as missing (``!= False``); markers never seen are skipped here (the decoder would fail on
+      them); the de-duplication test compares the raw millimetre midpoint with the already NORMALISED landmarks
+      (:233-238), so it only ever fires by coincidence — kept as is.
+    """
+    rows = _vicon_rows(robot_csv)
+    framerate = round(len(rows) / (end_capture_time - start_capture_time))
+    poses = [tuple(float(v) for v in r) for r in rows if len(r) == 8]
+    timed = [(int(p[0]) / framerate + start_capture_time + delay,) + p[1:] for p in poses]
+    start = min(timed, key=lambda p: abs(p[0] - first_timestamp))
+    if abs(start[0] - first_timestamp) > 2:
+        raise ValueError("no ground-truth pose within 2 s of the bag's first event "
+                         f"(closest differs by {start[0] - first_timestamp:.3f} s): pass a delay")
+    th0, x0, y0 = start[4], start[5], start[6]
+    out = []
+    for p in timed:
+        x, y = _into_start_frame(x0, y0, p[5], p[6], th0)
+        out.append(Event(p[0], "ground_truth", ((x - x0) / 1000, (y - y0) / 1000)))
+    marks = [r for r in _vicon_rows(trajectories_csv) if len(r) > 4]
+    vals = [[float(v) if v != "" else 0.0 for v in r] for r in marks]     # 0.0 doubles as "missing", as in the decoder
+    n_marks = (len(vals[0]) + 1) // 3 if vals else 0                      # len(time-stamped row) // 3 (:197)
+    landmarks = []
+    for k in range(n_marks):
+        xs = [v[3 * k + 2] for v in vals if len(v) > 3 * k + 2 and v[3 * k + 2] != 0.0]
+        ys = [v[3 * k + 3] for v in vals if len(v) > 3 * k + 3 and v[3 * k + 3] != 0.0]
+        if not xs or not ys:
+            continue
+        mx, my = (max(xs) + min(xs)) / 2, (max(ys) + min(ys)) / 2
+        if any((mx - lx) ** 2 + (my - ly) ** 2 < 10 ** 2 for lx, ly in landmarks):
+            continue
+        x, y = _into_start_frame(x0, y0, mx, my, th0)
+        landmarks.append(((x - x0) / 1000, (y - y0) / 1000))
+    out.insert(0, Event(first_timestamp, "landmarks", landmarks))
     return out

@@ -26,15 +26,20 @@ def test_uniforms_strictly_inside_unit_interval():
     assert 0.0 < lo[0] == 2.0 ** -53 and hi[0] == 1.0 - 2.0 ** -53 < 1.0
 
 
-def test_inverse_cdf_and_log_accuracy():
-    from scipy.special import ndtri
-    u = np.concatenate([np.linspace(1e-10, 0.999999, 200001), 1 - np.logspace(-16, -1, 1000), np.logspace(-300, -1, 3000),
-                        [2.0 ** -53, 1 - 2.0 ** -53, 0.5, 0.075, 0.925]])
-    u = u[(u > 0) & (u < 1)]
-    z, zr = mn.normal_icdf(u), ndtri(u)
-    assert np.max(np.abs(z - zr) / np.maximum(np.abs(zr), 1e-3)) < 5e-15
-    x = np.concatenate([np.logspace(-300, 0, 5000), np.linspace(1e-3, 0.5, 5000)])
+def test_log_and_sincos_accuracy():
+    x = np.concatenate([np.logspace(-300, 0, 5000), np.linspace(1e-3, 1.0, 5000), [2.0 ** -53, 1 - 2.0 ** -53]])
     assert np.max(np.abs(mn.det_log(x) - np.log(x)) / np.maximum(np.abs(np.log(x)), 1e-3)) < 1e-15
+    t = np.concatenate([np.linspace(0, 1, 200001)[:-1], [2.0 ** -53, 1 - 2.0 ** -53, 0.125, 0.25, 0.375, 0.5, 0.625, 0.75, 0.875]])
+    s, c = mn.sincos_2pi(t)
+    assert np.max(np.abs(s - np.sin(2 * np.pi * t))) < 1e-15 and np.max(np.abs(c - np.cos(2 * np.pi * t))) < 1e-15
+    assert np.max(np.abs(s * s + c * c - 1.0)) < 1e-15
+
+
+def test_box_muller_reaches_the_tails():
+    z0, z1 = mn.box_muller(np.array([2.0 ** -53, 0.5, 1 - 2.0 ** -53]), np.array([0.0 + 2.0 ** -53, 0.25, 0.5]))
+    assert abs(np.hypot(z0[0], z1[0]) - np.sqrt(-2 * np.log(2.0 ** -53))) < 1e-12      # 8.57 sigma
+    assert abs(z0[1]) < 1e-15 and abs(z1[1] - np.sqrt(2 * np.log(2))) < 1e-15
+    assert np.hypot(z0[2], z1[2]) < 2e-8
 
 
 def test_normal_pairs_look_normal_and_streams_are_independent():
