@@ -579,6 +579,37 @@ def bench_large_map(updates=60, warm=6):
                                    "(16 n^2 + 3 x 96 n bytes per step), bitwise equal to 3 ekf_lm_update calls"}}
 
 
+def sustained_copy_reference(local, seconds=2.0):
+    """The denominator for the `sustained` figures: >= `seconds` of back-to-back device-to-device copies between two
+    2 GiB buffers (read + write bytes / time, per chunk of 20 copies), SM clock / power / throttle reasons sampled
+    alongside — what the HBM system itself sustains on THIS box under its power cap. Measurement only (torch copy_)."""
+    import torch
+    n = 1 << 28                                            # 2 GiB of doubles
+    a = torch.empty(n, dtype=torch.float64, device=f"cuda:{local}")
+    b = torch.empty_like(a)
+    a.fill_(1.0)
+    for _ in range(3):
+        b.copy_(a)
+    torch.cuda.synchronize()
+    per_copy_s = 2 * n * 8 / 6.5e12
+    chunk = 20
+    n_chunks = max(int(seconds / (per_copy_s * chunk)) + 1, 4)
+    clk = ClockSampler(local).start()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(n_chunks + 1)]
+    ev[0].record()
+    for c in range(n_chunks):
+        for _ in range(chunk):
+            b.copy_(a)
+        ev[c + 1].record()
+    torch.cuda.synchronize()
+    c_out = clk.stop()
+    gbs = np.array([chunk * 2 * n * 8 / (ev[c].elapsed_time(ev[c + 1]) * 1e-3) / 1e9 for c in range(n_chunks)])
+    del a, b
+    torch.cuda.empty_cache()
+    return {"gbs_median": float(np.median(gbs)), "gbs_first_chunk": float(gbs[0]), "gbs_last_chunk": float(gbs[-1]),
+            "seconds": float(sum(ev[c].elapsed_time(ev[c + 1]) for c in range(n_chunks)) / 1e3), "clocks": c_out}
+
+
 def _surrogate():
     """The decoded-bag fixture (tests/golden/surrogate: events.csv + detections sidecar synthesised from the bundled
     Vicon ground truth; the real .bag is not in the container)."""
@@ -900,6 +931,12 @@ def run_own_arm(args, wk, world):
         line["sustained"] = run.sustained(args.sustained_seconds, local, kern_ms)
     run.close()
     del run
+    copy_ref = None
+    if world == 1 and not args.no_sustained:
+        copy_ref = sustained_copy_reference(local, args.sustained_seconds)
+        line["sustained"]["copy_reference"] = copy_ref
+        line["sustained"]["roofline"]["frac_of_sustained_copy"] = (line["sustained"]["roofline"]["achieved"]
+                                                                   / copy_ref["gbs_median"])
 
     if world == 1:
         if not args.no_cpu_baseline and rank == 0:
@@ -918,6 +955,13 @@ def run_own_arm(args, wk, world):
         if not args.no_large_map:
             line["large_map"] = bench_large_map()
             if args.workload == "B":
+                wj = Workload("B", 1)
+                rj = BatchedRun(wj, local, rank, joseph=True, distinct=8)
+                line["joseph"] = batched_object(wj, rj, 20, 3, 1, rank=0, with_e2e=False)
+                line["joseph"]["cov_form"] = ("one-pass rank-4 Joseph form (SURVEY.md App. A.4) on the dispatched "
+                                              "W-in-registers kernel; same bytes as the plain form")
+                line["joseph"]["vs_plain"] = line["joseph"]["value"] / line["value"]
+                rj.close()
                 line["bag_ensemble"] = bench_bag_ensemble(local)
                 line["config1_replay"] = bench_config1()
                 wm = Workload("M", 1)
@@ -925,6 +969,9 @@ def run_own_arm(args, wk, world):
                 line["small_filters"] = batched_object(wm, rm, 20, 3, 1, rank=0, with_e2e=True,
                                                        sustained_s=0.0 if args.no_sustained else args.sustained_seconds,
                                                        local=local)
+                if copy_ref and "sustained" in line["small_filters"]:
+                    sm_ = line["small_filters"]["sustained"]
+                    sm_["roofline"]["frac_of_sustained_copy"] = sm_["roofline"]["achieved"] / copy_ref["gbs_median"]
                 rm.close()
     else:
         # the sharded modes on the line the driver runs (VERDICT r1 missing #1): strong-split config M with its own

@@ -271,11 +271,11 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
         kk.y = dot2(pht0[p], Si[0][1], pht1[p], Si[1][1]);
         *reinterpret_cast<d2*>(ku + 2 * t) = kk;  // zero for the pad row
         if (JOSEPH) {
-          wu[t] = hp0[p] - qn * kk.x;
-          wu[LD + t] = hp1[p] - qn * kk.y;
+          wu[t] = joseph_w(hp0[p], qn, kk.x);
+          wu[LD + t] = joseph_w(hp1[p], qn, kk.y);
           d2 av;
-          av.x = pht0[p] - (kk.x * Sq[0][0] + kk.y * Sq[1][0]);
-          av.y = pht1[p] - (kk.x * Sq[0][1] + kk.y * Sq[1][1]);
+          av.x = joseph_a(pht0[p], kk.x, kk.y, Sq[0][0], Sq[1][0]);
+          av.y = joseph_a(pht1[p], kk.x, kk.y, Sq[0][1], Sq[1][1]);
           *reinterpret_cast<d2*>(sA + u * HIST + 2 * t) = av;
         }
         if (t < N) sMu[t] = mu_inc(sMu[t], kk.x, kk.y, in.y0, in.y1);

@@ -32,14 +32,15 @@ bool batch_capacity_supported(int n_landmarks);
 size_t batch_step_smem_bytes(int n_landmarks, int m, bool joseph);
 cudaError_t batch_launch_step(int n_landmarks, const BatchStepArgs& a, int64_t batch, bool joseph,
                               cudaStream_t st);
-// W-in-registers variant (ekf_batched_regw.cu): plain covariance form, 1 <= m <= 6 observation slots
-bool batch_regw_supported(int m);
-size_t batch_regw_smem_bytes(int n_landmarks, int m);
-cudaError_t batch_launch_step_regw(int n_landmarks, const BatchStepArgs& a, int64_t batch, cudaStream_t st);
-// sub-warp groups for small filters (ekf_batched_group.cu): 8 or 16 lanes per filter, plain form, 1 <= m <= 4
+// W-in-registers variant (ekf_batched_regw.cu): plain form with 1-6 observation slots, Joseph form with 1-4
+bool batch_regw_supported(int m, bool joseph);
+size_t batch_regw_smem_bytes(int n_landmarks, int m, bool joseph);
+cudaError_t batch_launch_step_regw(int n_landmarks, const BatchStepArgs& a, int64_t batch, bool joseph,
+                                   cudaStream_t st);
+// sub-warp groups for small filters (ekf_batched_group.cu): 8 or 16 lanes per filter, 1 <= m <= 4; both forms
 bool batch_group_supported(int n_landmarks, int m);
 cudaError_t batch_launch_step_group(int n_landmarks, int group_width, const BatchStepArgs& a, int64_t batch,
-                                    cudaStream_t st);
+                                    bool joseph, cudaStream_t st);
 cudaError_t batch_launch_init(double* mu, double* P, int* n_known, int64_t batch, int n, int ld, double p0,
                               cudaStream_t st);
 cudaError_t batch_launch_pack(double* mu, double* P, const double* mean_ref, const double* cov_ref,

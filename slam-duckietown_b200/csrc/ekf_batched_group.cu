@@ -40,17 +40,18 @@ __device__ __forceinline__ double gcol(unsigned gmask, const double (&x)[NT], in
   return gshfl<GW>(gmask, mine, c - p * GW);
 }
 
-__host__ __device__ constexpr int group_slice_doubles(int nlm, int m, int gw) {
+__host__ __device__ constexpr int group_slice_doubles(int nlm, int m, int gw, bool joseph) {
   const int n = 3 + 2 * nlm, ld = (n + 3) & ~3;
-  const int raw = n * ld + ld + m * 2 * ld + 2;
+  const int raw = n * ld + ld + m * 2 * ld * (joseph ? 2 : 1) + 2;
   return gw == 8 ? raw + ((8 - raw % 16) + 16) % 16 : raw;
 }
 
 }  // namespace
 
 // 16 resident one-warp CTAs per SM: 128 registers per thread = four warps per scheduler's register file
-template <int NLM, int MT, int GW>
-__global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs a, int64_t batch, int pf) {
+// JOSEPH: one-pass rank-4 Joseph form, same per-element operation sequence as the staged kernel
+template <int NLM, int MT, int GW, bool JOSEPH>
+__global__ void __launch_bounds__(32, JOSEPH ? 12 : 16) batch_step_group_kernel(BatchStepArgs a, int64_t batch, int pf) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
   constexpr int HIST = 2 * LD;          // doubles of one update's K record: [LD][2]
@@ -59,7 +60,7 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
   constexpr int m = MT;
   // doubles of shared memory per filter; with four groups the slices start 64 bytes apart modulo the 128-byte bank
   // period, so the four 64-byte row segments the groups read in one instruction fall into two full wavefronts
-  constexpr int SLICE = group_slice_doubles(NLM, MT, GW);
+  constexpr int SLICE = group_slice_doubles(NLM, MT, GW, JOSEPH);
   static_assert(GW == 8 || GW == 16, "group width");
   static_assert(MT >= 1 && MT <= GW && MT <= BATCH_MAX_M, "observation count");
   static_assert(SLICE % 2 == 0, "16-byte aligned slices");
@@ -73,7 +74,8 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
   double* sP = reinterpret_cast<double*>(smem_raw) + g * SLICE;  // [N][LD]
   double* sMu = sP + N * LD;                                     // [LD]
   double* sK = sMu + LD;                                         // [m][LD][2]  (K_u[i,0], K_u[i,1]) pairs
-  uint64_t* bar = reinterpret_cast<uint64_t*>(sK + m * HIST);    // [2]: mu, P
+  double* sA = sK + m * HIST;                                    // [m][LD][2]  AHt_u pairs (Joseph only)
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sA + (JOSEPH ? m * HIST : 0));  // [2]: mu, P
   double* __restrict__ gP = a.P + b * (int64_t)(N * LD);
   double* __restrict__ gMu = a.mu + b * (int64_t)LD;
 
@@ -268,12 +270,27 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
       const d2 kj0 = lds128(sK + w * HIST + 2 * j), kj1 = lds128(sK + w * HIST + 2 * j + 2);
       const double w0j0 = gcol<GW, NT>(gmask, hW0[w], j), w1j0 = gcol<GW, NT>(gmask, hW1[w], j);
       const double w0j1 = gcol<GW, NT>(gmask, hW0[w], j + 1), w1j1 = gcol<GW, NT>(gmask, hW1[w], j + 1);
+      d2 aj0, aj1;
+      if (JOSEPH) {
+        aj0 = lds128(sA + w * HIST + 2 * j);
+        aj1 = lds128(sA + w * HIST + 2 * j + 2);
+      }
 #pragma unroll
       for (int p = 0; p < NT; ++p) {
         lr[0][p] = rank2(lr[0][p], kj0.x, kj0.y, hW0[w][p], hW1[w][p]);
         lr[1][p] = rank2(lr[1][p], kj1.x, kj1.y, hW0[w][p], hW1[w][p]);
         lc[0][p] = rank2(lc[0][p], hK[w][p].x, hK[w][p].y, w0j0, w1j0);
         lc[1][p] = rank2(lc[1][p], hK[w][p].x, hK[w][p].y, w0j1, w1j1);
+        if (JOSEPH) {
+          const int t = gl + GW * p;
+          d2 aw;
+          aw.x = 0.0; aw.y = 0.0;
+          if (t < LD) aw = lds128(sA + w * HIST + 2 * t);
+          lr[0][p] = rank2(lr[0][p], aj0.x, aj0.y, hK[w][p].x, hK[w][p].y);
+          lr[1][p] = rank2(lr[1][p], aj1.x, aj1.y, hK[w][p].x, hK[w][p].y);
+          lc[0][p] = rank2(lc[0][p], aw.x, aw.y, kj0.x, kj0.y);
+          lc[1][p] = rank2(lc[1][p], aw.x, aw.y, kj1.x, kj1.y);
+        }
       }
     }
     // (c) H P (rows) and P H^T (columns) for this lane's t, accumulated in idx5 order
@@ -301,7 +318,7 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
     }
     x0[3] = gcol<GW, NT>(gmask, hW0[u], j);     x1[3] = gcol<GW, NT>(gmask, hW1[u], j);
     x0[4] = gcol<GW, NT>(gmask, hW0[u], j + 1); x1[4] = gcol<GW, NT>(gmask, hW1[u], j + 1);
-    double S[2][2], Si[2][2];
+    double S[2][2], Si[2][2], Sq[2][2];
     {
       double acc00 = 0.0, acc01 = 0.0, acc10 = 0.0, acc11 = 0.0;
 #pragma unroll
@@ -311,11 +328,13 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
         acc10 = fma(x1[c], in.h[0][c], acc10);
         acc11 = fma(x1[c], in.h[1][c], acc11);
       }
+      Sq[0][0] = acc00; Sq[0][1] = acc01; Sq[1][0] = acc10; Sq[1][1] = acc11;
       S[0][0] = acc00 + qn; S[0][1] = acc01; S[1][0] = acc10; S[1][1] = acc11 + qn;
     }
     inv2(S, Si);
-    // (e) K_u = P H^T S^-1 (:473), mu += K_u y (:476)
+    // (e) K_u = P H^T S^-1 (:473), mu += K_u y (:476); Joseph: W = H P - Q K^T, AHt = P H^T - K (S - Q)
     double* ku = sK + u * HIST;
+    d2 acur[NT];
 #pragma unroll
     for (int p = 0; p < NT; ++p) {
       const int t = gl + GW * p;
@@ -323,8 +342,15 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
       kk.x = dot2(pht0[p], Si[0][0], pht1[p], Si[1][0]);
       kk.y = dot2(pht0[p], Si[0][1], pht1[p], Si[1][1]);
       hK[u][p] = kk;  // zero for the pad row and beyond
+      if (JOSEPH) {
+        hW0[u][p] = joseph_w(hW0[u][p], qn, kk.x);
+        hW1[u][p] = joseph_w(hW1[u][p], qn, kk.y);
+        acur[p].x = joseph_a(pht0[p], kk.x, kk.y, Sq[0][0], Sq[1][0]);
+        acur[p].y = joseph_a(pht1[p], kk.x, kk.y, Sq[0][1], Sq[1][1]);
+      }
       if (t < LD) {
         *reinterpret_cast<d2*>(ku + 2 * t) = kk;
+        if (JOSEPH) *reinterpret_cast<d2*>(sA + u * HIST + 2 * t) = acur[p];
         if (t < N) sMu[t] = mu_inc(sMu[t], kk.x, kk.y, in.y0, in.y1);
       }
     }
@@ -334,10 +360,18 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
         const d2 kr = lds128(ku + 2 * k);
+        const double wk0 = JOSEPH ? joseph_w(x0[k], qn, kr.x) : x0[k];
+        const double wk1 = JOSEPH ? joseph_w(x1[k], qn, kr.y) : x1[k];
+        d2 ar;
+        if (JOSEPH) ar = lds128(sA + u * HIST + 2 * k);
 #pragma unroll
         for (int p = 0; p < NT; ++p) {
           rr[k][p] = rank2(rr[k][p], kr.x, kr.y, hW0[u][p], hW1[u][p]);
-          rc[k][p] = rank2(rc[k][p], hK[u][p].x, hK[u][p].y, x0[k], x1[k]);
+          rc[k][p] = rank2(rc[k][p], hK[u][p].x, hK[u][p].y, wk0, wk1);
+          if (JOSEPH) {
+            rr[k][p] = rank2(rr[k][p], ar.x, ar.y, hK[u][p].x, hK[u][p].y);
+            rc[k][p] = rank2(rc[k][p], acur[p].x, acur[p].y, kr.x, kr.y);
+          }
         }
       }
     }
@@ -366,6 +400,11 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
             const d2 k = lds128(sK + u * HIST + 2 * (r0 + q));
 #pragma unroll
             for (int p = 0; p < NT; ++p) v[q][p] = rank2(v[q][p], k.x, k.y, hW0[u][p], hW1[u][p]);
+            if (JOSEPH) {
+              const d2 av = lds128(sA + u * HIST + 2 * (r0 + q));
+#pragma unroll
+              for (int p = 0; p < NT; ++p) v[q][p] = rank2(v[q][p], av.x, av.y, hK[u][p].x, hK[u][p].y);
+            }
           }
         }
       }
@@ -386,11 +425,11 @@ __global__ void __launch_bounds__(32, 16) batch_step_group_kernel(BatchStepArgs 
 // -------------------------------------------------------------------------------------------------------
 // launchers
 // -------------------------------------------------------------------------------------------------------
-template <int NLM, int MT, int GW>
+template <int NLM, int MT, int GW, bool JOSEPH>
 static cudaError_t launch_group(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
   constexpr int fpw = 32 / GW;
-  const size_t smem = (size_t)group_slice_doubles(NLM, MT, GW) * sizeof(double) * fpw;
-  auto kernel = batch_step_group_kernel<NLM, MT, GW>;
+  const size_t smem = (size_t)group_slice_doubles(NLM, MT, GW, JOSEPH) * sizeof(double) * fpw;
+  auto kernel = batch_step_group_kernel<NLM, MT, GW, JOSEPH>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -411,22 +450,29 @@ static cudaError_t launch_group(const BatchStepArgs& a, int64_t batch, cudaStrea
 
 bool batch_group_supported(int n_landmarks, int m) { return (n_landmarks == 4 || n_landmarks == 8) && m >= 1 && m <= 4; }
 
-template <int NLM, int GW>
+template <int NLM, int GW, bool JOSEPH>
 static cudaError_t launch_group_m(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
   switch (a.m) {
-    case 1: return launch_group<NLM, 1, GW>(a, batch, st);
-    case 2: return launch_group<NLM, 2, GW>(a, batch, st);
-    case 3: return launch_group<NLM, 3, GW>(a, batch, st);
-    case 4: return launch_group<NLM, 4, GW>(a, batch, st);
+    case 1: return launch_group<NLM, 1, GW, JOSEPH>(a, batch, st);
+    case 2: return launch_group<NLM, 2, GW, JOSEPH>(a, batch, st);
+    case 3: return launch_group<NLM, 3, GW, JOSEPH>(a, batch, st);
+    case 4: return launch_group<NLM, 4, GW, JOSEPH>(a, batch, st);
     default: return cudaErrorInvalidValue;
   }
 }
 
-// group width 8 (four filters per warp) or 16 (two per warp)
-cudaError_t batch_launch_step_group(int n_landmarks, int group_width, const BatchStepArgs& a, int64_t batch,
+// group width 8 (four filters per warp) or 16 (two per warp); the Joseph form is built at width 8 only
+cudaError_t batch_launch_step_group(int n_landmarks, int group_width, const BatchStepArgs& a, int64_t batch, bool joseph,
                                     cudaStream_t st) {
-  if (n_landmarks == 4) return group_width == 16 ? launch_group_m<4, 16>(a, batch, st) : launch_group_m<4, 8>(a, batch, st);
-  if (n_landmarks == 8) return group_width == 16 ? launch_group_m<8, 16>(a, batch, st) : launch_group_m<8, 8>(a, batch, st);
+  if (joseph) {
+    if (n_landmarks == 4) return launch_group_m<4, 8, true>(a, batch, st);
+    if (n_landmarks == 8) return launch_group_m<8, 8, true>(a, batch, st);
+    return cudaErrorInvalidValue;
+  }
+  if (n_landmarks == 4)
+    return group_width == 16 ? launch_group_m<4, 16, false>(a, batch, st) : launch_group_m<4, 8, false>(a, batch, st);
+  if (n_landmarks == 8)
+    return group_width == 16 ? launch_group_m<8, 16, false>(a, batch, st) : launch_group_m<8, 8, false>(a, batch, st);
   return cudaErrorInvalidValue;
 }
 

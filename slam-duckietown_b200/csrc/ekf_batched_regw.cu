@@ -35,12 +35,13 @@ __device__ __forceinline__ double col_bcast(const double (&x)[NT], int c) {
 // bound is a compile-time constant, so loads/stores carry immediate offsets and no predicates besides the tail's.
 // Main part: lane = column (W of it in mw0/mw1); tail: columns 32.. of row (2q + half), W of them in tw0/tw1.
 // ODD: the last pair has only its first row. PACK: both rows' tails in one instruction (lanes [0,T) / [T,2T)).
-template <int LD, int HIST, int M, int NPQ, bool ODD, bool PACK>
+template <int LD, int HIST, int M, int NPQ, bool ODD, bool PACK, bool JOSEPH>
 __device__ __forceinline__ void regw_stream_pairs(const double* __restrict__ sp, const double* __restrict__ sk,
-                                                  double* __restrict__ gp, const double (&mw0)[M],
-                                                  const double (&mw1)[M], const double (&tw0)[M],
-                                                  const double (&tw1)[M], unsigned valid, int lane, int half,
-                                                  int tcol, bool tact) {
+                                                  const double* __restrict__ sa, double* __restrict__ gp,
+                                                  const double (&mw0)[M], const double (&mw1)[M],
+                                                  const double (&tw0)[M], const double (&tw1)[M], const d2 (&mk)[M],
+                                                  const d2 (&tk)[M], unsigned valid, int lane, int half, int tcol,
+                                                  bool tact) {
   double va[NPQ], vb[NPQ], vt[NPQ], vs[PACK ? 1 : NPQ];
   const int toff = half * LD + tcol;  // tail element of this lane within a row pair
 #pragma unroll
@@ -55,6 +56,7 @@ __device__ __forceinline__ void regw_stream_pairs(const double* __restrict__ sp,
   for (int u = 0; u < M; ++u) {
     if (!((valid >> u) & 1u)) continue;
     const double* ku = sk + u * HIST;
+    const double* au = sa + u * HIST;
 #pragma unroll
     for (int q = 0; q < NPQ; ++q) {
       const bool two = !(ODD && q == NPQ - 1);
@@ -62,10 +64,21 @@ __device__ __forceinline__ void regw_stream_pairs(const double* __restrict__ sp,
       const d2 kt = PACK ? lds128(ku + 4 * q + 2 * half) : ka;  // K of the row this lane's tail element is in
       va[q] = rank2(va[q], ka.x, ka.y, mw0[u], mw1[u]);
       vt[q] = rank2(vt[q], kt.x, kt.y, tw0[u], tw1[u]);
+      if (JOSEPH) {  // second rank-2 term of the one-pass Joseph form: AHt of the row, K of the column
+        const d2 aa = lds128(au + 4 * q);
+        const d2 at = PACK ? lds128(au + 4 * q + 2 * half) : aa;
+        va[q] = rank2(va[q], aa.x, aa.y, mk[u].x, mk[u].y);
+        vt[q] = rank2(vt[q], at.x, at.y, tk[u].x, tk[u].y);
+      }
       if (two) {
         const d2 kb = lds128(ku + 4 * q + 2);
         vb[q] = rank2(vb[q], kb.x, kb.y, mw0[u], mw1[u]);
         if (!PACK) vs[q] = rank2(vs[q], kb.x, kb.y, tw0[u], tw1[u]);
+        if (JOSEPH) {
+          const d2 ab = lds128(au + 4 * q + 2);
+          vb[q] = rank2(vb[q], ab.x, ab.y, mk[u].x, mk[u].y);
+          if (!PACK) vs[q] = rank2(vs[q], ab.x, ab.y, tk[u].x, tk[u].y);
+        }
       }
     }
   }
@@ -81,33 +94,36 @@ __device__ __forceinline__ void regw_stream_pairs(const double* __restrict__ sp,
 
 }  // namespace
 
-// WPC = warps per CTA. WPC == 1: one filter per one-warp CTA (the hardware CTA scheduler balances the load).
-// WPC > 1: ONE persistent CTA per SM whose warps each pull filters from a device-side work counter — the
-// 1 KB of shared memory the system reserves per CTA is then paid once per SM instead of once per filter,
-// which is what lets a 13th filter fit at n = 43 (13 x 17.2 KB + 1 KB <= 228 KB). Opt-in (see launch_regw_mt).
+// WPC = warps per CTA; only WPC == 1 is built: one filter per one-warp CTA, the hardware CTA scheduler balances the
+// load. (The WPC > 1 code path — ONE persistent CTA per SM whose warps pull filters from a device-side work counter,
+// which pays the 1 KB system reservation of shared memory once per SM and so fits a 13th filter at n = 43 — is kept in
+// the kernel body but measured slower, see the launcher.)
 #ifndef EKF_REGW_MAX_BLOCKS
 #define EKF_REGW_MAX_BLOCKS 24
 #endif
 // resident one-warp CTAs per SM the register allocation should allow: what shared memory admits, at most
 // EKF_REGW_MAX_BLOCKS (small filters are otherwise register-limited to 16 warps: ncu, profiles/r1h_batchM.*)
-__host__ __device__ constexpr int regw_min_blocks(int nlm, int m, int wpc) {
+__host__ __device__ constexpr int regw_min_blocks(int nlm, int m, bool joseph) {
   const int n = 3 + 2 * nlm, ld = (n + 3) & ~3;
-  const int fit = 233472 / ((n * ld + ld * (1 + 2 * m) + 2) * 8 + 1024);
+  const int fit = 233472 / ((n * ld + ld * (1 + 2 * m * (joseph ? 2 : 1)) + 2) * 8 + 1024);
   // m > 4 (the decoded-bag-shaped steps with up to 6 updates): the W history alone is 4 m registers per lane, so the
   // register allocation is given room (<= 10 resident warps) instead of being squeezed into spills
   // capacities >= 12 landmarks at m <= 4: at most 16 resident warps, i.e. 128 registers (17+ forced spills)
   const int cap = (m > 4) ? 10 : (nlm >= 12 ? 16 : EKF_REGW_MAX_BLOCKS);
-  return wpc > 1 ? 1 : (fit < cap ? fit : cap);
+  return fit < cap ? fit : cap;
 }
 
-template <int NLM, int MT, int WPC>
-__global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch_step_regw_kernel(BatchStepArgs a, int64_t batch, int pf) {
+// JOSEPH: the covariance update is the one-pass rank-4 Joseph form — per update a second K-like
+// record AHt_u lives in shared memory, W_u becomes H P - Q K^T, and every element takes a second rank-2 term
+// (AHt of its row, K of its column), in the order of the staged kernel: bitwise equal to it.
+template <int NLM, int MT, int WPC, bool JOSEPH>
+__global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, JOSEPH)) batch_step_regw_kernel(BatchStepArgs a, int64_t batch, int pf) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
   constexpr int HIST = 2 * LD;        // doubles of one update's K record: [LD][2]
   constexpr int NT = (LD + 31) / 32;  // lane t handles indices t, t + 32
   constexpr int m = MT;
-  constexpr int SLICE = N * LD + LD + m * HIST + 2;  // doubles of shared memory per warp
+  constexpr int SLICE = N * LD + LD + m * HIST * (JOSEPH ? 2 : 1) + 2;  // doubles of shared memory per warp
   // K history of this lane's rows: in registers for m <= 4; for longer steps it is re-read from the K records in
   // shared memory (one LDS.128 per earlier update and half), which frees 4 m registers per lane
   constexpr bool KREG = (MT <= 4);
@@ -121,7 +137,8 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
   double* sP = reinterpret_cast<double*>(smem_raw) + warp * SLICE;  // [N][LD]
   double* sMu = sP + N * LD;                                        // [LD]
   double* sK = sMu + LD;                                            // [m][LD][2]  (K_u[i,0], K_u[i,1]) pairs
-  uint64_t* bar = reinterpret_cast<uint64_t*>(sK + m * HIST);       // [2]: mu, P
+  double* sA = sK + m * HIST;                                       // [m][LD][2]  AHt_u pairs (Joseph only)
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sA + (JOSEPH ? m * HIST : 0));  // [2]: mu, P
 
   if (lane == 0) {
     mbar_init(bar, 1);
@@ -147,31 +164,6 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
     mbar_expect_tx(bar + 1, (uint32_t)(N * LD * sizeof(double)));
     tma_bulk_g2s(sP, gP, (uint32_t)(N * LD * sizeof(double)), bar + 1);
     if (WPC > 1) b_next = total_warps + (int64_t)atomicAdd(work, 1ULL);  // latency hidden behind this filter
-  }
-  // L2 prefetch for the filter that will take this CTA's place on the SM (pf CTAs ahead, ekf_batched_dev.cuh)
-  // pf < 0: the same distance |pf|, but only the per-filter inputs and mu — P is left to the TMA load
-  if (WPC == 1 && pf != 0) {
-    const int64_t bn = b + (pf < 0 ? -pf : pf);
-    if (bn < batch) {
-      const void* src = nullptr;
-      switch (lane) {
-        case 1: src = a.ticks_l ? (const void*)(a.ticks_l + bn) : (a.ang ? (const void*)(a.ang + bn) : nullptr); break;
-        case 2: src = a.ticks_l ? (const void*)(a.ticks_r + bn) : (a.lin ? (const void*)(a.lin + bn) : nullptr); break;
-        case 3: src = a.motion_var + bn; break;
-        case 4: src = a.meas_var + bn; break;
-        case 5: src = a.n_known + bn; break;
-        case 6: src = a.slot + bn * m; break;
-        case 7: src = a.rng + bn * m; break;
-        case 8: src = a.brg + bn * m; break;
-        default: break;
-      }
-      if (lane == 0) {
-        if (pf > 0) l2_prefetch_bulk(a.P + bn * (int64_t)(N * LD), (uint32_t)(N * LD * sizeof(double)));
-        l2_prefetch_bulk(a.mu + bn * (int64_t)LD, (uint32_t)(LD * sizeof(double)));
-      } else if (src) {
-        l2_prefetch(src);
-      }
-    }
   }
   double ang, lin;
   if (a.ticks_common) {  // a1/a2 on the device from ticks every filter shares (Monte Carlo replay of one bag)
@@ -316,6 +308,12 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
       return (t < LD) ? lds128(sK + w * HIST + 2 * t) : z;
     }
   };
+  auto a_hist = [&](int w, int p) -> d2 {  // AHt_w of this lane's row t (Joseph)
+    const int t = lane + 32 * p;
+    d2 z;
+    z.x = 0.0; z.y = 0.0;
+    return (t < LD) ? lds128(sA + w * HIST + 2 * t) : z;
+  };
 #pragma unroll
   for (int u = 0; u < m; ++u) {
     if (!((valid >> u) & 1u)) continue;  // warp-uniform
@@ -340,6 +338,11 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
       const d2 kj0 = lds128(sK + w * HIST + 2 * j), kj1 = lds128(sK + w * HIST + 2 * j + 2);
       const double w0j0 = col_bcast<NT>(hW0[w], j), w1j0 = col_bcast<NT>(hW1[w], j);
       const double w0j1 = col_bcast<NT>(hW0[w], j + 1), w1j1 = col_bcast<NT>(hW1[w], j + 1);
+      d2 aj0, aj1;
+      if (JOSEPH) {
+        aj0 = lds128(sA + w * HIST + 2 * j);
+        aj1 = lds128(sA + w * HIST + 2 * j + 2);
+      }
 #pragma unroll
       for (int p = 0; p < NT; ++p) {
         const d2 kw = k_hist(w, p);
@@ -347,6 +350,13 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
         lr[1][p] = rank2(lr[1][p], kj1.x, kj1.y, hW0[w][p], hW1[w][p]);
         lc[0][p] = rank2(lc[0][p], kw.x, kw.y, w0j0, w1j0);
         lc[1][p] = rank2(lc[1][p], kw.x, kw.y, w0j1, w1j1);
+        if (JOSEPH) {
+          const d2 aw = a_hist(w, p);
+          lr[0][p] = rank2(lr[0][p], aj0.x, aj0.y, kw.x, kw.y);
+          lr[1][p] = rank2(lr[1][p], aj1.x, aj1.y, kw.x, kw.y);
+          lc[0][p] = rank2(lc[0][p], aw.x, aw.y, kj0.x, kj0.y);
+          lc[1][p] = rank2(lc[1][p], aw.x, aw.y, kj1.x, kj1.y);
+        }
       }
     }
     // (c) H P (rows) and P H^T (columns) for this lane's t, accumulated in idx5 order
@@ -374,7 +384,7 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
     }
     x0[3] = col_bcast<NT>(hW0[u], j);     x1[3] = col_bcast<NT>(hW1[u], j);
     x0[4] = col_bcast<NT>(hW0[u], j + 1); x1[4] = col_bcast<NT>(hW1[u], j + 1);
-    double S[2][2], Si[2][2];
+    double S[2][2], Si[2][2], Sq[2][2];
     {
       double acc00 = 0.0, acc01 = 0.0, acc10 = 0.0, acc11 = 0.0;
 #pragma unroll
@@ -384,12 +394,13 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
         acc10 = fma(x1[c], in.h[0][c], acc10);
         acc11 = fma(x1[c], in.h[1][c], acc11);
       }
+      Sq[0][0] = acc00; Sq[0][1] = acc01; Sq[1][0] = acc10; Sq[1][1] = acc11;
       S[0][0] = acc00 + qn; S[0][1] = acc01; S[1][0] = acc10; S[1][1] = acc11 + qn;
     }
     inv2(S, Si);
-    // (e) K_u = P H^T S^-1 (:473), mu += K_u y (:476)
+    // (e) K_u = P H^T S^-1 (:473), mu += K_u y (:476); Joseph: W = H P - Q K^T, AHt = P H^T - K (S - Q)
     double* ku = sK + u * HIST;
-    d2 kcur[NT];
+    d2 kcur[NT], acur[NT];
 #pragma unroll
     for (int p = 0; p < NT; ++p) {
       const int t = lane + 32 * p;
@@ -398,8 +409,15 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
       kk.y = dot2(pht0[p], Si[0][1], pht1[p], Si[1][1]);
       if constexpr (KREG) hK[u][p] = kk;  // zero for the pad row and beyond
       kcur[p] = kk;
+      if (JOSEPH) {
+        hW0[u][p] = joseph_w(hW0[u][p], qn, kk.x);
+        hW1[u][p] = joseph_w(hW1[u][p], qn, kk.y);
+        acur[p].x = joseph_a(pht0[p], kk.x, kk.y, Sq[0][0], Sq[1][0]);
+        acur[p].y = joseph_a(pht1[p], kk.x, kk.y, Sq[0][1], Sq[1][1]);
+      }
       if (t < LD) {
         *reinterpret_cast<d2*>(ku + 2 * t) = kk;
+        if (JOSEPH) *reinterpret_cast<d2*>(sA + u * HIST + 2 * t) = acur[p];
         if (t < N) sMu[t] = mu_inc(sMu[t], kk.x, kk.y, in.y0, in.y1);
       }
     }
@@ -409,10 +427,19 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
         const d2 kr = lds128(ku + 2 * k);
+        // W_u at column k as the lane owning that column holds it (Joseph: H P - Q K^T, same fma as there)
+        const double wk0 = JOSEPH ? joseph_w(x0[k], qn, kr.x) : x0[k];
+        const double wk1 = JOSEPH ? joseph_w(x1[k], qn, kr.y) : x1[k];
+        d2 ar;
+        if (JOSEPH) ar = lds128(sA + u * HIST + 2 * k);
 #pragma unroll
         for (int p = 0; p < NT; ++p) {
           rr[k][p] = rank2(rr[k][p], kr.x, kr.y, hW0[u][p], hW1[u][p]);
-          rc[k][p] = rank2(rc[k][p], kcur[p].x, kcur[p].y, x0[k], x1[k]);
+          rc[k][p] = rank2(rc[k][p], kcur[p].x, kcur[p].y, wk0, wk1);
+          if (JOSEPH) {
+            rr[k][p] = rank2(rr[k][p], ar.x, ar.y, kcur[p].x, kcur[p].y);
+            rc[k][p] = rank2(rc[k][p], acur[p].x, acur[p].y, kr.x, kr.y);
+          }
         }
       }
     }
@@ -434,10 +461,16 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
       tW1[u] = __shfl_sync(kFull, hW1[u][1], lane - half * TAIL);
     }
     double mW0[m], mW1[m];
+    d2 mK[m], tK[m];  // Joseph: K_u of this lane's main and tail column
 #pragma unroll
     for (int u = 0; u < m; ++u) {
       mW0[u] = hW0[u][0];
       mW1[u] = hW1[u][0];
+      mK[u].x = mK[u].y = tK[u].x = tK[u].y = 0.0;
+      if (JOSEPH && ((valid >> u) & 1u)) {
+        mK[u] = lds128(sK + u * HIST + 2 * lane);
+        if (tact) tK[u] = lds128(sK + u * HIST + 2 * tcol);
+      }
     }
     constexpr int CH = 4;  // row PAIRS in registers per lane
     constexpr int NPAIR = (N + 1) / 2;  // N is odd: the last pair holds one row
@@ -445,15 +478,19 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
     constexpr int MAINCH = (NPAIR - REM) / CH;
     const double* sp = sP;
     const double* sk = sK;
+    const double* sa = sA;
     double* gp = gP;
 #pragma unroll 1
     for (int c = 0; c < MAINCH; ++c) {
-      regw_stream_pairs<LD, HIST, m, CH, false, PACK>(sp, sk, gp, mW0, mW1, tW0, tW1, valid, lane, half, tcol, tact);
+      regw_stream_pairs<LD, HIST, m, CH, false, PACK, JOSEPH>(sp, sk, sa, gp, mW0, mW1, tW0, tW1, mK, tK, valid, lane,
+                                                              half, tcol, tact);
       sp += 2 * CH * LD;
       sk += 4 * CH;
+      sa += 4 * CH;
       gp += 2 * CH * LD;
     }
-    regw_stream_pairs<LD, HIST, m, REM, true, PACK>(sp, sk, gp, mW0, mW1, tW0, tW1, valid, lane, half, tcol, tact);
+    regw_stream_pairs<LD, HIST, m, REM, true, PACK, JOSEPH>(sp, sk, sa, gp, mW0, mW1, tW0, tW1, mK, tK, valid, lane, half,
+                                                            tcol, tact);
   } else {
     constexpr int CH = 8;
 #pragma unroll 1
@@ -471,6 +508,11 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
           if (r0 + q < N) {
             const d2 k = lds128(ku + 2 * (r0 + q));
             v[q] = rank2(v[q], k.x, k.y, hW0[u][0], hW1[u][0]);
+            if (JOSEPH) {
+              const d2 av = lds128(sA + u * HIST + 2 * (r0 + q));
+              const d2 kc = (lane < LD) ? lds128(ku + 2 * lane) : k;
+              v[q] = rank2(v[q], av.x, av.y, kc.x, kc.y);
+            }
           }
         }
       }
@@ -499,86 +541,53 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, WPC)) batch
 // -------------------------------------------------------------------------------------------------------
 // launchers
 // -------------------------------------------------------------------------------------------------------
-size_t batch_regw_smem_bytes(int n_landmarks, int m) {
+size_t batch_regw_smem_bytes(int n_landmarks, int m, bool joseph) {
   const int n = 3 + 2 * n_landmarks, ld = (n + 3) & ~3;
-  return ((size_t)n * ld + ld + (size_t)m * 2 * ld + 2) * sizeof(double);
+  return ((size_t)n * ld + ld + (size_t)m * 2 * ld * (joseph ? 2 : 1) + 2) * sizeof(double);
 }
 
-bool batch_regw_supported(int m) { return m >= 1 && m <= 6; }
+// plain form: 1-6 observation slots; Joseph form: 1-4 (the K history stays in registers there)
+bool batch_regw_supported(int m, bool joseph) { return m >= 1 && m <= (joseph ? 4 : 6); }
 
-// warps of one persistent CTA that fit an SM (shared memory: 227 KB per CTA; registers: <= 16 warps), and
-// resident one-warp CTAs (each also pays the 1 KB system reservation; <= 32 CTAs per SM)
-constexpr int regw_slice_bytes(int nlm, int m) {
-  return (((3 + 2 * nlm) * (((3 + 2 * nlm) + 3) & ~3)) + (((3 + 2 * nlm) + 3) & ~3) * (1 + 2 * m) + 2) * 8;
-}
-constexpr int regw_persist_warps(int nlm, int m) {
-  return (232448 / regw_slice_bytes(nlm, m)) < 16 ? (232448 / regw_slice_bytes(nlm, m)) : 16;
-}
-constexpr int regw_single_warps(int nlm, int m) {
-  return (233472 / (regw_slice_bytes(nlm, m) + 1024)) < 16 ? (233472 / (regw_slice_bytes(nlm, m) + 1024)) : 16;
-}
-
-template <int NLM, int MT, int WPC>
-static cudaError_t launch_regw_wpc(const BatchStepArgs& a, int64_t batch, unsigned grid, cudaStream_t st) {
-  const size_t smem = batch_regw_smem_bytes(NLM, MT) * WPC;
-  auto kernel = batch_step_regw_kernel<NLM, MT, WPC>;
+template <int NLM, int MT, bool JOSEPH>
+static cudaError_t launch_regw_mt(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+  const size_t smem = batch_regw_smem_bytes(NLM, MT, JOSEPH);
+  auto kernel = batch_step_regw_kernel<NLM, MT, 1, JOSEPH>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   if (e != cudaSuccess) return e;
-  // L2-prefetch distance in CTAs. OFF by default for this kernel: at n = 43 it already runs at 97 % of the device-copy
-  // rate and the prefetch costs 5 % (207.3 -> 197 M filter-steps/s at every distance from 222 to 1332, measured);
-  // EKF_REGW_PREFETCH=<CTAs> turns it on for experiments (negative: inputs + mu only, no P). The group kernel (small
-  // filters) has it on.
-  static const int pf = [] {
-    if (WPC > 1) return 0;
-    const char* v = getenv("EKF_REGW_PREFETCH");
-    return v ? atoi(v) : 0;
-  }();
-  kernel<<<grid, 32 * WPC, smem, st>>>(a, batch, pf);
+  // One filter per one-warp CTA: the hardware CTA scheduler balances the load. (A persistent CTA per SM pulling
+  // filters from a work counter was measured at 0.433 ms against 0.327 ms per 65 536-filter step in round 1 —
+  // phase-locked warps, bursty HBM demand — and an L2 prefetch of the successor's data costs this kernel 5-7 % at every
+  // distance: profiles/r1r_regw_prefetch_inputs_only_rejected.txt. Both code paths were removed in round 2.)
+  kernel<<<(unsigned)batch, 32, smem, st>>>(a, batch, 0);
   return cudaGetLastError();
 }
 
-template <int NLM, int MT>
-static cudaError_t launch_regw_mt(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
-  constexpr int PW = regw_persist_warps(NLM, MT);
-  // EKF_BATCH_PERSIST=1 selects the persistent CTA. Measured on B200 at n = 43, m = 3: 13 warps per SM but
-  // 0.433 ms per 65 536-filter step against 0.327 ms for one-warp CTAs (persistent warps stay phase-locked, so
-  // the TMA loads of all 1 924 warps arrive in bursts) — kept for experiments, off by default.
-  static const bool persist = [] { const char* v = getenv("EKF_BATCH_PERSIST"); return v && atoi(v) == 1; }();
-  if (persist && PW > 1) {
-    int dev = 0, sms = 0;
-    cudaError_t e = cudaGetDevice(&dev);
-    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (e != cudaSuccess) return e;
-    const int64_t need = (batch + PW - 1) / PW;
-    return launch_regw_wpc<NLM, MT, (PW > 1 ? PW : 2)>(a, batch, (unsigned)(need < sms ? need : sms), st);
-  }
-  return launch_regw_wpc<NLM, MT, 1>(a, batch, (unsigned)batch, st);
-}
-
-template <int NLM>
+template <int NLM, bool JOSEPH>
 static cudaError_t launch_regw_t(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
   switch (a.m) {
-    case 1: return launch_regw_mt<NLM, 1>(a, batch, st);
-    case 2: return launch_regw_mt<NLM, 2>(a, batch, st);
-    case 3: return launch_regw_mt<NLM, 3>(a, batch, st);
-    case 4: return launch_regw_mt<NLM, 4>(a, batch, st);
-    case 5: return launch_regw_mt<NLM, 5>(a, batch, st);
-    case 6: return launch_regw_mt<NLM, 6>(a, batch, st);
+    case 1: return launch_regw_mt<NLM, 1, JOSEPH>(a, batch, st);
+    case 2: return launch_regw_mt<NLM, 2, JOSEPH>(a, batch, st);
+    case 3: return launch_regw_mt<NLM, 3, JOSEPH>(a, batch, st);
+    case 4: return launch_regw_mt<NLM, 4, JOSEPH>(a, batch, st);
+    case 5: if constexpr (!JOSEPH) return launch_regw_mt<NLM, 5, false>(a, batch, st); else return cudaErrorInvalidValue;
+    case 6: if constexpr (!JOSEPH) return launch_regw_mt<NLM, 6, false>(a, batch, st); else return cudaErrorInvalidValue;
     default: return cudaErrorInvalidValue;
   }
 }
 
-cudaError_t batch_launch_step_regw(int n_landmarks, const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+cudaError_t batch_launch_step_regw(int n_landmarks, const BatchStepArgs& a, int64_t batch, bool joseph,
+                                   cudaStream_t st) {
   switch (n_landmarks) {
-    case 4: return launch_regw_t<4>(a, batch, st);
-    case 8: return launch_regw_t<8>(a, batch, st);
-    case 12: return launch_regw_t<12>(a, batch, st);
-    case 16: return launch_regw_t<16>(a, batch, st);
-    case 20: return launch_regw_t<20>(a, batch, st);
-    case 24: return launch_regw_t<24>(a, batch, st);
-    case 28: return launch_regw_t<28>(a, batch, st);
+    case 4: return joseph ? launch_regw_t<4, true>(a, batch, st) : launch_regw_t<4, false>(a, batch, st);
+    case 8: return joseph ? launch_regw_t<8, true>(a, batch, st) : launch_regw_t<8, false>(a, batch, st);
+    case 12: return joseph ? launch_regw_t<12, true>(a, batch, st) : launch_regw_t<12, false>(a, batch, st);
+    case 16: return joseph ? launch_regw_t<16, true>(a, batch, st) : launch_regw_t<16, false>(a, batch, st);
+    case 20: return joseph ? launch_regw_t<20, true>(a, batch, st) : launch_regw_t<20, false>(a, batch, st);
+    case 24: return joseph ? launch_regw_t<24, true>(a, batch, st) : launch_regw_t<24, false>(a, batch, st);
+    case 28: return joseph ? launch_regw_t<28, true>(a, batch, st) : launch_regw_t<28, false>(a, batch, st);
     default: return cudaErrorInvalidValue;
   }
 }

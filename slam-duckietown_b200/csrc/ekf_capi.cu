@@ -233,10 +233,12 @@ static int batch_step_common(ekf_batch_t* h, ekf::BatchStepArgs& a, int m, void*
   a.flags = h->flags;
   CU(cudaSetDevice(h->device));
   const bool joseph = (h->flags & ekf::kFlagJoseph) != 0;
-  if (!joseph && (h->kernel == 0 || h->kernel >= 8) && ekf::batch_group_supported(h->nlm, m))
-    CU(ekf::batch_launch_step_group(h->nlm, h->kernel >= 8 ? h->kernel : 8, a, h->batch, (cudaStream_t)stream));
-  else if (!joseph && (h->kernel == 0 || h->kernel == 3 || h->kernel >= 8) && ekf::batch_regw_supported(m))
-    CU(ekf::batch_launch_step_regw(h->nlm, a, h->batch, (cudaStream_t)stream));
+  // dispatch (both covariance forms): capacities <= 8 landmarks -> sub-warp group kernel; otherwise one warp per filter
+  // with W in registers; the fully staged kernel takes what is left (Joseph with 5+ slots, 7-8 slots, EKF_BATCH_KERNEL)
+  if ((h->kernel == 0 || h->kernel >= 8) && ekf::batch_group_supported(h->nlm, m))
+    CU(ekf::batch_launch_step_group(h->nlm, h->kernel >= 8 ? h->kernel : 8, a, h->batch, joseph, (cudaStream_t)stream));
+  else if ((h->kernel == 0 || h->kernel == 3 || h->kernel >= 8) && ekf::batch_regw_supported(m, joseph))
+    CU(ekf::batch_launch_step_regw(h->nlm, a, h->batch, joseph, (cudaStream_t)stream));
   else
     CU(ekf::batch_launch_step(h->nlm, a, h->batch, joseph, (cudaStream_t)stream));
   return EKF_OK;

@@ -129,6 +129,15 @@ __device__ __forceinline__ double mu_inc(double mu, double k0, double k1, double
   return __dadd_rn(mu, fma(k1, y1, __dmul_rn(k0, y0)));
 }
 
+// Joseph form as a one-pass rank-4 update: W = H P - Q K^T and AHt = P H^T - K (S - Q), entry by
+// entry, with the rounding sequence spelled out so that every kernel that forms them (staged / W-in-registers /
+// sub-warp group batched kernels, large-map gathers) agrees bitwise. sq = S - Q (the innovation covariance before the
+// measurement noise is added).
+__device__ __forceinline__ double joseph_w(double hp, double qn, double k) { return fma(-qn, k, hp); }
+__device__ __forceinline__ double joseph_a(double pht, double k0, double k1, double sq0, double sq1) {
+  return __dsub_rn(pht, fma(k1, sq1, __dmul_rn(k0, sq0)));
+}
+
 // 256-bit global accesses (sm_100a: LDG.E.256 / STG.E.256)
 struct __align__(32) double4x {
   double a, b, c, d;

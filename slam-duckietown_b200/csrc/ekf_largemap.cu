@@ -244,10 +244,10 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
   if (a.flags & kFlagJoseph) {
     // single-GPU only (the host refuses Joseph on a shard): K[t] of every column t is local.
     const double qn = a.mm * a.mm;
-    a.W0[t] = hp0 - qn * k0;
-    a.W1[t] = hp1 - qn * k1;
-    a.A0[t] = pht0 - (k0 * ssq[0][0] + k1 * ssq[1][0]);
-    a.A1[t] = pht1 - (k0 * ssq[0][1] + k1 * ssq[1][1]);
+    a.W0[t] = joseph_w(hp0, qn, k0);
+    a.W1[t] = joseph_w(hp1, qn, k1);
+    a.A0[t] = joseph_a(pht0, k0, k1, ssq[0][0], ssq[1][0]);
+    a.A1[t] = joseph_a(pht1, k0, k1, ssq[0][1], ssq[1][1]);
   } else {
     a.W0[t] = hp0;
     a.W1[t] = hp1;

@@ -365,6 +365,23 @@ def test_ekf3_surface(eb):
 
 
 @pytest.mark.parametrize("name", ["batched_b48_l20.npz", "batched_b32_l8.npz"])
+def test_batched_joseph_variants_bitwise_equal(eb, name, monkeypatch):
+    """One-pass Joseph form: the dispatched kernels (W-in-registers at 20 landmarks, sub-warp groups at 8) apply the
+    staged kernel's per-element operation sequence (two rank-2 terms per update: K W, then AHt K^T): BITWISE equal."""
+    z = golden(name)
+    outs = {}
+    variants = ("auto", "staged", "regw", "group8")
+    for variant in variants:
+        monkeypatch.setenv("EKF_BATCH_KERNEL", variant)
+        outs[variant], _ = _run_batched(eb, z, joseph=True)
+    for variant in variants[1:]:
+        for t, (mu, p) in outs["auto"].items():
+            mu2, p2 = outs[variant][t]
+            assert np.array_equal(mu, mu2), f"{name} joseph {variant} mu differs at t={t}"
+            assert np.array_equal(p, p2), f"{name} joseph {variant} P differs at t={t}"
+
+
+@pytest.mark.parametrize("name", ["batched_b48_l20.npz", "batched_b32_l8.npz"])
 def test_batched_kernel_variants_bitwise_equal(eb, name, monkeypatch):
     """The W-in-registers kernel (default at 20 landmarks), the sub-warp group kernels (default at <= 8 landmarks),
     and the fully staged kernel apply the same per-element operation sequence: their states
