@@ -152,11 +152,15 @@ int ekf_batch_mc_record_doubles(int m, int64_t* doubles);
 int ekf_batch_perturb(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int m,
                       const double* record_dev, const double* sigma4, double* ang_dev, double* lin_dev,
                       int32_t* slot_dev, double* rng_dev, double* brg_dev, void* stream);
+/* the fused filter-step with the per-member inputs drawn INSIDE the step kernel (the numbers ekf_batch_perturb would
+ * write, generated by m + 1 lanes while the TMA load of the filter's state is in flight): no per-filter input arrays  */
+int ekf_batch_step_generated(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int m,
+                             const double* record_dev, const double* sigma4, void* stream);
 /* per-filter perturbation of the window's detections for ekf_batch_associate: noise_tx / noise_tz [n_det][batch]  */
 int ekf_batch_detection_noise(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int n_det,
                               double sigma, double* noise_tx_dev, double* noise_tz_dev, void* stream);
 /* One pipelined Monte Carlo step from a HOST record (same pipeline, stream contract and ekf_batch_host_sync as
- * ekf_batch_step_host_async): H2D of the record (< 200 bytes), perturbation generator, fused step, optionally
+ * ekf_batch_step_host_async): H2D of the record (< 200 bytes), the fused step drawing its inputs in the kernel, optionally
  * sse_dev[b] += squared position error against (gt_x, gt_y) when score != 0, and the 12 pose moments copied to
  * pose_moments_host (may be NULL). Per step the host sends the common record and receives 96 bytes.             */
 int ekf_batch_mc_step_host_async(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int m,

@@ -66,6 +66,7 @@ SIGNATURES = {
     "ekf_batch_pose_moments": (_i, [_p, _p, _p]),
     "ekf_batch_mc_record_doubles": (_i, [_i, C.POINTER(_l)]),
     "ekf_batch_perturb": (_i, [_p, _u64, _u64, _u64, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "ekf_batch_step_generated": (_i, [_p, _u64, _u64, _u64, _i, _p, _p, _p]),
     "ekf_batch_detection_noise": (_i, [_p, _u64, _u64, _u64, _i, _d, _p, _p, _p]),
     "ekf_batch_mc_step_host_async": (_i, [_p, _u64, _u64, _u64, _i, _p, _p, _i, _d, _d, _p, _p, _p]),
     "ekf_lm_layout": (_i, [_i, C.POINTER(_i), C.POINTER(_l)]),

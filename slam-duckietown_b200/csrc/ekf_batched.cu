@@ -32,7 +32,7 @@ namespace ekf {
 
 // MT = number of observation slots per filter-step when known at compile time (the update loops unroll and the
 // per-update validity tests become predicates), 0 = read it from the arguments.
-template <int NLM, bool JOSEPH, int MT>
+template <int NLM, bool JOSEPH, int MT, bool GEN>
 __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
     const double dl = delta_phi(a.ticks_l[b], a.prev_l[b], a.resolution);
     const double dr = delta_phi(a.ticks_r[b], a.prev_r[b], a.resolution);
     displacement(a.wheel_radius, a.baseline, dl, dr, &ang, &lin);
-  } else {
+  } else if (!GEN) {
     ang = a.ang[b];
     lin = a.lin[b];
   }
@@ -82,7 +82,19 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
   // observation u lives in lane u and is broadcast with a shuffle when its turn comes
   double o_rng = 0.0, o_brg = 0.0;
   int o_slot = -1;
-  if (lane < m) {
+  if constexpr (GEN) {  // this filter's Monte Carlo inputs, drawn here while its state is still in flight
+    double z0 = 0.0, z1 = 0.0;
+    if (lane <= m)
+      normal_pair(a.gen_seed, a.gen_first + (unsigned long long)b, a.gen_step,
+                  lane < m ? kStreamObservation0 + lane : kStreamOdometry, &z0, &z1);
+    if (lane < m) {
+      o_slot = reinterpret_cast<const int32_t*>(a.gen_record + 2 + 2 * m)[lane];
+      o_rng = __dadd_rn(a.gen_record[2 + lane], __dmul_rn(a.gen_s_rng, z0));
+      o_brg = __dadd_rn(a.gen_record[2 + m + lane], __dmul_rn(a.gen_s_brg, z1));
+    }
+    ang = __shfl_sync(kFull, __dadd_rn(a.gen_record[0], __dmul_rn(a.gen_s_ang, z0)), m);
+    lin = __shfl_sync(kFull, __dadd_rn(a.gen_record[1], __dmul_rn(a.gen_s_lin, z1)), m);
+  } else if (lane < m) {
     o_slot = a.slot[b * m + lane];
     o_rng = a.rng[b * m + lane];
     o_brg = a.brg[b * m + lane];
@@ -417,10 +429,10 @@ size_t batch_step_smem_bytes(int n_landmarks, int m, bool joseph) {
   return d * sizeof(double);
 }
 
-template <int NLM, bool JOSEPH, int MT>
-static cudaError_t launch_step_mt(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+template <int NLM, bool JOSEPH, int MT, bool GEN>
+static cudaError_t launch_step_g(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
   const size_t smem = batch_step_smem_bytes(NLM, a.m, JOSEPH);
-  auto kernel = batch_step_kernel<NLM, JOSEPH, MT>;
+  auto kernel = batch_step_kernel<NLM, JOSEPH, MT, GEN>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   // as many one-warp CTAs per SM as shared memory allows (11 at n = 43, m = 3)
@@ -428,6 +440,13 @@ static cudaError_t launch_step_mt(const BatchStepArgs& a, int64_t batch, cudaStr
   if (e != cudaSuccess) return e;
   kernel<<<(unsigned)batch, 32, smem, st>>>(a);
   return cudaGetLastError();
+}
+
+// generated inputs (BatchStepArgs::gen_record) run on the general-m instantiation of this staged kernel (both forms)
+template <int NLM, bool JOSEPH, int MT>
+static cudaError_t launch_step_mt(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+  if (a.gen_record) return launch_step_g<NLM, JOSEPH, 0, true>(a, batch, st);
+  return launch_step_g<NLM, JOSEPH, MT, false>(a, batch, st);
 }
 
 template <int NLM, bool JOSEPH>

@@ -23,6 +23,14 @@ struct BatchStepArgs {
   const int32_t* slot;           // [B][m]
   const double* rng;             // [B][m]
   const double* brg;             // [B][m]
+  // Monte Carlo inputs generated IN the kernel (gen_record != null; ang / lin / slot / rng / brg are then unused): the
+  // step's COMMON record (device: doubles [ang, lin, rng[0..m), brg[0..m)] then int32 slot[0..m)) plus this filter's
+  // perturbation, a pure function of (gen_seed, gen_first + b, gen_step, stream) — ekf_philox.cuh. Lanes 0..m-1 draw
+  // the pair of observation u = lane, lane m the odometry pair, while the TMA load of the filter's state is in flight.
+  const double* gen_record;
+  unsigned long long gen_seed, gen_first;
+  unsigned gen_step;
+  double gen_s_ang, gen_s_lin, gen_s_rng, gen_s_brg;
   unsigned long long* faults;    // device counter
   int m;
   int flags;
@@ -33,7 +41,7 @@ size_t batch_step_smem_bytes(int n_landmarks, int m, bool joseph);
 cudaError_t batch_launch_step(int n_landmarks, const BatchStepArgs& a, int64_t batch, bool joseph,
                               cudaStream_t st);
 // W-in-registers variant (ekf_batched_regw.cu): plain form with 1-6 observation slots, Joseph form with 1-4
-bool batch_regw_supported(int m, bool joseph);
+bool batch_regw_supported(int m, bool joseph, bool generated);
 size_t batch_regw_smem_bytes(int n_landmarks, int m, bool joseph);
 cudaError_t batch_launch_step_regw(int n_landmarks, const BatchStepArgs& a, int64_t batch, bool joseph,
                                    cudaStream_t st);

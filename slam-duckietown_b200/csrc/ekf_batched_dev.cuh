@@ -2,6 +2,7 @@
 // 128/256-bit shared/global accesses and the rank-2 element update (sm_100a).
 #pragma once
 #include "ekf_common.cuh"
+#include "ekf_philox.cuh"
 
 namespace ekf {
 

@@ -50,7 +50,7 @@ __host__ __device__ constexpr int group_slice_doubles(int nlm, int m, int gw, bo
 
 // 16 resident one-warp CTAs per SM: 128 registers per thread = four warps per scheduler's register file
 // JOSEPH: one-pass rank-4 Joseph form, same per-element operation sequence as the staged kernel
-template <int NLM, int MT, int GW, bool JOSEPH>
+template <int NLM, int MT, int GW, bool JOSEPH, bool GEN>
 __global__ void __launch_bounds__(32, JOSEPH ? 12 : 16) batch_step_group_kernel(BatchStepArgs a, int64_t batch, int pf) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
@@ -101,14 +101,14 @@ __global__ void __launch_bounds__(32, JOSEPH ? 12 : 16) batch_step_group_kernel(
         case 3: src = a.motion_var + bn; break;
         case 4: src = a.meas_var + bn; break;
         case 5: src = a.n_known + bn; break;
-        case 6: src = a.slot + bn * m; break;
-        case 7: src = a.rng + bn * m; break;
+        case 6: src = a.slot ? a.slot + bn * m : nullptr; break;
+        case 7: src = a.rng ? a.rng + bn * m : nullptr; break;
         default: break;
       }
       if (gl == 0) {
         l2_prefetch_bulk(a.P + bn * (int64_t)(N * LD), (uint32_t)(N * LD * sizeof(double)));
         l2_prefetch_bulk(a.mu + bn * (int64_t)LD, (uint32_t)(LD * sizeof(double)));
-        l2_prefetch(a.brg + bn * m);
+        if (a.brg) l2_prefetch(a.brg + bn * m);
       } else if (src) {
         l2_prefetch(src);
       }
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(32, JOSEPH ? 12 : 16) batch_step_group_kernel(
     const double dl = delta_phi(a.ticks_l[b], a.prev_l[b], a.resolution);
     const double dr = delta_phi(a.ticks_r[b], a.prev_r[b], a.resolution);
     displacement(a.wheel_radius, a.baseline, dl, dr, &ang, &lin);
-  } else {
+  } else if (!GEN) {
     ang = a.ang[b];
     lin = a.lin[b];
   }
@@ -133,7 +133,19 @@ __global__ void __launch_bounds__(32, JOSEPH ? 12 : 16) batch_step_group_kernel(
   int nk = a.n_known[b];
   double o_rng = 0.0, o_brg = 0.0;  // observation u lives in lane u of the group
   int o_slot = -1;
-  if (gl < m) {
+  if constexpr (GEN) {  // this filter's Monte Carlo inputs, drawn here while its state is still in flight
+    double z0 = 0.0, z1 = 0.0;
+    if (gl <= m)
+      normal_pair(a.gen_seed, a.gen_first + (unsigned long long)b, a.gen_step,
+                  gl < m ? kStreamObservation0 + gl : kStreamOdometry, &z0, &z1);
+    if (gl < m) {
+      o_slot = reinterpret_cast<const int32_t*>(a.gen_record + 2 + 2 * m)[gl];
+      o_rng = __dadd_rn(a.gen_record[2 + gl], __dmul_rn(a.gen_s_rng, z0));
+      o_brg = __dadd_rn(a.gen_record[2 + m + gl], __dmul_rn(a.gen_s_brg, z1));
+    }
+    ang = gshfl<GW>(gmask, __dadd_rn(a.gen_record[0], __dmul_rn(a.gen_s_ang, z0)), m);
+    lin = gshfl<GW>(gmask, __dadd_rn(a.gen_record[1], __dmul_rn(a.gen_s_lin, z1)), m);
+  } else if (gl < m) {
     o_slot = a.slot[b * m + gl];
     o_rng = a.rng[b * m + gl];
     o_brg = a.brg[b * m + gl];
@@ -425,11 +437,11 @@ __global__ void __launch_bounds__(32, JOSEPH ? 12 : 16) batch_step_group_kernel(
 // -------------------------------------------------------------------------------------------------------
 // launchers
 // -------------------------------------------------------------------------------------------------------
-template <int NLM, int MT, int GW, bool JOSEPH>
-static cudaError_t launch_group(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+template <int NLM, int MT, int GW, bool JOSEPH, bool GEN>
+static cudaError_t launch_group_g(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
   constexpr int fpw = 32 / GW;
   const size_t smem = (size_t)group_slice_doubles(NLM, MT, GW, JOSEPH) * sizeof(double) * fpw;
-  auto kernel = batch_step_group_kernel<NLM, MT, GW, JOSEPH>;
+  auto kernel = batch_step_group_kernel<NLM, MT, GW, JOSEPH, GEN>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -446,6 +458,15 @@ static cudaError_t launch_group(const BatchStepArgs& a, int64_t batch, cudaStrea
   }();
   kernel<<<(unsigned)((batch + fpw - 1) / fpw), 32, smem, st>>>(a, batch, pf);
   return cudaGetLastError();
+}
+
+template <int NLM, int MT, int GW, bool JOSEPH>
+static cudaError_t launch_group(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+  if constexpr (!JOSEPH && GW == 8) {  // generated inputs: plain form, four filters per warp
+    if (a.gen_record) return launch_group_g<NLM, MT, 8, false, true>(a, batch, st);
+  }
+  if (a.gen_record) return cudaErrorInvalidValue;
+  return launch_group_g<NLM, MT, GW, JOSEPH, false>(a, batch, st);
 }
 
 bool batch_group_supported(int n_landmarks, int m) { return (n_landmarks == 4 || n_landmarks == 8) && m >= 1 && m <= 4; }
@@ -469,6 +490,7 @@ cudaError_t batch_launch_step_group(int n_landmarks, int group_width, const Batc
     if (n_landmarks == 8) return launch_group_m<8, 8, true>(a, batch, st);
     return cudaErrorInvalidValue;
   }
+  if (a.gen_record) group_width = 8;  // generated inputs are built at width 8
   if (n_landmarks == 4)
     return group_width == 16 ? launch_group_m<4, 16, false>(a, batch, st) : launch_group_m<4, 8, false>(a, batch, st);
   if (n_landmarks == 8)

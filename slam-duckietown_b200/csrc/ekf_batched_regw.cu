@@ -116,7 +116,9 @@ __host__ __device__ constexpr int regw_min_blocks(int nlm, int m, bool joseph) {
 // JOSEPH: the covariance update is the one-pass rank-4 Joseph form — per update a second K-like
 // record AHt_u lives in shared memory, W_u becomes H P - Q K^T, and every element takes a second rank-2 term
 // (AHt of its row, K of its column), in the order of the staged kernel: bitwise equal to it.
-template <int NLM, int MT, int WPC, bool JOSEPH>
+// GEN: the filter's Monte Carlo inputs are drawn inside the kernel (BatchStepArgs::gen_record); a separate instantiation,
+// so that the kernels fed from arrays stay instruction for instruction what they were
+template <int NLM, int MT, int WPC, bool JOSEPH, bool GEN>
 __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, JOSEPH)) batch_step_regw_kernel(BatchStepArgs a, int64_t batch, int pf) {
   constexpr int N = 3 + 2 * NLM;
   constexpr int LD = (N + 3) & ~3;
@@ -174,7 +176,7 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, JOSEPH)) ba
     const double dl = delta_phi(a.ticks_l[b], a.prev_l[b], a.resolution);
     const double dr = delta_phi(a.ticks_r[b], a.prev_r[b], a.resolution);
     displacement(a.wheel_radius, a.baseline, dl, dr, &ang, &lin);
-  } else {
+  } else if (!GEN) {
     ang = a.ang[b];
     lin = a.lin[b];
   }
@@ -184,7 +186,19 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, JOSEPH)) ba
   int nk = a.n_known[b];
   double o_rng = 0.0, o_brg = 0.0;  // observation u lives in lane u
   int o_slot = -1;
-  if (lane < m) {
+  if constexpr (GEN) {  // this filter's Monte Carlo inputs, drawn here while its state is still in flight
+    double z0 = 0.0, z1 = 0.0;
+    if (lane <= m)
+      normal_pair(a.gen_seed, a.gen_first + (unsigned long long)b, a.gen_step,
+                  lane < m ? kStreamObservation0 + lane : kStreamOdometry, &z0, &z1);
+    if (lane < m) {
+      o_slot = reinterpret_cast<const int32_t*>(a.gen_record + 2 + 2 * m)[lane];
+      o_rng = __dadd_rn(a.gen_record[2 + lane], __dmul_rn(a.gen_s_rng, z0));
+      o_brg = __dadd_rn(a.gen_record[2 + m + lane], __dmul_rn(a.gen_s_brg, z1));
+    }
+    ang = __shfl_sync(kFull, __dadd_rn(a.gen_record[0], __dmul_rn(a.gen_s_ang, z0)), m);
+    lin = __shfl_sync(kFull, __dadd_rn(a.gen_record[1], __dmul_rn(a.gen_s_lin, z1)), m);
+  } else if (lane < m) {
     o_slot = a.slot[b * m + lane];
     o_rng = a.rng[b * m + lane];
     o_brg = a.brg[b * m + lane];
@@ -547,12 +561,14 @@ size_t batch_regw_smem_bytes(int n_landmarks, int m, bool joseph) {
 }
 
 // plain form: 1-6 observation slots; Joseph form: 1-4 (the K history stays in registers there)
-bool batch_regw_supported(int m, bool joseph) { return m >= 1 && m <= (joseph ? 4 : 6); }
+bool batch_regw_supported(int m, bool joseph, bool generated) {
+  return m >= 1 && m <= ((joseph || generated) ? 4 : 6) && !(joseph && generated);
+}
 
-template <int NLM, int MT, bool JOSEPH>
-static cudaError_t launch_regw_mt(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+template <int NLM, int MT, bool JOSEPH, bool GEN>
+static cudaError_t launch_regw_g(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
   const size_t smem = batch_regw_smem_bytes(NLM, MT, JOSEPH);
-  auto kernel = batch_step_regw_kernel<NLM, MT, 1, JOSEPH>;
+  auto kernel = batch_step_regw_kernel<NLM, MT, 1, JOSEPH, GEN>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -563,6 +579,15 @@ static cudaError_t launch_regw_mt(const BatchStepArgs& a, int64_t batch, cudaStr
   // distance: profiles/r1r_regw_prefetch_inputs_only_rejected.txt. Both code paths were removed in round 2.)
   kernel<<<(unsigned)batch, 32, smem, st>>>(a, batch, 0);
   return cudaGetLastError();
+}
+
+template <int NLM, int MT, bool JOSEPH>
+static cudaError_t launch_regw_mt(const BatchStepArgs& a, int64_t batch, cudaStream_t st) {
+  if constexpr (!JOSEPH && MT <= 4) {  // generated inputs: plain form, up to 4 observation slots
+    if (a.gen_record) return launch_regw_g<NLM, MT, false, true>(a, batch, st);
+  }
+  if (a.gen_record) return cudaErrorInvalidValue;
+  return launch_regw_g<NLM, MT, JOSEPH, false>(a, batch, st);
 }
 
 template <int NLM, bool JOSEPH>

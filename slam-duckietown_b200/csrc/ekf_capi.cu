@@ -80,7 +80,7 @@ struct ekf_lm {
   int flags = ekf::kFlagCircular | ekf::kFlagMeasurement;
   double *K0 = nullptr, *K1 = nullptr, *A0 = nullptr, *A1 = nullptr, *W0 = nullptr, *W1 = nullptr,
          *scal = nullptr;
-  double *mK = nullptr, *mW = nullptr, *my = nullptr;  // fused multi-update records [LM_MAX_FUSED][2][ldw], y [..][2]
+  double *mK = nullptr, *mW = nullptr, *mA = nullptr, *my = nullptr;  // fused multi-update records [LM_MAX_FUSED][2][ldw], y [..][2]
   double* mKR = nullptr;                               // K_u at the exchanged rows [LM_MAX_FUSED][LM_MAX_ROWS][2]
   // peer-memory row exchange (ekf_lm_p2p_*)
   int p2p_world = 0, p2p_rank = 0;
@@ -222,7 +222,7 @@ static int batch_step_common(ekf_batch_t* h, ekf::BatchStepArgs& a, int m, void*
   if (!h->mu) return fail(EKF_ESTATE, "state not bound");
   if (!h->mv) return fail(EKF_ESTATE, "noise not set");
   if (m < 0 || m > ekf::BATCH_MAX_M) return fail(EKF_EINVAL, "m must be in [0, %d]", ekf::BATCH_MAX_M);
-  if (m > 0 && (!a.slot || !a.rng || !a.brg)) return fail(EKF_EINVAL, "observation arrays are null");
+  if (m > 0 && !a.gen_record && (!a.slot || !a.rng || !a.brg)) return fail(EKF_EINVAL, "observation arrays are null");
   a.mu = h->mu;
   a.P = h->P;
   a.n_known = h->n_known;
@@ -235,9 +235,10 @@ static int batch_step_common(ekf_batch_t* h, ekf::BatchStepArgs& a, int m, void*
   const bool joseph = (h->flags & ekf::kFlagJoseph) != 0;
   // dispatch (both covariance forms): capacities <= 8 landmarks -> sub-warp group kernel; otherwise one warp per filter
   // with W in registers; the fully staged kernel takes what is left (Joseph with 5+ slots, 7-8 slots, EKF_BATCH_KERNEL)
-  if ((h->kernel == 0 || h->kernel >= 8) && ekf::batch_group_supported(h->nlm, m))
+  const bool gen = a.gen_record != nullptr;  // in-kernel inputs: plain form on the fast kernels, else the staged kernel
+  if ((h->kernel == 0 || h->kernel >= 8) && ekf::batch_group_supported(h->nlm, m) && !(gen && joseph))
     CU(ekf::batch_launch_step_group(h->nlm, h->kernel >= 8 ? h->kernel : 8, a, h->batch, joseph, (cudaStream_t)stream));
-  else if ((h->kernel == 0 || h->kernel == 3 || h->kernel >= 8) && ekf::batch_regw_supported(m, joseph))
+  else if ((h->kernel == 0 || h->kernel == 3 || h->kernel >= 8) && ekf::batch_regw_supported(m, joseph, gen))
     CU(ekf::batch_launch_step_regw(h->nlm, a, h->batch, joseph, (cudaStream_t)stream));
   else
     CU(ekf::batch_launch_step(h->nlm, a, h->batch, joseph, (cudaStream_t)stream));
@@ -293,6 +294,23 @@ int ekf_batch_step_ticks_common(ekf_batch_t* h, int32_t ticks_left, int32_t tick
   a.rng = rng_dev;
   a.brg = brg_dev;
   return batch_step_common(h, a, m, stream);
+}
+
+static int batch_step_generated(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int m,
+                                const double* record_dev, const double* sigma4, void* stream) {
+  if (!record_dev || !sigma4) return fail(EKF_EINVAL, "null argument");
+  if (step > 0xffffffffull) return fail(EKF_EINVAL, "step must fit 32 bits");
+  ekf::BatchStepArgs a{};
+  a.gen_record = record_dev;
+  a.gen_seed = seed; a.gen_first = first_filter; a.gen_step = (unsigned)step;
+  a.gen_s_ang = sigma4[0]; a.gen_s_lin = sigma4[1]; a.gen_s_rng = sigma4[2]; a.gen_s_brg = sigma4[3];
+  return batch_step_common(h, a, m, stream);
+}
+
+int ekf_batch_step_generated(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int m,
+                             const double* record_dev, const double* sigma4, void* stream) {
+  if (!h) return fail(EKF_EINVAL, "null handle");
+  return batch_step_generated(h, seed, step, first_filter, m, record_dev, sigma4, stream);
 }
 
 int ekf_batch_pack(ekf_batch_t* h, const double* mean_ref_dev, const double* cov_ref_dev, int64_t first,
@@ -381,8 +399,8 @@ struct PipeSet {
   int32_t* slot;
 };
 
-template <typename Fill, typename Post>
-static int pipe_step(ekf_batch_t* h, int m, void* caller, void* out_host, size_t out_bytes, Fill fill, Post post) {
+template <typename Fill, typename Step, typename Post>
+static int pipe_step(ekf_batch_t* h, void* caller, void* out_host, size_t out_bytes, Fill fill, Step step, Post post) {
   CU(cudaSetDevice(h->device));
   const int64_t B = h->batch;
   const int M = ekf::BATCH_MAX_M;
@@ -416,7 +434,7 @@ static int pipe_step(ekf_batch_t* h, int m, void* caller, void* out_host, size_t
   // compute: after this step's inputs have landed and the result area of step i-2 has drained
   CU(cudaStreamWaitEvent(h->stream, h->ev_in[set], 0));
   if (h->pipe_step >= 2) CU(cudaStreamWaitEvent(h->stream, h->ev_out[set], 0));
-  rc = ekf_batch_step(h, ps.ang, ps.lin, ps.slot, ps.rng, ps.brg, m, h->stream);
+  rc = step(ps, h->stream);
   if (rc != EKF_OK) return rc;
   rc = post(ps, h->stream);
   if (rc != EKF_OK) return rc;
@@ -444,7 +462,7 @@ int ekf_batch_step_host_async(ekf_batch_t* h, const double* ang_host, const doub
   if (m > 0 && (!slot_host || !rng_host || !brg_host)) return fail(EKF_EINVAL, "observation arrays are null");
   const int64_t B = h->batch;
   return pipe_step(
-      h, m, stream, pose_host, (size_t)B * 3 * sizeof(double),
+      h, stream, pose_host, (size_t)B * 3 * sizeof(double),
       [&](const PipeSet& ps, cudaStream_t st) -> int {
         CU(cudaMemcpyAsync(ps.ang, ang_host, B * sizeof(double), cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(ps.lin, lin_host, B * sizeof(double), cudaMemcpyHostToDevice, st));
@@ -454,6 +472,9 @@ int ekf_batch_step_host_async(ekf_batch_t* h, const double* ang_host, const doub
           CU(cudaMemcpyAsync(ps.brg, brg_host, B * m * sizeof(double), cudaMemcpyHostToDevice, st));
         }
         return EKF_OK;
+      },
+      [&](const PipeSet& ps, cudaStream_t st) -> int {
+        return ekf_batch_step(h, ps.ang, ps.lin, ps.slot, ps.rng, ps.brg, m, st);
       },
       [&](const PipeSet& ps, cudaStream_t st) -> int {
         CU(ekf::batch_launch_pose(h->mu, ps.result, B, h->ld, st));
@@ -526,14 +547,16 @@ int ekf_batch_mc_step_host_async(ekf_batch_t* h, uint64_t seed, uint64_t step, u
     for (int i = 0; i < 2; ++i) CU(cudaMalloc(&h->mc_record[i], sizeof(double) * 32));
   const int set = (int)(h->pipe_step & 1);
   const size_t rec_bytes = sizeof(double) * (size_t)(2 + 2 * m + (m + 1) / 2);
+  // the per-member inputs are drawn INSIDE the fused step (BatchStepArgs::gen_record): the copy-in stream only
+  // carries the < 200-byte record; no perturbation kernel, no per-filter staging arrays
   return pipe_step(
-      h, m, stream, pose_moments_host, pose_moments_host ? 12 * sizeof(double) : 0,
-      [&](const PipeSet& ps, cudaStream_t st) -> int {
+      h, stream, pose_moments_host, pose_moments_host ? 12 * sizeof(double) : 0,
+      [&](const PipeSet&, cudaStream_t st) -> int {
         CU(cudaMemcpyAsync(h->mc_record[set], record_host, rec_bytes, cudaMemcpyHostToDevice, st));
-        a.record = h->mc_record[set];
-        a.ang = ps.ang; a.lin = ps.lin; a.slot = ps.slot; a.rng = ps.rng; a.brg = ps.brg;
-        CU(ekf::batch_launch_perturb(a, st));
         return EKF_OK;
+      },
+      [&](const PipeSet&, cudaStream_t st) -> int {
+        return batch_step_generated(h, seed, step, first_filter, m, h->mc_record[set], sigma4, st);
       },
       [&](const PipeSet& ps, cudaStream_t st) -> int {
         if (score) CU(ekf::batch_launch_ate(h->mu, h->ld, h->batch, gt_x, gt_y, sse_dev, st));
@@ -675,7 +698,7 @@ int ekf_lm_create(int capacity_landmarks, int device, ekf_lm_t** out) {
   const char* v = getenv("EKF_LM_VARIANT");
   h->variant = v ? atoi(v) : 0;
   double* ws = nullptr;
-  const size_t ws_doubles = (size_t)(6 + 4 * ekf::LM_MAX_FUSED) * h->ldw + ekf::kScalCount + 2 * ekf::LM_MAX_FUSED +
+  const size_t ws_doubles = (size_t)(6 + 6 * ekf::LM_MAX_FUSED) * h->ldw + ekf::kScalCount + 2 * ekf::LM_MAX_FUSED +
                             2 * ekf::LM_MAX_FUSED * ekf::LM_MAX_ROWS;
   cudaError_t e = cudaMalloc(&ws, ws_doubles * sizeof(double));
   if (e == cudaSuccess) e = cudaMemset(ws, 0, ws_doubles * sizeof(double));
@@ -694,7 +717,8 @@ int ekf_lm_create(int capacity_landmarks, int device, ekf_lm_t** out) {
   h->my = h->scal + ekf::kScalCount;
   h->mK = h->my + 2 * ekf::LM_MAX_FUSED;
   h->mW = h->mK + 2 * ekf::LM_MAX_FUSED * h->ldw;
-  h->mKR = h->mW + 2 * ekf::LM_MAX_FUSED * h->ldw;
+  h->mA = h->mW + 2 * ekf::LM_MAX_FUSED * h->ldw;
+  h->mKR = h->mA + 2 * ekf::LM_MAX_FUSED * h->ldw;
   *out = h;
   return EKF_OK;
 }
@@ -883,7 +907,7 @@ static int lm_multi_check(ekf_lm_t* h, int m, const int32_t* slots_host, const d
 // (peer-memory exchange: owners do not push to themselves), otherwise every row comes from xrows (replicated buffer)
 static void lm_multi_fill(ekf_lm_t* h, ekf::LmMultiArgs& a, int g, const int32_t* slots, const double* rng,
                           const double* brg, const double* xrows, bool own_local = false) {
-  a.P = h->P; a.mu = h->mu; a.K = h->mK; a.W = h->mW; a.y = h->my; a.KR = h->mKR;
+  a.P = h->P; a.mu = h->mu; a.K = h->mK; a.W = h->mW; a.A = h->mA; a.y = h->my; a.KR = h->mKR;
   a.xrows = xrows;
   a.ld = h->ld; a.ldw = h->ldw; a.ldx = h->ld + 4;
   a.n = h->n; a.m = g; a.row_begin = h->row_begin; a.row_end = h->row_end; a.mm = h->mm;
@@ -912,7 +936,7 @@ int ekf_lm_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const dou
   const bool whole = (h->row_begin == 0 && h->row_end == h->n);
   const bool joseph = (h->flags & ekf::kFlagJoseph) != 0;
   if (!(h->flags & ekf::kFlagMeasurement)) return EKF_OK;
-  if (!whole || joseph) {  // no fused form there: the sequential path (fails on a shard like ekf_lm_update)
+  if (!whole) {  // a shard goes through ekf_lm_update_multi_from_rows / ekf_lm_p2p_update_multi (fails like ekf_lm_update)
     for (int u = 0; u < m; ++u) {
       const int rc = lm_update_impl(h, slots_host[u], rng_host[u], brg_host[u], nullptr, stream);
       if (rc != EKF_OK) return rc;
@@ -929,6 +953,7 @@ int ekf_lm_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const dou
     }
     ekf::LmMultiArgs a{};
     lm_multi_fill(h, a, g, slots_host + first, rng_host + first, brg_host + first, nullptr);
+    a.joseph = joseph ? 1 : 0;
     CU(ekf::lm_launch_update_multi(a, (cudaStream_t)stream));
   }
   return EKF_OK;

@@ -256,6 +256,7 @@ __global__ void __launch_bounds__(256) batch_pose_moments_partial_kernel(const d
   double acc[9];
 #pragma unroll
   for (int q = 0; q < 9; ++q) acc[q] = 0.0;
+#pragma unroll 4
   for (int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; b < batch; b += (int64_t)gridDim.x * blockDim.x) {
     const double x = mu[b * mu_stride], y = mu[b * mu_stride + 1], t = mu[b * mu_stride + 2];
     acc[0] = __dadd_rn(acc[0], x);

@@ -51,7 +51,7 @@ cudaError_t batch_launch_detection_noise(int64_t batch, uint64_t seed, uint64_t 
                                          double sigma, double* noise_tx, double* noise_tz, cudaStream_t st);
 // ensemble moments of the robot pose only: sums[0..2] = sum_b (x, y, theta), sums[3 + 3 i + k] = sum_b pose_i pose_k;
 // two passes, fixed summation order; partial: scratch [POSE_MOM_CTAS][12]
-constexpr int POSE_MOM_CTAS = 1184;  // 8 x 148 SMs
+constexpr int POSE_MOM_CTAS = 592;  // 4 x 148 SMs
 cudaError_t batch_launch_pose_moments(const double* mu, int64_t mu_stride, int64_t batch, double* partial, double* sums,
                                       cudaStream_t st);
 constexpr int MOM_CTAS = 592;  // 4 x 148 SMs: partial sums of the ensemble moments

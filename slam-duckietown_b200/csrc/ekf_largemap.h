@@ -98,6 +98,8 @@ struct LmMultiArgs {
   double* P;
   double* mu;
   double* K;    // [m][2][ldw]: K_u[:,0] at K + 2u ldw, K_u[:,1] at K + (2u+1) ldw
+  double* A;    // [m][2][ldw]: AHt_u, same indexing (Joseph form only)
+  int joseph;   // 1: one-pass Joseph form (whole matrix on one GPU only)
   double* W;    // [m][2][ldw]: (H P)_u rows, same indexing
   double* y;    // [m][2] innovations
   double* KR;   // [m][LM_MAX_ROWS][2] K_u at the exchanged rows R = {0,1,2} U {j_u, j_u+1} (replicated on every rank)

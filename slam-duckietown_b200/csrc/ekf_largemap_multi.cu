@@ -44,9 +44,14 @@ __device__ __forceinline__ const double* rho_ptr(const LmMultiArgs& a, int rho) 
 // round trip and a launch between consecutive updates: 36 us of a 196 us step at 4096 landmarks) collapse into one
 // launch whose serial part is M innovations. Every value keeps its operation sequence: results unchanged bitwise.
 // Block 0 publishes K_u[R, :] (a.KR) and y_u (a.y) for the streaming kernel.
-template <int M>
+// JOSEPH (whole matrix on one GPU only: K at every column must be local): W_u = H P - Q K^T, AHt_u = P H^T - K (S - Q)
+// and every rebuilt entry takes the second rank-2 term (AHt of its row, K of its column) after the first, update by
+// update — the operation sequence of the sequential Joseph kernels.
+template <int M, bool JOSEPH>
 __global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
   constexpr int NR = 3 + 2 * M;
+  __shared__ double sAR[JOSEPH ? M : 1][NR][2];  // AHt_u[R, :]
+  __shared__ double ssq[JOSEPH ? M : 1][2][2];   // S_u - Q
   __shared__ double sB[NR][NR + 1];  // P0[R, R]
   __shared__ double smuR[NR];        // mu[R], kept current through the updates
   __shared__ double sKR[M][NR][2];   // K_u[R, :]
@@ -109,7 +114,7 @@ __global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
   if (tid < 32) {
     const int rho = tid < NR ? tid : 0;
     const bool vt = tid < NR;
-    double vK[M][2], vW[M][2];
+    double vK[M][2], vW[M][2], vA[M][2];
 #pragma unroll
     for (int u = 0; u < M; ++u) {
       const int rho5[5] = {0, 1, 2, 3 + 2 * u, 4 + 2 * u};
@@ -126,6 +131,10 @@ __global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
           for (int w = 0; w < u; ++w) {
             pr[k] = rank2e(pr[k], sKR[w][rho5[k]][0], sKR[w][rho5[k]][1], vW[w][0], vW[w][1]);
             pc[k] = rank2e(pc[k], vK[w][0], vK[w][1], sWR[w][0][rho5[k]], sWR[w][1][rho5[k]]);
+            if (JOSEPH) {
+              pr[k] = rank2e(pr[k], sAR[w][rho5[k]][0], sAR[w][rho5[k]][1], vK[w][0], vK[w][1]);
+              pc[k] = rank2e(pc[k], vA[w][0], vA[w][1], sKR[w][rho5[k]][0], sKR[w][rho5[k]][1]);
+            }
           }
 #pragma unroll
         for (int k = 0; k < 5; ++k) spk[rho][k] = pc[k];
@@ -157,6 +166,9 @@ __global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
             s[r][b] = acc;
           }
         const double qn = a.mm * a.mm;
+        if (JOSEPH) {
+          ssq[u][0][0] = s[0][0]; ssq[u][0][1] = s[0][1]; ssq[u][1][0] = s[1][0]; ssq[u][1][1] = s[1][1];
+        }
         s[0][0] += qn;
         s[1][1] += qn;
         inv2(s, si);
@@ -182,6 +194,15 @@ __global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
         }
         vK[u][0] = dot2(pht0, ssi[u][0][0], pht1, ssi[u][1][0]);
         vK[u][1] = dot2(pht0, ssi[u][0][1], pht1, ssi[u][1][1]);
+        if (JOSEPH) {
+          const double qn = a.mm * a.mm;
+          vA[u][0] = joseph_a(pht0, vK[u][0], vK[u][1], ssq[u][0][0], ssq[u][1][0]);
+          vA[u][1] = joseph_a(pht1, vK[u][0], vK[u][1], ssq[u][0][1], ssq[u][1][1]);
+          hp0 = joseph_w(hp0, qn, vK[u][0]);
+          hp1 = joseph_w(hp1, qn, vK[u][1]);
+          sAR[u][rho][0] = vA[u][0];
+          sAR[u][rho][1] = vA[u][1];
+        }
         vW[u][0] = hp0;
         vW[u][1] = hp1;
         sKR[u][rho][0] = vK[u][0];
@@ -203,7 +224,7 @@ __global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
   }
   __syncthreads();
   if (!live) return;
-  double hK[M][2], hW[M][2];
+  double hK[M][2], hW[M][2], hA[M][2];
 #pragma unroll
   for (int u = 0; u < M; ++u) {
     const int rho5[5] = {0, 1, 2, 3 + 2 * u, 4 + 2 * u};
@@ -219,6 +240,10 @@ __global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
       for (int w = 0; w < u; ++w) {
         pr[k] = rank2e(pr[k], sKR[w][rho5[k]][0], sKR[w][rho5[k]][1], hW[w][0], hW[w][1]);
         pc[k] = rank2e(pc[k], hK[w][0], hK[w][1], sWR[w][0][rho5[k]], sWR[w][1][rho5[k]]);
+        if (JOSEPH) {
+          pr[k] = rank2e(pr[k], sAR[w][rho5[k]][0], sAR[w][rho5[k]][1], hK[w][0], hK[w][1]);
+          pc[k] = rank2e(pc[k], hA[w][0], hA[w][1], sKR[w][rho5[k]][0], sKR[w][rho5[k]][1]);
+        }
       }
     double hp0 = 0.0, hp1 = 0.0, pht0 = 0.0, pht1 = 0.0;
 #pragma unroll
@@ -230,6 +255,15 @@ __global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
     }
     hK[u][0] = local ? dot2(pht0, ssi[u][0][0], pht1, ssi[u][1][0]) : 0.0;
     hK[u][1] = local ? dot2(pht0, ssi[u][0][1], pht1, ssi[u][1][1]) : 0.0;
+    if (JOSEPH) {
+      const double qn = a.mm * a.mm;
+      hA[u][0] = joseph_a(pht0, hK[u][0], hK[u][1], ssq[u][0][0], ssq[u][1][0]);
+      hA[u][1] = joseph_a(pht1, hK[u][0], hK[u][1], ssq[u][0][1], ssq[u][1][1]);
+      hp0 = joseph_w(hp0, qn, hK[u][0]);
+      hp1 = joseph_w(hp1, qn, hK[u][1]);
+      a.A[(2 * u) * a.ldw + t] = hA[u][0];
+      a.A[(2 * u + 1) * a.ldw + t] = hA[u][1];
+    }
     hW[u][0] = hp0;
     hW[u][1] = hp1;
     if (local) {
@@ -251,9 +285,17 @@ __device__ __forceinline__ void xm_prepush4(const LmExchange& x, int row, int c,
 }
 
 // PRE: rank 0 of a peer-memory exchange — row tile 0 also pushes the updated robot rows for the NEXT step
-template <int RB, int UNROLL, int M, bool PRE>
+// second rank-2 term of the one-pass Joseph form on 4 columns: AHt of the row (a0, a1), K of the columns (kc0, kc1)
+__device__ __forceinline__ void joseph4(double4x& v, double a0, double a1, const double4x& kc0, const double4x& kc1) {
+  v.a = rank2e(v.a, a0, a1, kc0.a, kc1.a);
+  v.b = rank2e(v.b, a0, a1, kc0.b, kc1.b);
+  v.c = rank2e(v.c, a0, a1, kc0.c, kc1.c);
+  v.d = rank2e(v.d, a0, a1, kc0.d, kc1.d);
+}
+
+template <int RB, int UNROLL, int M, bool PRE, bool JOSEPH>
 __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMultiArgs a) {
-  __shared__ double sk[RB][2 * M];
+  __shared__ double sk[RB][(JOSEPH ? 4 : 2) * M];  // K_u of the rows, then (Joseph) AHt_u of the rows
   const int tid = threadIdx.x;
   pdl_wait();
   // this launch follows the gather on the stream: the exchange buffer of step x.seq is no longer read here
@@ -276,6 +318,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
   for (int e = tid; e < nrows * 2 * M; e += LM_THREADS) {
     const int r = e / (2 * M), q = e - r * (2 * M);
     sk[r][q] = a.K[(int64_t)q * a.ldw + r0 + r];
+    if (JOSEPH) sk[r][2 * M + q] = a.A[(int64_t)q * a.ldw + r0 + r];
   }
   __syncthreads();
   if (blockIdx.x == 0) {
@@ -298,6 +341,14 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
       w0[u] = ldg256(a.W + (int64_t)(2 * u) * a.ldw + c);
       w1[u] = ldg256(a.W + (int64_t)(2 * u + 1) * a.ldw + c);
     }
+    double4x kc0[JOSEPH ? M : 1], kc1[JOSEPH ? M : 1];  // Joseph: K_u of this thread's 4 columns
+    if (JOSEPH) {
+#pragma unroll
+      for (int u = 0; u < M; ++u) {
+        kc0[u] = ldg256(a.K + (int64_t)(2 * u) * a.ldw + c);
+        kc1[u] = ldg256(a.K + (int64_t)(2 * u + 1) * a.ldw + c);
+      }
+    }
     double* p = Pblk + c;
     int r = 0;
     for (; r + UNROLL <= nrows; r += UNROLL) {
@@ -313,6 +364,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
           v[q].b = rank2e(v[q].b, k0, k1, w0[u].b, w1[u].b);
           v[q].c = rank2e(v[q].c, k0, k1, w0[u].c, w1[u].c);
           v[q].d = rank2e(v[q].d, k0, k1, w0[u].d, w1[u].d);
+          if (JOSEPH) joseph4(v[q], sk[r + q][2 * M + 2 * u], sk[r + q][2 * M + 2 * u + 1], kc0[u], kc1[u]);
         }
 #pragma unroll
       for (int q = 0; q < UNROLL; ++q) stg256(p + (int64_t)(r + q) * a.ld, v[q]);
@@ -330,6 +382,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
         v.b = rank2e(v.b, k0, k1, w0[u].b, w1[u].b);
         v.c = rank2e(v.c, k0, k1, w0[u].c, w1[u].c);
         v.d = rank2e(v.d, k0, k1, w0[u].d, w1[u].d);
+        if (JOSEPH) joseph4(v, sk[r][2 * M + 2 * u], sk[r][2 * M + 2 * u + 1], kc0[u], kc1[u]);
       }
       stg256(p + (int64_t)r * a.ld, v);
       if (pre && r < 3 && nrows < UNROLL) xm_prepush4(a.x, r, c, v);
@@ -350,6 +403,9 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
         v.b = rank2e(v.b, k0, k1, w0.b, w1.b);
         v.c = rank2e(v.c, k0, k1, w0.c, w1.c);
         v.d = rank2e(v.d, k0, k1, w0.d, w1.d);
+        if (JOSEPH)
+          joseph4(v, sk[r][2 * M + 2 * u], sk[r][2 * M + 2 * u + 1], ldg256(a.K + (int64_t)(2 * u) * a.ldw + c),
+                  ldg256(a.K + (int64_t)(2 * u + 1) * a.ldw + c));
       }
       stg256(Pblk + (int64_t)r * a.ld + c, v);
       if (pre && r < 3) xm_prepush4(a.x, r, c, v);
@@ -377,35 +433,38 @@ cudaError_t lm_launch_export_rows_multi(const LmMultiArgs& a, double* rows, cuda
   return cudaGetLastError();
 }
 
-template <int M>
+template <int M, bool JOSEPH>
 static cudaError_t launch_multi_t(const LmMultiArgs& a, cudaStream_t st) {
-  constexpr int RB = 32, UNROLL = 8;
+  constexpr int RB = 32, UNROLL = JOSEPH ? 4 : 8;
   const int rows = a.row_end - a.row_begin;
   if (rows <= 0) return cudaSuccess;
   dim3 grid(a.full_tiles + (a.tail_groups ? 1 : 0), (rows + RB - 1) / RB);
-  if (a.prepush && a.x.peers)
-    return launch_pdl(lm_rank_update_multi_kernel<RB, UNROLL, M, true>, grid, dim3(LM_THREADS), 0, st, a);
-  return launch_pdl(lm_rank_update_multi_kernel<RB, UNROLL, M, false>, grid, dim3(LM_THREADS), 0, st, a);
+  if constexpr (!JOSEPH) {
+    if (a.prepush && a.x.peers)
+      return launch_pdl(lm_rank_update_multi_kernel<RB, UNROLL, M, true, false>, grid, dim3(LM_THREADS), 0, st, a);
+  }
+  return launch_pdl(lm_rank_update_multi_kernel<RB, UNROLL, M, false, JOSEPH>, grid, dim3(LM_THREADS), 0, st, a);
+}
+
+template <int M, bool JOSEPH>
+static cudaError_t launch_fused_t(const LmMultiArgs& a, cudaStream_t st) {
+  const dim3 ggrid((a.n + 255) / 256), gblock(256);
+  cudaError_t e = launch_pdl(lm_gather_fused_kernel<M, JOSEPH>, ggrid, gblock, 0, st, a);
+  if (e != cudaSuccess) return e;
+  return launch_multi_t<M, JOSEPH>(a, st);
 }
 
 cudaError_t lm_launch_update_multi(const LmMultiArgs& a0, cudaStream_t st) {
   LmMultiArgs a = a0;
   if (a.m < 2 || a.m > LM_MAX_FUSED) return cudaErrorInvalidValue;
+  if (a.joseph && (a.xrows || a.row_begin != 0 || a.row_end != a.n)) return cudaErrorInvalidValue;
   const int groups = (a.n + 3) / 4;
   a.full_tiles = groups / LM_THREADS;
   a.tail_groups = groups - a.full_tiles * LM_THREADS;
-  const dim3 ggrid((a.n + 255) / 256), gblock(256);
-  cudaError_t e;
   switch (a.m) {
-    case 2: e = launch_pdl(lm_gather_fused_kernel<2>, ggrid, gblock, 0, st, a); break;
-    case 3: e = launch_pdl(lm_gather_fused_kernel<3>, ggrid, gblock, 0, st, a); break;
-    default: e = launch_pdl(lm_gather_fused_kernel<4>, ggrid, gblock, 0, st, a); break;
-  }
-  if (e != cudaSuccess) return e;
-  switch (a.m) {
-    case 2: return launch_multi_t<2>(a, st);
-    case 3: return launch_multi_t<3>(a, st);
-    default: return launch_multi_t<4>(a, st);
+    case 2: return a.joseph ? launch_fused_t<2, true>(a, st) : launch_fused_t<2, false>(a, st);
+    case 3: return a.joseph ? launch_fused_t<3, true>(a, st) : launch_fused_t<3, false>(a, st);
+    default: return a.joseph ? launch_fused_t<4, true>(a, st) : launch_fused_t<4, false>(a, st);
   }
 }
 

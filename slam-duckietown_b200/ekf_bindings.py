@@ -503,6 +503,13 @@ class BatchedEKF:
                   _stream_ptr(t))
         return ang, lin, slot, rng, brg
 
+    def step_generated(self, seed, step, record_dev, m, sigma4, first_filter=0):
+        """One fused filter-step whose per-member inputs are drawn inside the kernel from the device-resident common
+        record (bitwise the step of ``perturb`` + ``step``, without the per-filter arrays)."""
+        sg = (C.c_double * 4)(*[float(x) for x in sigma4])
+        capi.call("ekf_batch_step_generated", self._h, int(seed), int(step), int(first_filter), int(m),
+                  _ptr(record_dev), sg, _stream_ptr(self.torch))
+
     def detection_noise(self, seed, step, n_det, sigma, first_filter=0):
         """(noise_tx, noise_tz) device tensors (n_det, B) for ``associate``."""
         t = self.torch

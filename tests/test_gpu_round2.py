@@ -264,3 +264,44 @@ def test_tracked_rows_leg_on_emulated_shards(eb):
     print(f"tracked rows on 3 emulated shards, n = {sh.n}: {e}")
     assert max(e) <= TOL, e
     sh.close()
+
+
+@pytest.mark.parametrize("n_lm,group", [(700, 3), (256, 4), (1024, 2)])
+def test_large_map_fused_joseph_bitwise(eb, n_lm, group):
+    """Joseph form: ekf_lm_update_multi (one pass over P, two rank-2 terms per update) == the same updates through the
+    sequential Joseph kernels, BITWISE, and both match the oracle's Joseph update."""
+    import torch
+    from slam_duckietown_b200 import workloads as wl
+    w = wl.make_large_map(n_lm, updates=18)
+    seq, fus = eb.LargeMapEKF(n_lm), eb.LargeMapEKF(n_lm)
+    m_o, c_o = w.mu0.copy(), w.p0()
+    for g in (seq, fus):
+        g.set_noise(0.2, 0.5)
+        g.set_flags(joseph=True)
+        g.load(w.mu0, w.p0())
+    fl = eo.Flags(motion_var=0.2, meas_var=0.5, joseph=True)
+    pend = []
+
+    def flush():
+        if pend:
+            fus.update_multi([o[1] for o in pend], [o[2] for o in pend], [o[3] for o in pend])
+            pend.clear()
+    for op in w.ops:
+        if op[0] == "update":
+            seq.update(op[1], op[2], op[3])
+            eo.update_rank(m_o, c_o, op[1], op[2], op[3], 0.5, joseph=True)
+            pend.append(op)
+            if len(pend) == group:
+                flush()
+        else:
+            flush()
+            for g in (seq, fus):
+                g.predict(op[1], op[2])
+            dx, dy, th, g0, g1 = eo.motion_step(m_o[2], op[1], op[2], fl)
+            m_o[0] += dx; m_o[1] += dy; m_o[2] = th
+            eo.predict_cov_rank(c_o, g0, g1, 0.2)
+    flush()
+    assert torch.equal(seq.mu, fus.mu), "mu differs between sequential and fused Joseph updates"
+    assert torch.equal(seq.P, fus.P), "P differs between sequential and fused Joseph updates"
+    mu, p = fus.state()
+    assert_parity(mu, p, m_o, c_o, what=f"fused Joseph n_lm={n_lm} group={group}")

@@ -200,3 +200,35 @@ def test_generated_association_and_common_ticks_equal_array_forms_bitwise(eb):
         assert torch.equal(a, b)
     assert res[0][4] == res[1][4]
     del rs
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("L,m,variant", [(20, 3, "auto"), (8, 2, "auto"), (16, 6, "auto"), (20, 3, "staged"),
+                                         (8, 4, "group16"), (12, 1, "regw")])
+def test_in_kernel_generation_equals_perturb_then_step_bitwise(eb, monkeypatch, L, m, variant):
+    """ekf_batch_step_generated (inputs drawn by m + 1 lanes inside the step kernel, under the TMA load) ==
+    ekf_batch_perturb followed by ekf_batch_step, BITWISE, on every kernel family."""
+    import torch
+    from slam_duckietown_b200 import workloads as wl
+    monkeypatch.setenv("EKF_BATCH_KERNEL", variant)
+    B = 2003
+    base = wl.make_batched(1, L, m, steps=-(-L // m) + 5)
+    rs = np.random.default_rng(8)
+    mv, mm = rs.uniform(0.05, 0.5, B), rs.uniform(0.1, 1.0, B)
+    sigma = (0.01, 0.003, 0.02, 0.02)
+    outs = []
+    for mode in ("perturb", "generated"):
+        f = eb.BatchedEKF(B, L)
+        f.set_noise(mv, mm)
+        f.init(0.1)
+        for t in range(base.steps):
+            rec = torch.from_numpy(f.mc_record(base.ang[t, 0], base.lin[t, 0], base.slot[t, 0], base.rng[t, 0],
+                                               base.brg[t, 0])).to(f.dev)
+            if mode == "perturb":
+                f.step(*f.perturb(77, t, rec, m, sigma, first_filter=10 ** 10))
+            else:
+                f.step_generated(77, t, rec, m, sigma, first_filter=10 ** 10)
+        assert f.fault_count() == 0 and int(f.n_known.min()) == L
+        outs.append((f.mu.clone(), f.P.clone()))
+        f.close()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])

@@ -1,13 +1,13 @@
-# round 2, 1-GPU check after Joseph on the dispatched kernels + Box-Muller generator
+# round 2, 1-GPU check after in-kernel generation of the Monte Carlo inputs
 set -x
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -m gpu -x -q --durations=5 > gpurun_out/r2f_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r2f_pytest.log
-timeout 300 python tools/mc_probe.py > gpurun_out/r2f_mc_probe.json 2> gpurun_out/r2f_mc_probe.err
-timeout 900 python bench.py > gpurun_out/r2f_bench1.json 2> gpurun_out/r2f_bench1.err; echo "bench1 rc=$?" >> gpurun_out/r2f_bench1.err
-tail -6 gpurun_out/r2f_pytest.log; cat gpurun_out/r2f_mc_probe.json; tail -3 gpurun_out/r2f_bench1.err
+timeout 1500 python -m pytest tests -m gpu -x -q --durations=5 > gpurun_out/r2g_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r2g_pytest.log
+timeout 300 python tools/mc_probe.py > gpurun_out/r2g_mc_probe.json 2> gpurun_out/r2g_mc_probe.err
+timeout 900 python bench.py > gpurun_out/r2g_bench1.json 2> gpurun_out/r2g_bench1.err; echo "bench1 rc=$?" >> gpurun_out/r2g_bench1.err
+tail -6 gpurun_out/r2g_pytest.log; cat gpurun_out/r2g_mc_probe.json; tail -3 gpurun_out/r2g_bench1.err
 python - <<'PY'
 import json
-d=json.load(open('gpurun_out/r2f_bench1.json'))
+d=json.load(open('gpurun_out/r2g_bench1.json'))
 print('B', d['value'], d['roofline']['frac'], 'e2e', d['e2e']['value'], 'gen', d['e2e']['generated_inputs']['value'])
 print('sustained', d['sustained']['value'], d['sustained']['roofline']['frac_of_8TBs'], d['sustained']['clocks'])
 j=d['joseph']; print('joseph', j['value'], j['roofline']['frac'], j['vs_plain'])
