@@ -461,12 +461,17 @@ static cudaError_t launch_step_t(const BatchStepArgs& a, int64_t batch, cudaStre
 bool batch_capacity_supported(int n_landmarks) {
   switch (n_landmarks) {
     case 4: case 8: case 12: case 16: case 20: case 24: case 28: return true;
+    case 32: case 40: case 48: case 56: return true;  // staged kernel only (general m); beyond: LargeMapEKF per filter
     default: return false;
   }
 }
 
 #define EKF_STEP_CASE(L) \
   case L: return joseph ? launch_step_t<L, true>(a, batch, st) : launch_step_t<L, false>(a, batch, st)
+// capacities above 28 landmarks: the general-m instantiation only (the map of the reference grows without bound,
+// replay_no_ros.py:341-352; one warp still stages the whole covariance: 106 KB at 56 landmarks)
+#define EKF_BIG_CASE(L) \
+  case L: return joseph ? launch_step_mt<L, true, 0>(a, batch, st) : launch_step_mt<L, false, 0>(a, batch, st)
 cudaError_t batch_launch_step(int n_landmarks, const BatchStepArgs& a, int64_t batch, bool joseph,
                               cudaStream_t st) {
   switch (n_landmarks) {
@@ -477,10 +482,15 @@ cudaError_t batch_launch_step(int n_landmarks, const BatchStepArgs& a, int64_t b
     EKF_STEP_CASE(20);
     EKF_STEP_CASE(24);
     EKF_STEP_CASE(28);
+    EKF_BIG_CASE(32);
+    EKF_BIG_CASE(40);
+    EKF_BIG_CASE(48);
+    EKF_BIG_CASE(56);
     default: return cudaErrorInvalidValue;
   }
 }
 #undef EKF_STEP_CASE
+#undef EKF_BIG_CASE
 
 cudaError_t batch_launch_init(double* mu, double* P, int* n_known, int64_t batch, int n, int ld, double p0,
                               cudaStream_t st) {

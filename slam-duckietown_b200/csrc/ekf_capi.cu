@@ -133,7 +133,7 @@ int ekf_batch_layout(int n_landmarks, int* n, int* ld, int64_t* p_stride, int64_
 int ekf_batch_create(int n_landmarks, int64_t batch, int device, ekf_batch_t** out) {
   if (!out) return fail(EKF_EINVAL, "out is null");
   if (!ekf::batch_capacity_supported(n_landmarks))
-    return fail(EKF_EINVAL, "landmark capacity %d not built (use 4, 8, 12, 16, 20, 24 or 28)", n_landmarks);
+    return fail(EKF_EINVAL, "landmark capacity %d not built (use 4, 8, ..., 28, 32, 40, 48 or 56)", n_landmarks);
   if (batch <= 0 || batch > 0x7fffffffLL) return fail(EKF_EINVAL, "batch out of range");
   CU(cudaSetDevice(device));
   ekf_batch* h = new (std::nothrow) ekf_batch();
@@ -238,7 +238,7 @@ static int batch_step_common(ekf_batch_t* h, ekf::BatchStepArgs& a, int m, void*
   const bool gen = a.gen_record != nullptr;  // in-kernel inputs: plain form on the fast kernels, else the staged kernel
   if ((h->kernel == 0 || h->kernel >= 8) && ekf::batch_group_supported(h->nlm, m) && !(gen && joseph))
     CU(ekf::batch_launch_step_group(h->nlm, h->kernel >= 8 ? h->kernel : 8, a, h->batch, joseph, (cudaStream_t)stream));
-  else if ((h->kernel == 0 || h->kernel == 3 || h->kernel >= 8) && ekf::batch_regw_supported(m, joseph, gen))
+  else if ((h->kernel == 0 || h->kernel == 3 || h->kernel >= 8) && ekf::batch_regw_supported(m, joseph, gen) && h->nlm <= 28)
     CU(ekf::batch_launch_step_regw(h->nlm, a, h->batch, joseph, (cudaStream_t)stream));
   else
     CU(ekf::batch_launch_step(h->nlm, a, h->batch, joseph, (cudaStream_t)stream));
