@@ -93,6 +93,8 @@ struct ekf_lm {
   unsigned long long p2p_seq = 0;
   unsigned long long p2p_robot_seq = 0;  // update number whose buffer already holds rows 0-2 (pre-pushed by rank 0)
   int variant = 0;
+  bool single_launch = true;             // gather + streaming update of one update in one launch (EKF_LM_SINGLE=0: two)
+  unsigned long long single_calls = 0;   // single-launch updates issued so far (the ready counter's target grows with it)
 };
 
 extern "C" {
@@ -697,6 +699,7 @@ int ekf_lm_create(int capacity_landmarks, int device, ekf_lm_t** out) {
   h->ldw = (((int64_t)h->n + 15) & ~15LL) + 16;
   const char* v = getenv("EKF_LM_VARIANT");
   h->variant = v ? atoi(v) : 0;
+  if (const char* sl = getenv("EKF_LM_SINGLE")) h->single_launch = atoi(sl) != 0;
   double* ws = nullptr;
   const size_t ws_doubles = (size_t)(6 + 6 * ekf::LM_MAX_FUSED) * h->ldw + ekf::kScalCount + 2 * ekf::LM_MAX_FUSED +
                             2 * ekf::LM_MAX_FUSED * ekf::LM_MAX_ROWS;
@@ -870,7 +873,6 @@ static int lm_update_impl_split(ekf_lm_t* h, int slot, double rng, double brg, c
   g.mm = h->mm;
   g.shard = rows5 ? 1 : 0;
   g.mu_out = h->mu;
-  CU(ekf::lm_launch_gather(g, (cudaStream_t)stream));
   u.P = h->P;
   u.mu = h->mu;
   u.K0 = h->K0; u.K1 = h->K1; u.A0 = h->A0; u.A1 = h->A1; u.W0 = h->W0; u.W1 = h->W1; u.scal = h->scal;
@@ -878,6 +880,16 @@ static int lm_update_impl_split(ekf_lm_t* h, int slot, double rng, double brg, c
   u.n = h->n;
   u.row_begin = h->row_begin;
   u.row_end = h->row_end;
+  if (!joseph && h->variant == 0 && h->single_launch && !p2p) {
+    // ONE launch: the leading CTAs run the gather, the streaming tiles pre-load their first rows and wait for it.
+    // Not with the peer-memory exchange: measured no gain there (4096 landmarks on 8 GPUs: 0.0419 vs 0.0403 ms) and,
+    // at 32 768 landmarks, one rank's flag wait of the very first update ran into its 2 s budget (results intact; cause
+    // not found: gpurun_out r2j, 4 GPUs) — the sharded update keeps its two PDL-chained launches.
+    CU(ekf::lm_launch_update_single(g, u, reinterpret_cast<unsigned long long*>(h->scal + ekf::kScalReady),
+                                    &h->single_calls, (cudaStream_t)stream));
+    return EKF_OK;
+  }
+  CU(ekf::lm_launch_gather(g, (cudaStream_t)stream));
   CU(ekf::lm_launch_update(u, joseph, h->variant, (cudaStream_t)stream));
   return EKF_OK;
 }

@@ -119,15 +119,16 @@ __global__ void __launch_bounds__(256) lm_predict_kernel(double* __restrict__ mu
 // 5 columns (one or two 32-byte sectors per row) and K[t, :]. Nothing in P or mu is written here, so the
 // streaming kernel that follows can update P in place.
 // -------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
+// bid / nblocks: this CTA's index among the CTAs running the gather and their number (the kernel's own blockIdx.x /
+// gridDim.x when launched alone; the leading CTAs of the single-launch update otherwise)
+__device__ __forceinline__ void lm_gather_body(const LmGatherArgs& a, int bid, int nblocks) {
   __shared__ double sh[2][5];
   __shared__ double ssi[2][2];
   __shared__ double ssq[2][2];  // S - Q
   __shared__ double sy[2];
-  pdl_wait();
   const int j = a.j;
   const int idx5[5] = {0, 1, 2, j, j + 1};
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int t = bid * blockDim.x + threadIdx.x;
   const bool live = t < a.n;
   const bool local = live && (t >= a.row_begin && t < a.row_end);
   // this thread's column gathers touch only the local block: issued first, they fly under the exchange below and
@@ -152,7 +153,7 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
           if (t == 0) dst[a.ld] = m;
         }
       }
-      x_publish(a.x, a.x.count, gridDim.x, a.x.seq, (unsigned)a.push_mask);
+      x_publish(a.x, a.x.count, (unsigned)nblocks, a.x.seq, (unsigned)a.push_mask);
     }
     // ... then everyone waits for the parts that come from a peer
     if (a.wait_mask) {
@@ -201,7 +202,7 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
     }
     sy[0] = in.y0;
     sy[1] = in.y1;
-    if (blockIdx.x == 0) {
+    if (bid == 0) {
       a.scal[kScalY0] = in.y0;
       a.scal[kScalY1] = in.y1;
     }
@@ -254,6 +255,11 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
   }
 }
 
+__global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
+  pdl_wait();
+  lm_gather_body(a, blockIdx.x, gridDim.x);
+}
+
 // -------------------------------------------------------------------------------------------------------
 // a10-a11 streaming update (:476-480): P[i, c] -= K[i,0] W[0,c] + K[i,1] W[1,c]  (+ Joseph terms), in place.
 //
@@ -271,20 +277,42 @@ __device__ __forceinline__ void x_prepush4(const LmExchange& x, int row, int c, 
 }
 
 // PRE: rank 0 of a peer-memory exchange — row tile 0 also pushes the updated robot rows (see LmExchange)
+// (bx, by) of nbx column tiles: this CTA's tile. ready != null (single-launch update): the CTA first requests its first
+// UNROLL rows of P — they do not depend on the gather — and only then waits until the gather CTAs of the same launch
+// have counted in (`*ready >= target`); nothing of P is stored before that, so the gather still sees the old P.
 template <int RB, int UNROLL, bool JOSEPH, bool PRE>
-__global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs a) {
+__device__ __forceinline__ void lm_rank_update_body(const LmUpdateArgs& a, int bx, int by, int nbx,
+                                                    const unsigned long long* ready, unsigned long long target) {
   __shared__ double sk[RB][4];
   const int tid = threadIdx.x;
-  pdl_wait();
-  // this launch follows the gather on the stream: the exchange buffer of update x.seq is no longer read here
-  if (a.x.peers && blockIdx.x == 0 && blockIdx.y == 0) x_ack(a.x);
-  const bool pre = PRE && blockIdx.y == 0;
-  if (pre) {  // the buffer of update seq + 1 was last read by the gathers of update seq - 1
-    if (tid == 0) x_wait_acks(a.x, a.x.seq > 1 ? a.x.seq - 1 : 0);
+  const bool pre = PRE && by == 0;
+  const int r0 = a.row_begin + by * RB;          // first global row of this CTA
+  const int nrows = min(RB, a.row_end - r0);
+  double* __restrict__ Pblk = a.P + (int64_t)(r0 - a.row_begin) * a.ld;
+  double4x v0[UNROLL];                            // rows 0..UNROLL-1 of a full tile, requested ahead of the wait
+  const bool ahead = ready != nullptr && bx < a.full_tiles && nrows >= UNROLL;
+  if (ahead) {
+    const double* p = Pblk + (bx * LM_THREADS + tid) * 4;
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) v0[u] = ldg256_stream(p + (int64_t)u * a.ld);
+  }
+  if (ready) {
+    if (tid == 0) {
+      const long long t0 = clock64();
+      while (*reinterpret_cast<const volatile unsigned long long*>(ready) < target) {
+        if (clock64() - t0 > kSpinBudget) break;  // cannot happen (the gather CTAs wait on nothing local)
+        __nanosleep(20);
+      }
+      __threadfence();
+    }
     __syncthreads();
   }
-  const int r0 = a.row_begin + blockIdx.y * RB;          // first global row of this CTA
-  const int nrows = min(RB, a.row_end - r0);
+  // the gather of this update is complete on this rank: its exchange buffer is no longer read here
+  if (a.x.peers && bx == 0 && by == 0) x_ack(a.x);
+  if (pre) {  // the buffer of update seq + 1 was last read by the gathers of update seq - 1
+    if (tid == 0) x_wait_acks(a.x, a.x.seq > 1 ? a.x.seq - 1 : 0, 2);
+    __syncthreads();
+  }
   for (int r = tid; r < nrows; r += LM_THREADS) {
     sk[r][0] = a.K0[r0 + r];
     sk[r][1] = a.K1[r0 + r];
@@ -294,7 +322,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs
     }
   }
   __syncthreads();
-  if (blockIdx.x == 0) {  // a10: mu += K y for this CTA's rows
+  if (bx == 0) {  // a10: mu += K y for this CTA's rows
     const double y0 = a.scal[kScalY0], y1 = a.scal[kScalY1];
     for (int r = tid; r < nrows; r += LM_THREADS) {
       const double m = mu_inc(a.mu[r0 + r], sk[r][0], sk[r][1], y0, y1);
@@ -304,9 +332,8 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs
           if (d != a.x.rank) x_row(a.x.peers[d], a.x, a.x.seq + 1, r)[a.ld] = m;
     }
   }
-  double* __restrict__ Pblk = a.P + (int64_t)(r0 - a.row_begin) * a.ld;
-  if ((int)blockIdx.x < a.full_tiles) {
-    const int c = (blockIdx.x * LM_THREADS + tid) * 4;
+  if (bx < a.full_tiles) {
+    const int c = (bx * LM_THREADS + tid) * 4;
     const double4x w0 = ldg256(a.W0 + c), w1 = ldg256(a.W1 + c);
     double4x kc0, kc1;
     if (JOSEPH) {
@@ -318,7 +345,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs
     for (; r + UNROLL <= nrows; r += UNROLL) {
       double4x v[UNROLL];
 #pragma unroll
-      for (int u = 0; u < UNROLL; ++u) v[u] = ldg256_stream(p + (int64_t)(r + u) * a.ld);
+      for (int u = 0; u < UNROLL; ++u) v[u] = (ahead && r == 0) ? v0[u] : ldg256_stream(p + (int64_t)(r + u) * a.ld);
 #pragma unroll
       for (int u = 0; u < UNROLL; ++u) {
         const double k0 = -sk[r + u][0], k1 = -sk[r + u][1];
@@ -383,7 +410,41 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs
       if (pre && r < 3) x_prepush4(a.x, r, c, v);
     }
   }
-  if (pre) x_publish(a.x, a.x.count + kPrepushCounter, gridDim.x, a.x.seq + 1, 1u);
+  if (pre) x_publish(a.x, a.x.count + kPrepushCounter, (unsigned)nbx, a.x.seq + 1, 1u);
+}
+
+
+template <int RB, int UNROLL, bool JOSEPH, bool PRE>
+__global__ void __launch_bounds__(LM_THREADS) lm_rank_update_kernel(LmUpdateArgs a) {
+  pdl_wait();
+  lm_rank_update_body<RB, UNROLL, JOSEPH, PRE>(a, blockIdx.x, blockIdx.y, gridDim.x, nullptr, 0ULL);
+}
+
+// ONE launch per update (round 2): the first `gather_ctas` CTAs — dispatched first — run the gather and count in on
+// `ready`; the others are the streaming tiles, which pre-load their first rows and then wait for that count. The
+// gather's dependent chain (loads -> innovation -> S^-1 -> dot products -> stores, 8-9 us at 4096 landmarks) and one
+// kernel boundary disappear behind the first wave of P loads. `ready` only ever grows: `target` = gather_ctas x the
+// number of single-launch updates issued on this handle, so it needs no reset.
+struct LmFusedArgs {
+  LmGatherArgs g;
+  LmUpdateArgs u;
+  unsigned long long* ready;
+  unsigned long long target;
+  int gather_ctas, nbx;
+};
+template <int RB, int UNROLL, bool PRE>
+__global__ void __launch_bounds__(LM_THREADS) lm_update_single_launch_kernel(LmFusedArgs f) {
+  pdl_wait();
+  const int bid = blockIdx.x;
+  if (bid < f.gather_ctas) {
+    lm_gather_body(f.g, bid, f.gather_ctas);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) atomicAdd(f.ready, 1ULL);
+  } else {
+    const int idx = bid - f.gather_ctas;
+    lm_rank_update_body<RB, UNROLL, false, PRE>(f.u, idx % f.nbx, idx / f.nbx, f.nbx, f.ready, f.target);
+  }
 }
 
 // shard export: copy the locally owned ones of rows {0,1,2,j,j+1} (and their mu entries, stashed at column
@@ -451,6 +512,27 @@ cudaError_t lm_launch_update(const LmUpdateArgs& a, bool joseph, int variant, cu
     case 5: return launch_update_t<32, 16>(a, joseph, st);
     default: return launch_update_t<32, 8>(a, joseph, st);
   }
+}
+
+cudaError_t lm_launch_update_single(const LmGatherArgs& g, const LmUpdateArgs& u0, unsigned long long* ready,
+                                    unsigned long long* calls, cudaStream_t st) {
+  constexpr int RB = 32, UNROLL = 8;
+  LmFusedArgs f{};
+  f.g = g;
+  f.u = u0;
+  const int groups = (u0.n + 3) / 4;
+  f.u.full_tiles = groups / LM_THREADS;
+  f.u.tail_groups = groups - f.u.full_tiles * LM_THREADS;
+  const int rows = u0.row_end - u0.row_begin;
+  f.nbx = f.u.full_tiles + (f.u.tail_groups ? 1 : 0);
+  const int nby = rows > 0 ? (rows + RB - 1) / RB : 0;
+  f.gather_ctas = (g.n + LM_THREADS - 1) / LM_THREADS;
+  f.ready = ready;
+  f.target = (unsigned long long)f.gather_ctas * ++(*calls);
+  dim3 grid(f.gather_ctas + f.nbx * nby);
+  if (u0.prepush && u0.x.peers)
+    return launch_pdl(lm_update_single_launch_kernel<RB, UNROLL, true>, grid, dim3(LM_THREADS), 0, st, f);
+  return launch_pdl(lm_update_single_launch_kernel<RB, UNROLL, false>, grid, dim3(LM_THREADS), 0, st, f);
 }
 
 cudaError_t lm_launch_export_rows(const double* P, const double* mu, int64_t ld, int row_begin, int row_end,

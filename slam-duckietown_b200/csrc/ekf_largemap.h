@@ -38,7 +38,7 @@ __device__ __forceinline__ void pdl_wait() {
 constexpr int LM_THREADS = 128;  // threads per CTA of the streaming update = column groups per tile
 
 // slots of the small scalar workspace (device doubles)
-enum : int { kScalG0 = 0, kScalG1 = 1, kScalY0 = 2, kScalY1 = 3, kScalArrive = 6 /* u64 arrival counter of the predict */, kScalCount = 8 };
+enum : int { kScalG0 = 0, kScalG1 = 1, kScalY0 = 2, kScalY1 = 3, kScalArrive = 6 /* u64 arrival counter of the predict */, kScalReady = 7 /* u64 gather-done counter of the single-launch update */, kScalCount = 8 };
 
 // Peer-memory row exchange, folded into the update's own kernels (round 2; round 1 launched a separate push kernel
 // per row part: 14.8 us per update against a 17 us streaming pass at 8 GPUs, profiles/r1o_lm_launches.summary.txt).
@@ -138,6 +138,9 @@ cudaError_t lm_launch_predict(double* mu, double* P, int64_t ld, int n, int row_
                               double* scal, double ang, double lin, double mv, int flags, cudaStream_t st);
 cudaError_t lm_launch_gather(const LmGatherArgs& a, cudaStream_t st);
 cudaError_t lm_launch_update(const LmUpdateArgs& a, bool joseph, int variant, cudaStream_t st);
+// gather + streaming update in ONE launch (plain form); ready: device u64 counter, calls: host count of such launches
+cudaError_t lm_launch_update_single(const LmGatherArgs& g, const LmUpdateArgs& u, unsigned long long* ready,
+                                    unsigned long long* calls, cudaStream_t st);
 cudaError_t lm_launch_export_rows(const double* P, const double* mu, int64_t ld, int row_begin, int row_end,
                                   int j, double* rows5, int64_t ldx, cudaStream_t st);
 

@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
   if (a.x.peers && blockIdx.x == 0 && blockIdx.y == 0) x_ack(a.x);
   const bool pre = PRE && blockIdx.y == 0;
   if (pre) {
-    if (tid == 0) x_wait_acks(a.x, a.x.seq > 1 ? a.x.seq - 1 : 0);
+    if (tid == 0) x_wait_acks(a.x, a.x.seq > 1 ? a.x.seq - 1 : 0, 2);
     __syncthreads();
   }
   const int r0 = a.row_begin + blockIdx.y * RB;  // first global row of this CTA

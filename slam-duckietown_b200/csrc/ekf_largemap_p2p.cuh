@@ -20,12 +20,14 @@ namespace ekf {
 constexpr long long kSpinBudget = 4000000000LL;  // ~2 s of SM clocks
 constexpr int kPrepushCounter = P2P_PARTS;       // index of the streaming kernel's CTA counter in LmExchange::count
 
+// on expiry: err = max(err, code << 32 | the number waited for) — code 1: acks before a gather-side push, 2: acks
+// before the streaming kernel's pre-push, 3: a row part's flag
 __device__ __forceinline__ bool spin_until_ge(const volatile unsigned long long* p, unsigned long long want,
-                                              unsigned long long* err) {
+                                              unsigned long long* err, unsigned long long code = 1) {
   const long long t0 = clock64();
   while (*p < want) {
     if (clock64() - t0 > kSpinBudget) {
-      atomicExch(err, 1ULL);
+      atomicMax(err, (code << 32) | (want & 0xffffffffULL));
       return false;
     }
     __nanosleep(32);
@@ -43,10 +45,10 @@ __device__ __forceinline__ volatile unsigned long long* x_flag(double* area, con
 }
 
 // thread 0 of a CTA: every rank has acknowledged the gather of update `need` (so its buffer may be overwritten)
-__device__ __forceinline__ void x_wait_acks(const LmExchange& x, unsigned long long need) {
+__device__ __forceinline__ void x_wait_acks(const LmExchange& x, unsigned long long need, unsigned long long code = 1) {
   if (need == 0) return;
   for (int r = 0; r < x.world; ++r)
-    if (!spin_until_ge(x.acks + r, need, x.err)) return;
+    if (!spin_until_ge(x.acks + r, need, x.err, code)) return;
 }
 
 // After a CTA's stores into the peers' buffers: count the CTA in; the last of `total` CTAs publishes `seq` in the flag
@@ -72,7 +74,7 @@ __device__ __forceinline__ void x_publish(const LmExchange& x, unsigned* counter
 __device__ __forceinline__ void x_wait_parts(const LmExchange& x, const unsigned long long* flags, unsigned part_mask) {
   for (int p = 0; p < P2P_PARTS; ++p)
     if ((part_mask >> p) & 1u)
-      if (!spin_until_ge(flags + p, x.seq, x.err)) break;
+      if (!spin_until_ge(flags + p, x.seq, x.err, 3)) break;
   __threadfence_system();
 }
 
