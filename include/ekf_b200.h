@@ -162,7 +162,9 @@ int ekf_batch_detection_noise(ekf_batch_t* h, uint64_t seed, uint64_t step, uint
 /* One pipelined Monte Carlo step from a HOST record (same pipeline, stream contract and ekf_batch_host_sync as
  * ekf_batch_step_host_async): H2D of the record (< 200 bytes), the fused step drawing its inputs in the kernel, optionally
  * sse_dev[b] += squared position error against (gt_x, gt_y) when score != 0, and the 12 pose moments copied to
- * pose_moments_host (may be NULL). Per step the host sends the common record and receives 96 bytes.             */
+ * pose_moments_host (may be NULL). Per step the host sends the common record and receives 96 bytes. ATE and the moments
+ * are formed from a compact pose copy on the copy-out stream while the next step runs: sse_dev and pose_moments_host
+ * are complete after ekf_batch_host_sync.                                                                      */
 int ekf_batch_mc_step_host_async(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int m,
                                  const double* record_host, const double* sigma4, int score, double gt_x, double gt_y,
                                  double* sse_dev, double* pose_moments_host, void* stream);

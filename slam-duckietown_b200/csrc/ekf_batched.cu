@@ -369,6 +369,9 @@ __global__ void __launch_bounds__(32) batch_step_kernel(BatchStepArgs a) {
     const int t = lane + 32 * p;
     if (t < LD) gMu[t] = sMu[t];
   }
+  if constexpr (GEN) {
+    if (a.gen_pose_out && lane < 3) a.gen_pose_out[b * 3 + lane] = sMu[lane];
+  }
 }
 
 // -------------------------------------------------------------------------------------------------------

@@ -31,6 +31,8 @@ struct BatchStepArgs {
   unsigned long long gen_seed, gen_first;
   unsigned gen_step;
   double gen_s_ang, gen_s_lin, gen_s_rng, gen_s_brg;
+  double* gen_pose_out;          // GEN kernels only: compact copy [B][3] of the updated pose (null = none), so that the
+                                 // per-step result (ATE, pose moments) can be formed on another stream while the next step runs
   unsigned long long* faults;    // device counter
   int m;
   int flags;

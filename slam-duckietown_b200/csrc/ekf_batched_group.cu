@@ -432,6 +432,9 @@ __global__ void __launch_bounds__(32, JOSEPH ? 12 : 16) batch_step_group_kernel(
     const int t = gl + GW * p;
     if (t < LD) gMu[t] = sMu[t];
   }
+  if constexpr (GEN) {
+    if (a.gen_pose_out && gl < 3) a.gen_pose_out[b * 3 + gl] = sMu[gl];
+  }
 }
 
 // -------------------------------------------------------------------------------------------------------

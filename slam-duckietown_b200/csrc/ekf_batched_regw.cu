@@ -540,6 +540,9 @@ __global__ void __launch_bounds__(32 * WPC, regw_min_blocks(NLM, MT, JOSEPH)) ba
     const int t = lane + 32 * p;
     if (t < LD) gMu[t] = sMu[t];
   }
+  if constexpr (GEN) {
+    if (a.gen_pose_out && lane < 3) a.gen_pose_out[b * 3 + lane] = sMu[lane];
+  }
   __syncwarp();  // every lane is done with this filter's shared memory before the next TMA lands
   b = __shfl_sync(kFull, b_next, 0);
   }  // filter loop

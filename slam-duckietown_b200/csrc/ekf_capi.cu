@@ -68,6 +68,7 @@ struct ekf_batch {
   cudaEvent_t ev_caller = nullptr;  // orders the handle's streams after the caller's stream
   double* mom_partial = nullptr;  // scratch of ekf_batch_moments
   double* pose_partial = nullptr;  // scratch of ekf_batch_pose_moments
+  double* mc_moments[2] = {nullptr, nullptr};  // pose moments of the step in flight on each staging set
   double* mc_record[2] = {nullptr, nullptr};  // device copies of the common step record (one per staging set)
 };
 
@@ -165,6 +166,8 @@ int ekf_batch_destroy(ekf_batch_t* h) {
   cudaFree(h->faults);
   cudaFree(h->mom_partial);
   cudaFree(h->pose_partial);
+  cudaFree(h->mc_moments[0]);
+  cudaFree(h->mc_moments[1]);
   cudaFree(h->mc_record[0]);
   cudaFree(h->mc_record[1]);
   cudaFree(h->d_ang);
@@ -299,20 +302,21 @@ int ekf_batch_step_ticks_common(ekf_batch_t* h, int32_t ticks_left, int32_t tick
 }
 
 static int batch_step_generated(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int m,
-                                const double* record_dev, const double* sigma4, void* stream) {
+                                const double* record_dev, const double* sigma4, double* pose_out, void* stream) {
   if (!record_dev || !sigma4) return fail(EKF_EINVAL, "null argument");
   if (step > 0xffffffffull) return fail(EKF_EINVAL, "step must fit 32 bits");
   ekf::BatchStepArgs a{};
   a.gen_record = record_dev;
   a.gen_seed = seed; a.gen_first = first_filter; a.gen_step = (unsigned)step;
   a.gen_s_ang = sigma4[0]; a.gen_s_lin = sigma4[1]; a.gen_s_rng = sigma4[2]; a.gen_s_brg = sigma4[3];
+  a.gen_pose_out = pose_out;
   return batch_step_common(h, a, m, stream);
 }
 
 int ekf_batch_step_generated(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int m,
                              const double* record_dev, const double* sigma4, void* stream) {
   if (!h) return fail(EKF_EINVAL, "null handle");
-  return batch_step_generated(h, seed, step, first_filter, m, record_dev, sigma4, stream);
+  return batch_step_generated(h, seed, step, first_filter, m, record_dev, sigma4, nullptr, stream);
 }
 
 int ekf_batch_pack(ekf_batch_t* h, const double* mean_ref_dev, const double* cov_ref_dev, int64_t first,
@@ -401,8 +405,11 @@ struct PipeSet {
   int32_t* slot;
 };
 
-template <typename Fill, typename Step, typename Post>
-static int pipe_step(ekf_batch_t* h, void* caller, void* out_host, size_t out_bytes, Fill fill, Step step, Post post) {
+// `drain` runs on the copy-out stream before the device-to-host copy (work on the step's compact result that may
+// overlap the NEXT step's kernel); out_dev: where the bytes copied to out_host live (null = the set's result area)
+template <typename Fill, typename Step, typename Post, typename Drain>
+static int pipe_step(ekf_batch_t* h, void* caller, void* out_host, size_t out_bytes, const void* out_dev, Fill fill,
+                     Step step, Post post, Drain drain) {
   CU(cudaSetDevice(h->device));
   const int64_t B = h->batch;
   const int M = ekf::BATCH_MAX_M;
@@ -445,8 +452,10 @@ static int pipe_step(ekf_batch_t* h, void* caller, void* out_host, size_t out_by
   CU(cudaStreamWaitEvent((cudaStream_t)caller, h->ev_done[set], 0));
   // copy-out
   CU(cudaStreamWaitEvent(h->s_out, h->ev_done[set], 0));
+  rc = drain(ps, h->s_out);
+  if (rc != EKF_OK) return rc;
   if (out_host && out_bytes)
-    CU(cudaMemcpyAsync(out_host, ps.result, out_bytes, cudaMemcpyDeviceToHost, h->s_out));
+    CU(cudaMemcpyAsync(out_host, out_dev ? out_dev : ps.result, out_bytes, cudaMemcpyDeviceToHost, h->s_out));
   CU(cudaEventRecord(h->ev_out[set], h->s_out));
   ++h->pipe_step;
   return EKF_OK;
@@ -464,7 +473,7 @@ int ekf_batch_step_host_async(ekf_batch_t* h, const double* ang_host, const doub
   if (m > 0 && (!slot_host || !rng_host || !brg_host)) return fail(EKF_EINVAL, "observation arrays are null");
   const int64_t B = h->batch;
   return pipe_step(
-      h, stream, pose_host, (size_t)B * 3 * sizeof(double),
+      h, stream, pose_host, (size_t)B * 3 * sizeof(double), nullptr,
       [&](const PipeSet& ps, cudaStream_t st) -> int {
         CU(cudaMemcpyAsync(ps.ang, ang_host, B * sizeof(double), cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(ps.lin, lin_host, B * sizeof(double), cudaMemcpyHostToDevice, st));
@@ -481,7 +490,8 @@ int ekf_batch_step_host_async(ekf_batch_t* h, const double* ang_host, const doub
       [&](const PipeSet& ps, cudaStream_t st) -> int {
         CU(ekf::batch_launch_pose(h->mu, ps.result, B, h->ld, st));
         return EKF_OK;
-      });
+      },
+      [&](const PipeSet&, cudaStream_t) -> int { return EKF_OK; });
 }
 
 // ---- Monte Carlo replay with the perturbations generated on the device --------------------------------------
@@ -550,19 +560,25 @@ int ekf_batch_mc_step_host_async(ekf_batch_t* h, uint64_t seed, uint64_t step, u
   const int set = (int)(h->pipe_step & 1);
   const size_t rec_bytes = sizeof(double) * (size_t)(2 + 2 * m + (m + 1) / 2);
   // the per-member inputs are drawn INSIDE the fused step (BatchStepArgs::gen_record): the copy-in stream only
-  // carries the < 200-byte record; no perturbation kernel, no per-filter staging arrays
+  // carries the < 200-byte record; no perturbation kernel, no per-filter staging arrays. The step kernel leaves a
+  // compact copy of every member's pose in the set's result area; ATE and the pose moments are formed from it on the
+  // copy-out stream, i.e. while the NEXT step already runs.
+  if (!h->mc_moments[0])
+    for (int i = 0; i < 2; ++i) CU(cudaMalloc(&h->mc_moments[i], sizeof(double) * 12));
   return pipe_step(
-      h, stream, pose_moments_host, pose_moments_host ? 12 * sizeof(double) : 0,
+      h, stream, pose_moments_host, pose_moments_host ? 12 * sizeof(double) : 0, h->mc_moments[set],
       [&](const PipeSet&, cudaStream_t st) -> int {
         CU(cudaMemcpyAsync(h->mc_record[set], record_host, rec_bytes, cudaMemcpyHostToDevice, st));
         return EKF_OK;
       },
-      [&](const PipeSet&, cudaStream_t st) -> int {
-        return batch_step_generated(h, seed, step, first_filter, m, h->mc_record[set], sigma4, st);
-      },
       [&](const PipeSet& ps, cudaStream_t st) -> int {
-        if (score) CU(ekf::batch_launch_ate(h->mu, h->ld, h->batch, gt_x, gt_y, sse_dev, st));
-        if (pose_moments_host) CU(ekf::batch_launch_pose_moments(h->mu, h->ld, h->batch, h->pose_partial, ps.result, st));
+        return batch_step_generated(h, seed, step, first_filter, m, h->mc_record[set], sigma4, ps.result, st);
+      },
+      [&](const PipeSet&, cudaStream_t) -> int { return EKF_OK; },
+      [&](const PipeSet& ps, cudaStream_t st) -> int {
+        if (score) CU(ekf::batch_launch_ate(ps.result, 3, h->batch, gt_x, gt_y, sse_dev, st));
+        if (pose_moments_host)
+          CU(ekf::batch_launch_pose_moments(ps.result, 3, h->batch, h->pose_partial, h->mc_moments[set], st));
         return EKF_OK;
       });
 }
