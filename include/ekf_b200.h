@@ -178,6 +178,11 @@ int ekf_lm_destroy(ekf_lm_t* h);
 /* mu_dev [ld]; p_dev holds rows [row_begin, row_end) of P, row-major with leading dimension ld.
  * Single GPU: row_begin = 0, row_end = n. Pad entries must be zero.                                     */
 int ekf_lm_bind_state(ekf_lm_t* h, double* mu_dev, double* p_dev, int64_t ld, int row_begin, int row_end);
+/* Reference layout on the HOST (mean (m,), covariance (m,m) C order, m <= n) <-> the bound device state, one call
+ * each: upload zeroes the rest of the capacity (landmarks not yet seen) and copies this block's rows; download copies
+ * mean[0..m) and the block's live rows [row_begin, min(row_end, m)) x m, and is synchronous on `stream`.          */
+int ekf_lm_upload(ekf_lm_t* h, int m, const double* mean_host, const double* cov_host, void* stream);
+int ekf_lm_download(ekf_lm_t* h, int m, double* mean_host, double* cov_host, void* stream);
 int ekf_lm_set_noise(ekf_lm_t* h, double motion_var, double meas_var);
 int ekf_lm_set_flags(ekf_lm_t* h, int circular, int measurement, int disable_motion, int cov_form);
 /* a5: new landmark `slot` at (gx, gy): mu entries + 10000 on the two new diagonals (:355-360)            */

@@ -73,6 +73,8 @@ SIGNATURES = {
     "ekf_lm_create": (_i, [_i, _i, C.POINTER(_p)]),
     "ekf_lm_destroy": (_i, [_p]),
     "ekf_lm_bind_state": (_i, [_p, _p, _p, _l, _i, _i]),
+    "ekf_lm_upload": (_i, [_p, _i, _p, _p, _p]),
+    "ekf_lm_download": (_i, [_p, _i, _p, _p, _p]),
     "ekf_lm_set_noise": (_i, [_p, _d, _d]),
     "ekf_lm_set_flags": (_i, [_p, _i, _i, _i, _i]),
     "ekf_lm_augment": (_i, [_p, _i, _d, _d, _p]),

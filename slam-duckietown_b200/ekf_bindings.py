@@ -159,26 +159,23 @@ class LargeMapEKF:
 
     # -- state transfer (reference layout <-> device layout) ---------------------------------------------
     def load(self, mean: np.ndarray, cov: np.ndarray):
-        """Upload a reference-layout state of size m <= n (rows of this block only)."""
-        torch = self.torch
+        """Upload a reference-layout state of size m <= n (rows of this block only): ONE C-ABI call, the rest of the
+        capacity is zeroed on the device."""
+        mean = np.ascontiguousarray(mean, dtype=np.float64)
+        cov = np.ascontiguousarray(cov, dtype=np.float64)
         m = len(mean)
         if m > self.n or cov.shape != (m, m):
             raise ValueError("state larger than capacity or inconsistent shapes")
-        mu = np.zeros(self.ld)
-        mu[:m] = mean
-        self.mu.copy_(torch.from_numpy(mu))
-        lo, hi = self.row_begin, min(self.row_end, m)
-        # only the live block travels: the rest of the device buffer is zeroed in place (no host staging of the pad)
-        self.P.zero_()
-        if hi > lo:
-            self.P[: hi - lo, :m].copy_(torch.from_numpy(np.ascontiguousarray(cov[lo:hi, :])))
+        capi.call("ekf_lm_upload", self._h, m, mean.ctypes.data, cov.ctypes.data, _stream_ptr(self.torch))
+        self.torch.cuda.current_stream().synchronize()        # the host arrays may be released by the caller
 
     def state(self, m: int | None = None):
-        """Download (mean[:m], cov block[:, :m]) as numpy float64."""
-        m = self.n if m is None else m
-        mu = self.mu[:m].cpu().numpy().copy()
+        """Download (mean[:m], cov block[:, :m]) as NEW numpy float64 arrays: ONE C-ABI call."""
+        m = self.n if m is None else int(m)
         hi = min(self.row_end, m)
-        blk = self.P[: max(hi - self.row_begin, 0), :m].cpu().numpy().copy()
+        mu = np.empty(m)
+        blk = np.empty((max(hi - self.row_begin, 0), m))
+        capi.call("ekf_lm_download", self._h, m, mu.ctypes.data, blk.ctypes.data, _stream_ptr(self.torch))
         return mu, blk
 
     # -- steps ------------------------------------------------------------------------------------------
