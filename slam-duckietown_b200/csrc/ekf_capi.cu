@@ -93,7 +93,8 @@ struct ekf_lm {
   unsigned long long* p2p_err = nullptr;
   unsigned long long p2p_seq = 0;
   unsigned long long p2p_robot_seq = 0;  // update number whose buffer already holds rows 0-2 (pre-pushed by rank 0)
-  int variant = 0;
+  int variant = 0;          // tiling of the streaming kernel (EKF_LM_VARIANT; default chosen at bind time, see there)
+  bool variant_auto = true;
   bool single_launch = true;             // gather + streaming update of one update in one launch (EKF_LM_SINGLE=0: two)
   unsigned long long single_calls = 0;   // single-launch updates issued so far (the ready counter's target grows with it)
 };
@@ -715,6 +716,7 @@ int ekf_lm_create(int capacity_landmarks, int device, ekf_lm_t** out) {
   h->ldw = (((int64_t)h->n + 15) & ~15LL) + 16;
   const char* v = getenv("EKF_LM_VARIANT");
   h->variant = v ? atoi(v) : 0;
+  h->variant_auto = (v == nullptr);
   if (const char* sl = getenv("EKF_LM_SINGLE")) h->single_launch = atoi(sl) != 0;
   double* ws = nullptr;
   const size_t ws_doubles = (size_t)(6 + 6 * ekf::LM_MAX_FUSED) * h->ldw + ekf::kScalCount + 2 * ekf::LM_MAX_FUSED +
@@ -768,6 +770,10 @@ int ekf_lm_bind_state(ekf_lm_t* h, double* mu_dev, double* p_dev, int64_t ld, in
   h->ld = ld;
   h->row_begin = row_begin;
   h->row_end = row_end;
+  // tiling of the streaming kernel: a row block that fits L2 (a 1/8 or 1/4 shard of the 4096-landmark map: 67 / 134 MB)
+  // runs 6-12 % faster with 16-row tiles (twice the CTAs for the launch ramp and the tail; tools/lm_shard_probe.py:
+  // 20.7 -> 18.3 us at 1027 rows, 49.9 -> 47.1 us at 2051), blocks that stream from HBM keep the 32-row tiles
+  if (h->variant_auto) h->variant = ((int64_t)(row_end - row_begin) * ld * 8 <= (160LL << 20)) ? 1 : 0;
   return EKF_OK;
 }
 
@@ -932,12 +938,12 @@ static int lm_update_impl_split(ekf_lm_t* h, int slot, double rng, double brg, c
   u.n = h->n;
   u.row_begin = h->row_begin;
   u.row_end = h->row_end;
-  if (!joseph && h->variant == 0 && h->single_launch && !p2p) {
+  if (!joseph && h->variant <= 1 && h->single_launch && !p2p) {
     // ONE launch: the leading CTAs run the gather, the streaming tiles pre-load their first rows and wait for it.
     // Not with the peer-memory exchange: measured no gain there (4096 landmarks on 8 GPUs: 0.0419 vs 0.0403 ms) and,
     // at 32 768 landmarks, one rank's flag wait of the very first update ran into its 2 s budget (results intact; cause
     // not found: gpurun_out r2j, 4 GPUs) — the sharded update keeps its two PDL-chained launches.
-    CU(ekf::lm_launch_update_single(g, u, reinterpret_cast<unsigned long long*>(h->scal + ekf::kScalReady),
+    CU(ekf::lm_launch_update_single(g, u, h->variant, reinterpret_cast<unsigned long long*>(h->scal + ekf::kScalReady),
                                     &h->single_calls, (cudaStream_t)stream));
     return EKF_OK;
   }
@@ -975,6 +981,7 @@ static void lm_multi_fill(ekf_lm_t* h, ekf::LmMultiArgs& a, int g, const int32_t
   a.xrows = xrows;
   a.ld = h->ld; a.ldw = h->ldw; a.ldx = h->ld + 4;
   a.n = h->n; a.m = g; a.row_begin = h->row_begin; a.row_end = h->row_end; a.mm = h->mm;
+  a.variant = h->variant == 1 ? 1 : 0;
   for (int u = 0; u < g; ++u) {
     a.j[u] = 3 + 2 * slots[u];
     if (rng) a.rng[u] = rng[u];

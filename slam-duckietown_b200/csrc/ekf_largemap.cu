@@ -514,9 +514,9 @@ cudaError_t lm_launch_update(const LmUpdateArgs& a, bool joseph, int variant, cu
   }
 }
 
-cudaError_t lm_launch_update_single(const LmGatherArgs& g, const LmUpdateArgs& u0, unsigned long long* ready,
-                                    unsigned long long* calls, cudaStream_t st) {
-  constexpr int RB = 32, UNROLL = 8;
+template <int RB, int UNROLL>
+static cudaError_t launch_update_single_t(const LmGatherArgs& g, const LmUpdateArgs& u0, unsigned long long* ready,
+                                          unsigned long long* calls, cudaStream_t st) {
   LmFusedArgs f{};
   f.g = g;
   f.u = u0;
@@ -533,6 +533,13 @@ cudaError_t lm_launch_update_single(const LmGatherArgs& g, const LmUpdateArgs& u
   if (u0.prepush && u0.x.peers)
     return launch_pdl(lm_update_single_launch_kernel<RB, UNROLL, true>, grid, dim3(LM_THREADS), 0, st, f);
   return launch_pdl(lm_update_single_launch_kernel<RB, UNROLL, false>, grid, dim3(LM_THREADS), 0, st, f);
+}
+
+// variant 0: 32-row tiles (blocks that stream from HBM); variant 1: 16-row tiles (row blocks that fit L2)
+cudaError_t lm_launch_update_single(const LmGatherArgs& g, const LmUpdateArgs& u, int variant, unsigned long long* ready,
+                                    unsigned long long* calls, cudaStream_t st) {
+  if (variant == 1) return launch_update_single_t<16, 8>(g, u, ready, calls, st);
+  return launch_update_single_t<32, 8>(g, u, ready, calls, st);
 }
 
 cudaError_t lm_launch_export_rows(const double* P, const double* mu, int64_t ld, int row_begin, int row_end,

@@ -100,6 +100,7 @@ struct LmMultiArgs {
   double* K;    // [m][2][ldw]: K_u[:,0] at K + 2u ldw, K_u[:,1] at K + (2u+1) ldw
   double* A;    // [m][2][ldw]: AHt_u, same indexing (Joseph form only)
   int joseph;   // 1: one-pass Joseph form (whole matrix on one GPU only)
+  int variant;  // tiling of the streaming kernel: 0 = 32-row tiles, 1 = 16-row tiles
   double* W;    // [m][2][ldw]: (H P)_u rows, same indexing
   double* y;    // [m][2] innovations
   double* KR;   // [m][LM_MAX_ROWS][2] K_u at the exchanged rows R = {0,1,2} U {j_u, j_u+1} (replicated on every rank)
@@ -139,7 +140,7 @@ cudaError_t lm_launch_predict(double* mu, double* P, int64_t ld, int n, int row_
 cudaError_t lm_launch_gather(const LmGatherArgs& a, cudaStream_t st);
 cudaError_t lm_launch_update(const LmUpdateArgs& a, bool joseph, int variant, cudaStream_t st);
 // gather + streaming update in ONE launch (plain form); ready: device u64 counter, calls: host count of such launches
-cudaError_t lm_launch_update_single(const LmGatherArgs& g, const LmUpdateArgs& u, unsigned long long* ready,
+cudaError_t lm_launch_update_single(const LmGatherArgs& g, const LmUpdateArgs& u, int variant, unsigned long long* ready,
                                     unsigned long long* calls, cudaStream_t st);
 cudaError_t lm_launch_export_rows(const double* P, const double* mu, int64_t ld, int row_begin, int row_end,
                                   int j, double* rows5, int64_t ldx, cudaStream_t st);

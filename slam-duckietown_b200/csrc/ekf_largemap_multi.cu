@@ -433,9 +433,9 @@ cudaError_t lm_launch_export_rows_multi(const LmMultiArgs& a, double* rows, cuda
   return cudaGetLastError();
 }
 
-template <int M, bool JOSEPH>
-static cudaError_t launch_multi_t(const LmMultiArgs& a, cudaStream_t st) {
-  constexpr int RB = 32, UNROLL = JOSEPH ? 4 : 8;
+template <int M, bool JOSEPH, int RB>
+static cudaError_t launch_multi_rb(const LmMultiArgs& a, cudaStream_t st) {
+  constexpr int UNROLL = JOSEPH ? 4 : 8;
   const int rows = a.row_end - a.row_begin;
   if (rows <= 0) return cudaSuccess;
   dim3 grid(a.full_tiles + (a.tail_groups ? 1 : 0), (rows + RB - 1) / RB);
@@ -444,6 +444,13 @@ static cudaError_t launch_multi_t(const LmMultiArgs& a, cudaStream_t st) {
       return launch_pdl(lm_rank_update_multi_kernel<RB, UNROLL, M, true, false>, grid, dim3(LM_THREADS), 0, st, a);
   }
   return launch_pdl(lm_rank_update_multi_kernel<RB, UNROLL, M, false, JOSEPH>, grid, dim3(LM_THREADS), 0, st, a);
+}
+
+// variant 1: 16-row tiles for row blocks that fit L2 (see ekf_lm_bind_state), else 32-row tiles
+template <int M, bool JOSEPH>
+static cudaError_t launch_multi_t(const LmMultiArgs& a, cudaStream_t st) {
+  if (a.variant == 1) return launch_multi_rb<M, JOSEPH, 16>(a, st);
+  return launch_multi_rb<M, JOSEPH, 32>(a, st);
 }
 
 template <int M, bool JOSEPH>
