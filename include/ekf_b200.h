@@ -139,6 +139,19 @@ int ekf_batch_moments(ekf_batch_t* h, double* sums_dev, void* stream);
 /* the same for the robot pose only: sums_dev[0..2] = sum_b (x, y, theta), sums_dev[3 + 3 i + k] = sum_b pose_i pose_k
  * (12 doubles) — the per-step result of a Monte Carlo replay (mean trajectory and its spread)                  */
 int ekf_batch_pose_moments(ekf_batch_t* h, double* sums_dev, void* stream);
+/* NO COUNTERPART IN THE REFERENCE: added for callers that may not allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). The result of
+ * ekf_batch_pose_moments — bit for bit, same kernels and summation order — for batch records of mu_stride doubles
+ * at mu_dev (record b starts with x, y, theta at mu_dev + b * mu_stride), 12 doubles into sums_dev, on `device`
+ * and `stream`. Takes no handle and calls no cudaMalloc / cudaFree / allocating routine: the per-CTA partial sums
+ * live in a file-scope device array of 592 x 9 doubles (42,624 bytes) that every GPU loading the library holds until
+ * exit. Limit: batch <= EKF_POSE_MOMENTS_NOALLOC_MAX_FILTERS, beyond it EKF_EINVAL. All calls on one device share
+ * the array (it keeps the last call's contents; every slot a call reads it has written itself, so nothing needs
+ * clearing): calls that OVERLAP on the GPU (different streams, or graphs replayed concurrently) race — serialise
+ * them. The first call on a device resolves the array's address (cudaGetSymbolAddress); make it before capture. */
+#define EKF_POSE_MOMENTS_NOALLOC_MAX_FILTERS 4194304
+int ekf_pose_moments_noalloc(const double* mu_dev, int64_t mu_stride, int64_t batch, double* sums_dev, int device,
+                             void* stream);
 
 /* ---- Monte Carlo perturbations generated ON the device ---------------------------------------------------------
  * The batched mode replays ONE common trajectory per ensemble member with member-specific perturbations (north star:

@@ -64,6 +64,7 @@ SIGNATURES = {
     "ekf_batch_accumulate_ate": (_i, [_p, _d, _d, _p, _p]),
     "ekf_batch_moments": (_i, [_p, _p, _p]),
     "ekf_batch_pose_moments": (_i, [_p, _p, _p]),
+    "ekf_pose_moments_noalloc": (_i, [_p, _l, _l, _p, _i, _p]),
     "ekf_batch_mc_record_doubles": (_i, [_i, C.POINTER(_l)]),
     "ekf_batch_perturb": (_i, [_p, _u64, _u64, _u64, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
     "ekf_batch_step_generated": (_i, [_p, _u64, _u64, _u64, _i, _p, _p, _p]),

@@ -546,6 +546,18 @@ int ekf_batch_pose_moments(ekf_batch_t* h, double* sums_dev, void* stream) {
   return EKF_OK;
 }
 
+int ekf_pose_moments_noalloc(const double* mu_dev, int64_t mu_stride, int64_t batch, double* sums_dev, int device,
+                             void* stream) {
+  if (!mu_dev || !sums_dev) return fail(EKF_EINVAL, "null argument");
+  if (mu_stride < 3) return fail(EKF_EINVAL, "mu_stride < 3 (a record starts with x, y, theta)");
+  if (batch < 1) return fail(EKF_EINVAL, "batch < 1");
+  if (batch > ekf::POSE_MOM_STATIC_MAX_FILTERS)
+    return fail(EKF_EINVAL, "ekf_pose_moments_noalloc: batch exceeds EKF_POSE_MOMENTS_NOALLOC_MAX_FILTERS (4194304); "
+                            "use ekf_batch_pose_moments or split the call");
+  CU(ekf::batch_launch_pose_moments_static(mu_dev, mu_stride, batch, sums_dev, device, (cudaStream_t)stream));
+  return EKF_OK;
+}
+
 int ekf_batch_mc_step_host_async(ekf_batch_t* h, uint64_t seed, uint64_t step, uint64_t first_filter, int m,
                                  const double* record_host, const double* sigma4, int score, double gt_x, double gt_y,
                                  double* sse_dev, double* pose_moments_host, void* stream) {

@@ -12,6 +12,8 @@
 // One THREAD per filter: the work per filter is a few dozen scalar operations; every per-filter array is laid out
 // [item][B] so that consecutive threads touch consecutive addresses (coalesced), except the [B][m] output block,
 // whose layout is the step kernel's.
+#include <mutex>
+
 #include "ekf_common.cuh"
 #include "ekf_ensemble.h"
 #include "ekf_philox.cuh"
@@ -308,6 +310,42 @@ cudaError_t batch_launch_pose_moments(const double* mu, int64_t mu_stride, int64
   if (e != cudaSuccess) return e;
   batch_pose_moments_final_kernel<<<1, 288, 0, st>>>(partial, ctas, sums);
   return cudaGetLastError();
+}
+
+// -------------------------------------------------------------------------------------------------------
+// The same two passes with the per-CTA partials in a file-scope device array instead of a cudaMalloc'ed buffer, for
+// callers that may not allocate (CUDA graph capture, serving loops). Every GPU that loads the library holds the
+// array (POSE_MOM_CTAS x 9 doubles = 42,624 bytes) until exit. In HOST code `g_pose_partial_static` is only a
+// stand-in for the symbol: its device address is resolved once per device with cudaGetSymbolAddress (that device
+// current) and cached; the kernels get the resolved pointer. All calls on a device share the array: pass 2 reads
+// only the slots pass 1 of the same call wrote, so nothing needs clearing, but calls that overlap on the GPU race.
+// -------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_pose_partial_static[POSE_MOM_CTAS * 9];
+
+namespace {
+constexpr int kMaxStaticDevices = 64;
+std::mutex g_static_mu;
+double* g_pose_partial_addr[kMaxStaticDevices] = {};
+}  // namespace
+
+cudaError_t batch_launch_pose_moments_static(const double* mu, int64_t mu_stride, int64_t batch, double* sums,
+                                             int device, cudaStream_t st) {
+  if (device < 0 || device >= kMaxStaticDevices) return cudaErrorInvalidDevice;
+  if (batch < 1 || batch > POSE_MOM_STATIC_MAX_FILTERS) return cudaErrorInvalidValue;
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return e;
+  double* partial = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_pose_partial_addr[device]) {
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_pose_partial_static);  // this device's copy of the array
+      if (e != cudaSuccess) return e;
+      g_pose_partial_addr[device] = static_cast<double*>(p);
+    }
+    partial = g_pose_partial_addr[device];
+  }
+  return batch_launch_pose_moments(mu, mu_stride, batch, partial, sums, st);
 }
 
 cudaError_t batch_launch_associate(const AssocArgs& a, cudaStream_t st) {

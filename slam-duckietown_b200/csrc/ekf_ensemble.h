@@ -54,6 +54,11 @@ cudaError_t batch_launch_detection_noise(int64_t batch, uint64_t seed, uint64_t 
 constexpr int POSE_MOM_CTAS = 592;  // 4 x 148 SMs
 cudaError_t batch_launch_pose_moments(const double* mu, int64_t mu_stride, int64_t batch, double* partial, double* sums,
                                       cudaStream_t st);
+// the same result with the partials in a file-scope device array (no allocation anywhere on the path); at most
+// POSE_MOM_STATIC_MAX_FILTERS filters per call; calls on one device share the array and must not overlap
+constexpr int64_t POSE_MOM_STATIC_MAX_FILTERS = int64_t(1) << 22;
+cudaError_t batch_launch_pose_moments_static(const double* mu, int64_t mu_stride, int64_t batch, double* sums,
+                                             int device, cudaStream_t st);
 constexpr int MOM_CTAS = 592;  // 4 x 148 SMs: partial sums of the ensemble moments
 // sums[n + n*n] = (sum_b mu_b, sum_b mu_b mu_b^T) in a fixed order; partial: scratch [MOM_CTAS][n + n*n]
 cudaError_t batch_launch_moments(const double* mu, int64_t mu_stride, int64_t batch, int n, double* partial,
