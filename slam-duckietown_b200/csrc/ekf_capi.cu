@@ -89,7 +89,6 @@ struct ekf_lm {
   double* p2p_peer_host[ekf::P2P_MAX_WORLD] = {};
   bool p2p_opened[ekf::P2P_MAX_WORLD] = {};
   double** p2p_peers_dev = nullptr;
-  unsigned* p2p_push_count = nullptr;
   unsigned long long* p2p_err = nullptr;
   unsigned long long p2p_seq = 0;
   unsigned long long p2p_robot_seq = 0;  // update number whose buffer already holds rows 0-2 (pre-pushed by rank 0)
@@ -763,7 +762,6 @@ int ekf_lm_destroy(ekf_lm_t* h) {
     if (h->p2p_opened[r]) cudaIpcCloseMemHandle(h->p2p_peer_host[r]);
   cudaFree(h->p2p_area);
   cudaFree(h->p2p_peers_dev);
-  cudaFree(h->p2p_push_count);
   cudaFree(h->p2p_err);
   cudaFree(h->K0);
   delete h;
@@ -849,10 +847,11 @@ int ekf_lm_augment(ekf_lm_t* h, int slot, double gx, double gy, void* stream) {
   return EKF_OK;
 }
 
-// The robot rows pre-pushed for update p2p_seq + 1 have gone stale (predict, external write to P). Their flag already
-// carries the number p2p_seq + 1, so that number is BURNT: the next update takes p2p_seq + 2 and rank 0's gather pushes
-// fresh rows under it — a waiter can never mistake the stale push for the fresh one. Every rank makes the same calls
-// in the same order, so the numbering stays in step; acks and flags are compared with >=, so a skipped number is fine.
+// The robot rows pre-pushed for update p2p_seq + 1 have gone stale (predict, external write to P). Their cells already
+// carry the tag p2p_seq + 1, so that number is BURNT: the next update takes p2p_seq + 2 and rank 0's gather pushes
+// fresh rows under it — a consumer can never mistake the stale push for the fresh one (tags are matched exactly).
+// Every rank makes the same calls in the same order, so the numbering stays in step; acks are compared with >=, so a
+// skipped number is fine.
 static void p2p_drop_prepush(ekf_lm_t* h) {
   if (h->p2p_robot_seq != 0 && h->p2p_robot_seq == h->p2p_seq + 1) ++h->p2p_seq;
   h->p2p_robot_seq = 0;
@@ -869,17 +868,17 @@ int ekf_lm_predict(ekf_lm_t* h, double ang, double lin, void* stream) {
 }
 
 // exchange descriptor of update / step number `seq` of this handle's peer-memory exchange
-static int64_t p2p_flag_off(const ekf_lm* h) { return 2 * ekf::P2P_ROWS * (h->ld + 4); }
-static int64_t p2p_area_doubles(const ekf_lm* h) { return p2p_flag_off(h) + 2 * ekf::P2P_PARTS + ekf::P2P_MAX_WORLD; }
+// area = [2][P2P_ROWS][ld + 4] 16-byte cells (two doubles each), then the ack words (ekf_largemap.h)
+static int64_t p2p_flag_off(const ekf_lm* h) { return 2 * ekf::P2P_ROWS * (h->ld + 4) * 2; }
+static int64_t p2p_area_doubles(const ekf_lm* h) { return p2p_flag_off(h) + ekf::P2P_MAX_WORLD; }
 
 static ekf::LmExchange p2p_exchange(ekf_lm_t* h, unsigned long long seq) {
   ekf::LmExchange x{};
   x.peers = h->p2p_peers_dev;
   x.ldx = h->ld + 4;
   x.flag_off = p2p_flag_off(h);
-  x.acks = reinterpret_cast<unsigned long long*>(h->p2p_area + x.flag_off) + 2 * ekf::P2P_PARTS;
+  x.acks = reinterpret_cast<unsigned long long*>(h->p2p_area + x.flag_off);
   x.err = h->p2p_err;
-  x.count = h->p2p_push_count;
   x.seq = seq;
   x.world = h->p2p_world;
   x.rank = h->p2p_rank;
@@ -905,12 +904,13 @@ static int lm_update_impl_split(ekf_lm_t* h, int slot, double rng, double brg, c
   ekf::LmGatherArgs g{};
   ekf::LmUpdateArgs u{};
   g.P = h->P;
-  const int64_t ldx = h->ld + 4;
+  int64_t ldx = h->ld + 4, mu_off = h->ld;  // replicated rows buffer: plain doubles, mu entry at column ld
   if (p2p) {
     const unsigned long long seq = ++h->p2p_seq;
     g.x = u.x = p2p_exchange(h, seq);
+    ldx = 2 * (h->ld + 4);  // exchange buffer: 16-byte cells
+    mu_off = 2 * h->ld;
     rows5 = h->p2p_area + (int64_t)(seq & 1) * ekf::P2P_ROWS * ldx;
-    g.wait_flags = reinterpret_cast<const unsigned long long*>(h->p2p_area + g.x.flag_off) + (seq & 1) * ekf::P2P_PARTS;
     const bool robot_there = (h->p2p_robot_seq == seq);  // pre-pushed by rank 0's previous streaming kernel
     if (h->p2p_rank == 0) {
       if (!robot_there) g.push_mask |= 1;
@@ -925,7 +925,7 @@ static int lm_update_impl_split(ekf_lm_t* h, int slot, double rng, double brg, c
     const bool own = idx5[k] >= h->row_begin && idx5[k] < h->row_end;
     if (rows5 && !(p2p && own)) {
       g.row[k] = rows5 + k * ldx;
-      g.mu5[k] = rows5 + k * ldx + h->ld;
+      g.mu5[k] = rows5 + k * ldx + mu_off;
     } else {
       g.row[k] = h->P + (int64_t)(idx5[k] - h->row_begin) * h->ld;
       g.mu5[k] = h->mu + idx5[k];
@@ -952,9 +952,9 @@ static int lm_update_impl_split(ekf_lm_t* h, int slot, double rng, double brg, c
   u.row_end = h->row_end;
   if (!joseph && h->variant <= 1 && h->single_launch && !p2p) {
     // ONE launch: the leading CTAs run the gather, the streaming tiles pre-load their first rows and wait for it.
-    // Not with the peer-memory exchange: measured no gain there (4096 landmarks on 8 GPUs: 0.0419 vs 0.0403 ms) and,
-    // at 32 768 landmarks, one rank's flag wait of the very first update ran into its 2 s budget (results intact; cause
-    // not found: gpurun_out r2j, 4 GPUs) — the sharded update keeps its two PDL-chained launches.
+    // Not with the peer-memory exchange: measured no gain there with the flag protocol of the time (4096 landmarks on
+    // 8 GPUs: 0.0419 vs 0.0403 ms) and, at 32 768 landmarks, one rank's wait of the very first update ran into its
+    // 2 s budget (results intact; cause not found) — the sharded update keeps its two PDL-chained launches.
     CU(ekf::lm_launch_update_single(g, u, h->variant, reinterpret_cast<unsigned long long*>(h->scal + ekf::kScalReady),
                                     &h->single_calls, (cudaStream_t)stream));
     return EKF_OK;
@@ -987,8 +987,10 @@ static int lm_multi_check(ekf_lm_t* h, int m, const int32_t* slots_host, const d
 
 // xrows: exchanged rows of a row-block shard ([3 + 2g][ldx]); own_local: rows this rank owns are read from its own P
 // (peer-memory exchange: owners do not push to themselves), otherwise every row comes from xrows (replicated buffer)
+// (those xrows are then the 16-byte cells of the exchange buffer, not plain doubles)
 static void lm_multi_fill(ekf_lm_t* h, ekf::LmMultiArgs& a, int g, const int32_t* slots, const double* rng,
                           const double* brg, const double* xrows, bool own_local = false) {
+  const int64_t xscale = own_local ? 2 : 1;
   a.P = h->P; a.mu = h->mu; a.K = h->mK; a.W = h->mW; a.A = h->mA; a.y = h->my; a.KR = h->mKR;
   a.xrows = xrows;
   a.ld = h->ld; a.ldw = h->ldw; a.ldx = h->ld + 4;
@@ -1003,8 +1005,8 @@ static void lm_multi_fill(ekf_lm_t* h, ekf::LmMultiArgs& a, int g, const int32_t
     const int row = rho < 3 ? rho : a.j[(rho - 3) >> 1] + ((rho - 3) & 1);
     const bool own = row >= h->row_begin && row < h->row_end;
     if (xrows && !(own_local && own)) {
-      a.rowp[rho] = xrows + (int64_t)rho * a.ldx;
-      a.mup[rho] = a.rowp[rho] + h->ld;
+      a.rowp[rho] = xrows + (int64_t)rho * a.ldx * xscale;
+      a.mup[rho] = a.rowp[rho] + h->ld * xscale;
     } else {
       a.rowp[rho] = h->P + (int64_t)(row - h->row_begin) * h->ld;
       a.mup[rho] = h->mu + row;
@@ -1098,8 +1100,6 @@ int ekf_lm_p2p_init(ekf_lm_t* h, int world, int rank, unsigned char* handle_out,
   CU(cudaMalloc(&h->p2p_area, bytes));
   CU(cudaMemset(h->p2p_area, 0, bytes));
   CU(cudaMalloc(&h->p2p_peers_dev, ekf::P2P_MAX_WORLD * sizeof(double*)));
-  CU(cudaMalloc(&h->p2p_push_count, ekf::P2P_MAX_WORLD * sizeof(unsigned)));
-  CU(cudaMemset(h->p2p_push_count, 0, ekf::P2P_MAX_WORLD * sizeof(unsigned)));
   CU(cudaMalloc(&h->p2p_err, sizeof(unsigned long long)));
   CU(cudaMemset(h->p2p_err, 0, sizeof(unsigned long long)));
   cudaIpcMemHandle_t hd;
@@ -1181,9 +1181,8 @@ int ekf_lm_p2p_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const
   const unsigned long long seq = ++h->p2p_seq;
   ekf::LmMultiArgs g{};
   lm_multi_fill(h, g, m, slots_host, rng_host, brg_host,
-                h->p2p_area + (int64_t)(seq & 1) * ekf::P2P_ROWS * (h->ld + 4), /*own_local=*/true);
+                h->p2p_area + (int64_t)(seq & 1) * ekf::P2P_ROWS * (h->ld + 4) * 2, /*own_local=*/true);
   g.x = p2p_exchange(h, seq);
-  g.wait_flags = reinterpret_cast<const unsigned long long*>(h->p2p_area + g.x.flag_off) + (seq & 1) * ekf::P2P_PARTS;
   const bool robot_there = (h->p2p_robot_seq == seq);
   if (h->p2p_rank == 0) {
     if (!robot_there) g.push_mask |= 1;

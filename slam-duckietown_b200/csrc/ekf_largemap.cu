@@ -19,6 +19,21 @@
 // streaming kernel `lm_rank_update_kernel` moves the 16 n^2 with 256-bit loads/stores.
 #include "ekf_common.cuh"
 #include "ekf_largemap.h"
+
+#ifdef EKF_LM_TIMELINE
+// Diagnostic build only (make timeline -> libekf_b200_tl.so, tools/lm_p2p_timeline.py): globaltimer stamps of the
+// phases of the sharded single update, indexed by the update's sequence number. Never compiled into libekf_b200.so.
+namespace ekf {
+__device__ unsigned long long g_lm_tl[256][10];
+__device__ __forceinline__ unsigned long long lm_gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+}  // namespace ekf
+#define EKF_TL(seq, k) (ekf::g_lm_tl[(seq) & 255][k] = ekf::lm_gtime())
+#define EKF_TLMAX(seq, k) atomicMax(&ekf::g_lm_tl[(seq) & 255][k], ekf::lm_gtime())
+#endif
 #include "ekf_largemap_p2p.cuh"
 
 namespace ekf {
@@ -126,6 +141,7 @@ __device__ __forceinline__ void lm_gather_body(const LmGatherArgs& a, int bid, i
   __shared__ double ssi[2][2];
   __shared__ double ssq[2][2];  // S - Q
   __shared__ double sy[2];
+  __shared__ double sb5[5][5], sm5[5];  // P[idx5, idx5], mu[idx5]
   const int j = a.j;
   const int idx5[5] = {0, 1, 2, j, j + 1};
   const int t = bid * blockDim.x + threadIdx.x;
@@ -136,42 +152,57 @@ __device__ __forceinline__ void lm_gather_body(const LmGatherArgs& a, int bid, i
   double pr[5], pc[5];
 #pragma unroll
   for (int k = 0; k < 5; ++k) pc[k] = local ? a.P[(int64_t)(t - a.row_begin) * a.ld + idx5[k]] : 0.0;
-  if (a.x.peers) {
-    // peer-memory exchange inside this kernel (LmExchange, ekf_largemap.h): owners push their rows first ...
-    if (a.push_mask) {
-      if (threadIdx.x == 0) x_wait_acks(a.x, a.x.seq > 2 ? a.x.seq - 2 : 0);
-      __syncthreads();
+  const bool tl = a.x.peers && bid == 0 && threadIdx.x == 0;
+  if (tl) EKF_TL(a.x.seq, 0);
+  // which of the two row parts (0: rows 0-2, 1: rows j, j+1) are read as cells of the exchange buffer
+  const bool ll0 = a.x.peers && (a.wait_mask & 1), ll1 = a.x.peers && (a.wait_mask & 2);
+  if (a.x.peers && a.push_mask) {
+    // peer-memory exchange inside this kernel (LmExchange, ekf_largemap.h): the owner stores its rows as tagged
+    // cells into every peer's buffer; nothing to publish, the consumers poll the cells themselves
+    if (threadIdx.x < 32) x_wait_acks(a.x, a.x.seq > 2 ? a.x.seq - 2 : 0);
+    __syncthreads();
+    if (tl) EKF_TL(a.x.seq, 1);
 #pragma unroll
-      for (int k = 0; k < 5; ++k) {
-        if (!((a.push_mask >> (k < 3 ? 0 : 1)) & 1)) continue;
-        const double v = live ? a.row[k][t] : 0.0;                     // a.row[k] points into this rank's own P
-        const double m = (t == 0) ? *a.mu5[k] : 0.0;
-        for (int d = 0; d < a.x.world; ++d) {
-          if (d == a.x.rank) continue;
-          double* dst = x_row(a.x.peers[d], a.x, a.x.seq, k);
-          if (live) dst[t] = v;
-          if (t == 0) dst[a.ld] = m;
-        }
+    for (int k = 0; k < 5; ++k) {
+      if (!((a.push_mask >> (k < 3 ? 0 : 1)) & 1)) continue;
+      const double v = live ? a.row[k][t] : 0.0;                     // a.row[k] points into this rank's own P
+      const double m = (t == 0) ? *a.mu5[k] : 0.0;
+      for (int d = 0; d < a.x.world; ++d) {
+        if (d == a.x.rank) continue;
+        double* dst = x_row(a.x.peers[d], a.x, a.x.seq, k);
+        if (live) ll_store(dst, t, v, a.x.seq);
+        if (t == 0) ll_store(dst, a.ld, m, a.x.seq);
       }
-      x_publish(a.x, a.x.count, (unsigned)nblocks, a.x.seq, (unsigned)a.push_mask);
     }
-    // ... then everyone waits for the parts that come from a peer
-    if (a.wait_mask) {
-      if (threadIdx.x == 0) x_wait_parts(a.x, a.wait_flags, (unsigned)a.wait_mask);
-      __syncthreads();
-    }
+    if (tl) EKF_TL(a.x.seq, 2);
   }
+  // the 25 entries P[idx5, idx5] and the 5 mu entries every CTA's scalar chain needs: one per lane of warp 0
+  if (threadIdx.x < 30) {
+    const int k = threadIdx.x < 25 ? threadIdx.x / 5 : threadIdx.x - 25;
+    const bool ll = k < 3 ? ll0 : ll1;
+    if (threadIdx.x < 25) sb5[k][threadIdx.x - 5 * k] = x_read(a.row[k], idx5[threadIdx.x - 5 * k], ll, a.x);
+    else sm5[k] = x_read(a.mu5[k], 0, ll, a.x);
+  }
+  {  // this thread's column of the five rows: all five requests in flight before the first is examined
+    LLRaw raw[5];
 #pragma unroll
-  for (int k = 0; k < 5; ++k) pr[k] = live ? a.row[k][t] : 0.0;
+    for (int k = 0; k < 5; ++k)
+      if (live && (k < 3 ? ll0 : ll1)) raw[k] = ll_peek(a.row[k], t);
+#pragma unroll
+    for (int k = 0; k < 5; ++k)
+      pr[k] = !live ? 0.0 : (k < 3 ? ll0 : ll1) ? ll_resolve(raw[k], a.row[k], t, a.x.seq, a.x.err) : a.row[k][t];
+  }
+  __syncthreads();
+  if (tl) EKF_TL(a.x.seq, 3);
   if (threadIdx.x == 0) {
-    const Innov in = innovation(*a.mu5[0], *a.mu5[1], *a.mu5[2], *a.mu5[3], *a.mu5[4], a.rng, a.brg);
+    const Innov in = innovation(sm5[0], sm5[1], sm5[2], sm5[3], sm5[4], a.rng, a.brg);
     double hp5[2][5];
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
       double s0 = 0.0, s1 = 0.0;
 #pragma unroll
       for (int k = 0; k < 5; ++k) {
-        const double p = a.row[k][idx5[c]];
+        const double p = sb5[k][c];
         s0 = fma(in.h[0][k], p, s0);
         s1 = fma(in.h[1][k], p, s1);
       }
@@ -206,6 +237,7 @@ __device__ __forceinline__ void lm_gather_body(const LmGatherArgs& a, int bid, i
       a.scal[kScalY0] = in.y0;
       a.scal[kScalY1] = in.y1;
     }
+    if (tl) EKF_TL(a.x.seq, 4);
   }
   __syncthreads();
   if (!live) return;
@@ -216,7 +248,7 @@ __device__ __forceinline__ void lm_gather_body(const LmGatherArgs& a, int bid, i
     double ph0 = 0.0, ph1 = 0.0;
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
-      const double p = a.row[t][idx5[k]];
+      const double p = sb5[t][k];  // == a.row[t][idx5[k]]
       ph0 = fma(p, sh[0][k], ph0);
       ph1 = fma(p, sh[1][k], ph1);
     }
@@ -253,6 +285,7 @@ __device__ __forceinline__ void lm_gather_body(const LmGatherArgs& a, int bid, i
     a.W0[t] = hp0;
     a.W1[t] = hp1;
   }
+  if (a.x.peers && threadIdx.x == 0) EKF_TLMAX(a.x.seq, 5);
 }
 
 __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
@@ -270,10 +303,15 @@ __global__ void __launch_bounds__(256) lm_gather_kernel(LmGatherArgs a) {
 // are done by an extra column of CTAs with a (row, group) mapping. CTAs of column tile 0 also apply
 // mu += K y for their rows.
 // -------------------------------------------------------------------------------------------------------
-// push of rows 0-2 (just updated, still in registers) into every peer's buffer of the NEXT update: 256-bit stores
+// push of rows 0-2 (just updated, still in registers) into every peer's buffer of the NEXT update: tagged cells,
+// two per 256-bit store
 __device__ __forceinline__ void x_prepush4(const LmExchange& x, int row, int c, const double4x& v) {
-  for (int d = 0; d < x.world; ++d)
-    if (d != x.rank) stg256(x_row(x.peers[d], x, x.seq + 1, row) + c, v);
+  for (int d = 0; d < x.world; ++d) {
+    if (d == x.rank) continue;
+    double* dst = x_row(x.peers[d], x, x.seq + 1, row);
+    ll_store2(dst, c, v.a, v.b, x.seq + 1);
+    ll_store2(dst, c + 2, v.c, v.d, x.seq + 1);
+  }
 }
 
 // PRE: rank 0 of a peer-memory exchange — row tile 0 also pushes the updated robot rows (see LmExchange)
@@ -308,9 +346,12 @@ __device__ __forceinline__ void lm_rank_update_body(const LmUpdateArgs& a, int b
     __syncthreads();
   }
   // the gather of this update is complete on this rank: its exchange buffer is no longer read here
-  if (a.x.peers && bx == 0 && by == 0) x_ack(a.x);
+  if (a.x.peers && bx == 0 && by == 0) {
+    if (tid == 0) EKF_TL(a.x.seq, 6);
+    x_ack(a.x);
+  }
   if (pre) {  // the buffer of update seq + 1 was last read by the gathers of update seq - 1
-    if (tid == 0) x_wait_acks(a.x, a.x.seq > 1 ? a.x.seq - 1 : 0, 2);
+    if (tid < 32) x_wait_acks(a.x, a.x.seq > 1 ? a.x.seq - 1 : 0, 2);
     __syncthreads();
   }
   for (int r = tid; r < nrows; r += LM_THREADS) {
@@ -329,7 +370,7 @@ __device__ __forceinline__ void lm_rank_update_body(const LmUpdateArgs& a, int b
       a.mu[r0 + r] = m;
       if (pre && r < 3)  // r0 == 0 here: the pose entries ride at column ld of the pushed rows
         for (int d = 0; d < a.x.world; ++d)
-          if (d != a.x.rank) x_row(a.x.peers[d], a.x, a.x.seq + 1, r)[a.ld] = m;
+          if (d != a.x.rank) ll_store(x_row(a.x.peers[d], a.x, a.x.seq + 1, r), a.ld, m, a.x.seq + 1);
     }
   }
   if (bx < a.full_tiles) {
@@ -410,7 +451,8 @@ __device__ __forceinline__ void lm_rank_update_body(const LmUpdateArgs& a, int b
       if (pre && r < 3) x_prepush4(a.x, r, c, v);
     }
   }
-  if (pre) x_publish(a.x, a.x.count + kPrepushCounter, (unsigned)nbx, a.x.seq + 1, 1u);
+  if (pre && bx == 0 && tid == 0) EKF_TL(a.x.seq, 8);
+  if (a.x.peers && tid == 0) EKF_TLMAX(a.x.seq, 7);
 }
 
 
@@ -541,6 +583,20 @@ cudaError_t lm_launch_update_single(const LmGatherArgs& g, const LmUpdateArgs& u
   if (variant == 1) return launch_update_single_t<16, 8>(g, u, ready, calls, st);
   return launch_update_single_t<32, 8>(g, u, ready, calls, st);
 }
+
+#ifdef EKF_LM_TIMELINE
+}  // namespace ekf
+extern "C" int ekf_lm_debug_timeline(unsigned long long* out_host, int clear) {
+  if (out_host && cudaMemcpyFromSymbol(out_host, ekf::g_lm_tl, sizeof(ekf::g_lm_tl)) != cudaSuccess) return -1;
+  if (clear) {
+    void* p = nullptr;
+    if (cudaGetSymbolAddress(&p, ekf::g_lm_tl) != cudaSuccess) return -1;
+    if (cudaMemset(p, 0, sizeof(ekf::g_lm_tl)) != cudaSuccess) return -1;
+  }
+  return 0;
+}
+namespace ekf {
+#endif
 
 cudaError_t lm_launch_export_rows(const double* P, const double* mu, int64_t ld, int row_begin, int row_end,
                                   int j, double* rows5, int64_t ldx, cudaStream_t st) {

@@ -42,20 +42,21 @@ enum : int { kScalG0 = 0, kScalG1 = 1, kScalY0 = 2, kScalY1 = 3, kScalArrive = 6
 
 // Peer-memory row exchange, folded into the update's own kernels (round 2; round 1 launched a separate push kernel
 // per row part: 14.8 us per update against a 17 us streaming pass at 8 GPUs, profiles/r1o_lm_launches.summary.txt).
-//   * landmark rows {j, j+1}: the OWNER's gather kernel pushes them (+ their mu entries) to every peer at its head
-//     (CTA b = column chunk b), publishes the part's flag from its last CTA, and itself reads the rows from its own P;
-//   * robot rows {0, 1, 2}: rank 0's STREAMING kernel of update s pushes the rows it has just brought up to date
-//     (row tile 0, from registers) into the buffer of update s + 1 and publishes that flag — the next gather finds
-//     three of its five rows already there. A predict (or an external write to P) in between invalidates the
-//     pre-push; rank 0's next gather then pushes the robot rows itself, like a landmark part.
-// The buffer of update s is s & 1; a push into it first waits (in the pushing CTA) until every rank has acknowledged
-// the gather of update s - 2 (landmark part) resp. s - 1 (pre-push into the buffer of s + 1).
+//   * landmark rows {j, j+1}: the OWNER's gather kernel stores them (+ their mu entries) into every peer's buffer at
+//     its head (CTA b = column chunk b) and itself reads the rows from its own P;
+//   * robot rows {0, 1, 2}: rank 0's STREAMING kernel of update s stores the rows it has just brought up to date
+//     (row tile 0, from registers) into the buffer of update s + 1 — the next gather finds three of its five rows
+//     already there. A predict (or an external write to P) in between invalidates the pre-push; rank 0's next gather
+//     then pushes the robot rows itself, like a landmark part.
+// Rows travel as 16-byte cells that carry the update's sequence number next to each half of the value; consumers
+// poll the cells they need (ekf_largemap_p2p.cuh): no flags, no fences. The buffer of update s is s & 1; a push into
+// it first checks (warp 0 of the pushing CTA) that every rank has acknowledged the gather of update s - 2 (landmark
+// part) resp. s - 1 (pre-push into the buffer of s + 1).
 struct LmExchange {
   double* const* peers;          // device array [world]: every rank's exchange area; null = no exchange
   unsigned long long* acks;      // this rank's ack words [world] (local memory)
-  unsigned long long* err;       // set to 1 when a spin ran out of budget
-  unsigned* count;               // device CTA counters [P2P_PARTS] of the in-kernel pushes
-  int64_t ldx, flag_off;
+  unsigned long long* err;       // code << 32 | sequence number of a spin that ran out of budget
+  int64_t ldx, flag_off;         // cells per exchanged row; offset (doubles) of the ack words in an area
   unsigned long long seq;        // sequence number of THIS update (starts at 1)
   int world, rank;
 };
@@ -71,9 +72,9 @@ struct LmGatherArgs {
   double* mu_out;         // shard only: replicated pose entries are refreshed here
   double rng, brg, mm;
   // peer-memory exchange (x.peers != null): bit k of push_mask = this rank pushes part k (0: rows 0-2, 1: rows j, j+1)
-  // at the head of the kernel; bit k of wait_mask = part k arrives from a peer: wait for its flag before reading it
+  // at the head of the kernel; bit k of wait_mask = part k arrives from a peer: row[] / mu5[] of that part point at
+  // CELLS of the exchange buffer, which are polled for this update's tag
   LmExchange x;
-  const unsigned long long* wait_flags;  // this rank's flag words of buffer seq & 1
   int push_mask, wait_mask;
 };
 
@@ -112,7 +113,6 @@ struct LmMultiArgs {
   // 0) pushes the updated rows 0-2 for the next step. rowp / mup: where row R[rho] of the step's initial covariance and
   // its mu entry are read from — this rank's own P / mu when it owns the row, the exchange buffer otherwise.
   LmExchange x;
-  const unsigned long long* wait_flags;
   int push_mask, wait_mask, prepush;
   const double* rowp[LM_MAX_ROWS];
   const double* mup[LM_MAX_ROWS];
@@ -124,13 +124,11 @@ struct LmMultiArgs {
 cudaError_t lm_launch_update_multi(const LmMultiArgs& a, cudaStream_t st);
 cudaError_t lm_launch_export_rows_multi(const LmMultiArgs& a, double* rows, cudaStream_t st);
 
-// peer-memory row exchange of the row-block shards (ekf_largemap_p2p.cu). One exchange AREA per rank (doubles):
-//   [2][P2P_ROWS][ldx] double-buffered rows {0,1,2} U {j_u, j_u+1 : u < m} (+ mu entry at column ld), then at
-//   flag_off: u64 flags[2][P2P_PARTS] (buffer, part: 0 = robot rows, 1 + u = landmark rows of update u),
-//   u64 acks[P2P_MAX_WORLD]
+// peer-memory row exchange of the row-block shards (ekf_largemap_p2p.cuh). One exchange AREA per rank:
+//   [2][P2P_ROWS][ldx] double-buffered rows {0,1,2} U {j_u, j_u+1 : u < m} of 16-byte cells (the mu entry rides in
+//   cell ld), then at flag_off (doubles): u64 acks[P2P_MAX_WORLD]
 constexpr int P2P_MAX_WORLD = 16;
 constexpr int P2P_ROWS = 11;   // == LM_MAX_ROWS: rows of a fused step of up to 4 updates
-constexpr int P2P_PARTS = 8;   // flag words per buffer (1 + LM_MAX_FUSED used)
 // in-kernel push helpers (ekf_largemap_p2p.cuh) are shared by the gather and streaming kernels
 
 cudaError_t lm_launch_augment(double* mu, double* P, int64_t ld, int row_begin, int row_end, int j, double gx,

@@ -32,6 +32,12 @@ __device__ __forceinline__ int rho_row(const LmMultiArgs& a, int rho) {
 // row rho of the step's INITIAL covariance: this rank's own P where it owns the row, the exchange buffer otherwise
 // (a.rowp / a.mup are filled by the host; the whole matrix on one GPU: all of them point into P / mu)
 __device__ __forceinline__ const double* rho_ptr(const LmMultiArgs& a, int rho) { return a.rowp[rho]; }
+// exchange part of row rho (0: rows 0-2, 1 + u: rows j_u, j_u + 1) and whether it is read as CELLS of the exchange
+// buffer (it arrives from a peer) rather than as plain doubles (own P / replicated rows buffer)
+__device__ __forceinline__ int rho_part(int rho) { return rho < 3 ? 0 : 1 + ((rho - 3) >> 1); }
+__device__ __forceinline__ bool rho_ll(const LmMultiArgs& a, int rho) {
+  return a.x.peers && ((a.wait_mask >> rho_part(rho)) & 1);
+}
 
 // a8-a9 for ALL M updates of the step in one launch. Update u works on the covariance as it stands after updates
 // 0..u-1 (never materialised). Thread t needs, over the whole step, only column t of the exchanged rows R
@@ -73,42 +79,39 @@ __global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
 #pragma unroll
     for (int rho = 0; rho < NR; ++rho) pc0[rho] = local ? prow[rho_row(a, rho)] : 0.0;  // row t, column R[rho]
   }
-  if (a.x.peers) {  // peer-memory exchange inside this kernel: part 0 = rows 0-2, part 1 + u = rows j_u, j_u + 1
-    if (a.push_mask) {
-      if (tid == 0) x_wait_acks(a.x, a.x.seq > 2 ? a.x.seq - 2 : 0);
-      __syncthreads();
+  if (a.x.peers && a.push_mask) {  // peer-memory exchange inside this kernel: tagged cells into every peer's buffer
+    if (tid < 32) x_wait_acks(a.x, a.x.seq > 2 ? a.x.seq - 2 : 0);
+    __syncthreads();
 #pragma unroll
-      for (int rho = 0; rho < NR; ++rho) {
-        const int part = rho < 3 ? 0 : 1 + ((rho - 3) >> 1);
-        if (!((a.push_mask >> part) & 1)) continue;
-        const double v = live ? a.rowp[rho][t] : 0.0;  // this rank's own P
-        const double m = (t == 0) ? *a.mup[rho] : 0.0;
-        for (int d = 0; d < a.x.world; ++d) {
-          if (d == a.x.rank) continue;
-          double* dst = x_row(a.x.peers[d], a.x, a.x.seq, rho);
-          if (live) dst[t] = v;
-          if (t == 0) dst[a.ld] = m;
-        }
+    for (int rho = 0; rho < NR; ++rho) {
+      if (!((a.push_mask >> rho_part(rho)) & 1)) continue;
+      const double v = live ? a.rowp[rho][t] : 0.0;  // this rank's own P
+      const double m = (t == 0) ? *a.mup[rho] : 0.0;
+      for (int d = 0; d < a.x.world; ++d) {
+        if (d == a.x.rank) continue;
+        double* dst = x_row(a.x.peers[d], a.x, a.x.seq, rho);
+        if (live) ll_store(dst, t, v, a.x.seq);
+        if (t == 0) ll_store(dst, a.ld, m, a.x.seq);
       }
-      x_publish(a.x, a.x.count, gridDim.x, a.x.seq, (unsigned)a.push_mask);
-    }
-    if (a.wait_mask) {
-      if (tid == 0) x_wait_parts(a.x, a.wait_flags, (unsigned)a.wait_mask);
-      __syncthreads();
     }
   }
   if (tid < NR * NR) {
     const int r = tid / NR, c = tid - r * NR;
-    sB[r][c] = rho_ptr(a, r)[rho_row(a, c)];
+    sB[r][c] = x_read(rho_ptr(a, r), rho_row(a, c), rho_ll(a, r), a.x);
   } else if (tid >= 128 && tid < 128 + NR) {
-    // the step's initial mean: riding at column ld of the exchanged row on a shard (local copies of non-local
+    // the step's initial mean: riding in cell ld of the exchanged row on a shard (local copies of non-local
     // entries are stale there), mu itself otherwise (it is written by the streaming kernel only)
     const int rho = tid - 128;
-    smuR[rho] = *a.mup[rho];
+    smuR[rho] = x_read(a.mup[rho], 0, rho_ll(a, rho), a.x);
   }
-  if (live) {
+  if (live) {  // row R[rho], column t: every request in flight before the first is examined
+    LLRaw raw[NR];
 #pragma unroll
-    for (int rho = 0; rho < NR; ++rho) pr0[rho] = rho_ptr(a, rho)[t];  // row R[rho], column t
+    for (int rho = 0; rho < NR; ++rho)
+      if (rho_ll(a, rho)) raw[rho] = ll_peek(rho_ptr(a, rho), t);
+#pragma unroll
+    for (int rho = 0; rho < NR; ++rho)
+      pr0[rho] = rho_ll(a, rho) ? ll_resolve(raw[rho], rho_ptr(a, rho), t, a.x.seq, a.x.err) : rho_ptr(a, rho)[t];
   }
   __syncthreads();
   if (tid < 32) {
@@ -280,8 +283,12 @@ __global__ void __launch_bounds__(256) lm_gather_fused_kernel(LmMultiArgs a) {
 // groups of 4 doubles x RB rows; W_u of a thread's 4 columns stays in registers (8 M doubles), K_u of the RB rows
 // in shared memory, UNROLL rows of P in flight per thread (256-bit streaming loads, in-place 256-bit stores).
 __device__ __forceinline__ void xm_prepush4(const LmExchange& x, int row, int c, const double4x& v) {
-  for (int d = 0; d < x.world; ++d)
-    if (d != x.rank) stg256(x_row(x.peers[d], x, x.seq + 1, row) + c, v);
+  for (int d = 0; d < x.world; ++d) {
+    if (d == x.rank) continue;
+    double* dst = x_row(x.peers[d], x, x.seq + 1, row);
+    ll_store2(dst, c, v.a, v.b, x.seq + 1);
+    ll_store2(dst, c + 2, v.c, v.d, x.seq + 1);
+  }
 }
 
 // PRE: rank 0 of a peer-memory exchange — row tile 0 also pushes the updated robot rows for the NEXT step
@@ -302,7 +309,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
   if (a.x.peers && blockIdx.x == 0 && blockIdx.y == 0) x_ack(a.x);
   const bool pre = PRE && blockIdx.y == 0;
   if (pre) {
-    if (tid == 0) x_wait_acks(a.x, a.x.seq > 1 ? a.x.seq - 1 : 0, 2);
+    if (tid < 32) x_wait_acks(a.x, a.x.seq > 1 ? a.x.seq - 1 : 0, 2);
     __syncthreads();
   }
   const int r0 = a.row_begin + blockIdx.y * RB;  // first global row of this CTA
@@ -329,7 +336,7 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
       a.mu[r0 + r] = v;
       if (pre && r < 3)
         for (int d = 0; d < a.x.world; ++d)
-          if (d != a.x.rank) x_row(a.x.peers[d], a.x, a.x.seq + 1, r)[a.ld] = v;
+          if (d != a.x.rank) ll_store(x_row(a.x.peers[d], a.x, a.x.seq + 1, r), a.ld, v, a.x.seq + 1);
     }
   }
   double* __restrict__ Pblk = a.P + (int64_t)(r0 - a.row_begin) * a.ld;
@@ -411,7 +418,6 @@ __global__ void __launch_bounds__(LM_THREADS) lm_rank_update_multi_kernel(LmMult
       if (pre && r < 3) xm_prepush4(a.x, r, c, v);
     }
   }
-  if (pre) x_publish(a.x, a.x.count + kPrepushCounter, gridDim.x, a.x.seq + 1, 1u);
 }
 
 // shard export of a fused step: the locally owned ones of the rows R (and their mu entries at column ld) into the

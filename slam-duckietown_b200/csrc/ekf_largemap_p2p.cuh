@@ -3,87 +3,124 @@
 //
 // Per range-bearing update every rank needs the five rows {0, 1, 2, j, j+1} of P (and their mu entries); rows 0-2
 // live on rank 0, rows j, j+1 on owner(j). Round 1 first ran two NCCL broadcasts per update (~60 us
-// of launch + protocol latency), then a separate push kernel per row part (14.8 us per update under ncu, and 14 % of
-// pure protocol cost even at world = 1). Now there is NO extra launch: the owners' gather CTAs store their chunk of the
-// rows straight into every peer's exchange buffer through peer-mapped pointers (cudaIpc, one process per GPU) and the
-// last CTA publishes a sequence number; rank 0's streaming kernel does the same for the robot rows of the NEXT update
-// from the registers that hold them. Consumers wait on flags in their OWN memory.
-//  * ordering: data stores, __threadfence_system(), CTA barrier, then an atomic CTA count; the last CTA fences again and
-//    stores the flags (the threadfence-reduction pattern); a waiter polls with volatile loads and fences before the
-//    CTA reads the buffer;
+// of launch + protocol latency), then a separate push kernel per row part (14.8 us per update under ncu). Round 2
+// moved the stores into the update's own kernels, first with a flag protocol (data stores, __threadfence_system(),
+// CTA count, second fence, flag store; consumer: poll flag, fence): correct, but the globaltimer timeline
+// (tools/lm_p2p_timeline.py, profiles/r2t_p2p_timeline_flags.txt) showed that the two system-scope fences and the
+// flag round trip cost 8.6-11.8 us per push — 65 KB of data — and stretched rank 0's streaming kernel from 13.3 to
+// 19.5 us. Now the data carries its own validity (the LL idea of NCCL's low-latency protocol):
+//  * a row of the exchange buffer is an array of 16-byte CELLS {value.lo, tag, value.hi, tag}, tag = the low 32 bits
+//    of the update's sequence number; a cell is written with ONE 16-byte volatile store and each 8-byte half carries
+//    its own tag, so only 8-byte store atomicity over NVLink is assumed;
+//  * the producer just stores cells into every peer's buffer through peer-mapped pointers (cudaIpc, one process per
+//    GPU): no fence, no flag, no CTA counter; the consumer thread that needs an entry polls that cell with 16-byte
+//    volatile loads until both tags match. One-way store latency is all that is left on the critical path;
+//  * buffer of update s is s & 1; before overwriting it the producer checks (one lane per rank, local memory) that
+//    every rank has acknowledged the gather of update s - 2 (landmark part) resp. s - 1 (pre-push into s + 1);
 //  * every spin has a cycle budget: on expiry the kernel sets an error word and goes on instead of hanging the GPU.
 #pragma once
 #include "ekf_largemap.h"
 
+#ifndef EKF_TL  // diagnostic stamps exist only in the timeline build of ekf_largemap.cu
+#define EKF_TL(seq, k) ((void)0)
+#define EKF_TLMAX(seq, k) ((void)0)
+#endif
+
 namespace ekf {
 
 constexpr long long kSpinBudget = 4000000000LL;  // ~2 s of SM clocks
-constexpr int kPrepushCounter = P2P_PARTS;       // index of the streaming kernel's CTA counter in LmExchange::count
 
-// on expiry: err = max(err, code << 32 | the number waited for) — code 1: acks before a gather-side push, 2: acks
-// before the streaming kernel's pre-push, 3: a row part's flag
-__device__ __forceinline__ bool spin_until_ge(const volatile unsigned long long* p, unsigned long long want,
-                                              unsigned long long* err, unsigned long long code = 1) {
-  const long long t0 = clock64();
-  while (*p < want) {
-    if (clock64() - t0 > kSpinBudget) {
-      atomicMax(err, (code << 32) | (want & 0xffffffffULL));
-      return false;
-    }
-    __nanosleep(32);
-  }
-  return true;
-}
-
-// row slot k / flag word `part` of the buffer of update `seq` inside one rank's exchange area
+// cells of row slot k of the buffer of update `seq` inside one rank's exchange area (x.ldx cells per row)
 __device__ __forceinline__ double* x_row(double* area, const LmExchange& x, unsigned long long seq, int k) {
-  return area + ((int64_t)(seq & 1) * P2P_ROWS + k) * x.ldx;
-}
-__device__ __forceinline__ volatile unsigned long long* x_flag(double* area, const LmExchange& x, unsigned long long seq,
-                                                               int part) {
-  return reinterpret_cast<unsigned long long*>(area + x.flag_off) + (seq & 1) * P2P_PARTS + part;
+  return area + ((int64_t)(seq & 1) * P2P_ROWS + k) * x.ldx * 2;
 }
 
-// thread 0 of a CTA: every rank has acknowledged the gather of update `need` (so its buffer may be overwritten)
+__device__ __forceinline__ void ll_store(double* row_cells, int64_t c, double v, unsigned long long seq) {
+  const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  const unsigned tag = (unsigned)seq;
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(reinterpret_cast<uint4*>(row_cells) + c),
+               "r"((unsigned)b), "r"(tag), "r"((unsigned)(b >> 32)), "r"(tag)
+               : "memory");
+}
+
+// two adjacent cells (c even: 32-byte aligned) in one 32-byte store
+__device__ __forceinline__ void ll_store2(double* row_cells, int64_t c, double va, double vb, unsigned long long seq) {
+  const unsigned long long a = (unsigned long long)__double_as_longlong(va);
+  const unsigned long long b = (unsigned long long)__double_as_longlong(vb);
+  const unsigned long long tag = (unsigned long long)(unsigned)seq << 32;
+  asm volatile("st.volatile.global.v4.u64 [%0], {%1, %2, %3, %4};" ::"l"(reinterpret_cast<uint4*>(row_cells) + c),
+               "l"((a & 0xffffffffULL) | tag), "l"((a >> 32) | tag), "l"((b & 0xffffffffULL) | tag), "l"((b >> 32) | tag)
+               : "memory");
+}
+
+// one look at a cell (no waiting): several of these can be in flight before the first ll_resolve
+struct LLRaw {
+  unsigned lo, t0, hi, t1;
+};
+__device__ __forceinline__ LLRaw ll_peek(const double* row_cells, int64_t c) {
+  LLRaw r;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.lo), "=r"(r.t0), "=r"(r.hi), "=r"(r.t1)
+               : "l"(reinterpret_cast<const uint4*>(row_cells) + c)
+               : "memory");
+  return r;
+}
+
+// on expiry: err = max(err, 3 << 32 | tag)
+__device__ __forceinline__ double ll_load(const double* row_cells, int64_t c, unsigned long long seq,
+                                          unsigned long long* err) {
+  const uint4* p = reinterpret_cast<const uint4*>(row_cells) + c;
+  const unsigned tag = (unsigned)seq;
+  unsigned lo, t0, hi, t1;
+  long long start = 0;
+  for (int it = 0;; ++it) {
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(lo), "=r"(t0), "=r"(hi), "=r"(t1) : "l"(p) : "memory");
+    if (t0 == tag && t1 == tag) break;
+    if (it == 0) {
+      start = clock64();
+    } else if (clock64() - start > kSpinBudget) {
+      atomicMax(err, (3ULL << 32) | tag);
+      break;
+    }
+  }
+  return __longlong_as_double((long long)(((unsigned long long)hi << 32) | lo));
+}
+
+__device__ __forceinline__ double ll_resolve(const LLRaw& r, const double* row_cells, int64_t c, unsigned long long seq,
+                                             unsigned long long* err) {
+  if (r.t0 == (unsigned)seq && r.t1 == (unsigned)seq)
+    return __longlong_as_double((long long)(((unsigned long long)r.hi << 32) | r.lo));
+  return ll_load(row_cells, c, seq, err);
+}
+
+// entry c of an exchanged row: a cell of the exchange buffer (ll) or a plain double (own P / replicated rows buffer)
+__device__ __forceinline__ double x_read(const double* row, int64_t c, bool ll, const LmExchange& x) {
+  return ll ? ll_load(row, c, x.seq, x.err) : row[c];
+}
+
+// warp 0 of a CTA (all 32 lanes): every rank has acknowledged the gather of update `need`, so the buffer it read may
+// be overwritten. Lane r polls rank r's ack word (local memory). on expiry: err = max(err, code << 32 | need) —
+// code 1: before a gather-side push, 2: before the streaming kernel's pre-push
 __device__ __forceinline__ void x_wait_acks(const LmExchange& x, unsigned long long need, unsigned long long code = 1) {
-  if (need == 0) return;
-  for (int r = 0; r < x.world; ++r)
-    if (!spin_until_ge(x.acks + r, need, x.err, code)) return;
-}
-
-// After a CTA's stores into the peers' buffers: count the CTA in; the last of `total` CTAs publishes `seq` in the flag
-// words of `part_mask` (bit p = part p) of the buffer of update `seq` at every peer. Call with all threads of the CTA.
-__device__ __forceinline__ void x_publish(const LmExchange& x, unsigned* counter, unsigned total, unsigned long long seq,
-                                          unsigned part_mask) {
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    if (atomicAdd(counter, 1u) == total - 1) {  // every other CTA's stores are fenced and counted in
-      *counter = 0;
-      __threadfence_system();
-      for (int d = 0; d < x.world; ++d) {
-        if (d == x.rank) continue;
-        for (int p = 0; p < P2P_PARTS; ++p)
-          if ((part_mask >> p) & 1u) *x_flag(x.peers[d], x, seq, p) = seq;
+  const int lane = threadIdx.x & 31;
+  if (need != 0 && lane < x.world) {
+    const volatile unsigned long long* p = x.acks + lane;
+    const long long t0 = clock64();
+    while (*p < need) {
+      if (clock64() - t0 > kSpinBudget) {
+        atomicMax(x.err, (code << 32) | (need & 0xffffffffULL));
+        break;
       }
     }
   }
-}
-
-// thread 0 of a CTA: the parts of `part_mask` of this update's buffer have arrived in THIS rank's area
-__device__ __forceinline__ void x_wait_parts(const LmExchange& x, const unsigned long long* flags, unsigned part_mask) {
-  for (int p = 0; p < P2P_PARTS; ++p)
-    if ((part_mask >> p) & 1u)
-      if (!spin_until_ge(flags + p, x.seq, x.err, 3)) break;
-  __threadfence_system();
+  __syncwarp();
 }
 
 // the streaming kernels' first CTA: this rank's gather of update x.seq is complete (the launch follows it on the stream)
 __device__ __forceinline__ void x_ack(const LmExchange& x) {
   const int d = threadIdx.x;
   if (d < x.world) {
-    volatile unsigned long long* ack =
-        reinterpret_cast<unsigned long long*>(x.peers[d] + x.flag_off) + 2 * P2P_PARTS + x.rank;
+    volatile unsigned long long* ack = reinterpret_cast<unsigned long long*>(x.peers[d] + x.flag_off) + x.rank;
     *ack = x.seq;
   }
 }

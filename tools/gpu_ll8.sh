@@ -1,0 +1,19 @@
+set -x
+mkdir -p gpurun_out
+N=$(nvidia-smi -L | wc -l)
+timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "p2p" > gpurun_out/ll8_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/ll8_pytest.log
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29561 tools/lm_p2p_timeline.py 4096 60 > gpurun_out/tl_${N}.txt 2> gpurun_out/tl_${N}.err; echo "rc=$?" >> gpurun_out/tl_${N}.err
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29551 bench.py --gpus $N --steps 20 --warmup 3 > gpurun_out/ll8_bench.json 2> gpurun_out/ll8_bench.err; echo "bench rc=$?" >> gpurun_out/ll8_bench.err
+tail -3 gpurun_out/ll8_pytest.log; cat gpurun_out/tl_${N}.txt; tail -3 gpurun_out/tl_${N}.err; tail -3 gpurun_out/ll8_bench.err
+python - <<'PY'
+import json
+try:
+    txt=open('gpurun_out/ll8_bench.json').read()
+    d=json.loads([l for l in txt.splitlines() if l.startswith('{')][-1])
+    sf=d['small_filters']; lm=d['large_map_sharded']
+    print(d['n_gpus'],'GPUs: B',d['value'],'e2e',d['e2e']['value'],'| M',sf['value'],'frac',sf['roofline']['frac'],'e2e',sf['e2e']['value'],sf['e2e']['frac_of_device_resident'])
+    for k in ('l4096','xl'):
+        v=lm[k]
+        print('  ',k,{a:v.get(a) for a in ('ms_per_update','sharded_equals_unsharded_bitwise','p2p_error','finite','error')}, 'frac',v.get('roofline',{}).get('frac'),'fused',v.get('fused_step',{}).get('ms_per_step'),'parity',v.get('tracked_rows_parity',{}).get('worst'))
+except Exception as e: print('parse',e)
+PY
