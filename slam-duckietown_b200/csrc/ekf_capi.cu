@@ -897,7 +897,8 @@ static int lm_update_impl_split(ekf_lm_t* h, int slot, double rng, double brg, c
   const bool p2p = owner >= 0;
   if (!rows5 && !whole && !p2p) return fail(EKF_ESTATE, "row-block shard: use ekf_lm_update_from_rows");
   const bool joseph = (h->flags & ekf::kFlagJoseph) != 0;
-  if (joseph && !whole) return fail(EKF_EINVAL, "Joseph form is not available on a row-block shard");
+  if (joseph && !whole && !p2p)
+    return fail(EKF_EINVAL, "Joseph form on a row-block shard needs the peer-memory exchange (ekf_lm_p2p_update)");
   CU(cudaSetDevice(h->device));
   const int j = 3 + 2 * slot;
   const int idx5[5] = {0, 1, 2, j, j + 1};
@@ -918,8 +919,11 @@ static int lm_update_impl_split(ekf_lm_t* h, int slot, double rng, double brg, c
       g.wait_mask |= 1;
     }
     if (h->p2p_rank == owner) g.push_mask |= 2; else g.wait_mask |= 2;
-    u.prepush = (h->p2p_rank == 0);
-    h->p2p_robot_seq = seq + 1;                          // every rank: the streaming kernels of this update pre-push
+    // every rank keeps the same book: rank 0's streaming kernel of this update pre-pushes the robot rows of the
+    // next one (plain form; the Joseph streaming kernel does not, so rank 0's next gather pushes them)
+    u.prepush = (h->p2p_rank == 0) && !joseph;
+    h->p2p_robot_seq = joseph ? 0 : seq + 1;
+    g.share_k = joseph ? 1 : 0;
   }
   for (int k = 0; k < 5; ++k) {
     const bool own = idx5[k] >= h->row_begin && idx5[k] < h->row_end;
@@ -1169,8 +1173,14 @@ int ekf_lm_p2p_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const
   if (!owners_host) return fail(EKF_EINVAL, "owners_host is null");
   if (m < 2 || m > ekf::LM_MAX_FUSED) return fail(EKF_EINVAL, "m must be in [2, %d]", ekf::LM_MAX_FUSED);
   if (h->p2p_world == 1) return ekf_lm_update_multi(h, m, slots_host, rng_host, brg_host, stream);
-  if (h->flags & ekf::kFlagJoseph) return fail(EKF_EINVAL, "Joseph form is not available on a row-block shard");
   if (!(h->flags & ekf::kFlagMeasurement)) return EKF_OK;
+  if (h->flags & ekf::kFlagJoseph) {  // no fused Joseph step on a shard: the step's updates one after the other
+    for (int u = 0; u < m; ++u) {
+      const int rc = ekf_lm_p2p_update(h, slots_host[u], rng_host[u], brg_host[u], owners_host[u], stream);
+      if (rc != EKF_OK) return rc;
+    }
+    return EKF_OK;
+  }
   for (int u = 0; u < m; ++u) {
     const int j = 3 + 2 * slots_host[u];
     if (owners_host[u] < 0 || owners_host[u] >= h->p2p_world) return fail(EKF_EINVAL, "owner out of range");

@@ -156,7 +156,7 @@ __device__ __forceinline__ void lm_gather_body(const LmGatherArgs& a, int bid, i
   if (tl) EKF_TL(a.x.seq, 0);
   // which of the two row parts (0: rows 0-2, 1: rows j, j+1) are read as cells of the exchange buffer
   const bool ll0 = a.x.peers && (a.wait_mask & 1), ll1 = a.x.peers && (a.wait_mask & 2);
-  if (a.x.peers && a.push_mask) {
+  if (a.x.peers && (a.push_mask || a.share_k)) {
     // peer-memory exchange inside this kernel (LmExchange, ekf_largemap.h): the owner stores its rows as tagged
     // cells into every peer's buffer; nothing to publish, the consumers poll the cells themselves
     if (threadIdx.x < 32) x_wait_acks(a.x, a.x.seq > 2 ? a.x.seq - 2 : 0);
@@ -275,7 +275,25 @@ __device__ __forceinline__ void lm_gather_body(const LmGatherArgs& a, int bid, i
     a.K1[t] = k1;
   }
   if (a.flags & kFlagJoseph) {
-    // single-GPU only (the host refuses Joseph on a shard): K[t] of every column t is local.
+    // W needs K at EVERY column t. Whole matrix on one GPU: K[t] is local. Row-block shard (peer-memory exchange):
+    // every rank stores K of its rows into every peer's buffer and takes the others' from its own (tagged cells).
+    if (a.share_k) {
+      if (local) {
+        for (int d = 0; d < a.x.world; ++d) {
+          if (d == a.x.rank) continue;
+          ll_store(x_row(a.x.peers[d], a.x, a.x.seq, P2P_KROW), t, k0, a.x.seq);
+          ll_store(x_row(a.x.peers[d], a.x, a.x.seq, P2P_KROW + 1), t, k1, a.x.seq);
+        }
+      } else {
+        double* mine = a.x.peers[a.x.rank];
+        const LLRaw r0 = ll_peek(x_row(mine, a.x, a.x.seq, P2P_KROW), t);
+        const LLRaw r1 = ll_peek(x_row(mine, a.x, a.x.seq, P2P_KROW + 1), t);
+        k0 = ll_resolve(r0, x_row(mine, a.x, a.x.seq, P2P_KROW), t, a.x.seq, a.x.err);
+        k1 = ll_resolve(r1, x_row(mine, a.x, a.x.seq, P2P_KROW + 1), t, a.x.seq, a.x.err);
+        a.K0[t] = k0;  // the streaming kernel reads K at its tile's columns
+        a.K1[t] = k1;
+      }
+    }
     const double qn = a.mm * a.mm;
     a.W0[t] = joseph_w(hp0, qn, k0);
     a.W1[t] = joseph_w(hp1, qn, k1);
@@ -526,7 +544,9 @@ cudaError_t lm_launch_predict(double* mu, double* P, int64_t ld, int n, int row_
 }
 
 cudaError_t lm_launch_gather(const LmGatherArgs& a, cudaStream_t st) {
-  const int threads = 256;
+  // peer-memory exchange: smaller CTAs put the owner's stores to its peers on twice as many SMs (the timeline showed
+  // ~17 GB/s of peer stores per SM, so 33 CTAs could not fill the NVLink ports)
+  const int threads = a.x.peers ? 128 : 256;
   return launch_pdl(lm_gather_kernel, dim3((a.n + threads - 1) / threads), dim3(threads), 0, st, a);
 }
 

@@ -76,6 +76,7 @@ struct LmGatherArgs {
   // CELLS of the exchange buffer, which are polled for this update's tag
   LmExchange x;
   int push_mask, wait_mask;
+  int share_k;  // Joseph form on a row-block shard: all-gather K through the exchange buffer (rows P2P_KROW, +1)
 };
 
 struct LmUpdateArgs {
@@ -128,7 +129,9 @@ cudaError_t lm_launch_export_rows_multi(const LmMultiArgs& a, double* rows, cuda
 //   [2][P2P_ROWS][ldx] double-buffered rows {0,1,2} U {j_u, j_u+1 : u < m} of 16-byte cells (the mu entry rides in
 //   cell ld), then at flag_off (doubles): u64 acks[P2P_MAX_WORLD]
 constexpr int P2P_MAX_WORLD = 16;
-constexpr int P2P_ROWS = 11;   // == LM_MAX_ROWS: rows of a fused step of up to 4 updates
+constexpr int P2P_KROW = 11;   // == LM_MAX_ROWS: rows of a fused step of up to 4 updates come first ...
+constexpr int P2P_ROWS = 13;   // ... then two rows of cells for K[:, 0] and K[:, 1] (Joseph form on shards: every rank
+                               // needs K at every column; each rank stores its rows' K into every peer's buffer)
 // in-kernel push helpers (ekf_largemap_p2p.cuh) are shared by the gather and streaming kernels
 
 cudaError_t lm_launch_augment(double* mu, double* P, int64_t ld, int row_begin, int row_end, int j, double gx,

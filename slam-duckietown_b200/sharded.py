@@ -107,8 +107,12 @@ class ShardedLargeMapEKF:
     def set_noise(self, motion_var: float, meas_var: float):
         self.local.set_noise(motion_var, meas_var)
 
-    def set_flags(self, circular=True, measurement=True, disable_motion=False):
-        self.local.set_flags(circular, measurement, disable_motion, joseph=False)
+    def set_flags(self, circular=True, measurement=True, disable_motion=False, joseph=False):
+        """joseph=True (one-pass Joseph form) needs K at every column on every rank: the peer-memory exchange
+        all-gathers it inside the gather kernel; the broadcast exchange does not carry it."""
+        if joseph and self.exchange != "p2p" and self.world > 1:
+            raise ValueError("the Joseph form on row-block shards needs exchange='p2p'")
+        self.local.set_flags(circular, measurement, disable_motion, joseph=joseph)
 
     def load(self, mean, cov_rows):
         """``mean`` (m,) replicated; ``cov_rows``: the FULL (m, m) covariance or a callable

@@ -1,5 +1,5 @@
 """Worker of test_p2p_row_exchange_two_processes: one rank of a row-block sharded large-map filter whose row
-exchange runs over CUDA IPC peer memory. Usage: python _p2p_worker.py RANK WORLD PORT DEVICE"""
+exchange runs over CUDA IPC peer memory. Usage: python _p2p_worker.py RANK WORLD PORT DEVICE [joseph]"""
 import json
 import os
 import sys
@@ -10,6 +10,7 @@ sys.path.insert(0, ROOT)
 
 def main():
     rank, world, port, device = (int(x) for x in sys.argv[1:5])
+    joseph = len(sys.argv) > 5 and sys.argv[5] == "joseph"
     import torch
     import torch.distributed as dist
     from slam_duckietown_b200 import ekf_bindings as eb, workloads as wl
@@ -22,6 +23,7 @@ def main():
     ref = eb.LargeMapEKF(L, device=device)
     for g in (f, ref):
         g.set_noise(0.2, 0.5)
+        g.set_flags(joseph=joseph)
     p0 = w.p0()
     f.load(w.mu0, p0)
     ref.load(w.mu0, p0)

@@ -626,11 +626,12 @@ def test_group_kernel_ragged_batch_and_mixed_observations(eb, monkeypatch):
     assert bool(torch.isfinite(res["regw"][0]).all())
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_p2p_row_exchange_two_processes(eb, world):
+@pytest.mark.parametrize("world,form", [(2, "plain"), (3, "plain"), (2, "joseph"), (3, "joseph")])
+def test_p2p_row_exchange_two_processes(eb, world, form):
     """Row-block shards in TWO processes (one per rank, both on cuda:0 here; one per GPU on a multi-GPU box) exchange
     their rows over CUDA IPC peer memory — owners store tagged cells, consumers poll them, no collective: every shard must equal
-    the same rows of an unsharded filter BITWISE and no spin may have timed out."""
+    the same rows of an unsharded filter BITWISE and no spin may have timed out. form "joseph": the one-pass Joseph
+    form, whose W needs K at every column — all-gathered through the same exchange inside the gather kernel."""
     import json
     import socket
     import subprocess
@@ -643,7 +644,7 @@ def test_p2p_row_exchange_two_processes(eb, world):
         with socket.socket() as s:
             s.bind(("127.0.0.1", 0))
             port = s.getsockname()[1]
-        procs = [subprocess.Popen([sys.executable, worker, str(r), str(world), str(port), str(r % ndev)],
+        procs = [subprocess.Popen([sys.executable, worker, str(r), str(world), str(port), str(r % ndev), form],
                                   stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True) for r in range(world)]
         res = []
         for p in procs:
