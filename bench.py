@@ -793,7 +793,7 @@ def bench_large_map_sharded(L, rank, world, local, updates, warm, fused=3, bitwi
         buf = torch.zeros(f.ld, dtype=torch.float64, device=dev)
         common_rows0 = np.zeros((len(common), n))
         for i, r in enumerate(common):                                 # the owners' rows to everyone (set-up plumbing)
-            owner = 0 if r < 3 else owner_of_slot((r - 3) // 2, L, world)
+            owner = 0 if r < 3 else f.owner((r - 3) // 2)
             if owner == rank:
                 buf.copy_(f.local.P[r - lo])
             if world > 1:
@@ -889,8 +889,9 @@ def bench_large_map_sharded(L, rank, world, local, updates, warm, fused=3, bitwi
     out.update({
         "metric": f"ms/update @{L} lm", "landmarks": L, "n": n, "p_gb": 8 * n * n / 1e9, "n_gpus": world,
         "ms_per_update": ms, "updates": len(timed), "scaling": "strong",
-        "exchange": "owners push rows {0,1,2} / {j,j+1} (+ mu entries) into every rank's buffer over NVLink peer "
-                    "memory (cudaIpc), consumers wait on flags in their own memory; no collective, 40 n bytes",
+        "exchange": "owners store rows {0,1,2} / {j,j+1} (+ mu entries) into every rank's buffer over NVLink peer "
+                    "memory (cudaIpc) as tagged 16-byte cells that the consumers poll in their own memory; no "
+                    "collective, no fence, 40 n bytes of payload (80 n on the wire)",
         "p2p_error": p2p_err, "finite": finite, "sharded_equals_unsharded_bitwise": same,
         "roofline": roofline_block(per_gpu, ms, bytes_per_update_per_gpu=per_gpu,
                                    bytes_per_update_total=lm_bytes_per_update(n),
@@ -898,6 +899,25 @@ def bench_large_map_sharded(L, rank, world, local, updates, warm, fused=3, bitwi
     if fms is not None:
         out["fused_step"] = {"updates_per_step": fused, "ms_per_step": fms, "ms_per_update_equiv": fms / fused,
                              "hbm_gbs_per_gpu": (16 * rows_max * n + fused * 96 * n) / (fms * 1e-3) / 1e9}
+    if L <= LM_LANDMARKS:
+        # the one-pass Joseph form on the same shards (K all-gathered through the exchange inside the gather kernel;
+        # parity: tests/test_gpu_parity.py::test_p2p_row_exchange_two_processes[*-joseph])
+        f.set_flags(joseph=True)
+        for o in ups[:warm]:
+            f.update(o[1], o[2], o[3])
+        sync()
+        j0, j1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        j0.record()
+        for o in timed:
+            f.update(o[1], o[2], o[3])
+        j1.record()
+        sync()
+        jms = _max_over_ranks(j0.elapsed_time(j1) / len(timed), world)
+        jfin = bool(torch.isfinite(f.local.mu[:n]).all()) and bool(torch.isfinite(f.local.P).all())
+        out["joseph"] = {"ms_per_update": jms, "updates": len(timed),
+                         "finite": bool(_min_over_ranks(1.0 if jfin else 0.0, world) == 1.0),
+                         "p2p_error": int(_max_over_ranks(float(f.local.p2p_error()), world)),
+                         "exchange_extra": "K[:, 0:2] of every rank's rows to every peer (32 n bytes as tagged cells)"}
     f.close()
     torch.cuda.empty_cache()
     return out

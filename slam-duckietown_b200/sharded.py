@@ -16,33 +16,70 @@ on CPU); everything that computes goes through the CUDA library and fails loudly
 """
 from __future__ import annotations
 
+import os
+
 from . import ekf_bindings as eb
 
 
-def row_partition(n_landmarks: int, world: int):
-    """[(row_begin, row_end)] per rank: landmarks split into ``world`` contiguous, near-equal ranges; rank 0
-    additionally owns rows 0-2. Every boundary is at a row 3 + 2k."""
+def _landmark_counts(n_landmarks: int, world: int, rank0_fewer: int = 0):
+    """Landmarks per rank: near-equal contiguous ranges; with ``rank0_fewer`` > 0 rank 0 takes that many landmarks
+    less than the equal share (never fewer than one) and the others split the rest evenly."""
     if world < 1:
         raise ValueError("world must be >= 1")
-    base, extra = divmod(n_landmarks, world)
+    if rank0_fewer < 0:
+        raise ValueError("rank0_fewer must be >= 0")
+    if world == 1 or rank0_fewer == 0:
+        base, extra = divmod(n_landmarks, world)
+        return [base + (1 if r < extra else 0) for r in range(world)]
+    first = min(n_landmarks, max(1, n_landmarks // world - rank0_fewer))
+    base, extra = divmod(n_landmarks - first, world - 1)
+    return [first] + [base + (1 if r < extra else 0) for r in range(world - 1)]
+
+
+def row_partition(n_landmarks: int, world: int, rank0_fewer: int = 0):
+    """[(row_begin, row_end)] per rank: landmarks split into ``world`` contiguous ranges (``_landmark_counts``);
+    rank 0 additionally owns rows 0-2. Every boundary is at a row 3 + 2k."""
     out, lm = [], 0
-    for r in range(world):
-        cnt = base + (1 if r < extra else 0)
+    for r, cnt in enumerate(_landmark_counts(n_landmarks, world, rank0_fewer)):
         begin = 0 if r == 0 else 3 + 2 * lm
         lm += cnt
         out.append((begin, 3 + 2 * lm))
     return out
 
 
-def owner_of_slot(slot: int, n_landmarks: int, world: int) -> int:
+def owner_of_slot(slot: int, n_landmarks: int, world: int, rank0_fewer: int = 0) -> int:
     """Rank that owns rows 3+2*slot and 4+2*slot under ``row_partition``."""
     if not 0 <= slot < n_landmarks:
         raise ValueError(f"slot {slot} outside [0, {n_landmarks})")
+    if world > 1 and rank0_fewer > 0:
+        counts = _landmark_counts(n_landmarks, world, rank0_fewer)
+        if slot < counts[0]:
+            return 0
+        base, extra = divmod(n_landmarks - counts[0], world - 1)
+        rest, split = slot - counts[0], extra * (base + 1)
+        return 1 + (rest // (base + 1) if rest < split else extra + (rest - split) // base)
     base, extra = divmod(n_landmarks, world)
     split = extra * (base + 1)
     if slot < split:
         return slot // (base + 1)
     return extra + (slot - split) // base
+
+
+def rank0_relief(n_landmarks: int, world: int) -> int:
+    """Landmarks rank 0 gives up under the peer-memory exchange. Besides its rows, rank 0 stores the three robot rows
+    of every update into all world - 1 peers (48 n (world - 1) bytes on the wire); next to an HBM-streaming pass that
+    costs the time of ~33 rows of its block per peer, whatever n is (32 768 landmarks on 8 GPUs: rank 0's streaming
+    kernel 1314 us against 1278 us on the others with equal shares; 1282 / 1285 us with the relief, 1327 -> 1318 us per
+    update; profiles/r2v_p2p_timeline_relief_spread_8gpu.txt). Equal finish times: rows_0 + 33 (world - 1) = rows_other.
+    Only for row blocks that stream from HBM: at 4096 landmarks on 8 GPUs (67 MB per rank, L2-resident) the update is
+    bound by the arrival of the rows, not by rank 0's pass, and the relief measured 3 % SLOWER (same file)."""
+    if world < 2:
+        return 0
+    n = 3 + 2 * n_landmarks
+    if 8.0 * n * n / world <= 160e6:      # the threshold of the 16-row-tile selection (ekf_lm_bind_state)
+        return 0
+    fewer = round(33 * (world - 1) * (world - 1) / (2.0 * world))
+    return int(min(fewer, max(0, n_landmarks // world // 2)))
 
 
 def exchange_rows(rows5, owner: int, group=None):
@@ -71,13 +108,20 @@ class ShardedLargeMapEKF:
     """One process per GPU; every rank calls the same methods with the same arguments (SPMD)."""
 
     def __init__(self, capacity: int, rank: int, world: int, device: int | None = None, group=None,
-                 exchange: str = "nccl"):
+                 exchange: str = "nccl", rank0_fewer: int | None = None):
         """exchange: "nccl" — export + two broadcasts per update through torch.distributed; "p2p" — the owners push
         their rows into every rank's exchange area over NVLink peer memory (cudaIpc) from INSIDE the update's own two
         kernels (gather: rows j, j+1; streaming: rows 0-2 for the next update), no collective and no extra launch."""
         self.capacity, self.rank, self.world, self.group = int(capacity), int(rank), int(world), group
         self.exchange = exchange
-        self.ranges = row_partition(self.capacity, self.world)
+        # rank 0 also feeds the robot rows to every peer: under the peer-memory exchange it owns fewer landmarks
+        # (rank0_relief; EKF_LM_RANK0_FEWER or the argument override it, 0 = equal shares)
+        if rank0_fewer is None:
+            env = os.environ.get("EKF_LM_RANK0_FEWER")
+            rank0_fewer = int(env) if env not in (None, "") else \
+                (rank0_relief(self.capacity, self.world) if exchange == "p2p" else 0)
+        self.rank0_fewer = int(rank0_fewer)
+        self.ranges = row_partition(self.capacity, self.world, self.rank0_fewer)
         self.local = eb.LargeMapEKF(self.capacity, device=self.rank if device is None else device,
                                     row_range=self.ranges[self.rank])
         self.n, self.ld = self.local.n, self.local.ld
@@ -103,6 +147,10 @@ class ShardedLargeMapEKF:
 
     def close(self):
         self.local.close()
+
+    def owner(self, slot: int) -> int:
+        """Rank that owns the rows of landmark ``slot`` under this job's partition."""
+        return owner_of_slot(slot, self.capacity, self.world, self.rank0_fewer)
 
     def set_noise(self, motion_var: float, meas_var: float):
         self.local.set_noise(motion_var, meas_var)
@@ -139,10 +187,10 @@ class ShardedLargeMapEKF:
 
     def update(self, slot: int, rng: float, brg: float):
         if self.exchange == "p2p":
-            self.local.p2p_update(slot, rng, brg, owner_of_slot(slot, self.capacity, self.world))
+            self.local.p2p_update(slot, rng, brg, self.owner(slot))
             return
         self.local.export_rows(slot)
-        exchange_rows(self.rows5, owner_of_slot(slot, self.capacity, self.world), self.group)
+        exchange_rows(self.rows5, self.owner(slot), self.group)
         self.local.update_from_rows(slot, rng, brg, self.rows5)
 
     def update_multi(self, slots, rngs, brgs):
@@ -155,10 +203,10 @@ class ShardedLargeMapEKF:
                 self.update(sl[0], rg[0], bg[0])
                 continue
             if self.exchange == "p2p":
-                self.local.p2p_update_multi(sl, rg, bg, [owner_of_slot(s, self.capacity, self.world) for s in sl])
+                self.local.p2p_update_multi(sl, rg, bg, [self.owner(s) for s in sl])
                 continue
             rows = self.local.export_rows_multi(sl)
-            exchange_rows_multi(rows, [owner_of_slot(s, self.capacity, self.world) for s in sl], self.group)
+            exchange_rows_multi(rows, [self.owner(s) for s in sl], self.group)
             self.local.update_multi_from_rows(sl, rg, bg, rows)
 
     def local_state(self):

@@ -32,6 +32,31 @@ def test_row_partition_covers_rows_on_landmark_pairs(n_lm, world):
         owner_of_slot(n_lm, n_lm, world)
 
 
+@pytest.mark.parametrize("n_lm,world,fewer", [(4096, 8, 101), (4096, 2, 8), (32768, 8, 101), (300, 3, 22), (13, 4, 5),
+                                              (3, 8, 2), (700, 3, 0)])
+def test_row_partition_with_rank0_relief(n_lm, world, fewer):
+    """Under the peer-memory exchange rank 0 also stores the robot rows to every peer, so it owns fewer landmarks: same
+    invariants (cover, landmark-pair boundaries, owner_of_slot consistent), rank 0 below the equal share by `fewer`
+    (at least one landmark left), the other ranks near-equal."""
+    from slam_duckietown_b200.sharded import owner_of_slot, rank0_relief, row_partition
+    parts = row_partition(n_lm, world, fewer)
+    n = 3 + 2 * n_lm
+    assert len(parts) == world and parts[0][0] == 0 and parts[-1][1] == n
+    for r in range(1, world):
+        assert parts[r][0] == parts[r - 1][1] and (parts[r][0] - 3) % 2 == 0
+    sizes = [(hi - max(lo, 3)) // 2 for lo, hi in parts]
+    assert sum(sizes) == n_lm
+    if fewer:
+        assert sizes[0] == min(n_lm, max(1, n_lm // world - fewer))
+        assert max(sizes[1:]) - min(sizes[1:]) <= 1
+    for slot in range(0, n_lm, max(1, n_lm // 97)):
+        lo, hi = parts[owner_of_slot(slot, n_lm, world, fewer)]
+        assert lo <= 3 + 2 * slot and 4 + 2 * slot < hi
+    assert owner_of_slot(n_lm - 1, n_lm, world, fewer) == max(r for r in range(world) if sizes[r] > 0)
+    # relief only where the row blocks stream from HBM (32 768 landmarks), not for L2-resident blocks (4096 on 8)
+    assert rank0_relief(32768, 8) == 101 and rank0_relief(4096, 8) == 0 and rank0_relief(32768, 1) == 0
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))

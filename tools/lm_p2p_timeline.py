@@ -65,9 +65,9 @@ def main():
     rows = tl[tl[:, 0] > 0]
     rows = rows[np.argsort(rows[:, 0])].astype(np.int64)
     assert len(rows) == len(timed), (len(rows), len(timed))
-    owners = [owner_of_slot(o[1], L, world) for o in timed]
+    owners = [f.owner(o[1]) for o in timed]
     rec = {"rank": rank, "world": world, "L": L, "host_us_per_call": host_us, "gpu_us_per_update": gpu_us,
-           "p2p_error": f.local.p2p_error(), "owners": owners, "stamps": rows.tolist()}
+           "p2p_error": f.local.p2p_error(), "rows": [hi - lo for lo, hi in f.ranges], "owners": owners, "stamps": rows.tolist()}
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     with open(os.path.join(ROOT, "gpurun_out", f"tl_{world}_{L}_rank{rank}.json"), "w") as fh:
         json.dump(rec, fh)
@@ -81,7 +81,7 @@ def summarise(world, L):
     recs = [json.load(open(os.path.join(ROOT, "gpurun_out", f"tl_{world}_{L}_rank{r}.json"))) for r in range(world)]
     print(f"== world {world}, {L} landmarks: gpu us/update {max(r['gpu_us_per_update'] for r in recs):.2f}, "
           f"host us/call {np.mean([r['host_us_per_call'] for r in recs]):.2f}, "
-          f"p2p_error {[hex(r['p2p_error']) for r in recs if r['p2p_error']]}")
+          f"p2p_error {[hex(r['p2p_error']) for r in recs if r['p2p_error']]}, rows per rank {recs[0]['rows']}")
     phases = {}
 
     def add(role, name, v):
