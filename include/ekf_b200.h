@@ -228,17 +228,22 @@ int ekf_lm_update_from_rows(ekf_lm_t* h, int slot, double rng, double brg, const
  * gathers the handles of all ranks (any transport) and passes them to ekf_lm_p2p_connect ([world][handle_bytes];
  * local_areas optionally gives device pointers of shards living in the same process). ekf_lm_p2p_update then runs
  * one sharded update in the SAME two launches as on one GPU: at the head of the gather kernel the owner of rows
- * {j,j+1} stores them (+ mu entries) into every peer's area and publishes a sequence number, the other ranks wait on
- * flags in their own memory; rank 0's streaming kernel pushes the rows {0,1,2} it has just updated into the buffer of
- * the NEXT update (a predict, or ekf_lm_p2p_invalidate after an external write to P, makes rank 0's next gather push
- * them instead). With world = 1 the call is ekf_lm_update. Every rank must make the same calls in the same order.
- * ekf_lm_p2p_error reports a spin that ran out of budget.                                                       */
+ * {j,j+1} stores them (+ mu entries) into every peer's area as 16-byte cells tagged with the update's sequence
+ * number, and every consumer thread polls the cells it needs in its own memory (no flag, no fence); rank 0's
+ * streaming kernel stores the rows {0,1,2} it has just updated into the buffer of the NEXT update (a predict, or
+ * ekf_lm_p2p_invalidate after an external write to P, makes rank 0's next gather push them instead). With the
+ * Joseph form every rank also stores K of its rows into every peer's area (W needs K at every column). With world
+ * = 1 the call is ekf_lm_update. Every rank must make the same calls in the same order. owner = the rank whose row
+ * block holds rows j, j+1 (any contiguous partition on landmark pairs; EKF_EINVAL if this rank is named but does
+ * not hold them). ekf_lm_p2p_error reports a spin that ran out of its 2 s budget (code << 32 | sequence number;
+ * code 1/2: acks before a push / pre-push, 3: a cell that never arrived).                                       */
 int ekf_lm_p2p_init(ekf_lm_t* h, int world, int rank, unsigned char* handle_out, int64_t handle_bytes);
 int ekf_lm_p2p_connect(ekf_lm_t* h, const unsigned char* handles, int64_t handle_bytes, void* const* local_areas);
 int ekf_lm_p2p_area(ekf_lm_t* h, void** area_dev);
 int ekf_lm_p2p_update(ekf_lm_t* h, int slot, double rng, double brg, int owner, void* stream);
-/* the fused step (2 <= m <= 4 updates, one pass over the local row block): the fused gather pushes / waits for its
- * 1 + m row parts (owners_host[u] = rank owning rows j_u, j_u+1), the streaming kernel pre-pushes rows {0,1,2}   */
+/* the fused step (2 <= m <= 4 updates, one pass over the local row block): the fused gather stores / polls its
+ * 1 + m row parts (owners_host[u] = rank owning rows j_u, j_u+1), the streaming kernel pre-pushes rows {0,1,2}.
+ * Joseph form: the step's updates run one after the other through ekf_lm_p2p_update                            */
 int ekf_lm_p2p_update_multi(ekf_lm_t* h, int m, const int32_t* slots_host, const double* rng_host,
                             const double* brg_host, const int32_t* owners_host, void* stream);
 int ekf_lm_p2p_invalidate(ekf_lm_t* h);
