@@ -6,7 +6,7 @@
 // of launch + protocol latency), then a separate push kernel per row part (14.8 us per update under ncu). Round 2
 // moved the stores into the update's own kernels, first with a flag protocol (data stores, __threadfence_system(),
 // CTA count, second fence, flag store; consumer: poll flag, fence): correct, but the globaltimer timeline
-// (tools/lm_p2p_timeline.py, profiles/r2t_p2p_timeline_flags.txt) showed that the two system-scope fences and the
+// (tools/lm_p2p_timeline.py, profiles/r2t_p2p_timeline_flags_8gpu.txt) showed that the two system-scope fences and the
 // flag round trip cost 8.6-11.8 us per push — 65 KB of data — and stretched rank 0's streaming kernel from 13.3 to
 // 19.5 us. Now the data carries its own validity (the LL idea of NCCL's low-latency protocol):
 //  * a row of the exchange buffer is an array of 16-byte CELLS {value.lo, tag, value.hi, tag}, tag = the low 32 bits

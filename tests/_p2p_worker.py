@@ -1,5 +1,5 @@
 """Worker of test_p2p_row_exchange_two_processes: one rank of a row-block sharded large-map filter whose row
-exchange runs over CUDA IPC peer memory. Usage: python _p2p_worker.py RANK WORLD PORT DEVICE [joseph]"""
+exchange runs over CUDA IPC peer memory. Usage: python _p2p_worker.py RANK WORLD PORT DEVICE [joseph|relief]"""
 import json
 import os
 import sys
@@ -11,6 +11,7 @@ sys.path.insert(0, ROOT)
 def main():
     rank, world, port, device = (int(x) for x in sys.argv[1:5])
     joseph = len(sys.argv) > 5 and sys.argv[5] == "joseph"
+    relief = 22 if len(sys.argv) > 5 and sys.argv[5] == "relief" else None   # rank 0 owns 22 landmarks fewer
     import torch
     import torch.distributed as dist
     from slam_duckietown_b200 import ekf_bindings as eb, workloads as wl
@@ -19,7 +20,7 @@ def main():
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
     L = 300
     w = wl.make_large_map(L, updates=20)
-    f = ShardedLargeMapEKF(L, rank, world, device=device, exchange="p2p")
+    f = ShardedLargeMapEKF(L, rank, world, device=device, exchange="p2p", rank0_fewer=relief)
     ref = eb.LargeMapEKF(L, device=device)
     for g in (f, ref):
         g.set_noise(0.2, 0.5)

@@ -626,12 +626,13 @@ def test_group_kernel_ragged_batch_and_mixed_observations(eb, monkeypatch):
     assert bool(torch.isfinite(res["regw"][0]).all())
 
 
-@pytest.mark.parametrize("world,form", [(2, "plain"), (3, "plain"), (2, "joseph"), (3, "joseph")])
+@pytest.mark.parametrize("world,form", [(2, "plain"), (3, "plain"), (2, "joseph"), (3, "joseph"), (3, "relief")])
 def test_p2p_row_exchange_two_processes(eb, world, form):
     """Row-block shards in TWO processes (one per rank, both on cuda:0 here; one per GPU on a multi-GPU box) exchange
     their rows over CUDA IPC peer memory — owners store tagged cells, consumers poll them, no collective: every shard must equal
     the same rows of an unsharded filter BITWISE and no spin may have timed out. form "joseph": the one-pass Joseph
-    form, whose W needs K at every column — all-gathered through the same exchange inside the gather kernel."""
+    form, whose W needs K at every column — all-gathered through the same exchange inside the gather kernel; "relief": the
+    uneven partition of large maps (rank 0 owns fewer landmarks), plain form."""
     import json
     import socket
     import subprocess

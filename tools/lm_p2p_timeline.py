@@ -5,9 +5,9 @@ leave globaltimer stamps per update; prints the mean phase durations per role (r
 
     python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tools/lm_p2p_timeline.py [L] [updates]
 
-Stamps (per update, per rank): 0 gather entry | 1 owner: acks seen, push starts | 2 owner: flags published |
-3 rows arrived (flag wait done) | 4 scalar chain done (S^-1 in shared memory) | 5 last gather CTA done |
-6 streaming kernel entry | 7 last streaming CTA done | 8 rank 0: pre-push of the robot rows published.
+Stamps (per update, per rank): 0 gather entry | 1 owner: acks seen, push starts | 2 owner: stores issued (flag protocol of the
+earlier build: flags published) | 3 rows arrived (cells polled) | 4 scalar chain done (S^-1 in shared memory) | 5 last gather CTA done |
+6 streaming kernel entry | 7 last streaming CTA done | 8 rank 0: pre-push of the robot rows issued by column tile 0.
 """
 import ctypes as C
 import json
@@ -27,7 +27,7 @@ def main():
     from slam_duckietown_b200 import capi
     capi.LIB_PATH = os.path.join(os.path.dirname(capi.LIB_PATH), "libekf_b200_tl.so")
     from slam_duckietown_b200 import workloads as wl
-    from slam_duckietown_b200.sharded import ShardedLargeMapEKF, owner_of_slot
+    from slam_duckietown_b200.sharded import ShardedLargeMapEKF
     import bench
     L = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
     timed_n = int(sys.argv[2]) if len(sys.argv) > 2 else 60
