@@ -583,7 +583,9 @@ def bench_large_map(updates=60, warm=6):
             "timing": "ms_per_update: the timed updates back to back between one CUDA-event pair; "
                       "ms_per_update_isolated: one event pair per update (no overlap across updates)",
             "roofline": roofline_block(b1, float(np.mean(ms)), bytes_per_update=b1,
-                                       traffic=ncu_traffic("lm_rank_update_kernel"),
+                                       traffic=ncu_traffic("lm_update_single_launch_kernel"),
+                                       traffic_source="profiles/ncu_traffic.json (static, one ncu --set full launch)",
+                                       kernel="lm_update_single_launch_kernel<32,8,0>",
                                        note="one launch per update: gather CTAs + streaming tiles (round 2)"),
             "fused_step": {"updates_per_step": 3, "ms_per_step": float(np.mean(ms3)),
                            "ms_per_update_equiv": float(np.mean(ms3)) / 3.0, "steps": len(ms3),
