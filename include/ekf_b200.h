@@ -156,8 +156,9 @@ int ekf_pose_moments_noalloc(const double* mu_dev, int64_t mu_stride, int64_t ba
 /* ---- Monte Carlo perturbations generated ON the device ---------------------------------------------------------
  * The batched mode replays ONE common trajectory per ensemble member with member-specific perturbations (north star:
  * "Monte Carlo noise replays of the same bag"). Every perturbation is a pure function of (seed, GLOBAL filter index
- * first_filter + b, step, stream): Philox4x32-10 -> inverse normal CDF evaluated with separately rounded IEEE
- * operations, so the host can regenerate any member's inputs bit for bit (oracle/mc_noise.py) whatever the sharding.
+ * first_filter + b, step, stream): Philox4x32-10 -> two 23-bit uniforms -> a pair of standard normals by Box-Muller in
+ * single precision (separately rounded IEEE operations only, widened to double before scaling; tails to 8 sigma), so the
+ * host can regenerate any member's inputs bit for bit (oracle/mc_noise.py) whatever the sharding.
  * The common step record is: doubles [ang, lin, rng[0..m), brg[0..m)] followed by int32 slot[0..m)
  * (ekf_batch_mc_record_doubles(m) doubles in all). sigma4 = std-dev of the perturbation of (ang, lin, rng, brg).  */
 int ekf_batch_mc_record_doubles(int m, int64_t* doubles);

@@ -147,7 +147,9 @@ class LargeMapEKF:
             capi.lib().ekf_lm_destroy(self._h)
             self._h = None
 
-    __del__ = close
+    def __del__(self):
+        if capi is not None:        # module globals are already gone at interpreter exit: the process frees the rest
+            self.close()
 
     # -- configuration ----------------------------------------------------------------------------------
     def set_noise(self, motion_var: float, meas_var: float):
@@ -370,7 +372,9 @@ class BatchedEKF:
             capi.lib().ekf_batch_destroy(self._h)
             self._h = None
 
-    __del__ = close
+    def __del__(self):
+        if capi is not None:        # module globals are already gone at interpreter exit: the process frees the rest
+            self.close()
 
     def set_noise(self, motion_var, meas_var):
         t = self.torch

@@ -1,5 +1,5 @@
 """The counter-based Monte Carlo perturbation generator: numpy twin (oracle/mc_noise.py) on CPU — Random123 known
-answers, accuracy of the inverse CDF — and, on the GPU, the device generator == the twin BIT FOR BIT, per-member
+answers, accuracy of the single-precision Box-Muller — and, on the GPU, the device generator == the twin BIT FOR BIT, per-member
 parity of a generated Monte Carlo replay against the oracle fed the same generated numbers, and invariance of every
 member under re-sharding of the ensemble."""
 import numpy as np
@@ -21,25 +21,42 @@ def test_philox4x32_10_known_answers():
 
 
 def test_uniforms_strictly_inside_unit_interval():
-    lo = mn.uniform52(np.array([0], dtype=np.uint32), np.array([0], dtype=np.uint32))
-    hi = mn.uniform52(np.array([0xffffffff], dtype=np.uint32), np.array([0xffffffff], dtype=np.uint32))
-    assert 0.0 < lo[0] == 2.0 ** -53 and hi[0] == 1.0 - 2.0 ** -53 < 1.0
+    u = mn.uniform23(np.array([0, 0xffffffff, 0x1ff, 0x200], dtype=np.uint32))
+    assert u.dtype == np.float32
+    assert 0.0 < u[0] == 2.0 ** -24 and u[1] == 1.0 - 2.0 ** -24 < 1.0 and u[2] == u[0] and u[3] == 1.5 * 2.0 ** -23
+    # the radial uniform: a second word refines the lowest cell, everything else is uniform23
+    t = mn.uniform23_tail(np.array([0, 0x1ff, 0x200, 0xffffffff], dtype=np.uint32),
+                          np.array([0, 0xffffffff, 123, 456], dtype=np.uint32))
+    assert t.dtype == np.float32
+    assert t[0] == 2.0 ** -47 and t[1] == (2.0 ** 23 - 0.5) * 2.0 ** -46 < 2.0 ** -23 and t[2] == u[3] and t[3] == u[1]
 
 
 def test_log_and_sincos_accuracy():
-    x = np.concatenate([np.logspace(-300, 0, 5000), np.linspace(1e-3, 1.0, 5000), [2.0 ** -53, 1 - 2.0 ** -53]])
-    assert np.max(np.abs(mn.det_log(x) - np.log(x)) / np.maximum(np.abs(np.log(x)), 1e-3)) < 1e-15
-    t = np.concatenate([np.linspace(0, 1, 200001)[:-1], [2.0 ** -53, 1 - 2.0 ** -53, 0.125, 0.25, 0.375, 0.5, 0.625, 0.75, 0.875]])
+    """Single precision is the design (noise deviates): ~2e-7 relative, and every value a float32."""
+    x = np.concatenate([np.logspace(-14.1, 0, 5000), np.linspace(1e-3, 1.0, 5000), [2.0 ** -47, 1 - 2.0 ** -24]])
+    x = x.astype(np.float32)
+    x64 = x.astype(np.float64)
+    got = mn.det_log(x)
+    assert got.dtype == np.float32
+    assert np.max(np.abs(got - np.log(x64)) / np.maximum(np.abs(np.log(x64)), 1e-3)) < 5e-7
+    t = np.concatenate([np.linspace(0, 1, 200001)[:-1], [2.0 ** -24, 1 - 2.0 ** -24, 0.125, 0.25, 0.375, 0.5, 0.625, 0.75, 0.875]])
+    t = t.astype(np.float32)
     s, c = mn.sincos_2pi(t)
-    assert np.max(np.abs(s - np.sin(2 * np.pi * t))) < 1e-15 and np.max(np.abs(c - np.cos(2 * np.pi * t))) < 1e-15
-    assert np.max(np.abs(s * s + c * c - 1.0)) < 1e-15
+    t64 = t.astype(np.float64)
+    assert s.dtype == np.float32 and c.dtype == np.float32
+    assert np.max(np.abs(s - np.sin(2 * np.pi * t64))) < 3e-7 and np.max(np.abs(c - np.cos(2 * np.pi * t64))) < 3e-7
+    assert np.max(np.abs(s.astype(np.float64) ** 2 + c.astype(np.float64) ** 2 - 1.0)) < 5e-7
 
 
 def test_box_muller_reaches_the_tails():
-    z0, z1 = mn.box_muller(np.array([2.0 ** -53, 0.5, 1 - 2.0 ** -53]), np.array([0.0 + 2.0 ** -53, 0.25, 0.5]))
-    assert abs(np.hypot(z0[0], z1[0]) - np.sqrt(-2 * np.log(2.0 ** -53))) < 1e-12      # 8.57 sigma
-    assert abs(z0[1]) < 1e-15 and abs(z1[1] - np.sqrt(2 * np.log(2))) < 1e-15
-    assert np.hypot(z0[2], z1[2]) < 2e-8
+    u1 = np.array([2.0 ** -47, 0.5, 1 - 2.0 ** -24], dtype=np.float32)
+    u2 = np.array([2.0 ** -24, 0.25, 0.5], dtype=np.float32)
+    z0, z1 = (z.astype(np.float64) for z in mn.box_muller(u1, u2))
+    assert abs(np.hypot(z0[0], z1[0]) - np.sqrt(-2 * np.log(2.0 ** -47))) < 1e-5      # 8.07 sigma
+    assert abs(z0[1]) < 1e-7 and abs(z1[1] - np.sqrt(2 * np.log(2))) < 1e-6
+    assert np.hypot(z0[2], z1[2]) < 4e-4
+    # without the refinement the radial uniform would stop at 2^-24: 5.77 sigma
+    assert np.sqrt(-2 * np.log(2.0 ** -24)) < 5.8
 
 
 def test_normal_pairs_look_normal_and_streams_are_independent():
