@@ -10,8 +10,8 @@
 // flag round trip cost 8.6-11.8 us per push — 65 KB of data — and stretched rank 0's streaming kernel from 13.3 to
 // 19.5 us. Now the data carries its own validity (the LL idea of NCCL's low-latency protocol):
 //  * a row of the exchange buffer is an array of 16-byte CELLS {value.lo, tag, value.hi, tag}, tag = the low 32 bits
-//    of the update's sequence number; a cell is written with ONE 16-byte volatile store and each 8-byte half carries
-//    its own tag, so only 8-byte store atomicity over NVLink is assumed;
+//    of the update's sequence number; a cell is written with ONE 16-byte volatile store of two 8-byte elements, each
+//    carrying its own tag, so nothing beyond the atomicity of an aligned 8-byte element is assumed;
 //  * the producer just stores cells into every peer's buffer through peer-mapped pointers (cudaIpc, one process per
 //    GPU): no fence, no flag, no CTA counter; the consumer thread that needs an entry polls that cell with 16-byte
 //    volatile loads until both tags match. One-way store latency is all that is left on the critical path;
@@ -35,11 +35,13 @@ __device__ __forceinline__ double* x_row(double* area, const LmExchange& x, unsi
   return area + ((int64_t)(seq & 1) * P2P_ROWS + k) * x.ldx * 2;
 }
 
+// a cell is two 8-byte words {tag << 32 | value.lo, tag << 32 | value.hi}: every word is one scalar element of the
+// vector access, so a reader can never see half a word
 __device__ __forceinline__ void ll_store(double* row_cells, int64_t c, double v, unsigned long long seq) {
   const unsigned long long b = (unsigned long long)__double_as_longlong(v);
-  const unsigned tag = (unsigned)seq;
-  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(reinterpret_cast<uint4*>(row_cells) + c),
-               "r"((unsigned)b), "r"(tag), "r"((unsigned)(b >> 32)), "r"(tag)
+  const unsigned long long tag = (unsigned long long)(unsigned)seq << 32;
+  asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(reinterpret_cast<uint4*>(row_cells) + c),
+               "l"((b & 0xffffffffULL) | tag), "l"((b >> 32) | tag)
                : "memory");
 }
 
@@ -55,42 +57,44 @@ __device__ __forceinline__ void ll_store2(double* row_cells, int64_t c, double v
 
 // one look at a cell (no waiting): several of these can be in flight before the first ll_resolve
 struct LLRaw {
-  unsigned lo, t0, hi, t1;
+  unsigned long long w0, w1;  // tag << 32 | lo, tag << 32 | hi
 };
 __device__ __forceinline__ LLRaw ll_peek(const double* row_cells, int64_t c) {
   LLRaw r;
-  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
-               : "=r"(r.lo), "=r"(r.t0), "=r"(r.hi), "=r"(r.t1)
+  asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];"
+               : "=l"(r.w0), "=l"(r.w1)
                : "l"(reinterpret_cast<const uint4*>(row_cells) + c)
                : "memory");
   return r;
+}
+__device__ __forceinline__ bool ll_valid(const LLRaw& r, unsigned long long seq) {
+  return (unsigned)(r.w0 >> 32) == (unsigned)seq && (unsigned)(r.w1 >> 32) == (unsigned)seq;
+}
+__device__ __forceinline__ double ll_value(const LLRaw& r) {
+  return __longlong_as_double((long long)((r.w1 << 32) | (r.w0 & 0xffffffffULL)));
 }
 
 // on expiry: err = max(err, 3 << 32 | tag)
 __device__ __forceinline__ double ll_load(const double* row_cells, int64_t c, unsigned long long seq,
                                           unsigned long long* err) {
-  const uint4* p = reinterpret_cast<const uint4*>(row_cells) + c;
-  const unsigned tag = (unsigned)seq;
-  unsigned lo, t0, hi, t1;
+  LLRaw r;
   long long start = 0;
   for (int it = 0;; ++it) {
-    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(lo), "=r"(t0), "=r"(hi), "=r"(t1) : "l"(p) : "memory");
-    if (t0 == tag && t1 == tag) break;
+    r = ll_peek(row_cells, c);
+    if (ll_valid(r, seq)) break;
     if (it == 0) {
       start = clock64();
     } else if (clock64() - start > kSpinBudget) {
-      atomicMax(err, (3ULL << 32) | tag);
+      atomicMax(err, (3ULL << 32) | (seq & 0xffffffffULL));
       break;
     }
   }
-  return __longlong_as_double((long long)(((unsigned long long)hi << 32) | lo));
+  return ll_value(r);
 }
 
 __device__ __forceinline__ double ll_resolve(const LLRaw& r, const double* row_cells, int64_t c, unsigned long long seq,
                                              unsigned long long* err) {
-  if (r.t0 == (unsigned)seq && r.t1 == (unsigned)seq)
-    return __longlong_as_double((long long)(((unsigned long long)r.hi << 32) | r.lo));
-  return ll_load(row_cells, c, seq, err);
+  return ll_valid(r, seq) ? ll_value(r) : ll_load(row_cells, c, seq, err);
 }
 
 // entry c of an exchanged row: a cell of the exchange buffer (ll) or a plain double (own P / replicated rows buffer)
