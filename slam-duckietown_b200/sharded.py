@@ -122,6 +122,10 @@ class ShardedLargeMapEKF:
                 (rank0_relief(self.capacity, self.world) if exchange == "p2p" else 0)
         self.rank0_fewer = int(rank0_fewer)
         self.ranges = row_partition(self.capacity, self.world, self.rank0_fewer)
+        if exchange == "p2p" and any(hi <= lo for lo, hi in self.ranges):
+            # a rank without rows launches no streaming kernel, so it would never acknowledge an exchange buffer
+            raise ValueError(f"peer-memory exchange needs at least one landmark per rank "
+                             f"({self.capacity} landmarks on {self.world} ranks)")
         self.local = eb.LargeMapEKF(self.capacity, device=self.rank if device is None else device,
                                     row_range=self.ranges[self.rank])
         self.n, self.ld = self.local.n, self.local.ld

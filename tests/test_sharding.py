@@ -57,6 +57,13 @@ def test_row_partition_with_rank0_relief(n_lm, world, fewer):
     assert rank0_relief(32768, 8) == 101 and rank0_relief(4096, 8) == 0 and rank0_relief(32768, 1) == 0
 
 
+def test_p2p_exchange_refuses_ranks_without_rows():
+    """Checked before anything touches the GPU or the library: 3 landmarks cannot feed 8 ranks."""
+    from slam_duckietown_b200.sharded import ShardedLargeMapEKF
+    with pytest.raises(ValueError, match="at least one landmark per rank"):
+        ShardedLargeMapEKF(3, 0, 8, device=0, exchange="p2p")
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
